@@ -1,0 +1,132 @@
+/* b200lmsfc.h -- C ABI of libb200lmsfc.so: the L-MSFC rate-distortion training step on B200 (sm_100a).
+ *
+ * The reference (herok97/L-MSFC-V2-Training = CompressAI-Vision 1.1.5.dev0 + CompressAI 1.2.4) has
+ * no FFI for this path: every function below replaces a PyTorch-eager interface (or, for the CDF
+ * builder, the pybind11 `_CXX` module) and cites it.  Paths are relative to
+ * /root/reference/compressai/compressai/.  INTEGRATION.md shows the ctypes stubs a maintainer adds.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every pointer is a DEVICE pointer unless it says "host";
+ *  - activations are NHWC bf16 ([B][H][W][C], C a multiple of 64); latents / likelihoods are NHWC fp32;
+ *  - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it, no internal threads;
+ *  - return 0 on success, non-zero on error (1 bad argument, 2 CUDA error, 3 domain error, the
+ *    ValueError cases of the reference); lmsfc_last_error() returns the thread-local message;
+ *  - caller owns all buffers; nothing is allocated or kept between calls.
+ */
+#ifndef B200LMSFC_H
+#define B200LMSFC_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* lmsfc_last_error(void);
+int lmsfc_version(void);
+
+/* ------------------------------------------------------------------ conv / deconv (tcgen05 implicit GEMM)
+ * Replaces models/utils.py:128-146: conv = nn.Conv2d(k, stride, padding=k/2),
+ * deconv = nn.ConvTranspose2d(k, stride, padding=k/2, output_padding=stride-1), and their autograd.
+ * Weights live in "GEMM layout" [D0][T][D1] with T = k*k taps: conv D0=Cout, D1=Cin (torch
+ * [Cout][Cin][kh][kw] permuted (0,2,3,1)); deconv D0=Cin, D1=Cout (torch [Cin][Cout][kh][kw] permuted).
+ * `w_direct` is the bf16 copy in that layout, `w_transposed` the bf16 copy as [D1][T][D0]. */
+typedef struct {
+  int kind;          /* 0 conv, 1 deconv */
+  int k, stride;     /* 5/2 or 3/1 in L-MSFC */
+  int B, Hin, Win;   /* input spatial size */
+  int Hout, Wout;    /* output spatial size: conv ceil(Hin/stride); deconv <= stride*Hin (cropped) */
+  int c0, c1;        /* input channels of source 0 and of the optional concatenated source 1 */
+  int Cout;
+} lmsfc_conv_desc;
+
+/* out = act(conv(cat[src0,src1]) + bias).  Any of out_bf16 / out_f32 / out_abs (|.| as bf16, the
+ * abs(y) fed to h_a, models/google.py:294) may be null.  conv needs w_direct, deconv w_transposed. */
+int lmsfc_conv_forward(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* w,
+                       const float* bias, int relu, void* out_bf16, float* out_f32, void* out_abs, void* stream);
+/* grad wrt the first n_in input channels (n_in <= c0; source 1 is data and gets none).
+ * conv needs w_transposed, deconv w_direct. */
+int lmsfc_conv_dgrad(const lmsfc_conv_desc* d, const void* gout, const void* w, int n_in, void* gin_bf16,
+                     void* stream);
+/* gw (fp32, GEMM layout, caller-zeroed) += weight gradient; gbias (fp32 [Cout], nullable) += column sums. */
+int lmsfc_conv_wgrad(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* gout, float* gw,
+                     float* gbias, void* stream);
+
+/* ------------------------------------------------------------------ GDN / IGDN   (layers/gdn.py:77-92)
+ * y = x * rsqrt(beta' + gamma' . x^2)  (inverse: * sqrt).  gamma_eff bf16 [C][C] ([out][in]) and
+ * beta_eff fp32 [C] are the reparametrised values (lmsfc_reparam_forward).  rn = rsqrt(norm) is
+ * saved (bf16) for backward; x2 / t are caller scratch of P*C bf16. */
+int lmsfc_gdn_forward(const void* x, const void* gamma_eff, const float* beta_eff, int inverse, int64_t P, int C,
+                      void* x2_scratch, void* y, void* rn, void* stream);
+/* gx written; g_gamma_eff fp32 [C][C] and g_beta_eff fp32 [C] accumulated (caller-zeroed).
+ * gamma_eff_t is gamma_eff transposed ([in][out], bf16). */
+int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void* gamma_eff_t, int inverse, int64_t P,
+                       int C, void* x2_scratch, void* t_scratch, void* gx, float* g_gamma_eff, float* g_beta_eff,
+                       void* stream);
+/* NonNegativeParametrizer (ops/parametrizers.py:38-64) with LowerBound's gradient (ops/bound_ops.py:40-42):
+ * out = max(p, bound)^2 - pedestal ; g_p += g_out * 2 max(p,bound) * [(p >= bound) | (g < 0)]. */
+int lmsfc_reparam_forward(const float* p, int64_t n, float bound, float pedestal, float* out_f32, void* out_bf16,
+                          void* stream);
+int lmsfc_reparam_backward(const float* g_out, const float* p, int64_t n, float bound, float* g_p, void* stream);
+
+/* ------------------------------------------------------------------ entropy models (entropy_models/entropy_models.py)
+ * mode: 0 "noise" (:161-165), 1 "dequantize" (:167-176).  noise: injected U(-.5,.5) draw (parity
+ * tests) or null -> in-kernel Philox keyed by (seed, offset [+ rng_state[1]]).  sum_ln (nullable):
+ * += sum(ln likelihood), the rate term of losses/rate_distortion.py:52-55. */
+int lmsfc_gc_forward(const float* y, const float* scales, const float* means, const float* noise, int64_t n, int mode,
+                     float scale_bound, float lik_bound, uint64_t seed, uint64_t offset, const uint64_t* rng_state,
+                     float* y_hat, float* lik, float* sum_ln, void* stream);            /* :650-682 */
+/* g_lik null -> g = rate_coef / lik (fused rate gradient).  g_yhat nullable.  g_means nullable. */
+int lmsfc_gc_backward(const float* y_hat, const float* scales, const float* means, const float* g_lik,
+                      const float* g_yhat, int64_t n, int mode, float scale_bound, float lik_bound, float rate_coef,
+                      float* g_y, float* g_scales, float* g_means, void* stream);
+/* EntropyBottleneck (:436-516).  x [P][C] fp32 NHWC; params [C][58] packed per channel as
+ * M0(3) b0(3) f0(3) | (M(9) b(3) f(3)) x3 | M4(3) b4(1); medians [C] (quantiles[:,0,1]) for mode 1. */
+int lmsfc_eb_forward(const float* x, const float* params, const float* medians, const float* noise, int64_t P, int C,
+                     int mode, float lik_bound, uint64_t seed, uint64_t offset, const uint64_t* rng_state, float* y_hat,
+                     float* lik, float* sum_ln, void* stream);
+int lmsfc_eb_backward(const float* y_hat, const float* params, const float* g_lik, const float* g_yhat, int64_t P, int C,
+                      int mode, float lik_bound, float rate_coef, float* g_x, float* g_params, void* stream);
+/* aux loss (:431-434): loss += sum |logits(quantiles) - target| ; g_quantiles [C][3] written. */
+int lmsfc_eb_aux_loss(const float* params, const float* quantiles, const float* target, int C, float* loss,
+                      float* g_quantiles, void* stream);
+int lmsfc_rng_advance(uint64_t* rng_state, void* stream);
+
+/* ------------------------------------------------------------------ RD loss (losses/rate_distortion.py:47-59) */
+/* sse += sum (xhat-x)^2 ; grad (nullable) = grad_coef*(xhat-x), bf16. */
+int lmsfc_mse_forward_backward(const void* xhat, const void* x, int64_t n, float grad_coef, float* sse, void* grad,
+                               void* stream);
+/* out[0]=bpp=sum_{i<n_rate} accum[i]*coef[i]; out[1]=D=sum over the next n_dist; out[2]=lambda_scale*D+bpp */
+int lmsfc_loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale, float* out,
+                        void* stream);
+
+/* ------------------------------------------------------------------ small gradients / layout */
+int lmsfc_relu_backward(void* g_bf16_inplace, const void* out_bf16, int64_t n, void* stream);
+int lmsfc_abs_backward(const float* g_direct, const void* g_abs_bf16, const float* y, int64_t n, void* g_out_bf16,
+                       void* stream);
+int lmsfc_colsum(const void* g_bf16, int64_t P, int C, float* out, void* stream);
+int lmsfc_cast_f32_bf16(const float* in, void* out, int64_t n, void* stream);
+int lmsfc_cast_bf16_f32(const void* in, float* out, int64_t n, void* stream);
+int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C, int HW, void* stream);
+/* fp32 [D0][T][D1] -> bf16 [D1][T][D0] */
+int lmsfc_transpose_weight(const float* in, void* out, int D0, int T, int D1, void* stream);
+
+/* ------------------------------------------------------------------ optimiser (examples/train.py:100-107) */
+int lmsfc_sumsq(const float* g, int64_t n, float* accum, void* stream);
+/* clip_grad_norm_(max_norm) + torch.optim.Adam step over a flat fp32 arena; p_bf16 (nullable) gets
+ * the bf16 shadow; step (device int) is incremented; scratch (>=4 floats) receives
+ * {clip_coef, bias_corr1, bias_corr2, grad_norm}.  sumsq null or max_norm<=0 -> no clipping. */
+int lmsfc_adam_step(float* p, float* m, float* v, const float* g, void* p_bf16, int64_t n, float lr, float beta1,
+                    float beta2, float eps, float max_norm, const float* sumsq, int* step, float* scratch,
+                    void* stream);
+
+/* ------------------------------------------------------------------ CDF tables (cpp_exts/ops/ops.cpp:40-109) */
+/* host pointers; cdf must hold n+1 entries.  Errors mirror the reference's ValueError cases. */
+int lmsfc_pmf_to_quantized_cdf(const float* pmf_host, int n, int precision, uint32_t* cdf_host);
+/* device: row r = pmf[r][0:pmf_length[r]] ++ tail[r] -> cdf[r][0:pmf_length[r]+2], zero padded
+ * (entropy_models.py:204-212).  status[r]: 0 ok, 1 bad element, 2 all-zero, 3 nothing to steal. */
+int lmsfc_pmf_rows_to_cdf(const float* pmf, int pmf_stride, const float* tail, const int* pmf_length, int rows,
+                          int precision, int32_t* cdf, int cdf_stride, int* status, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200LMSFC_H */

@@ -1,0 +1,293 @@
+// extern "C" surface of libb200lmsfc.so (declared in include/b200lmsfc.h): argument checking and
+// the mapping from conv/deconv/GDN semantics onto the two tcgen05 GEMM kernels.
+#include "../../include/b200lmsfc.h"
+
+#include <string.h>
+
+#include "igemm.cuh"
+#include "kernels.cuh"
+
+namespace lmsfc {
+const char* get_error();
+}
+using namespace lmsfc;
+typedef __nv_bfloat16 bf16;
+#define ST(s) ((cudaStream_t)(s))
+
+extern "C" const char* lmsfc_last_error(void) { return lmsfc::get_error(); }
+extern "C" int lmsfc_version(void) { return 100; }
+
+// ---------------------------------------------------------------- tap tables
+static void taps_regular(int k, int pad, int* ntaps, int8_t* dy, int8_t* dx, int16_t* widx) {
+  int n = 0;
+  for (int r = 0; r < k; ++r)
+    for (int t = 0; t < k; ++t) { dy[n] = (int8_t)(r - pad); dx[n] = (int8_t)(t - pad); widx[n] = (int16_t)(r * k + t); ++n; }
+  *ntaps = n;
+}
+// sub-pixel phase (py,px) of a stride-s transposed conv: out[s*h+py] gathers in[h + dy], dy = (py+pad-r)/s
+static void taps_phase(int k, int s, int pad, int py, int px, int* ntaps, int8_t* dy, int8_t* dx, int16_t* widx) {
+  int n = 0;
+  for (int r = 0; r < k; ++r) {
+    if ((py + pad - r) % s != 0) continue;
+    for (int t = 0; t < k; ++t) {
+      if ((px + pad - t) % s != 0) continue;
+      dy[n] = (int8_t)((py + pad - r) / s); dx[n] = (int8_t)((px + pad - t) / s); widx[n] = (int16_t)(r * k + t); ++n;
+    }
+  }
+  *ntaps = n;
+}
+
+static int check_desc(const lmsfc_conv_desc* d) {
+  LMSFC_CHECK_ARG(d != nullptr, "conv: null descriptor");
+  LMSFC_CHECK_ARG(d->kind == 0 || d->kind == 1, "conv: kind=%d", d->kind);
+  LMSFC_CHECK_ARG((d->k == 5 || d->k == 3 || d->k == 1) && d->stride >= 1 && d->stride <= 2, "conv: k=%d stride=%d", d->k,
+                  d->stride);
+  LMSFC_CHECK_ARG(d->B > 0 && d->Hin > 0 && d->Win > 0 && d->Hout > 0 && d->Wout > 0, "conv: empty shape");
+  LMSFC_CHECK_ARG(d->c0 > 0 && d->c0 % 64 == 0 && d->c1 % 64 == 0 && d->Cout % 128 == 0, "conv: channels %d+%d -> %d",
+                  d->c0, d->c1, d->Cout);
+  if (d->kind == 0)
+    LMSFC_CHECK_ARG(d->Hout == (d->Hin + d->stride - 1) / d->stride && d->Wout == (d->Win + d->stride - 1) / d->stride,
+                    "conv: output %dx%d does not match input %dx%d / stride %d", d->Hout, d->Wout, d->Hin, d->Win,
+                    d->stride);
+  else
+    LMSFC_CHECK_ARG(d->Hout <= d->stride * d->Hin && d->Wout <= d->stride * d->Win && d->c1 == 0,
+                    "deconv: output %dx%d exceeds %d x input %dx%d", d->Hout, d->Wout, d->stride, d->Hin, d->Win);
+  return LMSFC_OK;
+}
+
+// "regular" structure: out[h][w] = sum_taps src[h*s + r - pad][w*s + t - pad] . W[tap]
+static int run_regular(const bf16* s0, const bf16* s1, int c0, int c1, int B, int Hs, int Ws, int Hg, int Wg, int k, int s,
+                       const bf16* w, int w_rows, int N, IgemmParams& p, cudaStream_t st) {
+  p.src0 = s0; p.src1 = s1; p.c0 = c0; p.c1 = c1;
+  p.B = B; p.Hin = Hs; p.Win = Ws; p.Hg = Hg; p.Wg = Wg; p.M = B * Hg * Wg; p.sin = s;
+  taps_regular(k, k / 2, &p.ntaps, p.dy, p.dx, p.widx);
+  p.Hout = Hg; p.Wout = Wg; p.sout = 1; p.oy = 0; p.ox = 0; p.N = N;
+  p.w = w; p.w_rows = w_rows; p.w_cols = k * k * (c0 + c1);
+  return launch_igemm(p, st);
+}
+// "transposed" structure: out[s*h+py][s*w+px] = sum_{taps of phase} src[h+dy][w+dx] . W[tap]
+static int run_transposed(const bf16* s0, int c0, int B, int Hs, int Ws, int Ho, int Wo, int k, int s, const bf16* w,
+                          int w_rows, int N, IgemmParams& p, cudaStream_t st) {
+  p.src0 = s0; p.src1 = nullptr; p.c0 = c0; p.c1 = 0;
+  p.B = B; p.Hin = Hs; p.Win = Ws; p.sin = 1;
+  p.Hout = Ho; p.Wout = Wo; p.sout = s; p.N = N;
+  p.w = w; p.w_rows = w_rows; p.w_cols = k * k * c0;
+  for (int py = 0; py < s; ++py)
+    for (int px = 0; px < s; ++px) {
+      p.Hg = (Ho - py + s - 1) / s; p.Wg = (Wo - px + s - 1) / s;
+      if (p.Hg <= 0 || p.Wg <= 0) continue;
+      p.M = B * p.Hg * p.Wg; p.oy = py; p.ox = px;
+      taps_phase(k, s, k / 2, py, px, &p.ntaps, p.dy, p.dx, p.widx);
+      if (p.ntaps == 0) continue;
+      int rc = launch_igemm(p, st);
+      if (rc) return rc;
+    }
+  return LMSFC_OK;
+}
+
+extern "C" int lmsfc_conv_forward(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* w,
+                                  const float* bias, int relu, void* out_bf16, float* out_f32, void* out_abs,
+                                  void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  LMSFC_CHECK_ARG(src0 && w && (d->c1 == 0 || src1), "conv_forward: null operand");
+  IgemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.epi = EPI_BIAS; p.relu = relu; p.bias = bias;
+  p.out_bf16 = (bf16*)out_bf16; p.out_f32 = out_f32; p.out_abs = (bf16*)out_abs;
+  if (d->kind == 0)
+    return run_regular((const bf16*)src0, (const bf16*)src1, d->c0, d->c1, d->B, d->Hin, d->Win, d->Hout, d->Wout, d->k,
+                       d->stride, (const bf16*)w, d->Cout, d->Cout, p, ST(stream));
+  if (d->stride == 1)
+    LMSFC_CHECK_ARG(false, "deconv with stride 1 is not part of the L-MSFC path");
+  return run_transposed((const bf16*)src0, d->c0, d->B, d->Hin, d->Win, d->Hout, d->Wout, d->k, d->stride, (const bf16*)w,
+                        d->Cout, d->Cout, p, ST(stream));
+}
+
+extern "C" int lmsfc_conv_dgrad(const lmsfc_conv_desc* d, const void* gout, const void* w, int n_in, void* gin_bf16,
+                                void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  LMSFC_CHECK_ARG(gout && w && gin_bf16, "conv_dgrad: null operand");
+  LMSFC_CHECK_ARG(n_in > 0 && n_in <= d->c0 + d->c1 && n_in % 128 == 0, "conv_dgrad: n_in=%d", n_in);
+  IgemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.epi = EPI_BIAS; p.out_bf16 = (bf16*)gin_bf16;
+  const int cin = d->c0 + d->c1;
+  if (d->kind == 0) {
+    // grad of a strided conv = transposed structure over gout; stride-1 convs degenerate to one phase
+    return run_transposed((const bf16*)gout, d->Cout, d->B, d->Hout, d->Wout, d->Hin, d->Win, d->k, d->stride,
+                          (const bf16*)w, cin, n_in, p, ST(stream));
+  }
+  // grad of a transposed conv = regular strided conv over (cropped) gout
+  return run_regular((const bf16*)gout, nullptr, d->Cout, 0, d->B, d->Hout, d->Wout, d->Hin, d->Win, d->k, d->stride,
+                     (const bf16*)w, cin, n_in, p, ST(stream));
+}
+
+extern "C" int lmsfc_conv_wgrad(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* gout, float* gw,
+                                float* gbias, void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  LMSFC_CHECK_ARG(src0 && gout && gw && (d->c1 == 0 || src1), "conv_wgrad: null operand");
+  WgradParams p;
+  memset(&p, 0, sizeof(p));
+  p.B = d->B; p.sin = d->stride; p.T = d->k * d->k; p.out = gw;
+  taps_regular(d->k, d->k / 2, &p.ntaps, p.dy, p.dx, p.widx);
+  if (d->kind == 0) {   // dense = gout, gathered = input
+    p.dense = (const bf16*)gout; p.Cd = d->Cout; p.Hg = d->Hout; p.Wg = d->Wout;
+    p.g0 = (const bf16*)src0; p.g1 = (const bf16*)src1; p.gc0 = d->c0; p.gc1 = d->c1; p.Cg = d->c0 + d->c1;
+    p.Hin = d->Hin; p.Win = d->Win;
+  } else {              // dense = input, gathered = gout
+    p.dense = (const bf16*)src0; p.Cd = d->c0; p.Hg = d->Hin; p.Wg = d->Win;
+    p.g0 = (const bf16*)gout; p.g1 = nullptr; p.gc0 = d->Cout; p.gc1 = 0; p.Cg = d->Cout;
+    p.Hin = d->Hout; p.Win = d->Wout;
+  }
+  p.M = p.B * p.Hg * p.Wg;
+  rc = launch_wgrad(p, ST(stream));
+  if (rc) return rc;
+  if (gbias) return colsum_bf16((const bf16*)gout, (int64_t)d->B * d->Hout * d->Wout, d->Cout, gbias, ST(stream));
+  return LMSFC_OK;
+}
+
+// ---------------------------------------------------------------- GDN
+static void gdn_gemm_params(IgemmParams& p, const bf16* a, const bf16* w, int64_t P, int C) {
+  memset(&p, 0, sizeof(p));
+  p.src0 = a; p.c0 = C; p.B = 1; p.Hin = 1; p.Win = (int)P; p.Hg = 1; p.Wg = (int)P; p.M = (int)P; p.sin = 1;
+  p.ntaps = 1; p.dy[0] = 0; p.dx[0] = 0; p.widx[0] = 0;
+  p.Hout = 1; p.Wout = (int)P; p.sout = 1; p.N = C;
+  p.w = w; p.w_rows = C; p.w_cols = C;
+}
+
+extern "C" int lmsfc_gdn_forward(const void* x, const void* gamma_eff, const float* beta_eff, int inverse, int64_t P, int C,
+                                 void* x2_scratch, void* y, void* rn, void* stream) {
+  LMSFC_CHECK_ARG(x && gamma_eff && beta_eff && x2_scratch && y, "gdn_forward: null operand");
+  LMSFC_CHECK_ARG(C % 128 == 0 && P > 0 && P < (1ll << 31), "gdn_forward: P=%lld C=%d", (long long)P, C);
+  int rc = square_bf16((const bf16*)x, (bf16*)x2_scratch, P * C, ST(stream));
+  if (rc) return rc;
+  IgemmParams p;
+  gdn_gemm_params(p, (const bf16*)x2_scratch, (const bf16*)gamma_eff, P, C);
+  p.epi = EPI_GDN; p.inverse = inverse; p.bias = beta_eff; p.aux_x = (const bf16*)x;
+  p.out_bf16 = (bf16*)y; p.out_rn = (bf16*)rn;
+  return launch_igemm(p, ST(stream));
+}
+
+extern "C" int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void* gamma_eff_t, int inverse,
+                                  int64_t P, int C, void* x2_scratch, void* t_scratch, void* gx, float* g_gamma_eff,
+                                  float* g_beta_eff, void* stream) {
+  LMSFC_CHECK_ARG(gy && x && rn && gamma_eff_t && x2_scratch && t_scratch && gx && g_gamma_eff && g_beta_eff,
+                  "gdn_backward: null operand");
+  LMSFC_CHECK_ARG(C % 256 == 0 && P > 0 && P < (1ll << 31), "gdn_backward: P=%lld C=%d", (long long)P, C);
+  int rc = gdn_t((const bf16*)gy, (const bf16*)x, (const bf16*)rn, inverse, P, C, (bf16*)t_scratch, g_beta_eff, ST(stream));
+  if (rc) return rc;
+  rc = square_bf16((const bf16*)x, (bf16*)x2_scratch, P * C, ST(stream));
+  if (rc) return rc;
+  IgemmParams p;
+  gdn_gemm_params(p, (const bf16*)t_scratch, (const bf16*)gamma_eff_t, P, C);
+  p.epi = EPI_GDN_BWD; p.inverse = inverse; p.aux_x = (const bf16*)x; p.aux_gy = (const bf16*)gy; p.aux_rn = (const bf16*)rn;
+  p.out_bf16 = (bf16*)gx;
+  rc = launch_igemm(p, ST(stream));
+  if (rc) return rc;
+  WgradParams q;
+  memset(&q, 0, sizeof(q));
+  q.dense = (const bf16*)t_scratch; q.Cd = C; q.B = 1; q.Hg = 1; q.Wg = (int)P; q.M = (int)P;
+  q.g0 = (const bf16*)x2_scratch; q.gc0 = C; q.Cg = C; q.Hin = 1; q.Win = (int)P; q.sin = 1;
+  q.ntaps = 1; q.T = 1; q.out = g_gamma_eff;
+  return launch_wgrad(q, ST(stream));
+}
+
+extern "C" int lmsfc_reparam_forward(const float* p, int64_t n, float bound, float pedestal, float* out_f32, void* out_bf16,
+                                     void* stream) {
+  return reparam_fwd(p, n, bound, pedestal, out_f32, (bf16*)out_bf16, ST(stream));
+}
+extern "C" int lmsfc_reparam_backward(const float* g_out, const float* p, int64_t n, float bound, float* g_p, void* stream) {
+  return reparam_bwd(g_out, p, n, bound, g_p, ST(stream));
+}
+
+// ---------------------------------------------------------------- entropy models
+extern "C" int lmsfc_gc_forward(const float* y, const float* scales, const float* means, const float* noise, int64_t n,
+                                int mode, float scale_bound, float lik_bound, uint64_t seed, uint64_t offset,
+                                const uint64_t* rng_state, float* y_hat, float* lik, float* sum_ln, void* stream) {
+  LMSFC_CHECK_ARG(mode == 0 || mode == 1, "Invalid quantization mode: \"%d\"", mode);   // entropy_models.py:158-159
+  LMSFC_CHECK_ARG(n == 0 || (y && scales && y_hat && lik), "gc_forward: null operand");
+  GcArgs a{y, scales, means, noise, y_hat, lik, sum_ln, n, mode, scale_bound, lik_bound, seed, offset, rng_state};
+  return gc_forward(a, ST(stream));
+}
+extern "C" int lmsfc_gc_backward(const float* y_hat, const float* scales, const float* means, const float* g_lik,
+                                 const float* g_yhat, int64_t n, int mode, float scale_bound, float lik_bound,
+                                 float rate_coef, float* g_y, float* g_scales, float* g_means, void* stream) {
+  LMSFC_CHECK_ARG(mode == 0 || mode == 1, "Invalid quantization mode: \"%d\"", mode);
+  LMSFC_CHECK_ARG(n == 0 || (y_hat && scales && g_y && g_scales), "gc_backward: null operand");
+  GcBwdArgs a{y_hat, scales, means, g_lik, g_yhat, g_y, g_scales, g_means, n, mode, scale_bound, lik_bound, rate_coef};
+  return gc_backward(a, ST(stream));
+}
+extern "C" int lmsfc_eb_forward(const float* x, const float* params, const float* medians, const float* noise, int64_t P,
+                                int C, int mode, float lik_bound, uint64_t seed, uint64_t offset,
+                                const uint64_t* rng_state, float* y_hat, float* lik, float* sum_ln, void* stream) {
+  LMSFC_CHECK_ARG(mode == 0 || mode == 1, "Invalid quantization mode: \"%d\"", mode);
+  LMSFC_CHECK_ARG(P == 0 || (x && params && y_hat && lik), "eb_forward: null operand");
+  LMSFC_CHECK_ARG(mode == 0 || medians, "eb_forward: dequantize mode needs medians");
+  EbArgs a{x, params, medians, noise, y_hat, lik, sum_ln, P, C, mode, lik_bound, seed, offset, rng_state};
+  return eb_forward(a, ST(stream));
+}
+extern "C" int lmsfc_eb_backward(const float* y_hat, const float* params, const float* g_lik, const float* g_yhat,
+                                 int64_t P, int C, int mode, float lik_bound, float rate_coef, float* g_x, float* g_params,
+                                 void* stream) {
+  LMSFC_CHECK_ARG(P == 0 || (y_hat && params && g_x && g_params), "eb_backward: null operand");
+  EbBwdArgs a{y_hat, params, g_lik, g_yhat, g_x, g_params, P, C, mode, lik_bound, rate_coef};
+  return eb_backward(a, ST(stream));
+}
+extern "C" int lmsfc_eb_aux_loss(const float* params, const float* quantiles, const float* target, int C, float* loss,
+                                 float* g_quantiles, void* stream) {
+  LMSFC_CHECK_ARG(params && quantiles && target && loss && g_quantiles && C > 0, "eb_aux_loss: null operand");
+  return eb_aux(params, quantiles, target, C, loss, g_quantiles, ST(stream));
+}
+extern "C" int lmsfc_rng_advance(uint64_t* rng_state, void* stream) { return rng_advance(rng_state, ST(stream)); }
+
+// ---------------------------------------------------------------- loss / small ops / optimiser / cdf
+extern "C" int lmsfc_mse_forward_backward(const void* xhat, const void* x, int64_t n, float grad_coef, float* sse, void* grad,
+                                          void* stream) {
+  LMSFC_CHECK_ARG(n == 0 || (xhat && x && sse), "mse: null operand");
+  return mse_fwd_bwd((const bf16*)xhat, (const bf16*)x, n, grad_coef, sse, (bf16*)grad, ST(stream));
+}
+extern "C" int lmsfc_loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale,
+                                   float* out, void* stream) {
+  return loss_finalize(accum, coef, n_rate, n_dist, lambda_scale, out, ST(stream));
+}
+extern "C" int lmsfc_relu_backward(void* g, const void* out, int64_t n, void* stream) {
+  return relu_bwd_bf16((bf16*)g, (const bf16*)out, n, ST(stream));
+}
+extern "C" int lmsfc_abs_backward(const float* g_direct, const void* g_abs, const float* y, int64_t n, void* g_out,
+                                  void* stream) {
+  return abs_bwd(g_direct, (const bf16*)g_abs, y, n, (bf16*)g_out, ST(stream));
+}
+extern "C" int lmsfc_colsum(const void* g, int64_t P, int C, float* out, void* stream) {
+  return colsum_bf16((const bf16*)g, P, C, out, ST(stream));
+}
+extern "C" int lmsfc_cast_f32_bf16(const float* in, void* out, int64_t n, void* stream) {
+  return cast_f32_bf16(in, (bf16*)out, n, ST(stream));
+}
+extern "C" int lmsfc_cast_bf16_f32(const void* in, float* out, int64_t n, void* stream) {
+  return cast_bf16_f32((const bf16*)in, out, n, ST(stream));
+}
+extern "C" int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C, int HW, void* stream) {
+  return nchw_to_nhwc_bf16(in, (bf16*)out, B, C, HW, ST(stream));
+}
+extern "C" int lmsfc_transpose_weight(const float* in, void* out, int D0, int T, int D1, void* stream) {
+  return transpose_weight(in, (bf16*)out, D0, T, D1, ST(stream));
+}
+extern "C" int lmsfc_sumsq(const float* g, int64_t n, float* accum, void* stream) { return sumsq_f32(g, n, accum, ST(stream)); }
+extern "C" int lmsfc_adam_step(float* p, float* m, float* v, const float* g, void* p_bf16, int64_t n, float lr, float beta1,
+                               float beta2, float eps, float max_norm, const float* sumsq, int* step, float* scratch,
+                               void* stream) {
+  LMSFC_CHECK_ARG(n == 0 || (p && m && v && g && step && scratch), "adam_step: null operand");
+  AdamArgs a{p, m, v, g, (bf16*)p_bf16, n, lr, beta1, beta2, eps, max_norm, sumsq, step, scratch};
+  return adam_step(a, ST(stream));
+}
+extern "C" int lmsfc_pmf_to_quantized_cdf(const float* pmf_host, int n, int precision, uint32_t* cdf_host) {
+  LMSFC_CHECK_ARG(pmf_host && cdf_host && n >= 0, "pmf_to_quantized_cdf: null operand");
+  return pmf_to_quantized_cdf_host(pmf_host, n, precision, cdf_host);
+}
+extern "C" int lmsfc_pmf_rows_to_cdf(const float* pmf, int pmf_stride, const float* tail, const int* pmf_length, int rows,
+                                     int precision, int32_t* cdf, int cdf_stride, int* status, void* stream) {
+  return pmf_rows_to_cdf_device(pmf, pmf_stride, tail, pmf_length, rows, precision, cdf, cdf_stride, status, ST(stream));
+}

@@ -1,0 +1,262 @@
+// HBM-bound elementwise / reduction kernels: 16-byte vector accesses, grid sized in multiples of
+// the 148 SMs, warp-shuffle block reductions, one atomic per block.
+//
+//   RateDistortionLoss MSE + its gradient      compressai/losses/rate_distortion.py:47-59
+//   GDN helper passes (x^2, t, beta gradient)  compressai/layers/gdn.py:77-92
+//   NonNegativeParametrizer fwd/bwd            compressai/ops/parametrizers.py:38-64
+//   clip_grad_norm_ + Adam                     compressai/examples/train.py:100-103
+#include "kernels.cuh"
+
+namespace lmsfc {
+
+namespace {
+constexpr int TPB = 256;
+inline int grid1d(int64_t work_items) {
+  int64_t b = (work_items + TPB - 1) / TPB;
+  const int64_t cap = 148 * 8;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+__device__ __forceinline__ float lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+}  // namespace
+
+// ---------------------------------------------------------------- MSE forward + backward in one pass
+// sse += sum (xhat-x)^2 ; grad = grad_coef * (xhat - x).  5 bytes/element at bf16 (2 reads + 1 write).
+__global__ void __launch_bounds__(TPB) mse_kernel(const uint4* __restrict__ xh, const uint4* __restrict__ x, int64_t n8,
+                                                  float coef, float* sse, uint4* __restrict__ grad) {
+  float local = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n8; i += (int64_t)gridDim.x * TPB) {
+    const uint4 a = __ldg(xh + i), b = __ldg(x + i);
+    const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+    uint32_t gv[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float d0 = lo(av[j]) - lo(bv[j]), d1 = hi(av[j]) - hi(bv[j]);
+      local += d0 * d0 + d1 * d1;
+      gv[j] = pack_bf16(coef * d0, coef * d1);
+    }
+    if (grad) grad[i] = make_uint4(gv[0], gv[1], gv[2], gv[3]);
+  }
+  __shared__ float red[32];
+  local = block_sum(local, red);
+  if (threadIdx.x == 0) atomicAdd(sse, local);
+}
+
+int mse_fwd_bwd(const __nv_bfloat16* xhat, const __nv_bfloat16* x, int64_t n, float grad_coef, float* sse,
+                __nv_bfloat16* grad, cudaStream_t s) {
+  LMSFC_CHECK_ARG(n % 8 == 0, "mse: n=%lld must be a multiple of 8", (long long)n);
+  if (n == 0) return LMSFC_OK;
+  mse_kernel<<<grid1d(n / 8), TPB, 0, s>>>((const uint4*)xhat, (const uint4*)x, n / 8, grad_coef, sse, (uint4*)grad);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// out = {bpp, distortion, loss}: bpp = sum_{i<n_rate} accum[i]*coef[i];
+// D = sum_{n_rate<=i<n_rate+n_dist} accum[i]*coef[i]; loss = lambda_scale*D + bpp.
+__global__ void loss_finalize_kernel(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale,
+                                     float* out) {
+  float bpp = 0.f, d = 0.f;
+  for (int i = 0; i < n_rate; ++i) bpp += accum[i] * coef[i];
+  for (int i = 0; i < n_dist; ++i) d += accum[n_rate + i] * coef[n_rate + i];
+  out[0] = bpp; out[1] = d; out[2] = lambda_scale * d + bpp;
+}
+int loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale, float* out,
+                  cudaStream_t s) {
+  loss_finalize_kernel<<<1, 1, 0, s>>>(accum, coef, n_rate, n_dist, lambda_scale, out);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// ---------------------------------------------------------------- GDN helper passes
+__global__ void __launch_bounds__(TPB) square_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int64_t n8) {
+  for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n8; i += (int64_t)gridDim.x * TPB) {
+    const uint4 a = __ldg(x + i);
+    const uint32_t av[4] = {a.x, a.y, a.z, a.w};
+    uint32_t r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) r[j] = pack_bf16(lo(av[j]) * lo(av[j]), hi(av[j]) * hi(av[j]));
+    y[i] = make_uint4(r[0], r[1], r[2], r[3]);
+  }
+}
+int square_bf16(const __nv_bfloat16* x, __nv_bfloat16* x2, int64_t n, cudaStream_t s) {
+  LMSFC_CHECK_ARG(n % 8 == 0, "square: n must be a multiple of 8");
+  if (n == 0) return LMSFC_OK;
+  square_kernel<<<grid1d(n / 8), TPB, 0, s>>>((const uint4*)x, (uint4*)x2, n / 8);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// t = -1/2 gy x rn^3 (GDN) | +1/2 gy x rn (IGDN), bf16; g_beta[c] += sum_pix t.
+// Block = 32 x 8 threads: threadIdx.x covers 8 channels (one uint4), threadIdx.y strides pixels.
+__global__ void __launch_bounds__(256) gdn_t_kernel(const uint4* __restrict__ gy, const uint4* __restrict__ x,
+                                                    const uint4* __restrict__ rn, int inverse, int64_t P, int C8,
+                                                    uint4* __restrict__ t, float* g_beta) {
+  const int c8 = blockIdx.x * 32 + threadIdx.x;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (c8 < C8) {
+    for (int64_t p = (int64_t)blockIdx.y * 8 + threadIdx.y; p < P; p += (int64_t)gridDim.y * 8) {
+      const int64_t i = p * C8 + c8;
+      const uint4 g = __ldg(gy + i), xv = __ldg(x + i), r = __ldg(rn + i);
+      const uint32_t gv[4] = {g.x, g.y, g.z, g.w}, xx[4] = {xv.x, xv.y, xv.z, xv.w}, rv[4] = {r.x, r.y, r.z, r.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float r0 = lo(rv[j]), r1 = hi(rv[j]);
+        const float f0 = inverse ? 0.5f * r0 : -0.5f * r0 * r0 * r0;
+        const float f1 = inverse ? 0.5f * r1 : -0.5f * r1 * r1 * r1;
+        const float t0 = lo(gv[j]) * lo(xx[j]) * f0, t1 = hi(gv[j]) * hi(xx[j]) * f1;
+        acc[2 * j] += t0; acc[2 * j + 1] += t1;
+        o[j] = pack_bf16(t0, t1);
+      }
+      t[i] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+  __shared__ float red[8][32][9];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = acc[j];
+  __syncthreads();
+  if (threadIdx.y == 0 && c8 < C8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float v = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v += red[k][threadIdx.x][j];
+      atomicAdd(g_beta + c8 * 8 + j, v);
+    }
+  }
+}
+int gdn_t(const __nv_bfloat16* gy, const __nv_bfloat16* x, const __nv_bfloat16* rn, int inverse, int64_t P, int C,
+          __nv_bfloat16* t, float* g_beta, cudaStream_t s) {
+  LMSFC_CHECK_ARG(C % 8 == 0, "gdn_t: C must be a multiple of 8");
+  if (P == 0) return LMSFC_OK;
+  const int C8 = C / 8, bx = (C8 + 31) / 32;
+  int64_t by = (148 * 4 + bx - 1) / bx;
+  const int64_t maxy = (P + 7) / 8;
+  if (by > maxy) by = maxy;
+  gdn_t_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)gy, (const uint4*)x, (const uint4*)rn,
+                                                                inverse, P, C8, (uint4*)t, g_beta);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// column sums of a bf16 [P][C] matrix (conv bias gradients)
+__global__ void __launch_bounds__(256) colsum_kernel(const uint4* __restrict__ g, int64_t P, int C8, float* out) {
+  const int c8 = blockIdx.x * 32 + threadIdx.x;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (c8 < C8) {
+    for (int64_t p = (int64_t)blockIdx.y * 8 + threadIdx.y; p < P; p += (int64_t)gridDim.y * 8) {
+      const uint4 a = __ldg(g + p * C8 + c8);
+      const uint32_t av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { acc[2 * j] += lo(av[j]); acc[2 * j + 1] += hi(av[j]); }
+    }
+  }
+  __shared__ float red[8][32][9];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = acc[j];
+  __syncthreads();
+  if (threadIdx.y == 0 && c8 < C8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float v = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v += red[k][threadIdx.x][j];
+      atomicAdd(out + c8 * 8 + j, v);
+    }
+  }
+}
+int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream_t s) {
+  LMSFC_CHECK_ARG(C % 8 == 0, "colsum: C must be a multiple of 8");
+  if (P == 0) return LMSFC_OK;
+  const int C8 = C / 8, bx = (C8 + 31) / 32;
+  int64_t by = (148 * 4 + bx - 1) / bx;
+  const int64_t maxy = (P + 7) / 8;
+  if (by > maxy) by = maxy;
+  colsum_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)g, P, C8, out);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// ---------------------------------------------------------------- NonNegativeParametrizer
+__global__ void reparam_fwd_kernel(const float* p, int64_t n, float bound, float ped, float* o32, __nv_bfloat16* o16) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = fmaxf(p[i], bound);
+    const float r = v * v - ped;
+    if (o32) o32[i] = r;
+    if (o16) o16[i] = __float2bfloat16(r);
+  }
+}
+int reparam_fwd(const float* p, int64_t n, float bound, float pedestal, float* out_f32, __nv_bfloat16* out_bf16,
+                cudaStream_t s) {
+  if (n == 0) return LMSFC_OK;
+  reparam_fwd_kernel<<<grid1d(n), TPB, 0, s>>>(p, n, bound, pedestal, out_f32, out_bf16);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+__global__ void reparam_bwd_kernel(const float* g_out, const float* p, int64_t n, float bound, float* g_p) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = p[i];
+    const float g = g_out[i] * 2.f * fmaxf(v, bound);
+    g_p[i] += (v >= bound || g < 0.f) ? g : 0.f;
+  }
+}
+int reparam_bwd(const float* g_out, const float* p, int64_t n, float bound, float* g_p, cudaStream_t s) {
+  if (n == 0) return LMSFC_OK;
+  reparam_bwd_kernel<<<grid1d(n), TPB, 0, s>>>(g_out, p, n, bound, g_p);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// ---------------------------------------------------------------- small activation gradients
+__global__ void relu_bwd_kernel(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    if (!(__bfloat162float(out[i]) > 0.f)) g[i] = __float2bfloat16(0.f);
+}
+int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, cudaStream_t s) {
+  if (n == 0) return LMSFC_OK;
+  relu_bwd_kernel<<<grid1d(n), TPB, 0, s>>>(g, out, n);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+// g_out = bf16(g_direct + sign(y) * g_abs): gradient of y feeding both GaussianConditional and h_a(|y|)
+__global__ void abs_bwd_kernel(const float* gd, const __nv_bfloat16* ga, const float* y, int64_t n, __nv_bfloat16* o) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float yv = y[i];
+    const float sg = (yv > 0.f) ? 1.f : ((yv < 0.f) ? -1.f : 0.f);
+    o[i] = __float2bfloat16((gd ? gd[i] : 0.f) + (ga ? sg * __bfloat162float(ga[i]) : 0.f));
+  }
+}
+int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, int64_t n, __nv_bfloat16* g_out,
+            cudaStream_t s) {
+  if (n == 0) return LMSFC_OK;
+  abs_bwd_kernel<<<grid1d(n), TPB, 0, s>>>(g_direct, g_abs, y, n, g_out);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+__global__ void cast_f32_bf16_kernel(const float* in, __nv_bfloat16* out, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = __float2bfloat16(in[i]);
+}
+int cast_f32_bf16(const float* in, __nv_bfloat16* out, int64_t n, cudaStream_t s) {
+  if (n == 0) return LMSFC_OK;
+  cast_f32_bf16_kernel<<<grid1d(n), TPB, 0, s>>>(in, out, n);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+__global__ void cast_bf16_f32_kernel(const __nv_bfloat16* in, float* out, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = __bfloat162float(in[i]);
+}
+int cast_bf16_f32(const __nv_bfloat16* in, float* out, int64_t n, cudaStream_t s) {
+  if (n == 0) return LMSFC_OK;
+  cast_bf16_f32_kernel<<<grid1d(n), TPB, 0, s>>>(in, out, n);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+}  // namespace lmsfc

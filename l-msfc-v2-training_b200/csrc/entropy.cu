@@ -1,0 +1,352 @@
+// Fused, vectorised, warp-shuffle-reduced entropy-model kernels (fp32 arithmetic, HBM-bound).
+//
+//   GaussianConditional  compressai/entropy_models/entropy_models.py:650-682 (+ quantize :155-180)
+//   EntropyBottleneck    entropy_models.py:436-516 ; aux loss :431-434
+//   LowerBound gradient  compressai/ops/bound_ops.py:40-42
+//
+// Every forward kernel fuses quantise + likelihood + lower bound + the sum(ln L) reduction of
+// RateDistortionLoss (losses/rate_distortion.py:52-55); every backward kernel recomputes the
+// likelihood analytically instead of reading saved intermediates.
+#include "kernels.cuh"
+
+namespace lmsfc {
+
+// ---------------------------------------------------------------- Philox4x32-10
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+  const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+  const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+  const uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+  c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+}
+// uniform in [-0.5, 0.5) for element idx of draw `offset` under `seed`
+__device__ __forceinline__ float philox_uniform(uint64_t seed, uint64_t offset, uint64_t idx) {
+  uint32_t c[4] = {(uint32_t)(idx >> 2), (uint32_t)(idx >> 34), (uint32_t)offset, (uint32_t)(offset >> 32)};
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    philox_round(c, k0, k1);
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return (float)(c[idx & 3] >> 8) * (1.0f / 16777216.0f) - 0.5f;
+}
+
+__global__ void rng_advance_kernel(uint64_t* state) { state[1] += 1; }
+
+int rng_advance(uint64_t* state, cudaStream_t s) {
+  rng_advance_kernel<<<1, 1, 0, s>>>(state);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// ---------------------------------------------------------------- GaussianConditional
+__device__ __forceinline__ float std_cumulative(float x) {  // entropy_models.py:604-608
+  return 0.5f * erfcf(-0.70710678118654752440f * x);
+}
+__device__ __forceinline__ float normal_pdf(float t) { return 0.3989422804014327f * __expf(-0.5f * t * t); }
+
+__global__ void __launch_bounds__(256) gc_forward_kernel(GcArgs a) {
+  float local = 0.f;
+  const uint64_t seed = a.rng_state ? a.rng_state[0] : a.seed;
+  const uint64_t off = (a.rng_state ? a.rng_state[1] : 0) + a.offset;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float y = a.y[i], mu = a.means ? a.means[i] : 0.f;
+    float yh;
+    if (a.mode == QUANT_NOISE) {
+      const float u = a.noise ? a.noise[i] : philox_uniform(seed, off, (uint64_t)i);
+      yh = y + u;                                  // entropy_models.py:161-165
+    } else {
+      yh = rintf(y - mu) + mu;                     // :167-176 (torch.round = half to even)
+    }
+    const float v = fabsf(yh - mu);
+    const float s = fmaxf(a.scales[i], a.scale_bound);
+    const float L = std_cumulative((0.5f - v) / s) - std_cumulative((-0.5f - v) / s);
+    const float lik = fmaxf(L, a.lik_bound);
+    a.y_hat[i] = yh;
+    a.lik[i] = lik;
+    local += __logf(lik);
+  }
+  if (a.sum_ln) {
+    __shared__ float red[32];
+    local = block_sum(local, red);
+    if (threadIdx.x == 0) atomicAdd(a.sum_ln, local);
+  }
+}
+
+__global__ void __launch_bounds__(256) gc_backward_kernel(GcBwdArgs a) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float yh = a.y_hat[i], mu = a.means ? a.means[i] : 0.f;
+    const float d = yh - mu, v = fabsf(d);
+    const float sraw = a.scales[i];
+    const float s = fmaxf(sraw, a.scale_bound);
+    const float ta = (0.5f - v) / s, tb = (-0.5f - v) / s;
+    const float L = std_cumulative(ta) - std_cumulative(tb);
+    float g = a.g_lik ? a.g_lik[i] : a.rate_coef / fmaxf(L, a.lik_bound);
+    if (!(L >= a.lik_bound || g < 0.f)) g = 0.f;   // bound_ops.py:40-42
+    const float pa = normal_pdf(ta), pb = normal_pdf(tb);
+    const float gv = g * (pb - pa) / s;
+    float gs = g * (tb * pb - ta * pa) / s;
+    if (!(sraw >= a.scale_bound || gs < 0.f)) gs = 0.f;
+    const float sgn = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);
+    const float gyh = a.g_yhat ? a.g_yhat[i] : 0.f;
+    if (a.mode == QUANT_NOISE) {
+      a.g_y[i] = gyh + gv * sgn;
+      if (a.g_means) a.g_means[i] = -gv * sgn;
+    } else {
+      a.g_y[i] = 0.f;
+      if (a.g_means) a.g_means[i] = gyh;
+    }
+    a.g_scales[i] = gs;
+  }
+}
+
+static int grid_for(int64_t n, int threads) {
+  int64_t b = (n + threads - 1) / threads;
+  const int64_t cap = 148 * 8;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+int gc_forward(const GcArgs& a, cudaStream_t s) {
+  if (a.n <= 0) return LMSFC_OK;
+  gc_forward_kernel<<<grid_for(a.n, 256), 256, 0, s>>>(a);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+int gc_backward(const GcBwdArgs& a, cudaStream_t s) {
+  if (a.n <= 0) return LMSFC_OK;
+  gc_backward_kernel<<<grid_for(a.n, 256), 256, 0, s>>>(a);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// ---------------------------------------------------------------- EntropyBottleneck
+// Packed per-channel parameters, 58 floats (filters (3,3,3,3), entropy_models.py:355-377):
+//   [M0(3) b0(3) f0(3)] [M1(9) b1(3) f1(3)] [M2(9) b2(3) f2(3)] [M3(9) b3(3) f3(3)] [M4(3) b4(1)]
+constexpr int EB_NP = 58;
+
+__device__ __forceinline__ float softplus_t(float x) { return x > 20.f ? x : log1pf(__expf(x)); }  // torch threshold 20
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + __expf(-x)); }
+
+struct EbChan {
+  float sp0[3], b0[3], tf0[3];
+  float sp[3][9], b[3][3], tf[3][3];
+  float sp4[3], b4;
+};
+
+__device__ __forceinline__ void eb_load(const float* __restrict__ q, EbChan& c) {
+#pragma unroll
+  for (int j = 0; j < 3; ++j) { c.sp0[j] = softplus_t(q[j]); c.b0[j] = q[3 + j]; c.tf0[j] = tanhf(q[6 + j]); }
+#pragma unroll
+  for (int l = 0; l < 3; ++l) {
+    const float* r = q + 9 + 15 * l;
+#pragma unroll
+    for (int j = 0; j < 9; ++j) c.sp[l][j] = softplus_t(r[j]);
+#pragma unroll
+    for (int j = 0; j < 3; ++j) { c.b[l][j] = r[9 + j]; c.tf[l][j] = tanhf(r[12 + j]); }
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) c.sp4[j] = softplus_t(q[54 + j]);
+  c.b4 = q[57];
+}
+
+// logits_cumulative (entropy_models.py:436-455) for one scalar; optionally keeps the activations
+struct EbTape { float ta[4][3], h[4][3]; };   // tanh(pre-activation), gated output per layer
+
+template <bool TAPE>
+__device__ __forceinline__ float eb_logits(const EbChan& c, float v, EbTape* tp) {
+  float h[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float a = c.sp0[j] * v + c.b0[j];
+    const float t = tanhf(a);
+    h[j] = a + c.tf0[j] * t;
+    if (TAPE) { tp->ta[0][j] = t; tp->h[0][j] = h[j]; }
+  }
+#pragma unroll
+  for (int l = 0; l < 3; ++l) {
+    float n[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const float a = c.sp[l][3 * i] * h[0] + c.sp[l][3 * i + 1] * h[1] + c.sp[l][3 * i + 2] * h[2] + c.b[l][i];
+      const float t = tanhf(a);
+      n[i] = a + c.tf[l][i] * t;
+      if (TAPE) { tp->ta[l + 1][i] = t; tp->h[l + 1][i] = n[i]; }
+    }
+    h[0] = n[0]; h[1] = n[1]; h[2] = n[2];
+  }
+  return c.sp4[0] * h[0] + c.sp4[1] * h[1] + c.sp4[2] * h[2] + c.b4;
+}
+
+__device__ __forceinline__ float eb_lik_raw(float lower, float upper) {  // entropy_models.py:458-469
+  const float t = lower + upper;
+  const float sg = (t > 0.f) ? -1.f : ((t < 0.f) ? 1.f : 0.f);
+  return fabsf(sigmoid_f(sg * upper) - sigmoid_f(sg * lower));
+}
+
+// x is NHWC-flattened [P][C]; thread <-> channel, grid.y strides over pixels.
+__global__ void __launch_bounds__(128) eb_forward_kernel(EbArgs a) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  float local = 0.f;
+  if (c < a.C) {
+    EbChan ch;
+    eb_load(a.params + (size_t)c * EB_NP, ch);
+    const float med = a.medians ? a.medians[c] : 0.f;
+    const uint64_t seed = a.rng_state ? a.rng_state[0] : a.seed;
+    const uint64_t off = (a.rng_state ? a.rng_state[1] : 0) + a.offset;
+    for (int64_t p = blockIdx.y; p < a.P; p += gridDim.y) {
+      const int64_t i = p * a.C + c;
+      const float x = a.x[i];
+      float yh;
+      if (a.mode == QUANT_NOISE) {
+        const float u = a.noise ? a.noise[i] : philox_uniform(seed, off, (uint64_t)i);
+        yh = x + u;
+      } else {
+        yh = rintf(x - med) + med;
+      }
+      const float lo = eb_logits<false>(ch, yh - 0.5f, nullptr);
+      const float up = eb_logits<false>(ch, yh + 0.5f, nullptr);
+      const float lik = fmaxf(eb_lik_raw(lo, up), a.lik_bound);
+      a.y_hat[i] = yh;
+      a.lik[i] = lik;
+      local += __logf(lik);
+    }
+  }
+  if (a.sum_ln) {
+    __shared__ float red[32];
+    local = block_sum(local, red);
+    if (threadIdx.x == 0) atomicAdd(a.sum_ln, local);
+  }
+}
+
+// reverse pass through one logits evaluation; accumulates into the "effective" parameter
+// gradients (w.r.t. softplus(M), b, tanh(f)); returns d logits / d v times g.
+__device__ __forceinline__ float eb_logits_bwd(const EbChan& c, const EbTape& tp, float v, float g, float* G) {
+  // G layout mirrors the packed parameters (58)
+  float gh[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) { G[54 + j] += g * tp.h[3][j]; gh[j] = g * c.sp4[j]; }
+  G[57] += g;
+#pragma unroll
+  for (int l = 2; l >= 0; --l) {
+    float ga[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const float t = tp.ta[l + 1][i];
+      G[9 + 15 * l + 12 + i] += gh[i] * t;
+      ga[i] = gh[i] * (1.f + c.tf[l][i] * (1.f - t * t));
+      G[9 + 15 * l + 9 + i] += ga[i];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) G[9 + 15 * l + 3 * i + j] += ga[i] * tp.h[l][j];
+    }
+#pragma unroll
+    for (int j = 0; j < 3; ++j) gh[j] = ga[0] * c.sp[l][j] + ga[1] * c.sp[l][3 + j] + ga[2] * c.sp[l][6 + j];
+  }
+  float gv = 0.f;
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float t = tp.ta[0][j];
+    G[6 + j] += gh[j] * t;
+    const float ga = gh[j] * (1.f + c.tf0[j] * (1.f - t * t));
+    G[3 + j] += ga;
+    G[j] += ga * v;
+    gv += ga * c.sp0[j];
+  }
+  return gv;
+}
+
+__global__ void __launch_bounds__(128) eb_backward_kernel(EbBwdArgs a) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= a.C) return;
+  EbChan ch;
+  const float* q = a.params + (size_t)c * EB_NP;
+  eb_load(q, ch);
+  float G[EB_NP];
+#pragma unroll
+  for (int j = 0; j < EB_NP; ++j) G[j] = 0.f;
+  for (int64_t p = blockIdx.y; p < a.P; p += gridDim.y) {
+    const int64_t i = p * a.C + c;
+    const float yh = a.y_hat[i];
+    EbTape tl, tu;
+    const float lo = eb_logits<true>(ch, yh - 0.5f, &tl);
+    const float up = eb_logits<true>(ch, yh + 0.5f, &tu);
+    const float t = lo + up;
+    const float sg = (t > 0.f) ? -1.f : ((t < 0.f) ? 1.f : 0.f);
+    const float su = sigmoid_f(sg * up), sl = sigmoid_f(sg * lo);
+    const float D = su - sl, L = fabsf(D);
+    float g = a.g_lik ? a.g_lik[i] : a.rate_coef / fmaxf(L, a.lik_bound);
+    if (!(L >= a.lik_bound || g < 0.f)) g = 0.f;
+    const float sd = (D > 0.f) ? 1.f : ((D < 0.f) ? -1.f : 0.f);
+    const float gu = g * sd * su * (1.f - su) * sg;
+    const float gl = -g * sd * sl * (1.f - sl) * sg;
+    float gx = eb_logits_bwd(ch, tl, yh - 0.5f, gl, G);
+    gx += eb_logits_bwd(ch, tu, yh + 0.5f, gu, G);
+    const float gyh = a.g_yhat ? a.g_yhat[i] : 0.f;
+    a.g_x[i] = (a.mode == QUANT_NOISE) ? gx + gyh : 0.f;
+  }
+  // chain through softplus / tanh of the raw parameters, then one atomic per (channel, param)
+  float* out = a.g_params + (size_t)c * EB_NP;
+#pragma unroll
+  for (int j = 0; j < EB_NP; ++j) {
+    const bool is_m = (j < 3) || (j >= 9 && j < 54 && ((j - 9) % 15) < 9) || (j >= 54 && j < 57);
+    const bool is_f = (j >= 6 && j < 9) || (j >= 9 && j < 54 && ((j - 9) % 15) >= 12);
+    float g = G[j];
+    if (is_m) g *= (q[j] > 20.f) ? 1.f : sigmoid_f(q[j]);
+    if (is_f) { const float t = tanhf(q[j]); g *= 1.f - t * t; }
+    atomicAdd(out + j, g);
+  }
+}
+
+// aux loss (entropy_models.py:431-434): value and d/d quantiles in one pass; parameters detached.
+__global__ void __launch_bounds__(128) eb_aux_kernel(const float* params, const float* quantiles, const float* target,
+                                                     int C, float* loss, float* g_quantiles) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  float local = 0.f;
+  if (c < C) {
+    EbChan ch;
+    eb_load(params + (size_t)c * EB_NP, ch);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const float v = quantiles[c * 3 + k];
+      EbTape tp;
+      const float lg = eb_logits<true>(ch, v, &tp);
+      const float d = lg - target[k];
+      local += fabsf(d);
+      const float sd = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);
+      float G[EB_NP];
+#pragma unroll
+      for (int j = 0; j < EB_NP; ++j) G[j] = 0.f;
+      g_quantiles[c * 3 + k] = eb_logits_bwd(ch, tp, v, sd, G);
+    }
+  }
+  __shared__ float red[32];
+  local = block_sum(local, red);
+  if (threadIdx.x == 0) atomicAdd(loss, local);
+}
+
+static dim3 eb_grid(int C, int64_t P) {
+  const int bx = (C + 127) / 128;
+  int64_t by = (148 * 4 + bx - 1) / bx;
+  if (by > P) by = P;
+  if (by < 1) by = 1;
+  return dim3(bx, (unsigned)by);
+}
+
+int eb_forward(const EbArgs& a, cudaStream_t s) {
+  if (a.P <= 0 || a.C <= 0) return LMSFC_OK;
+  eb_forward_kernel<<<eb_grid(a.C, a.P), 128, 0, s>>>(a);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+int eb_backward(const EbBwdArgs& a, cudaStream_t s) {
+  if (a.P <= 0 || a.C <= 0) return LMSFC_OK;
+  eb_backward_kernel<<<eb_grid(a.C, a.P), 128, 0, s>>>(a);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+int eb_aux(const float* params, const float* quantiles, const float* target, int C, float* loss, float* g_quantiles,
+           cudaStream_t s) {
+  eb_aux_kernel<<<(C + 127) / 128, 128, 0, s>>>(params, quantiles, target, C, loss, g_quantiles);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+}  // namespace lmsfc

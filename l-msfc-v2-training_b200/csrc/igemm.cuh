@@ -1,0 +1,65 @@
+// Parameter blocks of the tcgen05 implicit-GEMM kernels (igemm.cu).
+#pragma once
+#include "common.cuh"
+
+namespace lmsfc {
+
+constexpr int kMaxTaps = 25;
+
+// epilogue modes of the forward/data-gradient kernel
+enum : int {
+  EPI_BIAS = 0,     // v = acc + bias[n]; optional ReLU; store bf16 / fp32 / |v| bf16
+  EPI_GDN = 1,      // nrm = acc + bias[n]; rn = rsqrt(nrm); y = x*rn (GDN) | x/rn (IGDN); store y, rn
+  EPI_GDN_BWD = 2,  // s = acc; gx = gy*f + 2*x*s, f = rn (GDN) | 1/rn (IGDN)
+};
+
+// Gathered-A x weight-B GEMM:  D[m][n] = sum_{tap,c} A[pixel(m)+tap][c] * W[n][widx(tap)*Ctot + c]
+struct IgemmParams {
+  CUtensorMap tmapB;        // filled by launch_igemm: box {64, BLOCK_N}, SWIZZLE_128B
+  const __nv_bfloat16* w;   // weights, bf16 [w_rows][w_cols], K (= tap*Ctot + c) contiguous
+  int w_rows, w_cols;
+  const __nv_bfloat16* src0;  // NHWC bf16 [B][Hin][Win][c0]
+  const __nv_bfloat16* src1;  // optional second source (channel concat), [B][Hin][Win][c1]
+  int c0, c1;
+  int B, Hin, Win;
+  int Hg, Wg, M;            // GEMM row grid: m = (b*Hg + hg)*Wg + wg
+  int sin;                  // input pixel = (hg*sin + dy, wg*sin + dx)
+  int ntaps;
+  int8_t dy[kMaxTaps], dx[kMaxTaps];
+  int16_t widx[kMaxTaps];   // weight tap index of each gathered tap
+  int Hout, Wout, sout, oy, ox;  // output pixel = (hg*sout + oy, wg*sout + ox)
+  int N;                    // output channels (row pitch of every output / aux tensor)
+  int epi, relu, inverse;
+  const float* bias;        // [N] or null
+  __nv_bfloat16* out_bf16;  // nullable
+  float* out_f32;           // nullable
+  __nv_bfloat16* out_abs;   // nullable, |v| (feeds h_a, models/google.py:294)
+  __nv_bfloat16* out_rn;    // EPI_GDN: rsqrt(norm), saved for backward
+  const __nv_bfloat16* aux_x;   // EPI_GDN / EPI_GDN_BWD
+  const __nv_bfloat16* aux_gy;  // EPI_GDN_BWD
+  const __nv_bfloat16* aux_rn;  // EPI_GDN_BWD
+};
+
+// Weight-gradient GEMM (K = pixels):
+//   G[d][widx(tap)][g] += sum_pix dense[pix][d] * gath[pixel(pix)+tap][g]
+struct WgradParams {
+  CUtensorMap tmapA;        // filled by launch_wgrad: box {64 ch, 64 px}, SWIZZLE_128B
+  const __nv_bfloat16* dense;  // dense operand, NHWC bf16 viewed as [M][Cd]
+  const __nv_bfloat16* g0;  // gathered NHWC bf16 [B][Hin][Win][gc0]
+  const __nv_bfloat16* g1;  // optional concat source [B][Hin][Win][gc1]
+  int gc0, gc1;
+  int B, Hin, Win;
+  int Hg, Wg, M;            // dense pixel grid
+  int sin;
+  int ntaps;
+  int8_t dy[kMaxTaps], dx[kMaxTaps];
+  int16_t widx[kMaxTaps];
+  float* out;               // fp32 [Cd][T][Cg], accumulated with red.global.add
+  int Cd, Cg, T;
+  int kb_total, kb_per_split;
+};
+
+int launch_igemm(IgemmParams& p, cudaStream_t stream);
+int launch_wgrad(WgradParams& p, cudaStream_t stream);
+
+}  // namespace lmsfc

@@ -1,0 +1,87 @@
+// Internal launch interfaces of the memory-bound kernels (entropy.cu, elementwise.cu, cdf.cu).
+#pragma once
+#include "common.cuh"
+
+namespace lmsfc {
+
+enum : int { QUANT_NOISE = 0, QUANT_DEQUANTIZE = 1 };
+
+struct GcArgs {
+  const float *y, *scales, *means, *noise;   // means / noise nullable
+  float *y_hat, *lik, *sum_ln;               // sum_ln nullable (atomicAdd of sum ln L)
+  int64_t n;
+  int mode;
+  float scale_bound, lik_bound;
+  uint64_t seed, offset;
+  const uint64_t* rng_state;                 // device {seed, step}; nullable
+};
+struct GcBwdArgs {
+  const float *y_hat, *scales, *means, *g_lik, *g_yhat;   // means / g_lik / g_yhat nullable
+  float *g_y, *g_scales, *g_means;                        // g_means nullable
+  int64_t n;
+  int mode;
+  float scale_bound, lik_bound, rate_coef;                // g_lik == null -> g = rate_coef / lik
+};
+struct EbArgs {
+  const float *x, *params, *medians, *noise;  // x: [P][C] (NHWC); params: [C][58]
+  float *y_hat, *lik, *sum_ln;
+  int64_t P;
+  int C, mode;
+  float lik_bound;
+  uint64_t seed, offset;
+  const uint64_t* rng_state;
+};
+struct EbBwdArgs {
+  const float *y_hat, *params, *g_lik, *g_yhat;
+  float *g_x, *g_params;                      // g_params [C][58], accumulated with atomicAdd
+  int64_t P;
+  int C, mode;
+  float lik_bound, rate_coef;
+};
+
+int gc_forward(const GcArgs& a, cudaStream_t s);
+int gc_backward(const GcBwdArgs& a, cudaStream_t s);
+int eb_forward(const EbArgs& a, cudaStream_t s);
+int eb_backward(const EbBwdArgs& a, cudaStream_t s);
+int eb_aux(const float* params, const float* quantiles, const float* target, int C, float* loss, float* g_quantiles,
+           cudaStream_t s);
+int rng_advance(uint64_t* state, cudaStream_t s);
+
+// ---- elementwise.cu
+int mse_fwd_bwd(const __nv_bfloat16* xhat, const __nv_bfloat16* x, int64_t n, float grad_coef, float* sse,
+                __nv_bfloat16* grad, cudaStream_t s);
+int loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale, float* out,
+                  cudaStream_t s);
+int square_bf16(const __nv_bfloat16* x, __nv_bfloat16* x2, int64_t n, cudaStream_t s);
+int gdn_t(const __nv_bfloat16* gy, const __nv_bfloat16* x, const __nv_bfloat16* rn, int inverse, int64_t P, int C,
+          __nv_bfloat16* t, float* g_beta, cudaStream_t s);
+int reparam_fwd(const float* p, int64_t n, float bound, float pedestal, float* out_f32, __nv_bfloat16* out_bf16,
+                cudaStream_t s);
+int reparam_bwd(const float* g_out, const float* p, int64_t n, float bound, float* g_p, cudaStream_t s);
+int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream_t s);
+int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, cudaStream_t s);
+int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, int64_t n, __nv_bfloat16* g_out,
+            cudaStream_t s);
+int cast_f32_bf16(const float* in, __nv_bfloat16* out, int64_t n, cudaStream_t s);
+int cast_bf16_f32(const __nv_bfloat16* in, float* out, int64_t n, cudaStream_t s);
+int transpose_weight(const float* in, __nv_bfloat16* out, int D0, int T, int D1, cudaStream_t s);
+int nchw_to_nhwc_bf16(const float* in, __nv_bfloat16* out, int B, int C, int HW, cudaStream_t s);
+int sumsq_f32(const float* g, int64_t n, float* accum, cudaStream_t s);
+struct AdamArgs {
+  float *p, *m, *v;
+  const float* g;
+  __nv_bfloat16* p_bf16;     // nullable: bf16 shadow written in the same pass
+  int64_t n;
+  float lr, beta1, beta2, eps, max_norm;   // max_norm <= 0: no clipping
+  const float* sumsq;        // device scalar with sum(g^2) (clip_grad_norm_); nullable
+  int* step;                 // device step counter, incremented by the prep kernel
+  float* scratch;            // >= 4 floats: {clip_coef, bias_corr1, bias_corr2, grad_norm}
+};
+int adam_step(const AdamArgs& a, cudaStream_t s);
+
+// ---- cdf.cu
+int pmf_to_quantized_cdf_host(const float* pmf, int n, int precision, uint32_t* cdf);
+int pmf_rows_to_cdf_device(const float* pmf, int pmf_stride, const float* tail, const int* pmf_length, int rows,
+                           int precision, int32_t* cdf, int cdf_stride, int* status, cudaStream_t s);
+
+}  // namespace lmsfc

@@ -1,0 +1,124 @@
+// Optimiser-side kernels over the flat parameter arena: fused clip_grad_norm_ + Adam with the
+// bf16 GEMM-operand shadow written in the same pass, weight repacking, layout conversion.
+//   compressai/examples/train.py:100-107 (clip, optimizer.step, aux_optimizer.step)
+//   torch.optim.Adam defaults (betas 0.9/0.999, eps 1e-8, no weight decay, no amsgrad)
+#include "kernels.cuh"
+
+namespace lmsfc {
+
+namespace {
+constexpr int TPB = 256;
+inline int grid1d(int64_t work_items) {
+  int64_t b = (work_items + TPB - 1) / TPB;
+  const int64_t cap = 148 * 8;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+}  // namespace
+
+// ---------------------------------------------------------------- sum of squares (grad norm)
+__global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g, int64_t n4, const float* tail, int ntail,
+                                                    float* accum) {
+  float local = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n4; i += (int64_t)gridDim.x * TPB) {
+    const float4 v = __ldg(g + i);
+    local += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  if (blockIdx.x == 0 && (int)threadIdx.x < ntail) local += tail[threadIdx.x] * tail[threadIdx.x];
+  __shared__ float red[32];
+  local = block_sum(local, red);
+  if (threadIdx.x == 0) atomicAdd(accum, local);
+}
+int sumsq_f32(const float* g, int64_t n, float* accum, cudaStream_t s) {
+  if (n == 0) return LMSFC_OK;
+  LMSFC_CHECK_ARG(((uintptr_t)g & 15) == 0, "sumsq: pointer must be 16-byte aligned");
+  const int64_t n4 = n / 4;
+  sumsq_kernel<<<grid1d(n4 > 0 ? n4 : 1), TPB, 0, s>>>((const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// ---------------------------------------------------------------- Adam
+// prep: one thread bumps the step counter and derives {clip_coef, bias_corr1, bias_corr2, norm}
+__global__ void adam_prep_kernel(AdamArgs a) {
+  const int step = *a.step + 1;
+  *a.step = step;
+  float clip = 1.f, norm = 0.f;
+  if (a.sumsq) {
+    norm = sqrtf(*a.sumsq);
+    if (a.max_norm > 0.f) clip = fminf(1.f, a.max_norm / (norm + 1e-6f));   // torch clip_grad_norm_
+  }
+  a.scratch[0] = clip;
+  a.scratch[1] = 1.f - powf(a.beta1, (float)step);
+  a.scratch[2] = 1.f - powf(a.beta2, (float)step);
+  a.scratch[3] = norm;
+}
+__global__ void __launch_bounds__(TPB) adam_kernel(AdamArgs a) {
+  const float clip = a.scratch[0], bc1 = a.scratch[1], bc2 = a.scratch[2];
+  const float step_size = a.lr / bc1, rs_bc2 = rsqrtf(bc2);
+  for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * TPB) {
+    const float g = a.g[i] * clip;
+    const float m = a.beta1 * a.m[i] + (1.f - a.beta1) * g;
+    const float v = a.beta2 * a.v[i] + (1.f - a.beta2) * g * g;
+    const float p = a.p[i] - step_size * m / (sqrtf(v) * rs_bc2 + a.eps);
+    a.m[i] = m; a.v[i] = v; a.p[i] = p;
+    if (a.p_bf16) a.p_bf16[i] = __float2bfloat16(p);
+  }
+}
+int adam_step(const AdamArgs& a, cudaStream_t s) {
+  if (a.n == 0) return LMSFC_OK;
+  adam_prep_kernel<<<1, 1, 0, s>>>(a);
+  LMSFC_LAUNCH_CHECK();
+  adam_kernel<<<grid1d(a.n), TPB, 0, s>>>(a);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// ---------------------------------------------------------------- weight repack
+// fp32 [D0][T][D1] -> bf16 [D1][T][D0]  (the "other side" GEMM operand of a conv / deconv)
+__global__ void __launch_bounds__(256) transpose_weight_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                               int D0, int T, int D1) {
+  __shared__ float tile[32][33];
+  const int t = blockIdx.z;
+  const int d1b = blockIdx.x * 32, d0b = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += 8) {
+    const int d0 = d0b + r, d1 = d1b + threadIdx.x;
+    tile[r][threadIdx.x] = (d0 < D0 && d1 < D1) ? in[((size_t)d0 * T + t) * D1 + d1] : 0.f;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += 8) {
+    const int d1 = d1b + r, d0 = d0b + threadIdx.x;
+    if (d0 < D0 && d1 < D1) out[((size_t)d1 * T + t) * D0 + d0] = __float2bfloat16(tile[threadIdx.x][r]);
+  }
+}
+int transpose_weight(const float* in, __nv_bfloat16* out, int D0, int T, int D1, cudaStream_t s) {
+  dim3 grid((D1 + 31) / 32, (D0 + 31) / 32, T);
+  transpose_weight_kernel<<<grid, dim3(32, 8), 0, s>>>(in, out, D0, T, D1);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+// fp32 NCHW -> bf16 NHWC (feature ingest for callers that hand over the reference's layout)
+__global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int C,
+                                                           int HW) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int pb = blockIdx.x * 32, cb = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += 8) {
+    const int c = cb + r, p = pb + threadIdx.x;
+    tile[r][threadIdx.x] = (c < C && p < HW) ? in[((size_t)b * C + c) * HW + p] : 0.f;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += 8) {
+    const int p = pb + r, c = cb + threadIdx.x;
+    if (c < C && p < HW) out[((size_t)b * HW + p) * C + c] = __float2bfloat16(tile[threadIdx.x][r]);
+  }
+}
+int nchw_to_nhwc_bf16(const float* in, __nv_bfloat16* out, int B, int C, int HW, cudaStream_t s) {
+  if (B == 0 || C == 0 || HW == 0) return LMSFC_OK;
+  dim3 grid((HW + 31) / 32, (C + 31) / 32, B);
+  nchw_to_nhwc_kernel<<<grid, dim3(32, 8), 0, s>>>(in, out, C, HW);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+}  // namespace lmsfc

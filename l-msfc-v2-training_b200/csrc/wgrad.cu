@@ -1,0 +1,201 @@
+// tcgen05 weight-gradient GEMM (K = pixels) for sm_100a.
+//
+//   G[d][widx(tap)][g] += sum_pix dense[pix][d] * gath[pixel(pix) + tap][g]
+//
+// Backward-by-weights of compressai/models/utils.py:128-146 (conv: dense = grad_out, gathered =
+// input; deconv: dense = input, gathered = grad_out) and of GDN's gamma (layers/gdn.py:86).
+// Both operands are channel-contiguous NHWC, i.e. MN-major for the MMA: the dense side arrives
+// by TMA (box 64 ch x 64 px, SWIZZLE_128B), the shifted/strided side by a cp.async gather into
+// the same 128-byte-row swizzled image.  One CTA = 128 dense channels x 256 gathered channels of
+// one filter tap over one K split; fp32 partials leave TMEM through red.global.add.v4.f32.
+#include "igemm.cuh"
+
+namespace lmsfc {
+
+namespace {
+constexpr int WG_BM = 128, WG_BN = 256, WG_BK = 64;
+constexpr int WG_A_BYTES = WG_BK * WG_BM * 2;   // 16 KB: 2 segments of [64 px][64 ch]
+constexpr int WG_B_BYTES = WG_BK * WG_BN * 2;   // 32 KB: 4 segments
+constexpr int WG_SEG_BYTES = WG_BK * 128;       // 8 KB
+constexpr int WG_STAGE_BYTES = WG_A_BYTES + WG_B_BYTES;
+constexpr int WG_STAGES = 4;
+constexpr int WG_SMEM_BYTES = WG_STAGES * WG_STAGE_BYTES + 1024 + 256;
+constexpr int WG_THREADS = 192;
+constexpr int WG_LAG = 2;
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+}  // namespace
+
+__global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_constant__ WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = (uint64_t*)(smem + WG_STAGES * WG_STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + WG_STAGES;
+  uint64_t* tmem_full_bar = empty_bar + WG_STAGES;
+  uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ntile_per_tap = p.Cg / WG_BN;
+  const int tap = blockIdx.x / ntile_per_tap;
+  const int n0 = (blockIdx.x % ntile_per_tap) * WG_BN;   // gathered-channel offset
+  const int d0 = blockIdx.y * WG_BM;                      // dense-channel offset
+  const int kb_begin = blockIdx.z * p.kb_per_split;
+  const int kb_end = min(kb_begin + p.kb_per_split, p.kb_total);
+  const int nkb = kb_end - kb_begin;
+  if (nkb <= 0) return;
+  const uint32_t smem_base = smem_u32(smem);
+
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&p.tmapA);
+    for (int s = 0; s < WG_STAGES; ++s) {
+      mbar_init(&full_bar[s], 128 + 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 5) tmem_alloc<WG_BN>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 4) {
+    // ============ gather of the shifted operand: 64 pixel rows x 256 channels per K block ============
+    const int chunk = tid & 7, r0 = tid >> 3;   // rows r0 + 16*i, i < 4
+    const bool first = n0 < p.gc0;
+    const __nv_bfloat16* src = first ? p.g0 : p.g1;
+    const int C = first ? p.gc0 : p.gc1;
+    const int coff = (first ? n0 : n0 - p.gc0) + chunk * 8;
+    const int dy = p.dy[tap], dx = p.dx[tap];
+    const uint32_t dst_thread = smem_base + WG_A_BYTES + r0 * 128 + ((chunk ^ (r0 & 7)) << 4);
+    int stage = 0, phase = 0;
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int pix0 = (kb_begin + kb) * WG_BK;
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      const uint32_t dst = dst_thread + stage * WG_STAGE_BYTES;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int m = pix0 + r0 + 16 * i;
+        bool ok = m < p.M;
+        const __nv_bfloat16* g = src;
+        if (ok) {
+          const int wg = m % p.Wg, t = m / p.Wg;
+          const int hg = t % p.Hg, b = t / p.Hg;
+          const int hi = hg * p.sin + dy, wi = wg * p.sin + dx;
+          ok = (unsigned)hi < (unsigned)p.Hin && (unsigned)wi < (unsigned)p.Win;
+          if (ok) g = src + ((size_t)((b * p.Hin + hi) * p.Win + wi) * C + coff);
+        }
+#pragma unroll
+        for (int seg = 0; seg < 4; ++seg)
+          cp_async16(dst + seg * WG_SEG_BYTES + i * 2048, g + seg * 64, ok ? 16u : 0u);
+      }
+      cp_async_commit();
+      if (kb >= WG_LAG) {
+        cp_async_wait<WG_LAG>();
+        fence_proxy_async_smem();
+        mbar_arrive(&full_bar[(kb - WG_LAG) % WG_STAGES]);
+      }
+      if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+    }
+    if (nkb >= 2) {
+      cp_async_wait<1>();
+      fence_proxy_async_smem();
+      mbar_arrive(&full_bar[(nkb - 2) % WG_STAGES]);
+    }
+    cp_async_wait<0>();
+    fence_proxy_async_smem();
+    mbar_arrive(&full_bar[(nkb - 1) % WG_STAGES]);
+
+    // ============ epilogue: fp32 partial tile -> red.global.add ============
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const int d = d0 + warp * 32 + lane;
+    float* orow = p.out + ((size_t)d * p.T + p.widx[tap]) * p.Cg + n0;
+#pragma unroll 1
+    for (int cb = 0; cb < WG_BN; cb += 32) {
+      uint32_t r[32];
+      tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + cb, r);
+      tmem_ld_wait();
+      if (d < p.Cd) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          red_add_v4(orow + cb + 4 * j, __uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                     __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+      }
+    }
+  } else if (warp == 4) {
+    // ============ dense operand by TMA: two [64 px][64 ch] boxes per K block ============
+    if (lane == 0) {
+      int stage = 0, phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full_bar[stage], WG_A_BYTES);
+        const int pix0 = (kb_begin + kb) * WG_BK;
+        const uint32_t sa = smem_base + stage * WG_STAGE_BYTES;
+        tma_load_2d(&p.tmapA, &full_bar[stage], sa, d0, pix0);
+        tma_load_2d(&p.tmapA, &full_bar[stage], sa + WG_SEG_BYTES, d0 + 64, pix0);
+        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ============ MMA issuer: both operands MN-major (channels contiguous, K = pixel rows) ============
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(WG_BM, WG_BN, 1, 1);
+      int stage = 0, phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_base + stage * WG_STAGE_BYTES;
+        const uint32_t sb = sa + WG_A_BYTES;
+#pragma unroll
+        for (int k = 0; k < WG_BK / 16; ++k) {
+          // K step of 16 pixel rows = 2 KB; LBO = next 64-channel segment, SBO = next 8 rows
+          const uint64_t ad = make_sdesc_sw128(sa + k * 2048, WG_SEG_BYTES, 1024);
+          const uint64_t bd = make_sdesc_sw128(sb + k * 2048, WG_SEG_BYTES, 1024);
+          umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0);
+        }
+        umma_commit(&empty_bar[stage]);
+        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(tmem_full_bar);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc<WG_BN>(tmem_base);
+  }
+}
+
+int launch_wgrad(WgradParams& p, cudaStream_t stream) {
+  LMSFC_CHECK_ARG(p.Cd % 128 == 0 && p.Cg % 256 == 0, "wgrad: Cd=%d must be a multiple of 128, Cg=%d of 256", p.Cd,
+                  p.Cg);
+  LMSFC_CHECK_ARG(p.gc0 + p.gc1 == p.Cg && p.gc0 % 256 == 0, "wgrad: gathered channels %d+%d != %d", p.gc0, p.gc1,
+                  p.Cg);
+  LMSFC_CHECK_ARG(p.ntaps >= 1 && p.ntaps <= kMaxTaps && p.M > 0, "wgrad: ntaps=%d M=%d", p.ntaps, p.M);
+  static bool attr_done = false;
+  if (!attr_done) {
+    LMSFC_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES));
+    attr_done = true;
+  }
+  int rc = make_tmap_2d_bf16(&p.tmapA, p.dense, (uint64_t)p.M, (uint64_t)p.Cd, (uint64_t)p.Cd, 64, 64);
+  if (rc) return rc;
+  p.kb_total = ceil_div(p.M, WG_BK);
+  const int tiles = p.ntaps * (p.Cg / WG_BN) * (p.Cd / WG_BM);
+  // split K (pixels) until the grid covers ~2 waves of the 148 SMs, keeping >= 4 K blocks per CTA
+  int ksplit = ceil_div(296, tiles);
+  ksplit = max(1, min(ksplit, ceil_div(p.kb_total, 4)));
+  p.kb_per_split = ceil_div(p.kb_total, ksplit);
+  ksplit = ceil_div(p.kb_total, p.kb_per_split);
+  dim3 grid(p.ntaps * (p.Cg / WG_BN), p.Cd / WG_BM, ksplit);
+  wgrad_kernel<<<grid, WG_THREADS, WG_SMEM_BYTES, stream>>>(p);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
+}  // namespace lmsfc
