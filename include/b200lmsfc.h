@@ -100,8 +100,9 @@ int lmsfc_loss_finalize(const float* accum, const float* coef, int n_rate, int n
 
 /* ------------------------------------------------------------------ small gradients / layout */
 int lmsfc_relu_backward(void* g_bf16_inplace, const void* out_bf16, int64_t n, void* stream);
-int lmsfc_abs_backward(const float* g_direct, const void* g_abs_bf16, const float* y, int64_t n, void* g_out_bf16,
-                       void* stream);
+/* gradient of a latent head that returned (fp32 y, bf16 |y|): g = [relu ? (y>0) : 1]*g_direct + sign(y)*g_abs */
+int lmsfc_abs_backward(const float* g_direct, const void* g_abs_bf16, const float* y, int64_t n, int relu,
+                       void* g_out_bf16, void* stream);
 int lmsfc_colsum(const void* g_bf16, int64_t P, int C, float* out, void* stream);
 int lmsfc_cast_f32_bf16(const float* in, void* out, int64_t n, void* stream);
 int lmsfc_cast_bf16_f32(const void* in, float* out, int64_t n, void* stream);

@@ -1,0 +1,91 @@
+"""ctypes binding of libb200lmsfc.so (C ABI in include/b200lmsfc.h).
+
+There is no CPU fallback: importing this module without the built library raises, and every call
+that fails raises with the library's message (ValueError for the reference's ValueError cases,
+RuntimeError for CUDA errors).
+"""
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int64, c_uint64, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200lmsfc.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+        "(or `make -C l-msfc-v2-training_b200/csrc`).  This package has no CPU / PyTorch fallback.")
+
+lib = ctypes.CDLL(LIB_PATH)
+
+
+class ConvDesc(Structure):
+    _fields_ = [("kind", c_int), ("k", c_int), ("stride", c_int), ("B", c_int), ("Hin", c_int), ("Win", c_int),
+                ("Hout", c_int), ("Wout", c_int), ("c0", c_int), ("c1", c_int), ("Cout", c_int)]
+
+
+P = c_void_p
+_SIGS = {
+    "lmsfc_conv_forward": [POINTER(ConvDesc), P, P, P, P, c_int, P, P, P, P],
+    "lmsfc_conv_dgrad": [POINTER(ConvDesc), P, P, c_int, P, P],
+    "lmsfc_conv_wgrad": [POINTER(ConvDesc), P, P, P, P, P, P],
+    "lmsfc_gdn_forward": [P, P, P, c_int, c_int64, c_int, P, P, P, P],
+    "lmsfc_gdn_backward": [P, P, P, P, c_int, c_int64, c_int, P, P, P, P, P, P],
+    "lmsfc_reparam_forward": [P, c_int64, c_float, c_float, P, P, P],
+    "lmsfc_reparam_backward": [P, P, c_int64, c_float, P, P],
+    "lmsfc_gc_forward": [P, P, P, P, c_int64, c_int, c_float, c_float, c_uint64, c_uint64, P, P, P, P, P],
+    "lmsfc_gc_backward": [P, P, P, P, P, c_int64, c_int, c_float, c_float, c_float, P, P, P, P],
+    "lmsfc_eb_forward": [P, P, P, P, c_int64, c_int, c_int, c_float, c_uint64, c_uint64, P, P, P, P, P],
+    "lmsfc_eb_backward": [P, P, P, P, c_int64, c_int, c_int, c_float, c_float, P, P, P],
+    "lmsfc_eb_aux_loss": [P, P, P, c_int, P, P, P],
+    "lmsfc_rng_advance": [P, P],
+    "lmsfc_mse_forward_backward": [P, P, c_int64, c_float, P, P, P],
+    "lmsfc_loss_finalize": [P, P, c_int, c_int, c_float, P, P],
+    "lmsfc_relu_backward": [P, P, c_int64, P],
+    "lmsfc_abs_backward": [P, P, P, c_int64, c_int, P, P],
+    "lmsfc_colsum": [P, c_int64, c_int, P, P],
+    "lmsfc_cast_f32_bf16": [P, P, c_int64, P],
+    "lmsfc_cast_bf16_f32": [P, P, c_int64, P],
+    "lmsfc_nchw_to_nhwc_bf16": [P, P, c_int, c_int, c_int, P],
+    "lmsfc_transpose_weight": [P, P, c_int, c_int, c_int, P],
+    "lmsfc_sumsq": [P, c_int64, P, P],
+    "lmsfc_adam_step": [P, P, P, P, P, c_int64, c_float, c_float, c_float, c_float, c_float, P, P, P, P],
+    "lmsfc_pmf_to_quantized_cdf": [P, c_int, c_int, P],
+    "lmsfc_pmf_rows_to_cdf": [P, c_int, P, P, c_int, c_int, P, c_int, P, P],
+}
+EXPORTS = ["lmsfc_last_error", "lmsfc_version"] + list(_SIGS)
+
+lib.lmsfc_last_error.restype = c_char_p
+lib.lmsfc_last_error.argtypes = []
+lib.lmsfc_version.restype = c_int
+lib.lmsfc_version.argtypes = []
+
+
+def _wrap(name, argtypes):
+    fn = getattr(lib, name)
+    fn.argtypes = argtypes
+    fn.restype = c_int
+
+    def call(*args):
+        rc = fn(*args)
+        if rc != 0:
+            msg = lib.lmsfc_last_error().decode("utf-8", "replace")
+            if rc in (1, 3):
+                raise ValueError(f"{name}: {msg}")
+            raise RuntimeError(f"{name}: {msg}")
+    call.__name__ = name
+    return call
+
+
+for _n, _a in _SIGS.items():
+    globals()[_n[len("lmsfc_"):]] = _wrap(_n, _a)
+
+
+def ptr(t):
+    """Device (or host) address of a tensor, None -> NULL."""
+    return None if t is None else t.data_ptr()
+
+
+def stream():
+    import torch
+    return torch.cuda.current_stream().cuda_stream

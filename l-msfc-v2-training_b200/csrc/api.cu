@@ -256,9 +256,9 @@ extern "C" int lmsfc_loss_finalize(const float* accum, const float* coef, int n_
 extern "C" int lmsfc_relu_backward(void* g, const void* out, int64_t n, void* stream) {
   return relu_bwd_bf16((bf16*)g, (const bf16*)out, n, ST(stream));
 }
-extern "C" int lmsfc_abs_backward(const float* g_direct, const void* g_abs, const float* y, int64_t n, void* g_out,
-                                  void* stream) {
-  return abs_bwd(g_direct, (const bf16*)g_abs, y, n, (bf16*)g_out, ST(stream));
+extern "C" int lmsfc_abs_backward(const float* g_direct, const void* g_abs, const float* y, int64_t n, int relu,
+                                  void* g_out, void* stream) {
+  return abs_bwd(g_direct, (const bf16*)g_abs, y, n, relu, (bf16*)g_out, ST(stream));
 }
 extern "C" int lmsfc_colsum(const void* g, int64_t P, int C, float* out, void* stream) {
   return colsum_bf16((const bf16*)g, P, C, out, ST(stream));

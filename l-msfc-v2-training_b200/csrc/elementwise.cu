@@ -223,17 +223,20 @@ int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, cudaStr
   return LMSFC_OK;
 }
 // g_out = bf16(g_direct + sign(y) * g_abs): gradient of y feeding both GaussianConditional and h_a(|y|)
-__global__ void abs_bwd_kernel(const float* gd, const __nv_bfloat16* ga, const float* y, int64_t n, __nv_bfloat16* o) {
+// relu != 0: y is a ReLU output, both branches are masked by (y > 0)
+__global__ void abs_bwd_kernel(const float* gd, const __nv_bfloat16* ga, const float* y, int64_t n, int relu,
+                               __nv_bfloat16* o) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float yv = y[i];
     const float sg = (yv > 0.f) ? 1.f : ((yv < 0.f) ? -1.f : 0.f);
-    o[i] = __float2bfloat16((gd ? gd[i] : 0.f) + (ga ? sg * __bfloat162float(ga[i]) : 0.f));
+    const float d = (relu && !(yv > 0.f)) ? 0.f : (gd ? gd[i] : 0.f);
+    o[i] = __float2bfloat16(d + (ga ? sg * __bfloat162float(ga[i]) : 0.f));
   }
 }
-int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, int64_t n, __nv_bfloat16* g_out,
+int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, int64_t n, int relu, __nv_bfloat16* g_out,
             cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
-  abs_bwd_kernel<<<grid1d(n), TPB, 0, s>>>(g_direct, g_abs, y, n, g_out);
+  abs_bwd_kernel<<<grid1d(n), TPB, 0, s>>>(g_direct, g_abs, y, n, relu, g_out);
   LMSFC_LAUNCH_CHECK();
   return LMSFC_OK;
 }

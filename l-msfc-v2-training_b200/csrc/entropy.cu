@@ -46,8 +46,9 @@ __device__ __forceinline__ float normal_pdf(float t) { return 0.3989422804014327
 
 __global__ void __launch_bounds__(256) gc_forward_kernel(GcArgs a) {
   float local = 0.f;
-  const uint64_t seed = a.rng_state ? a.rng_state[0] : a.seed;
-  const uint64_t off = (a.rng_state ? a.rng_state[1] : 0) + a.offset;
+  // key = seed perturbed per module (`offset`), counter = device step count
+  const uint64_t seed = (a.rng_state ? a.rng_state[0] : a.seed) + a.offset * 0x9E3779B97F4A7C15ull;
+  const uint64_t off = a.rng_state ? a.rng_state[1] : 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * blockDim.x) {
     const float y = a.y[i], mu = a.means ? a.means[i] : 0.f;
     float yh;
@@ -190,8 +191,9 @@ __global__ void __launch_bounds__(128) eb_forward_kernel(EbArgs a) {
     EbChan ch;
     eb_load(a.params + (size_t)c * EB_NP, ch);
     const float med = a.medians ? a.medians[c] : 0.f;
-    const uint64_t seed = a.rng_state ? a.rng_state[0] : a.seed;
-    const uint64_t off = (a.rng_state ? a.rng_state[1] : 0) + a.offset;
+    // key = seed perturbed per module (`offset`), counter = device step count
+    const uint64_t seed = (a.rng_state ? a.rng_state[0] : a.seed) + a.offset * 0x9E3779B97F4A7C15ull;
+    const uint64_t off = a.rng_state ? a.rng_state[1] : 0;
     for (int64_t p = blockIdx.y; p < a.P; p += gridDim.y) {
       const int64_t i = p * a.C + c;
       const float x = a.x[i];

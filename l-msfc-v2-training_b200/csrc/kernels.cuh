@@ -60,7 +60,7 @@ int reparam_fwd(const float* p, int64_t n, float bound, float pedestal, float* o
 int reparam_bwd(const float* g_out, const float* p, int64_t n, float bound, float* g_p, cudaStream_t s);
 int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream_t s);
 int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, cudaStream_t s);
-int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, int64_t n, __nv_bfloat16* g_out,
+int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, int64_t n, int relu, __nv_bfloat16* g_out,
             cudaStream_t s);
 int cast_f32_bf16(const float* in, __nv_bfloat16* out, int64_t n, cudaStream_t s);
 int cast_bf16_f32(const __nv_bfloat16* in, float* out, int64_t n, cudaStream_t s);

@@ -1,0 +1,450 @@
+"""torch.autograd bridges onto the C ABI (include/b200lmsfc.h).
+
+PyTorch supplies device memory, streams and the autograd tape; all arithmetic happens in
+libb200lmsfc.so.  Layout contract: activations are bf16 tensors of logical shape [B,C,H,W] stored
+channels-last (NHWC in memory); latents and likelihoods are fp32 channels-last.
+
+Parameter gradients are written by the backward kernels straight into `param.grad` (pre-allocated
+by the model as views of one flat arena, see model.ParamArena); the autograd Functions therefore
+return None for parameters.  `grad_ready` callbacks let the data-parallel wrapper launch bucketed
+all-reduces while backward is still running.
+"""
+import math
+
+import torch
+
+from . import _lib as L
+from ._lib import ConvDesc, ptr, stream
+
+BF16, F32 = torch.bfloat16, torch.float32
+CL = torch.channels_last
+
+
+def _require_cuda(t):
+    if not t.is_cuda:
+        raise RuntimeError("l-msfc-v2-training_b200 runs on CUDA tensors only (no CPU fallback)")
+
+
+def nhwc(t, dtype):
+    """Return `t` ([B,C,H,W]) as a channels-last tensor of `dtype` (no copy when already so)."""
+    _require_cuda(t)
+    if t.dim() != 4:
+        raise ValueError(f"expected a 4-D [B,C,H,W] tensor, got {tuple(t.shape)}")
+    if t.dtype == dtype and t.is_contiguous(memory_format=CL):
+        return t
+    if t.dtype == F32 and dtype == BF16 and t.is_contiguous() and not t.requires_grad:
+        B, C, H, W = t.shape
+        out = torch.empty((B, C, H, W), dtype=BF16, device=t.device, memory_format=CL)
+        L.nchw_to_nhwc_bf16(ptr(t), ptr(out), B, C, H * W, stream())
+        return out
+    return t.to(dtype=dtype, memory_format=CL)
+
+
+def empty_nhwc(B, C, H, W, dtype, device):
+    return torch.empty((B, C, H, W), dtype=dtype, device=device, memory_format=CL)
+
+
+def grad_view(param, layout_perm=None):
+    """`param.grad` (allocated zero-filled with the parameter's own strides when missing) and,
+    for permuted GEMM-layout parameters, its physically contiguous view."""
+    if param.grad is None:
+        param.grad = torch.zeros_like(param)   # preserve_format keeps the GEMM-layout strides
+    g = param.grad
+    if layout_perm is not None:
+        g = g.permute(*layout_perm)
+    if not g.is_contiguous():
+        return None
+    return g
+
+
+# ====================================================================== conv / deconv
+class ConvState:
+    """Per-layer device state shared by forward and backward: geometry, bf16 weight shadows
+    ([D0][T][D1] "direct" and [D1][T][D0] "transposed") and the parameters they shadow."""
+
+    def __init__(self, kind, k, stride, c0, c1, cout):
+        self.kind, self.k, self.stride, self.c0, self.c1, self.cout = kind, k, stride, c0, c1, cout
+        self.T = k * k
+        cin = c0 + c1
+        self.D0, self.D1 = (cout, cin) if kind == 0 else (cin, cout)
+        self.w_direct = None
+        self.w_trans = None
+        self._version = -1
+        self.grad_ready = None     # callable(list_of_params) set by the DP wrapper
+
+    def out_hw(self, H, W, target=None):
+        if self.kind == 0:
+            return (H + self.stride - 1) // self.stride, (W + self.stride - 1) // self.stride
+        if target is None:
+            return H * self.stride, W * self.stride
+        return int(target[0]), int(target[1])
+
+    def desc(self, B, Hin, Win, Hout, Wout):
+        return ConvDesc(self.kind, self.k, self.stride, B, Hin, Win, Hout, Wout, self.c0, self.c1, self.cout)
+
+    def gemm_weight(self, weight):
+        """[D0][T][D1]-contiguous view of the torch-layout parameter ([D0][D1][kh][kw])."""
+        w = weight.detach().permute(0, 2, 3, 1)
+        return w if w.is_contiguous() else None
+
+    def refresh(self, weight, force=False):
+        """(Re)build the bf16 shadows when the fp32 parameter changed."""
+        v = weight._version
+        if not force and self.w_direct is not None and v == self._version:
+            return
+        wg = self.gemm_weight(weight)
+        if wg is None:   # parameter not in GEMM layout (user-assigned tensor): stage a permuted copy
+            wg = weight.detach().permute(0, 2, 3, 1).contiguous()
+        if self.w_direct is None:
+            self.w_direct = torch.empty((self.D0, self.T, self.D1), dtype=BF16, device=weight.device)
+            self.w_trans = torch.empty((self.D1, self.T, self.D0), dtype=BF16, device=weight.device)
+        st = stream()
+        L.cast_f32_bf16(ptr(wg), ptr(self.w_direct), wg.numel(), st)
+        L.transpose_weight(ptr(wg), ptr(self.w_trans), self.D0, self.T, self.D1, st)
+        self._version = v
+
+
+class _ConvFn(torch.autograd.Function):
+    """conv / deconv (+bias, +ReLU) -- compressai/models/utils.py:128-146.
+    mode 0: returns bf16 activation; mode 1 (latent head): returns (fp32 y, bf16 |y|)."""
+
+    @staticmethod
+    def forward(ctx, x0, x1, weight, bias, state, relu, mode, out_hw):
+        B, _, H, W = x0.shape
+        Ho, Wo = state.out_hw(H, W, out_hw)
+        state.refresh(weight)
+        d = state.desc(B, H, W, Ho, Wo)
+        w = state.w_direct if state.kind == 0 else state.w_trans
+        dev = x0.device
+        out_b = out_f = out_a = None
+        if mode == 0:
+            out_b = empty_nhwc(B, state.cout, Ho, Wo, BF16, dev)
+        else:
+            out_f = empty_nhwc(B, state.cout, Ho, Wo, F32, dev)
+            out_a = empty_nhwc(B, state.cout, Ho, Wo, BF16, dev)
+        L.conv_forward(d, ptr(x0), ptr(x1), ptr(w), ptr(bias), int(relu), ptr(out_b), ptr(out_f), ptr(out_a), stream())
+        ctx.state, ctx.relu, ctx.mode, ctx.shape = state, relu, mode, (B, H, W, Ho, Wo)
+        ctx.weight, ctx.bias = weight, bias
+        ctx.need_dx = ctx.needs_input_grad[0]
+        if mode == 0:
+            ctx.save_for_backward(x0, x1, out_b if relu else None, None)
+            return out_b
+        ctx.save_for_backward(x0, x1, None, out_f)
+        return out_f, out_a
+
+    @staticmethod
+    def backward(ctx, *grads):
+        state = ctx.state
+        x0, x1, out_relu, y_f32 = ctx.saved_tensors
+        B, H, W, Ho, Wo = ctx.shape
+        st = stream()
+        if ctx.mode == 0:
+            g = nhwc(grads[0], BF16)
+            if ctx.relu:
+                g = g.clone(memory_format=CL)
+                L.relu_backward(ptr(g), ptr(out_relu), g.numel(), st)
+        else:
+            g_direct, g_abs = grads
+            g = empty_nhwc(B, state.cout, Ho, Wo, BF16, x0.device)
+            gd = None if g_direct is None else nhwc(g_direct, F32)
+            ga = None if g_abs is None else nhwc(g_abs, BF16)
+            L.abs_backward(ptr(gd), ptr(ga), ptr(y_f32), g.numel(), int(ctx.relu), ptr(g), st)
+        d = state.desc(B, H, W, Ho, Wo)
+        # ---- weight / bias gradients, straight into param.grad
+        weight, bias = ctx.weight, ctx.bias
+        ready = []
+        if weight.requires_grad:
+            gw = grad_view(weight, (0, 2, 3, 1))
+            gb = grad_view(bias) if (bias is not None and bias.requires_grad) else None
+            if gw is not None:
+                L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(gw), ptr(gb), st)
+            else:  # foreign (non GEMM-layout) parameter: stage and add
+                tmp = torch.zeros((state.D0, state.T, state.D1), dtype=F32, device=g.device)
+                L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(tmp), ptr(gb), st)
+                weight.grad.add_(tmp.view(state.D0, state.k, state.k, state.D1).permute(0, 3, 1, 2))
+            ready.append(weight)
+            if gb is not None:
+                ready.append(bias)
+        # ---- data gradient (only source 0 is differentiable: source 1 is input data)
+        gx = None
+        if ctx.need_dx:
+            w = state.w_trans if state.kind == 0 else state.w_direct
+            gx = empty_nhwc(B, state.c0, H, W, BF16, g.device)
+            L.conv_dgrad(d, ptr(g), ptr(w), state.c0, ptr(gx), st)
+        if state.grad_ready is not None and ready:
+            state.grad_ready(ready)
+        return gx, None, None, None, None, None, None, None
+
+
+def conv_apply(state, x0, x1, weight, bias, relu=False, mode=0, out_hw=None):
+    x0 = nhwc(x0, BF16)
+    if x1 is not None:
+        x1 = nhwc(x1, BF16)
+        if x1.shape[0] != x0.shape[0] or x1.shape[2:] != x0.shape[2:]:
+            raise ValueError(f"concat sources disagree: {tuple(x0.shape)} vs {tuple(x1.shape)}")
+    if x0.shape[1] != state.c0 or (x1 is not None and x1.shape[1] != state.c1):
+        raise ValueError(f"expected {state.c0}+{state.c1} input channels, got {x0.shape[1]}")
+    return _ConvFn.apply(x0, x1, weight, bias, state, relu, mode, out_hw)
+
+
+# ====================================================================== GDN / IGDN
+PEDESTAL = 2.0 ** -36   # reparam_offset**2, compressai/ops/parametrizers.py:47-53
+
+
+class GDNState:
+    def __init__(self, C, inverse, beta_bound, gamma_bound):
+        self.C, self.inverse = C, bool(inverse)
+        self.beta_bound, self.gamma_bound = float(beta_bound), float(gamma_bound)
+        self.grad_ready = None
+
+
+class _GDNFn(torch.autograd.Function):
+    """compressai/layers/gdn.py:77-92 with the NonNegativeParametrizer of beta / gamma
+    (ops/parametrizers.py:60-63) and LowerBound's custom gradient (ops/bound_ops.py:40-42)."""
+
+    @staticmethod
+    def forward(ctx, x, beta, gamma, state):
+        B, C, H, W = x.shape
+        P = B * H * W
+        dev, st = x.device, stream()
+        beta_eff = torch.empty(C, dtype=F32, device=dev)
+        gamma_eff = torch.empty((C, C), dtype=F32, device=dev)
+        gamma_bf = torch.empty((C, C), dtype=BF16, device=dev)
+        L.reparam_forward(ptr(beta), C, state.beta_bound, PEDESTAL, ptr(beta_eff), None, st)
+        L.reparam_forward(ptr(gamma), C * C, state.gamma_bound, PEDESTAL, ptr(gamma_eff), ptr(gamma_bf), st)
+        x2 = torch.empty_like(x)
+        y = torch.empty_like(x)
+        rn = torch.empty_like(x)
+        L.gdn_forward(ptr(x), ptr(gamma_bf), ptr(beta_eff), int(state.inverse), P, C, ptr(x2), ptr(y), ptr(rn), st)
+        ctx.state, ctx.beta, ctx.gamma = state, beta, gamma
+        ctx.save_for_backward(x, rn, gamma_eff)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        state = ctx.state
+        x, rn, gamma_eff = ctx.saved_tensors
+        B, C, H, W = x.shape
+        P = B * H * W
+        dev, st = x.device, stream()
+        gy = nhwc(gy, BF16)
+        gamma_t = torch.empty((C, C), dtype=BF16, device=dev)
+        L.transpose_weight(ptr(gamma_eff), ptr(gamma_t), C, 1, C, st)
+        x2 = torch.empty_like(x)
+        t = torch.empty_like(x)
+        gx = torch.empty_like(x)
+        g_gamma_eff = torch.zeros((C, C), dtype=F32, device=dev)
+        g_beta_eff = torch.zeros(C, dtype=F32, device=dev)
+        L.gdn_backward(ptr(gy), ptr(x), ptr(rn), ptr(gamma_t), int(state.inverse), P, C, ptr(x2), ptr(t), ptr(gx),
+                       ptr(g_gamma_eff), ptr(g_beta_eff), st)
+        beta, gamma = ctx.beta, ctx.gamma
+        gb, gg = grad_view(beta), grad_view(gamma)
+        L.reparam_backward(ptr(g_beta_eff), ptr(beta), C, state.beta_bound, ptr(gb), st)
+        L.reparam_backward(ptr(g_gamma_eff), ptr(gamma), C * C, state.gamma_bound, ptr(gg), st)
+        if state.grad_ready is not None:
+            state.grad_ready([beta, gamma])
+        return (gx if ctx.needs_input_grad[0] else None), None, None, None
+
+
+def gdn_apply(state, x, beta, gamma):
+    return _GDNFn.apply(nhwc(x, BF16), beta, gamma, state)
+
+
+# ====================================================================== entropy models
+MODES = {"noise": 0, "dequantize": 1}
+
+
+def _mode_id(mode):
+    if mode not in MODES:
+        raise ValueError(f'Invalid quantization mode: "{mode}"')   # entropy_models.py:158-159
+    return MODES[mode]
+
+
+class RNG:
+    """Counter-based Philox stream for the quantisation noise: {seed, step} lives on the device so
+    a captured CUDA graph draws fresh noise at every replay; `offset` separates draws in a step."""
+
+    def __init__(self, device, seed=0):
+        self.state = torch.tensor([seed, 0], dtype=torch.int64, device=device)
+        self.seed = int(seed)
+
+    def advance(self):
+        L.rng_advance(ptr(self.state), stream())
+
+
+_SUM_LN_ATTR = "_lmsfc_sum_ln"
+
+
+class _GCFn(torch.autograd.Function):
+    """GaussianConditional.forward, entropy_models.py:650-682."""
+
+    @staticmethod
+    def forward(ctx, y, scales, means, noise, mode, scale_bound, lik_bound, rng, offset):
+        n = y.numel()
+        y_hat = torch.empty_like(y)
+        lik = torch.empty_like(y)
+        sum_ln = torch.zeros(1, dtype=F32, device=y.device)
+        L.gc_forward(ptr(y), ptr(scales), ptr(means), ptr(noise), n, mode, scale_bound, lik_bound,
+                     rng.seed if rng is not None else 0, offset, ptr(rng.state) if rng is not None else None,
+                     ptr(y_hat), ptr(lik), ptr(sum_ln), stream())
+        ctx.save_for_backward(y_hat, scales, means)
+        ctx.cfg = (mode, scale_bound, lik_bound)
+        setattr(lik, _SUM_LN_ATTR, sum_ln)
+        return y_hat, lik
+
+    @staticmethod
+    def backward(ctx, g_yhat, g_lik):
+        y_hat, scales, means = ctx.saved_tensors
+        mode, scale_bound, lik_bound = ctx.cfg
+        n = y_hat.numel()
+        g_y = torch.empty_like(y_hat)
+        g_s = torch.empty_like(y_hat)
+        g_m = torch.empty_like(y_hat) if means is not None else None
+        if g_lik is None:
+            g_lik = torch.zeros_like(y_hat)
+        g_lik = g_lik.to(dtype=F32).contiguous(memory_format=CL)
+        if g_yhat is not None:
+            g_yhat = g_yhat.to(dtype=F32).contiguous(memory_format=CL)
+        L.gc_backward(ptr(y_hat), ptr(scales), ptr(means), ptr(g_lik), ptr(g_yhat), n, mode, scale_bound, lik_bound,
+                      0.0, ptr(g_y), ptr(g_s), ptr(g_m), stream())
+        return g_y, g_s, g_m, None, None, None, None, None, None
+
+
+def gc_apply(y, scales, means, noise, mode, scale_bound, lik_bound, rng=None, offset=1):
+    y = nhwc(y, F32)
+    scales = nhwc(scales, F32)
+    if means is not None:
+        means = nhwc(means, F32)
+    if noise is not None:
+        noise = nhwc(noise, F32)
+    return _GCFn.apply(y, scales, means, noise, _mode_id(mode), float(scale_bound), float(lik_bound), rng, offset)
+
+
+class _EBFn(torch.autograd.Function):
+    """EntropyBottleneck.forward, entropy_models.py:436-516, on the NHWC view [P][C]."""
+
+    @staticmethod
+    def forward(ctx, x, packed, medians, noise, mode, lik_bound, rng, offset):
+        B, C, H, W = x.shape
+        P = B * H * W
+        y_hat = torch.empty_like(x)
+        lik = torch.empty_like(x)
+        sum_ln = torch.zeros(1, dtype=F32, device=x.device)
+        L.eb_forward(ptr(x), ptr(packed), ptr(medians), ptr(noise), P, C, mode, lik_bound,
+                     rng.seed if rng is not None else 0, offset, ptr(rng.state) if rng is not None else None,
+                     ptr(y_hat), ptr(lik), ptr(sum_ln), stream())
+        ctx.save_for_backward(y_hat, packed)
+        ctx.cfg = (mode, lik_bound, P, C)
+        setattr(lik, _SUM_LN_ATTR, sum_ln)
+        return y_hat, lik
+
+    @staticmethod
+    def backward(ctx, g_yhat, g_lik):
+        y_hat, packed = ctx.saved_tensors
+        mode, lik_bound, P, C = ctx.cfg
+        g_x = torch.empty_like(y_hat)
+        g_p = torch.zeros_like(packed)
+        if g_lik is None:
+            g_lik = torch.zeros_like(y_hat)
+        g_lik = g_lik.to(dtype=F32).contiguous(memory_format=CL)
+        if g_yhat is not None:
+            g_yhat = g_yhat.to(dtype=F32).contiguous(memory_format=CL)
+        L.eb_backward(ptr(y_hat), ptr(packed), ptr(g_lik), ptr(g_yhat), P, C, mode, lik_bound, 0.0, ptr(g_x), ptr(g_p),
+                      stream())
+        return g_x, g_p, None, None, None, None, None, None
+
+
+def eb_apply(x, packed, medians, noise, mode, lik_bound, rng=None, offset=0):
+    x = nhwc(x, F32)
+    if noise is not None:
+        noise = nhwc(noise, F32)
+    return _EBFn.apply(x, packed.contiguous(), medians, noise, _mode_id(mode), float(lik_bound), rng, offset)
+
+
+class _EBAuxFn(torch.autograd.Function):
+    """EntropyBottleneck.loss, entropy_models.py:431-434 (gradient to `quantiles` only)."""
+
+    @staticmethod
+    def forward(ctx, quantiles, packed, target):
+        C = quantiles.shape[0]
+        q = quantiles.detach().reshape(C, 3).contiguous()
+        loss = torch.zeros(1, dtype=F32, device=q.device)
+        gq = torch.empty_like(q)
+        L.eb_aux_loss(ptr(packed), ptr(q), ptr(target), C, ptr(loss), ptr(gq), stream())
+        ctx.save_for_backward(gq)
+        ctx.qshape = quantiles.shape
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        (gq,) = ctx.saved_tensors
+        return (gq * g).reshape(ctx.qshape), None, None
+
+
+def eb_aux_apply(quantiles, packed, target):
+    return _EBAuxFn.apply(quantiles, packed.detach().contiguous(), target)
+
+
+# ====================================================================== RD loss
+_CONST_CACHE = {}
+
+
+def _const_tensor(values, device):
+    """Small fp32 constant vectors, uploaded once per (values, device): the training step must not
+    issue host->device copies of its own (it is captured into a CUDA graph)."""
+    key = (values, str(device))
+    t = _CONST_CACHE.get(key)
+    if t is None:
+        t = torch.tensor(values, dtype=F32, device=device)
+        _CONST_CACHE[key] = t
+    return t
+
+
+class _RDLossFn(torch.autograd.Function):
+    """RateDistortionLoss, compressai/losses/rate_distortion.py:47-59, for a pyramid of targets:
+    bpp = sum_k sum ln L_k / (-ln2 * num_pixels); D = sum_l w_l * mean((xhat_l - x_l)^2);
+    loss = lmbda_scale * D + bpp.  One pass per level produces both the squared error and the
+    gradient d loss / d xhat_l (the loss is assumed to be the root of backward)."""
+
+    @staticmethod
+    def forward(ctx, lmbda_scale, num_pixels, weights, n_lev, n_lik, *tensors):
+        xh = tensors[:n_lev]
+        xt = tensors[n_lev:2 * n_lev]
+        liks = tensors[2 * n_lev:2 * n_lev + n_lik]
+        dev, st = xh[0].device, stream()
+        accum = torch.zeros(n_lik + n_lev, dtype=F32, device=dev)
+        rate_c = 1.0 / (-math.log(2) * num_pixels)
+        coef = [rate_c] * n_lik
+        for i, lk in enumerate(liks):
+            s = getattr(lk, _SUM_LN_ATTR, None)
+            accum[i:i + 1] = s if s is not None else torch.log(lk.float()).sum()
+        grads = []
+        for i in range(n_lev):
+            n = xh[i].numel()
+            g = torch.empty_like(xh[i]) if ctx.needs_input_grad[5 + i] else None
+            L.mse_forward_backward(ptr(xh[i]), ptr(xt[i]), n, lmbda_scale * weights[i] * 2.0 / n, ptr(accum[n_lik + i:]),
+                                   ptr(g), st)
+            coef.append(weights[i] / n)
+            grads.append(g)
+        coef_t = _const_tensor(tuple(coef), dev)
+        out = torch.empty(3, dtype=F32, device=dev)
+        L.loss_finalize(ptr(accum), ptr(coef_t), n_lik, n_lev, lmbda_scale, ptr(out), st)
+        ctx.grads, ctx.rate_c, ctx.n_lev = grads, rate_c, n_lev
+        ctx.save_for_backward(*liks)
+        return out[2], out[0], out[1]
+
+    @staticmethod
+    def backward(ctx, g_loss, g_bpp, g_mse):
+        liks = ctx.saved_tensors
+        g_liks = [ctx.rate_c / lk for lk in liks]
+        return (None, None, None, None, None, *ctx.grads, *([None] * ctx.n_lev), *g_liks)
+
+
+def rd_loss_apply(x_hats, targets, liks, lmbda_scale, num_pixels, weights):
+    xh = [nhwc(t, BF16) for t in x_hats]
+    xt = [nhwc(t, BF16) for t in targets]
+    for a, b in zip(xh, xt):
+        if a.shape != b.shape:
+            raise ValueError(f"x_hat {tuple(a.shape)} vs target {tuple(b.shape)}")
+    return _RDLossFn.apply(float(lmbda_scale), float(num_pixels), [float(w) for w in weights], len(xh), len(liks),
+                           *xh, *xt, *liks)
