@@ -1,0 +1,65 @@
+"""Optimiser side of the train step: the "net" / "aux" parameter split of
+compressai/optimizers/net_aux.py:39-74 and clip_grad_norm_ + Adam (examples/train.py:100-107) as
+one fused launch over the flat arena (lmsfc_sumsq + lmsfc_adam_step).
+"""
+import torch
+
+from . import _lib as L
+from ._lib import ptr, stream
+
+
+class FusedAdam:
+    """torch.optim.Adam semantics (betas (0.9, 0.999), eps 1e-8, no weight decay / amsgrad) over a
+    flat fp32 arena.  `clip_max_norm` > 0 folds torch.nn.utils.clip_grad_norm_ into the update:
+    the squared-gradient sum is one reduction launch, the clip coefficient is computed on the
+    device (no host sync, so the step stays capturable)."""
+
+    def __init__(self, params, grads, lr, betas=(0.9, 0.999), eps=1e-8, bf16_shadow=None, clip_max_norm=0.0):
+        self.params, self.grads = params, grads
+        self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
+        self.clip_max_norm = float(clip_max_norm)
+        self.m = torch.zeros_like(params)
+        self.v = torch.zeros_like(params)
+        self.bf16_shadow = bf16_shadow
+        dev = params.device
+        self.step_count = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.scratch = torch.zeros(4, dtype=torch.float32, device=dev)   # clip, bc1, bc2, grad norm
+
+    def zero_grad(self, set_to_none=False):
+        self.grads.zero_()
+
+    def step(self):
+        st = stream()
+        n = self.params.numel()
+        clip = self.clip_max_norm > 0
+        if clip:
+            self.sumsq.zero_()
+            L.sumsq(ptr(self.grads), n, ptr(self.sumsq), st)
+        L.adam_step(ptr(self.params), ptr(self.m), ptr(self.v), ptr(self.grads), ptr(self.bf16_shadow), n, self.lr,
+                    self.betas[0], self.betas[1], self.eps, self.clip_max_norm, ptr(self.sumsq) if clip else None,
+                    ptr(self.step_count), ptr(self.scratch), st)
+
+    @property
+    def grad_norm(self):
+        return self.scratch[3]
+
+    def state_dict(self):
+        return {"m": self.m, "v": self.v, "step": self.step_count, "lr": self.lr}
+
+    def load_state_dict(self, sd):
+        self.m.copy_(sd["m"]); self.v.copy_(sd["v"]); self.step_count.copy_(sd["step"]); self.lr = float(sd["lr"])
+
+
+def net_aux_optimizer(model, conf=None, clip_max_norm=1.0):
+    """optimizers/net_aux.py:39-74: {"net": Adam(lr), "aux": Adam(aux lr)} over the model's arenas.
+    conf: {"net": {"type": "Adam", "lr": 1e-4}, "aux": {"type": "Adam", "lr": 1e-3}}."""
+    conf = conf or {"net": {"type": "Adam", "lr": 1e-4}, "aux": {"type": "Adam", "lr": 1e-3}}
+    for k in ("net", "aux"):
+        if conf[k].get("type", "Adam") != "Adam":
+            raise ValueError(f"only Adam is implemented on the fused path, got {conf[k]['type']}")
+    arena = model.arena or model.build_arena()
+    net = FusedAdam(arena.net_params, arena.net_grads, conf["net"]["lr"], bf16_shadow=arena.net_bf16,
+                    clip_max_norm=clip_max_norm)
+    aux = FusedAdam(arena.aux_params, arena.aux_grads, conf["aux"]["lr"])
+    return {"net": net, "aux": aux}

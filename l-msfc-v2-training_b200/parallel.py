@@ -1,0 +1,107 @@
+"""Data-parallel gradient exchange: one process per GPU, NCCL over NVLink 5 / NVSwitch.
+
+Replaces nn.DataParallel of compressai/examples/train.py:64-71,275-276.  The gradient arena is
+cut into contiguous buckets filled in reverse registration order (decoder first, the order
+backward produces them); as soon as the last weight-gradient kernel of a bucket has been
+*launched*, its all-reduce is enqueued on a side stream behind an event, so the exchange overlaps
+the remaining dgrad / wgrad work.  `quantiles` (aux loss) are data independent and identical on
+every rank: they are never reduced.
+"""
+import torch
+import torch.distributed as dist
+
+
+class BucketedGradReducer:
+    def __init__(self, model, bucket_mb=16.0, process_group=None):
+        if model.arena is None:
+            model.build_arena()
+        self.model, self.arena = model, model.arena
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.grads = self.arena.net_grads
+        self.comm_stream = torch.cuda.Stream(device=self.grads.device) if self.grads.is_cuda else None
+        # ---- buckets: walk parameters from the END of the arena, close a bucket every bucket_mb
+        cap = int(bucket_mb * (1 << 20) / 4)
+        names = self.arena.names("net")
+        self.buckets = []          # dicts {lo, hi, names(set), pending(int)}
+        hi = self.grads.numel()
+        cur_names, cur_lo = [], hi
+        for n in reversed(names):
+            cur_lo = self.arena.offsets[n]
+            cur_names.append(n)
+            if hi - cur_lo >= cap:
+                self.buckets.append({"lo": cur_lo, "hi": hi, "names": set(cur_names)})
+                hi, cur_names = cur_lo, []
+        if cur_names:
+            self.buckets.append({"lo": cur_lo, "hi": hi, "names": set(cur_names)})
+        self.bucket_of = {}
+        for i, b in enumerate(self.buckets):
+            for n in b["names"]:
+                self.bucket_of[n] = i
+        self.name_of = {id(p): n for n, p in self.arena.net}
+        self._pending = None
+        self._works = []
+        self.launched = []
+        # ---- hooks
+        for m in model.modules():
+            st = getattr(m, "_state", None)
+            if st is not None and hasattr(st, "grad_ready"):
+                st.grad_ready = self._on_ready
+        self.eb_names = [n for n in names if ".entropy_bottleneck." in n or n.startswith("entropy_bottleneck.")]
+
+    # called at the start of every step (before backward)
+    def begin(self):
+        self._pending = [set(b["names"]) for b in self.buckets]
+        self._works, self.launched = [], []
+
+    def _on_ready(self, params):
+        if self._pending is None:
+            return
+        for p in params:
+            n = self.name_of.get(id(p))
+            if n is None:
+                continue
+            i = self.bucket_of[n]
+            pend = self._pending[i]
+            pend.discard(n)
+            if not pend and i not in self.launched:
+                self._launch(i)
+
+    def mark_ready(self, names):
+        """For parameters whose gradients arrive through plain autograd (EntropyBottleneck)."""
+        for n in names:
+            i = self.bucket_of.get(n)
+            if i is None or self._pending is None:
+                continue
+            self._pending[i].discard(n)
+            if not self._pending[i] and i not in self.launched:
+                self._launch(i)
+
+    def _launch(self, i):
+        self.launched.append(i)
+        if self.world == 1:
+            return
+        b = self.buckets[i]
+        view = self.grads[b["lo"]:b["hi"]]
+        if self.comm_stream is not None:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            with torch.cuda.stream(self.comm_stream):
+                self.comm_stream.wait_event(ev)
+                dist.all_reduce(view, op=dist.ReduceOp.AVG, group=self.pg)
+        else:   # gloo (CPU tests of the host logic): no AVG op, no streams
+            w = dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+            self._works.append((w, view))
+
+    def finish(self):
+        """Flush buckets that never filled (unused parameters) and join the comm stream."""
+        if self._pending is not None:
+            for i in range(len(self.buckets)):
+                if i not in self.launched:
+                    self._launch(i)
+        for w, view in self._works:
+            w.wait()
+            view.div_(self.world)
+        if self.comm_stream is not None and self.world > 1:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self._pending = None
