@@ -22,6 +22,8 @@ extern "C" {
 
 const char* lmsfc_last_error(void);
 int lmsfc_version(void);
+/* number of CUDA kernels this library has launched (or captured into a graph) in this process */
+uint64_t lmsfc_launch_count(void);
 
 /* ------------------------------------------------------------------ conv / deconv (tcgen05 implicit GEMM)
  * Replaces models/utils.py:128-146: conv = nn.Conv2d(k, stride, padding=k/2),

@@ -53,12 +53,18 @@ _SIGS = {
     "lmsfc_pmf_to_quantized_cdf": [P, c_int, c_int, P],
     "lmsfc_pmf_rows_to_cdf": [P, c_int, P, P, c_int, c_int, P, c_int, P, P],
 }
-EXPORTS = ["lmsfc_last_error", "lmsfc_version"] + list(_SIGS)
+EXPORTS = ["lmsfc_last_error", "lmsfc_version", "lmsfc_launch_count"] + list(_SIGS)
 
 lib.lmsfc_last_error.restype = c_char_p
 lib.lmsfc_last_error.argtypes = []
 lib.lmsfc_version.restype = c_int
 lib.lmsfc_version.argtypes = []
+lib.lmsfc_launch_count.restype = c_uint64
+lib.lmsfc_launch_count.argtypes = []
+
+
+def launch_count():
+    return int(lib.lmsfc_launch_count())
 
 
 def _wrap(name, argtypes):

@@ -16,6 +16,7 @@ typedef __nv_bfloat16 bf16;
 
 extern "C" const char* lmsfc_last_error(void) { return lmsfc::get_error(); }
 extern "C" int lmsfc_version(void) { return 100; }
+extern "C" uint64_t lmsfc_launch_count(void) { return lmsfc::g_launch_count; }
 
 // ---------------------------------------------------------------- tap tables
 static void taps_regular(int k, int pad, int* ntaps, int8_t* dy, int8_t* dx, int16_t* widx) {

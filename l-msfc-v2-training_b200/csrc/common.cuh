@@ -35,7 +35,13 @@ void set_error(const char* fmt, ...);
     }                                                                          \
   } while (0)
 
-#define LMSFC_LAUNCH_CHECK() LMSFC_CUDA(cudaGetLastError())
+// every kernel launch site calls this exactly once: it also feeds lmsfc_launch_count()
+extern unsigned long long g_launch_count;
+#define LMSFC_LAUNCH_CHECK()              \
+  do {                                    \
+    ++::lmsfc::g_launch_count;            \
+    LMSFC_CUDA(cudaGetLastError());       \
+  } while (0)
 
 static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
