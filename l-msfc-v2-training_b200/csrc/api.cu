@@ -60,30 +60,36 @@ static int check_desc(const lmsfc_conv_desc* d) {
 static int run_regular(const bf16* s0, const bf16* s1, int c0, int c1, int B, int Hs, int Ws, int Hg, int Wg, int k, int s,
                        const bf16* w, int w_rows, int N, IgemmParams& p, cudaStream_t st) {
   p.src0 = s0; p.src1 = s1; p.c0 = c0; p.c1 = c1;
-  p.B = B; p.Hin = Hs; p.Win = Ws; p.Hg = Hg; p.Wg = Wg; p.M = B * Hg * Wg; p.sin = s;
-  taps_regular(k, k / 2, &p.ntaps, p.dy, p.dx, p.widx);
-  p.Hout = Hg; p.Wout = Wg; p.sout = 1; p.oy = 0; p.ox = 0; p.N = N;
+  p.B = B; p.Hin = Hs; p.Win = Ws; p.sin = s;
+  p.nphase = 1;
+  p.ph[0].Hg = Hg; p.ph[0].Wg = Wg; p.ph[0].M = B * Hg * Wg; p.ph[0].oy = 0; p.ph[0].ox = 0; p.ph[0].tap_begin = 0;
+  taps_regular(k, k / 2, &p.ph[0].ntaps, p.dy, p.dx, p.widx);
+  p.Hout = Hg; p.Wout = Wg; p.sout = 1; p.N = N;
   p.w = w; p.w_rows = w_rows; p.w_cols = k * k * (c0 + c1);
   return launch_igemm(p, st);
 }
-// "transposed" structure: out[s*h+py][s*w+px] = sum_{taps of phase} src[h+dy][w+dx] . W[tap]
+// "transposed" structure: out[s*h+py][s*w+px] = sum_{taps of phase} src[h+dy][w+dx] . W[tap];
+// the s*s sub-pixel phases partition the k*k taps and run as blockIdx.z slices of ONE launch
 static int run_transposed(const bf16* s0, int c0, int B, int Hs, int Ws, int Ho, int Wo, int k, int s, const bf16* w,
                           int w_rows, int N, IgemmParams& p, cudaStream_t st) {
   p.src0 = s0; p.src1 = nullptr; p.c0 = c0; p.c1 = 0;
   p.B = B; p.Hin = Hs; p.Win = Ws; p.sin = 1;
   p.Hout = Ho; p.Wout = Wo; p.sout = s; p.N = N;
   p.w = w; p.w_rows = w_rows; p.w_cols = k * k * c0;
+  int np = 0, tb = 0;
   for (int py = 0; py < s; ++py)
     for (int px = 0; px < s; ++px) {
-      p.Hg = (Ho - py + s - 1) / s; p.Wg = (Wo - px + s - 1) / s;
-      if (p.Hg <= 0 || p.Wg <= 0) continue;
-      p.M = B * p.Hg * p.Wg; p.oy = py; p.ox = px;
-      taps_phase(k, s, k / 2, py, px, &p.ntaps, p.dy, p.dx, p.widx);
-      if (p.ntaps == 0) continue;
-      int rc = launch_igemm(p, st);
-      if (rc) return rc;
+      const int Hg = (Ho - py + s - 1) / s, Wg = (Wo - px + s - 1) / s;
+      if (Hg <= 0 || Wg <= 0) continue;
+      int nt = 0;
+      taps_phase(k, s, k / 2, py, px, &nt, p.dy + tb, p.dx + tb, p.widx + tb);
+      if (nt == 0) continue;
+      IgemmPhase& ph = p.ph[np++];
+      ph.Hg = Hg; ph.Wg = Wg; ph.M = B * Hg * Wg; ph.oy = py; ph.ox = px; ph.tap_begin = tb; ph.ntaps = nt;
+      tb += nt;
     }
-  return LMSFC_OK;
+  p.nphase = np;
+  return launch_igemm(p, st);
 }
 
 extern "C" int lmsfc_conv_forward(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* w,
@@ -153,8 +159,10 @@ extern "C" int lmsfc_conv_wgrad(const lmsfc_conv_desc* d, const void* src0, cons
 // ---------------------------------------------------------------- GDN
 static void gdn_gemm_params(IgemmParams& p, const bf16* a, const bf16* w, int64_t P, int C) {
   memset(&p, 0, sizeof(p));
-  p.src0 = a; p.c0 = C; p.B = 1; p.Hin = 1; p.Win = (int)P; p.Hg = 1; p.Wg = (int)P; p.M = (int)P; p.sin = 1;
-  p.ntaps = 1; p.dy[0] = 0; p.dx[0] = 0; p.widx[0] = 0;
+  p.src0 = a; p.c0 = C; p.B = 1; p.Hin = 1; p.Win = (int)P; p.sin = 1;
+  p.nphase = 1;
+  p.ph[0].Hg = 1; p.ph[0].Wg = (int)P; p.ph[0].M = (int)P; p.ph[0].ntaps = 1;
+  p.dy[0] = 0; p.dx[0] = 0; p.widx[0] = 0;
   p.Hout = 1; p.Wout = (int)P; p.sout = 1; p.N = C;
   p.w = w; p.w_rows = C; p.w_cols = C;
 }

@@ -96,6 +96,7 @@ __global__ void __launch_bounds__(256) gdn_t_kernel(const uint4* __restrict__ gy
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
   if (c8 < C8) {
+#pragma unroll 4
     for (int64_t p = (int64_t)blockIdx.y * 8 + threadIdx.y; p < P; p += (int64_t)gridDim.y * 8) {
       const int64_t i = p * C8 + c8;
       const uint4 g = __ldg(gy + i), xv = __ldg(x + i), r = __ldg(rn + i);
@@ -132,7 +133,7 @@ int gdn_t(const __nv_bfloat16* gy, const __nv_bfloat16* x, const __nv_bfloat16* 
   LMSFC_CHECK_ARG(C % 8 == 0, "gdn_t: C must be a multiple of 8");
   if (P == 0) return LMSFC_OK;
   const int C8 = C / 8, bx = (C8 + 31) / 32;
-  int64_t by = (148 * 4 + bx - 1) / bx;
+  int64_t by = (148 * 2 + bx - 1) / bx;   // ~2 blocks per SM: few same-address atomics, 4 loads in flight per thread
   const int64_t maxy = (P + 7) / 8;
   if (by > maxy) by = maxy;
   gdn_t_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)gy, (const uint4*)x, (const uint4*)rn,
@@ -148,6 +149,7 @@ __global__ void __launch_bounds__(256) colsum_kernel(const uint4* __restrict__ g
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
   if (c8 < C8) {
+#pragma unroll 4
     for (int64_t p = (int64_t)blockIdx.y * 8 + threadIdx.y; p < P; p += (int64_t)gridDim.y * 8) {
       const uint4 a = __ldg(g + p * C8 + c8);
       const uint32_t av[4] = {a.x, a.y, a.z, a.w};
@@ -173,7 +175,7 @@ int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream
   LMSFC_CHECK_ARG(C % 8 == 0, "colsum: C must be a multiple of 8");
   if (P == 0) return LMSFC_OK;
   const int C8 = C / 8, bx = (C8 + 31) / 32;
-  int64_t by = (148 * 4 + bx - 1) / bx;
+  int64_t by = (148 * 2 + bx - 1) / bx;   // ~2 blocks per SM: few same-address atomics, 4 loads in flight per thread
   const int64_t maxy = (P + 7) / 8;
   if (by > maxy) by = maxy;
   colsum_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)g, P, C8, out);

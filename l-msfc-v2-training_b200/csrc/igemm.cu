@@ -5,13 +5,16 @@
 //   compressai/layers/gdn.py:77-92       the 1x1 channel contraction of GDN / IGDN
 // and their autograd backward passes.
 //
-// One CTA = one 128 x BLOCK_N output tile.  Warp roles (192 threads):
+// One CTA = one 128 x BLOCK_N output tile of one sub-pixel phase and one K slice.
+// Warp roles (192 threads):
 //   warps 0-3  gather the activation operand with cp.async (zero-filled padding, strided /
 //              sub-pixel-phase taps, two-source channel concat) into SWIZZLE_128B shared
 //              memory, then run the epilogue out of TMEM (tcgen05.ld)
 //   warp 4     TMA producer for the weight operand (cp.async.bulk.tensor, SWIZZLE_128B)
 //   warp 5     TMEM allocator + single-thread tcgen05.mma issuer
 // Pipelines: smem full/empty mbarrier ring (STAGES deep) and one TMEM-full barrier.
+// Small grids (latent-resolution layers) split K over blockIdx.z: partial tiles are summed with
+// red.global.add into a self-cleaning fp32 workspace and the last CTA to arrive runs the epilogue.
 #include "igemm.cuh"
 
 namespace lmsfc {
@@ -21,7 +24,6 @@ constexpr int BLOCK_K = 64;            // 64 bf16 = one 128-byte swizzle row
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
 constexpr int NUM_GATHER_THREADS = 128;
 constexpr int NUM_THREADS = 192;
-constexpr int GATHER_LAG = 2;          // cp.async groups kept in flight per thread
 
 template <int BLOCK_N>
 struct FwdCfg {
@@ -33,6 +35,76 @@ struct FwdCfg {
 
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+__device__ __forceinline__ void load_bf16x32(const __nv_bfloat16* p, uint32_t (&r)[16]) {
+  const uint4* s = reinterpret_cast<const uint4*>(p);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint4 q = __ldg(s + j);
+    r[4 * j] = q.x; r[4 * j + 1] = q.y; r[4 * j + 2] = q.z; r[4 * j + 3] = q.w;
+  }
+}
+__device__ __forceinline__ void store_bf16x32(__nv_bfloat16* p, const float (&v)[32]) {
+  uint4* d = reinterpret_cast<uint4*>(p);
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    d[j] = make_uint4(pack_bf16(v[8 * j], v[8 * j + 1]), pack_bf16(v[8 * j + 2], v[8 * j + 3]),
+                      pack_bf16(v[8 * j + 4], v[8 * j + 5]), pack_bf16(v[8 * j + 6], v[8 * j + 7]));
+}
+__device__ __forceinline__ float pick(const uint32_t (&r)[16], int j) {
+  return (j & 1) ? bf16_hi(r[j >> 1]) : bf16_lo(r[j >> 1]);
+}
+
+// epilogue maths for 32 consecutive output channels [nb, nb+32) of one output pixel at offset o
+__device__ __forceinline__ void epilogue_chunk(const IgemmParams& p, float (&v)[32], size_t o, int nb) {
+  if (p.epi == EPI_BIAS) {
+    if (p.bias) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + nb + j);
+    }
+    if (p.relu) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+    }
+    if (p.out_f32) {
+      float4* d = reinterpret_cast<float4*>(p.out_f32 + o);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    if (p.out_abs) {
+      float a[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) a[j] = fabsf(v[j]);
+      store_bf16x32(p.out_abs + o, a);
+    }
+  } else {
+    uint32_t xr[16];
+    load_bf16x32(p.aux_x + o, xr);
+    if (p.epi == EPI_GDN) {
+      float rn[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float nrm = v[j] + __ldg(p.bias + nb + j);
+        rn[j] = rsqrtf(nrm);
+        const float x = pick(xr, j);
+        v[j] = p.inverse ? x * (nrm * rn[j]) : x * rn[j];
+      }
+      if (p.out_rn) store_bf16x32(p.out_rn + o, rn);
+    } else {  // EPI_GDN_BWD
+      uint32_t gr[16], rr[16];
+      load_bf16x32(p.aux_gy + o, gr);
+      load_bf16x32(p.aux_rn + o, rr);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float rn = pick(rr, j);
+        const float f = p.inverse ? 1.f / rn : rn;
+        v[j] = pick(gr, j) * f + 2.f * pick(xr, j) * v[j];
+      }
+    }
+  }
+  if (p.out_bf16) store_bf16x32(p.out_bf16 + o, v);
+}
+
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 template <int BLOCK_N>
 __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_constant__ IgemmParams p) {
@@ -44,13 +116,20 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+  uint32_t* last_flag = tmem_slot + 1;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int phase_id = blockIdx.z / p.ksplit, ks = blockIdx.z % p.ksplit;
+  const IgemmPhase ph = p.ph[phase_id];
   const int m0 = blockIdx.x * BLOCK_M;
+  if (m0 >= ph.M) return;                       // phases differ in size: whole CTA exits together
   const int n0 = blockIdx.y * BLOCK_N;
   const int ctot = p.c0 + p.c1;
   const int kc_per_tap = ctot / BLOCK_K;
-  const int nkb = p.ntaps * kc_per_tap;
+  const int nkb_total = ph.ntaps * kc_per_tap;
+  const int kb_per = (nkb_total + p.ksplit - 1) / p.ksplit;
+  const int kb_begin = ks * kb_per;
+  const int nkb = min(kb_per, nkb_total - kb_begin);   // host guarantees >= 1
   const uint32_t smem_base = smem_u32(smem);
 
   if (warp == 4 && lane == 0) {
@@ -75,9 +154,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int m = m0 + r0 + 16 * i;
-      if (m < p.M) {
-        const int wg = m % p.Wg, t = m / p.Wg;
-        const int hg = t % p.Hg, b = t / p.Hg;
+      if (m < ph.M) {
+        const int wg = m % ph.Wg, t = m / ph.Wg;
+        const int hg = t % ph.Hg, b = t / ph.Hg;
         pixbase[i] = b * p.Hin * p.Win;
         hi0[i] = hg * p.sin;
         wi0[i] = wg * p.sin;
@@ -86,7 +165,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       }
     }
     const uint32_t dst_thread = smem_base + r0 * 128 + ((chunk ^ (r0 & 7)) << 4);
-    int stage = 0, phase = 0, tap = 0, kc = 0;
+    int stage = 0, phase = 0;
+    int tap = ph.tap_begin + kb_begin / kc_per_tap, kc = kb_begin % kc_per_tap;
     for (int kb = 0; kb < nkb; ++kb) {
       const int cbase = kc * BLOCK_K;
       const bool first = cbase < p.c0;
@@ -100,141 +180,94 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       for (int i = 0; i < 8; ++i) {
         const int hi = hi0[i] + dy, wi = wi0[i] + dx;
         const bool ok = (unsigned)hi < (unsigned)p.Hin && (unsigned)wi < (unsigned)p.Win;
-        const __nv_bfloat16* g =
-            ok ? src + ((size_t)(pixbase[i] + hi * p.Win + wi) * C + coff) : src;
+        const __nv_bfloat16* g = ok ? src + ((size_t)(pixbase[i] + hi * p.Win + wi) * C + coff) : src;
         cp_async16(dst + i * 2048, g, ok ? 16u : 0u);
       }
-      cp_async_commit();
-      if (kb >= GATHER_LAG) {
-        cp_async_wait<GATHER_LAG>();
-        fence_proxy_async_smem();
-        mbar_arrive(&full_bar[(kb - GATHER_LAG) % STAGES]);
-      }
+      cp_async_mbar_arrive_noinc(&full_bar[stage]);
       if (++kc == kc_per_tap) { kc = 0; ++tap; }
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
-    if (nkb >= 2) {
-      cp_async_wait<1>();
-      fence_proxy_async_smem();
-      mbar_arrive(&full_bar[(nkb - 2) % STAGES]);
-    }
-    cp_async_wait<0>();
-    fence_proxy_async_smem();
-    mbar_arrive(&full_bar[(nkb - 1) % STAGES]);
+    cp_async_wait_all();
 
     // ================= epilogue: TMEM -> registers -> global =================
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
+    if (nkb > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
     const int row = warp * 32 + lane;
     const int m = m0 + row;
-    bool ok = m < p.M;
+    bool ok = m < ph.M;
     size_t obase = 0;
     if (ok) {
-      const int wg = m % p.Wg, t = m / p.Wg;
-      const int hg = t % p.Hg, b = t / p.Hg;
-      const int ho = hg * p.sout + p.oy, wo = wg * p.sout + p.ox;
+      const int wg = m % ph.Wg, t = m / ph.Wg;
+      const int hg = t % ph.Hg, b = t / ph.Hg;
+      const int ho = hg * p.sout + ph.oy, wo = wg * p.sout + ph.ox;
       ok = ho < p.Hout && wo < p.Wout;
       obase = ((size_t)(b * p.Hout + ho) * p.Wout + wo) * p.N + n0;
     }
+    const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16);
+    if (p.ksplit == 1) {
 #pragma unroll 1
-    for (int cb = 0; cb < BLOCK_N; cb += 32) {
-      uint32_t r[32];
-      tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + cb, r);
-      tmem_ld_wait();
-      if (!ok) continue;
-      float v[32];
+      for (int cb = 0; cb < BLOCK_N; cb += 32) {
+        uint32_t r[32];
+        tmem_ld32(trow + cb, r);
+        tmem_ld_wait();
+        if (!ok) continue;
+        float v[32];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-      const size_t o = obase + cb;
-      if (p.epi == EPI_BIAS) {
-        if (p.bias) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + n0 + cb + j);
-        }
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-        }
-        if (p.out_f32) {
-          float4* d = reinterpret_cast<float4*>(p.out_f32 + o);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) d[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        }
-        if (p.out_abs) {
-          uint4* d = reinterpret_cast<uint4*>(p.out_abs + o);
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            d[j] = make_uint4(pack_bf16(fabsf(v[8 * j]), fabsf(v[8 * j + 1])),
-                              pack_bf16(fabsf(v[8 * j + 2]), fabsf(v[8 * j + 3])),
-                              pack_bf16(fabsf(v[8 * j + 4]), fabsf(v[8 * j + 5])),
-                              pack_bf16(fabsf(v[8 * j + 6]), fabsf(v[8 * j + 7])));
-        }
-      } else {
-        // GDN epilogues read x (and gy, rn) at the output coordinates
-        uint32_t xr[16];
-        {
-          const uint4* s = reinterpret_cast<const uint4*>(p.aux_x + o);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const uint4 q = __ldg(s + j);
-            xr[4 * j] = q.x; xr[4 * j + 1] = q.y; xr[4 * j + 2] = q.z; xr[4 * j + 3] = q.w;
-          }
-        }
-        if (p.epi == EPI_GDN) {
-          float rn[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float nrm = v[j] + __ldg(p.bias + n0 + cb + j);
-            rn[j] = rsqrtf(nrm);
-            const float x = (j & 1) ? bf16_hi(xr[j >> 1]) : bf16_lo(xr[j >> 1]);
-            v[j] = p.inverse ? x * (nrm * rn[j]) : x * rn[j];
-          }
-          if (p.out_rn) {
-            uint4* d = reinterpret_cast<uint4*>(p.out_rn + o);
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              d[j] = make_uint4(pack_bf16(rn[8 * j], rn[8 * j + 1]), pack_bf16(rn[8 * j + 2], rn[8 * j + 3]),
-                                pack_bf16(rn[8 * j + 4], rn[8 * j + 5]), pack_bf16(rn[8 * j + 6], rn[8 * j + 7]));
-          }
-        } else {  // EPI_GDN_BWD
-          uint32_t gr[16], rr[16];
-          const uint4* sg = reinterpret_cast<const uint4*>(p.aux_gy + o);
-          const uint4* sr = reinterpret_cast<const uint4*>(p.aux_rn + o);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const uint4 q = __ldg(sg + j);
-            gr[4 * j] = q.x; gr[4 * j + 1] = q.y; gr[4 * j + 2] = q.z; gr[4 * j + 3] = q.w;
-            const uint4 w = __ldg(sr + j);
-            rr[4 * j] = w.x; rr[4 * j + 1] = w.y; rr[4 * j + 2] = w.z; rr[4 * j + 3] = w.w;
-          }
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float x = (j & 1) ? bf16_hi(xr[j >> 1]) : bf16_lo(xr[j >> 1]);
-            const float gy = (j & 1) ? bf16_hi(gr[j >> 1]) : bf16_lo(gr[j >> 1]);
-            const float rn = (j & 1) ? bf16_hi(rr[j >> 1]) : bf16_lo(rr[j >> 1]);
-            const float f = p.inverse ? 1.f / rn : rn;
-            v[j] = gy * f + 2.f * x * v[j];
-          }
-        }
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        epilogue_chunk(p, v, obase + cb, n0 + cb);
       }
-      if (p.out_bf16) {
-        uint4* d = reinterpret_cast<uint4*>(p.out_bf16 + o);
+    } else {
+      // split K: add the partial tile into the workspace; the last slice to arrive finishes it
+      const int tile = (phase_id * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+      float* wrow = p.ws + ((size_t)tile * BLOCK_M + row) * BLOCK_N;
+#pragma unroll 1
+      for (int cb = 0; cb < BLOCK_N && nkb > 0; cb += 32) {
+        uint32_t r[32];
+        tmem_ld32(trow + cb, r);
+        tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          d[j] = make_uint4(pack_bf16(v[8 * j], v[8 * j + 1]), pack_bf16(v[8 * j + 2], v[8 * j + 3]),
-                            pack_bf16(v[8 * j + 4], v[8 * j + 5]), pack_bf16(v[8 * j + 6], v[8 * j + 7]));
+        for (int j = 0; j < 8; ++j)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(wrow + cb + 4 * j),
+                       "f"(__uint_as_float(r[4 * j])), "f"(__uint_as_float(r[4 * j + 1])),
+                       "f"(__uint_as_float(r[4 * j + 2])), "f"(__uint_as_float(r[4 * j + 3]))
+                       : "memory");
+      }
+      __threadfence();
+      epi_bar_sync();
+      if (tid == 0) {
+        const unsigned prev = atomicAdd(p.ws_count + tile, 1u);
+        *last_flag = (prev == (unsigned)p.ksplit - 1) ? 1u : 0u;
+        if (prev == (unsigned)p.ksplit - 1) p.ws_count[tile] = 0;    // self-cleaning
+      }
+      epi_bar_sync();
+      if (*last_flag) {
+        __threadfence();
+#pragma unroll 1
+        for (int cb = 0; cb < BLOCK_N; cb += 32) {
+          float v[32];
+          float4* w4 = reinterpret_cast<float4*>(wrow + cb);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 q = __ldcg(w4 + j);
+            v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
+            __stcg(w4 + j, make_float4(0.f, 0.f, 0.f, 0.f));
+          }
+          if (ok) epilogue_chunk(p, v, obase + cb, n0 + cb);
+        }
       }
     }
   } else if (warp == 4) {
     // ================= weight TMA producer =================
     if (lane == 0) {
-      int stage = 0, phase = 0, tap = 0, kc = 0;
+      int stage = 0, phase = 0;
+      int tap = ph.tap_begin + kb_begin / kc_per_tap, kc = kb_begin % kc_per_tap;
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         mbar_arrive_expect_tx(&full_bar[stage], Cfg::B_STAGE_BYTES);
         const int kcoord = (int)p.widx[tap] * ctot + kc * BLOCK_K;
-        tma_load_2d(&p.tmapB, &full_bar[stage], smem_base + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES,
-                    kcoord, n0);
+        tma_load_2d(&p.tmapB, &full_bar[stage], smem_base + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES, kcoord, n0);
         if (++kc == kc_per_tap) { kc = 0; ++tap; }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
@@ -258,7 +291,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
         umma_commit(&empty_bar[stage]);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      umma_commit(tmem_full_bar);
+      if (nkb > 0) umma_commit(tmem_full_bar);
     }
   }
   tc_fence_before();
@@ -269,8 +302,27 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   }
 }
 
+// ---------------------------------------------------------------- host side
+namespace {
+constexpr size_t kWsFloats = 8u << 20;     // 32 MB fp32 split-K workspace
+constexpr int kWsTiles = 4096;
+float* g_ws = nullptr;
+unsigned int* g_ws_count = nullptr;
+
+int ensure_workspace() {
+  if (g_ws) return LMSFC_OK;
+  // first use happens in an eager (un-captured) step; cudaMalloc is not capturable
+  LMSFC_CUDA(cudaMalloc(&g_ws, kWsFloats * sizeof(float)));
+  LMSFC_CUDA(cudaMalloc(&g_ws_count, kWsTiles * sizeof(unsigned int)));
+  LMSFC_CUDA(cudaMemset(g_ws, 0, kWsFloats * sizeof(float)));
+  LMSFC_CUDA(cudaMemset(g_ws_count, 0, kWsTiles * sizeof(unsigned int)));
+  LMSFC_CUDA(cudaDeviceSynchronize());
+  return LMSFC_OK;
+}
+}  // namespace
+
 template <int BLOCK_N>
-static int launch_fwd_t(const IgemmParams& p, cudaStream_t stream) {
+static int launch_fwd_t(const IgemmParams& p, dim3 grid, cudaStream_t stream) {
   using Cfg = FwdCfg<BLOCK_N>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -278,29 +330,50 @@ static int launch_fwd_t(const IgemmParams& p, cudaStream_t stream) {
                                     Cfg::SMEM_BYTES));
     attr_done = true;
   }
-  dim3 grid(ceil_div(p.M, BLOCK_M), p.N / BLOCK_N);
   igemm_fwd_kernel<BLOCK_N><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(p);
   LMSFC_LAUNCH_CHECK();
   return LMSFC_OK;
 }
 
-int igemm_block_n(int M, int N) {
-  // 256-wide tiles halve the gather traffic per flop; use them once the grid fills the 148 SMs.
-  if (N % 256 == 0 && (int64_t)ceil_div(M, BLOCK_M) * (N / 256) >= 120) return 256;
-  return 128;
-}
-
 int launch_igemm(IgemmParams& p, cudaStream_t stream) {
-  LMSFC_CHECK_ARG(p.M > 0 && p.N > 0 && p.N % 128 == 0, "igemm: N=%d must be a multiple of 128", p.N);
+  LMSFC_CHECK_ARG(p.N > 0 && p.N % 128 == 0, "igemm: N=%d must be a multiple of 128", p.N);
   LMSFC_CHECK_ARG(p.c0 % 64 == 0 && p.c1 % 64 == 0 && p.c0 > 0, "igemm: channels (%d,%d) must be multiples of 64",
                   p.c0, p.c1);
-  LMSFC_CHECK_ARG(p.ntaps >= 1 && p.ntaps <= kMaxTaps, "igemm: ntaps=%d", p.ntaps);
+  LMSFC_CHECK_ARG(p.nphase >= 1 && p.nphase <= kMaxPhases, "igemm: nphase=%d", p.nphase);
   LMSFC_CHECK_ARG(p.w_rows >= p.N && p.w_cols % 64 == 0, "igemm: weight matrix %dx%d", p.w_rows, p.w_cols);
-  const int bn = igemm_block_n(p.M, p.N);
+  int maxM = 0, min_taps = kMaxTaps;
+  int64_t tiles128 = 0;
+  for (int i = 0; i < p.nphase; ++i) {
+    LMSFC_CHECK_ARG(p.ph[i].M > 0 && p.ph[i].ntaps >= 1 && p.ph[i].tap_begin + p.ph[i].ntaps <= kMaxTaps,
+                    "igemm: phase %d M=%d ntaps=%d", i, p.ph[i].M, p.ph[i].ntaps);
+    maxM = max(maxM, p.ph[i].M);
+    min_taps = min(min_taps, p.ph[i].ntaps);
+    tiles128 += ceil_div(p.ph[i].M, BLOCK_M);
+  }
+  // 256-wide tiles halve the gather traffic per flop; use them once the grid fills the 148 SMs
+  const int bn = (p.N % 256 == 0 && tiles128 * (p.N / 256) >= 120) ? 256 : 128;
+  const int64_t tiles = tiles128 * (p.N / bn);
+  // split K when the tiles cannot fill the machine: >= 4 K blocks per slice
+  const int min_kb = min_taps * ((p.c0 + p.c1) / BLOCK_K);
+  int ksplit = 1;
+  if (tiles < 100) {
+    ksplit = (int)min((int64_t)ceil_div(148, tiles), (int64_t)max(1, min_kb / 4));
+    ksplit = max(1, min(ksplit, 32));
+  }
+  dim3 grid(ceil_div(maxM, BLOCK_M), p.N / bn, p.nphase * ksplit);
+  if (ksplit > 1) {
+    int rc = ensure_workspace();
+    if (rc) return rc;
+    const size_t need = (size_t)p.nphase * grid.x * grid.y * BLOCK_M * bn;
+    if (need > kWsFloats || (size_t)p.nphase * grid.x * grid.y > (size_t)kWsTiles) ksplit = 1, grid.z = p.nphase;
+  }
+  p.ksplit = ksplit;
+  p.ws = g_ws;
+  p.ws_count = g_ws_count;
   int rc = make_tmap_2d_bf16(&p.tmapB, p.w, (uint64_t)p.w_rows, (uint64_t)p.w_cols, (uint64_t)p.w_cols, bn, 64);
   if (rc) return rc;
-  if (bn == 256) return launch_fwd_t<256>(p, stream);
-  return launch_fwd_t<128>(p, stream);
+  if (bn == 256) return launch_fwd_t<256>(p, grid, stream);
+  return launch_fwd_t<128>(p, grid, stream);
 }
 
 }  // namespace lmsfc

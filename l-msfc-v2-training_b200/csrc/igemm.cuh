@@ -14,6 +14,14 @@ enum : int {
 };
 
 // Gathered-A x weight-B GEMM:  D[m][n] = sum_{tap,c} A[pixel(m)+tap][c] * W[n][widx(tap)*Ctot + c]
+// A launch covers up to 4 sub-pixel phases of a transposed conv (blockIdx.z / ksplit) and, for
+// small grids, `ksplit` slices of the K loop whose fp32 partials meet in a workspace.
+constexpr int kMaxPhases = 4;
+struct IgemmPhase {
+  int Hg, Wg, M;            // GEMM row grid of this phase: m = (b*Hg + hg)*Wg + wg
+  int oy, ox;               // output pixel = (hg*sout + oy, wg*sout + ox)
+  int tap_begin, ntaps;     // slice of the tap table
+};
 struct IgemmParams {
   CUtensorMap tmapB;        // filled by launch_igemm: box {64, BLOCK_N}, SWIZZLE_128B
   const __nv_bfloat16* w;   // weights, bf16 [w_rows][w_cols], K (= tap*Ctot + c) contiguous
@@ -22,14 +30,17 @@ struct IgemmParams {
   const __nv_bfloat16* src1;  // optional second source (channel concat), [B][Hin][Win][c1]
   int c0, c1;
   int B, Hin, Win;
-  int Hg, Wg, M;            // GEMM row grid: m = (b*Hg + hg)*Wg + wg
   int sin;                  // input pixel = (hg*sin + dy, wg*sin + dx)
-  int ntaps;
+  int nphase;
+  IgemmPhase ph[kMaxPhases];
   int8_t dy[kMaxTaps], dx[kMaxTaps];
   int16_t widx[kMaxTaps];   // weight tap index of each gathered tap
-  int Hout, Wout, sout, oy, ox;  // output pixel = (hg*sout + oy, wg*sout + ox)
+  int Hout, Wout, sout;
   int N;                    // output channels (row pitch of every output / aux tensor)
   int epi, relu, inverse;
+  int ksplit;               // filled by launch_igemm
+  float* ws;                // split-K workspace (zero between launches), filled by launch_igemm
+  unsigned int* ws_count;   // per-tile arrival counters (zero between launches)
   const float* bias;        // [N] or null
   __nv_bfloat16* out_bf16;  // nullable
   float* out_f32;           // nullable

@@ -21,7 +21,6 @@ constexpr int WG_STAGE_BYTES = WG_A_BYTES + WG_B_BYTES;
 constexpr int WG_STAGES = 4;
 constexpr int WG_SMEM_BYTES = WG_STAGES * WG_STAGE_BYTES + 1024 + 256;
 constexpr int WG_THREADS = 192;
-constexpr int WG_LAG = 2;
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
@@ -93,22 +92,10 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
         for (int seg = 0; seg < 4; ++seg)
           cp_async16(dst + seg * WG_SEG_BYTES + i * 2048, g + seg * 64, ok ? 16u : 0u);
       }
-      cp_async_commit();
-      if (kb >= WG_LAG) {
-        cp_async_wait<WG_LAG>();
-        fence_proxy_async_smem();
-        mbar_arrive(&full_bar[(kb - WG_LAG) % WG_STAGES]);
-      }
+      cp_async_mbar_arrive_noinc(&full_bar[stage]);
       if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
     }
-    if (nkb >= 2) {
-      cp_async_wait<1>();
-      fence_proxy_async_smem();
-      mbar_arrive(&full_bar[(nkb - 2) % WG_STAGES]);
-    }
-    cp_async_wait<0>();
-    fence_proxy_async_smem();
-    mbar_arrive(&full_bar[(nkb - 1) % WG_STAGES]);
+    cp_async_wait_all();
 
     // ============ epilogue: fp32 partial tile -> red.global.add ============
     mbar_wait(tmem_full_bar, 0);
