@@ -67,6 +67,60 @@ int loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist,
   return LMSFC_OK;
 }
 
+
+// Two-stage column reduction (same-address float atomics run at ~1 lane-op/cycle chip-wide, far
+// below HBM speed): every block parks its 256 partial sums in `scratch`, the last block to arrive
+// (device counter, self-resetting) adds the column totals to `out`.
+__device__ __forceinline__ void colsum_finish(const float (&acc)[8], int c8, int C8, float* out, float* scratch,
+                                              unsigned int* counter) {
+  __shared__ float red[8][32][9];
+  __shared__ unsigned int is_last;
+  const int C = C8 * 8;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = acc[j];
+  __syncthreads();
+  if (threadIdx.y == 0 && c8 < C8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float v = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v += red[k][threadIdx.x][j];
+      __stcg(scratch + (size_t)blockIdx.y * C + c8 * 8 + j, v);
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0 && threadIdx.y == 0) {
+    const unsigned int prev = atomicAdd(counter + blockIdx.x, 1u);
+    is_last = (prev == gridDim.y - 1) ? 1u : 0u;
+    if (is_last) counter[blockIdx.x] = 0;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    const int col = (blockIdx.x * 32 + threadIdx.x) * 8 + threadIdx.y;
+    if (col < C) {
+      float v = 0.f;
+      for (unsigned int b = 0; b < gridDim.y; ++b) v += __ldcg(scratch + (size_t)b * C + col);
+      out[col] += v;
+    }
+  }
+}
+
+namespace {
+float* g_red_scratch = nullptr;
+unsigned int* g_red_count = nullptr;
+constexpr int kRedBlocksY = 296, kRedMaxC = 2048;
+int ensure_reduce_scratch() {
+  if (g_red_scratch) return LMSFC_OK;
+  LMSFC_CUDA(cudaMalloc(&g_red_scratch, sizeof(float) * kRedBlocksY * kRedMaxC));
+  LMSFC_CUDA(cudaMalloc(&g_red_count, sizeof(unsigned int) * 64));
+  LMSFC_CUDA(cudaMemset(g_red_count, 0, sizeof(unsigned int) * 64));
+  LMSFC_CUDA(cudaDeviceSynchronize());
+  return LMSFC_OK;
+}
+}  // namespace
+
 // ---------------------------------------------------------------- GDN helper passes
 __global__ void __launch_bounds__(TPB) square_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int64_t n8) {
   for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n8; i += (int64_t)gridDim.x * TPB) {
@@ -90,7 +144,8 @@ int square_bf16(const __nv_bfloat16* x, __nv_bfloat16* x2, int64_t n, cudaStream
 // Block = 32 x 8 threads: threadIdx.x covers 8 channels (one uint4), threadIdx.y strides pixels.
 __global__ void __launch_bounds__(256) gdn_t_kernel(const uint4* __restrict__ gy, const uint4* __restrict__ x,
                                                     const uint4* __restrict__ rn, int inverse, int64_t P, int C8,
-                                                    uint4* __restrict__ t, float* g_beta) {
+                                                    uint4* __restrict__ t, float* g_beta, float* scratch,
+                                                    unsigned int* counter) {
   const int c8 = blockIdx.x * 32 + threadIdx.x;
   float acc[8];
 #pragma unroll
@@ -114,36 +169,28 @@ __global__ void __launch_bounds__(256) gdn_t_kernel(const uint4* __restrict__ gy
       t[i] = make_uint4(o[0], o[1], o[2], o[3]);
     }
   }
-  __shared__ float red[8][32][9];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = acc[j];
-  __syncthreads();
-  if (threadIdx.y == 0 && c8 < C8) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float v = 0.f;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) v += red[k][threadIdx.x][j];
-      atomicAdd(g_beta + c8 * 8 + j, v);
-    }
-  }
+  colsum_finish(acc, c8, C8, g_beta, scratch, counter);
 }
 int gdn_t(const __nv_bfloat16* gy, const __nv_bfloat16* x, const __nv_bfloat16* rn, int inverse, int64_t P, int C,
           __nv_bfloat16* t, float* g_beta, cudaStream_t s) {
   LMSFC_CHECK_ARG(C % 8 == 0, "gdn_t: C must be a multiple of 8");
+  LMSFC_CHECK_ARG(C <= kRedMaxC, "column reduction: C=%d too large", C);
+  if (int rc = ensure_reduce_scratch()) return rc;
   if (P == 0) return LMSFC_OK;
   const int C8 = C / 8, bx = (C8 + 31) / 32;
   int64_t by = (148 * 2 + bx - 1) / bx;   // ~2 blocks per SM: few same-address atomics, 4 loads in flight per thread
   const int64_t maxy = (P + 7) / 8;
   if (by > maxy) by = maxy;
   gdn_t_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)gy, (const uint4*)x, (const uint4*)rn,
-                                                                inverse, P, C8, (uint4*)t, g_beta);
+                                                                inverse, P, C8, (uint4*)t, g_beta, g_red_scratch,
+                                                                g_red_count);
   LMSFC_LAUNCH_CHECK();
   return LMSFC_OK;
 }
 
 // column sums of a bf16 [P][C] matrix (conv bias gradients)
-__global__ void __launch_bounds__(256) colsum_kernel(const uint4* __restrict__ g, int64_t P, int C8, float* out) {
+__global__ void __launch_bounds__(256) colsum_kernel(const uint4* __restrict__ g, int64_t P, int C8, float* out,
+                                                     float* scratch, unsigned int* counter) {
   const int c8 = blockIdx.x * 32 + threadIdx.x;
   float acc[8];
 #pragma unroll
@@ -157,28 +204,18 @@ __global__ void __launch_bounds__(256) colsum_kernel(const uint4* __restrict__ g
       for (int j = 0; j < 4; ++j) { acc[2 * j] += lo(av[j]); acc[2 * j + 1] += hi(av[j]); }
     }
   }
-  __shared__ float red[8][32][9];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = acc[j];
-  __syncthreads();
-  if (threadIdx.y == 0 && c8 < C8) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float v = 0.f;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) v += red[k][threadIdx.x][j];
-      atomicAdd(out + c8 * 8 + j, v);
-    }
-  }
+  colsum_finish(acc, c8, C8, out, scratch, counter);
 }
 int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream_t s) {
   LMSFC_CHECK_ARG(C % 8 == 0, "colsum: C must be a multiple of 8");
+  LMSFC_CHECK_ARG(C <= kRedMaxC, "column reduction: C=%d too large", C);
+  if (int rc = ensure_reduce_scratch()) return rc;
   if (P == 0) return LMSFC_OK;
   const int C8 = C / 8, bx = (C8 + 31) / 32;
   int64_t by = (148 * 2 + bx - 1) / bx;   // ~2 blocks per SM: few same-address atomics, 4 loads in flight per thread
   const int64_t maxy = (P + 7) / 8;
   if (by > maxy) by = maxy;
-  colsum_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)g, P, C8, out);
+  colsum_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)g, P, C8, out, g_red_scratch, g_red_count);
   LMSFC_LAUNCH_CHECK();
   return LMSFC_OK;
 }

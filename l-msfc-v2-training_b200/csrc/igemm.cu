@@ -341,31 +341,42 @@ int launch_igemm(IgemmParams& p, cudaStream_t stream) {
                   p.c0, p.c1);
   LMSFC_CHECK_ARG(p.nphase >= 1 && p.nphase <= kMaxPhases, "igemm: nphase=%d", p.nphase);
   LMSFC_CHECK_ARG(p.w_rows >= p.N && p.w_cols % 64 == 0, "igemm: weight matrix %dx%d", p.w_rows, p.w_cols);
-  int maxM = 0, min_taps = kMaxTaps;
+  int maxM = 0, min_taps = kMaxTaps, max_taps = 0;
   int64_t tiles128 = 0;
   for (int i = 0; i < p.nphase; ++i) {
     LMSFC_CHECK_ARG(p.ph[i].M > 0 && p.ph[i].ntaps >= 1 && p.ph[i].tap_begin + p.ph[i].ntaps <= kMaxTaps,
                     "igemm: phase %d M=%d ntaps=%d", i, p.ph[i].M, p.ph[i].ntaps);
     maxM = max(maxM, p.ph[i].M);
     min_taps = min(min_taps, p.ph[i].ntaps);
+    max_taps = max(max_taps, p.ph[i].ntaps);
     tiles128 += ceil_div(p.ph[i].M, BLOCK_M);
   }
-  // 256-wide tiles halve the gather traffic per flop; use them once the grid fills the 148 SMs
-  const int bn = (p.N % 256 == 0 && tiles128 * (p.N / 256) >= 120) ? 256 : 128;
-  const int64_t tiles = tiles128 * (p.N / bn);
-  // split K when the tiles cannot fill the machine: >= 4 K blocks per slice
-  const int min_kb = min_taps * ((p.c0 + p.c1) / BLOCK_K);
-  int ksplit = 1;
-  if (tiles < 100) {
-    ksplit = (int)min((int64_t)ceil_div(148, tiles), (int64_t)max(1, min_kb / 4));
-    ksplit = max(1, min(ksplit, 32));
+  // Tile width / split-K choice from a small cost model (us): waves * (K blocks * t_kb + fixed).
+  // 256-wide tiles halve the gather traffic per flop; splitting K fills the 148 SMs when the
+  // output has few tiles (latent-resolution layers); measured t_kb: 0.5 us (N=256), 0.3 us (N=128).
+  const int kc = (p.c0 + p.c1) / BLOCK_K;
+  const int grid_x = ceil_div(maxM, BLOCK_M);
+  int bn = 128, ksplit = 1;
+  double best = 1e30;
+  static const int ks_opts[] = {1, 2, 3, 4, 5, 6, 8, 10, 12, 16, 20, 25, 32};
+  for (int cand_bn = 128; cand_bn <= 256; cand_bn += 128) {
+    if (p.N % cand_bn != 0) continue;
+    const int64_t tiles = tiles128 * (p.N / cand_bn);
+    for (int ks : ks_opts) {
+      if (ks > 1) {
+        if (min_taps * kc / ks < 2) continue;
+        if ((size_t)p.nphase * grid_x * (p.N / cand_bn) * BLOCK_M * cand_bn > kWsFloats) continue;
+        if ((size_t)p.nphase * grid_x * (p.N / cand_bn) > (size_t)kWsTiles) continue;
+      }
+      const double waves = (double)ceil_div(tiles * ks, 148);
+      const double t = waves * (ceil_div(max_taps * kc, ks) * (cand_bn == 256 ? 0.5 : 0.3) + 5.0) + (ks > 1 ? 3.0 : 0.0);
+      if (t < best) { best = t; bn = cand_bn; ksplit = ks; }
+    }
   }
-  dim3 grid(ceil_div(maxM, BLOCK_M), p.N / bn, p.nphase * ksplit);
+  dim3 grid(grid_x, p.N / bn, p.nphase * ksplit);
   if (ksplit > 1) {
     int rc = ensure_workspace();
     if (rc) return rc;
-    const size_t need = (size_t)p.nphase * grid.x * grid.y * BLOCK_M * bn;
-    if (need > kWsFloats || (size_t)p.nphase * grid.x * grid.y > (size_t)kWsTiles) ksplit = 1, grid.z = p.nphase;
   }
   p.ksplit = ksplit;
   p.ws = g_ws;

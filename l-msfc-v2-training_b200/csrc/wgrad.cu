@@ -14,13 +14,20 @@ namespace lmsfc {
 
 namespace {
 constexpr int WG_BM = 128, WG_BN = 256, WG_BK = 64;
-constexpr int WG_A_BYTES = WG_BK * WG_BM * 2;   // 16 KB: 2 segments of [64 px][64 ch]
-constexpr int WG_B_BYTES = WG_BK * WG_BN * 2;   // 32 KB: 4 segments
+constexpr int WG_B_BYTES = WG_BK * WG_BN * 2;   // 32 KB: 4 segments of [64 px][64 ch]
 constexpr int WG_SEG_BYTES = WG_BK * 128;       // 8 KB
-constexpr int WG_STAGE_BYTES = WG_A_BYTES + WG_B_BYTES;
-constexpr int WG_STAGES = 4;
-constexpr int WG_SMEM_BYTES = WG_STAGES * WG_STAGE_BYTES + 1024 + 256;
 constexpr int WG_THREADS = 192;
+// MT = number of 128-channel dense tiles per CTA.  MT = 2 keeps two 128x256 fp32 accumulators in
+// the 512 TMEM columns and feeds both from ONE gathered operand tile, halving the cp.async
+// traffic per flop (the gather, not the tensor pipe, bounds MT = 1).
+template <int MT>
+struct WgCfg {
+  static constexpr int A_BYTES = MT * WG_BK * WG_BM * 2;          // 16 KB per dense tile
+  static constexpr int STAGE_BYTES = A_BYTES + WG_B_BYTES;
+  static constexpr int STAGES = (MT == 2) ? 3 : 4;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+  static constexpr int TMEM_COLS = MT * WG_BN;
+};
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
@@ -28,7 +35,12 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 }
 }  // namespace
 
+template <int MT>
 __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_constant__ WgradParams p) {
+  using Cfg = WgCfg<MT>;
+  constexpr int WG_STAGES = Cfg::STAGES;
+  constexpr int WG_STAGE_BYTES = Cfg::STAGE_BYTES;
+  constexpr int WG_A_BYTES = Cfg::A_BYTES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = (uint64_t*)(smem + WG_STAGES * WG_STAGE_BYTES);
@@ -40,7 +52,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
   const int ntile_per_tap = p.Cg / WG_BN;
   const int tap = blockIdx.x / ntile_per_tap;
   const int n0 = (blockIdx.x % ntile_per_tap) * WG_BN;   // gathered-channel offset
-  const int d0 = blockIdx.y * WG_BM;                      // dense-channel offset
+  const int d0 = blockIdx.y * WG_BM * MT;                 // dense-channel offset
   const int kb_begin = blockIdx.z * p.kb_per_split;
   const int kb_end = min(kb_begin + p.kb_per_split, p.kb_total);
   const int nkb = kb_end - kb_begin;
@@ -56,7 +68,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
     mbar_init(tmem_full_bar, 1);
     fence_barrier_init();
   }
-  if (warp == 5) tmem_alloc<WG_BN>(tmem_slot);
+  if (warp == 5) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -100,22 +112,25 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
     // ============ epilogue: fp32 partial tile -> red.global.add ============
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
-    const int d = d0 + warp * 32 + lane;
-    float* orow = p.out + ((size_t)d * p.T + p.widx[tap]) * p.Cg + n0;
 #pragma unroll 1
-    for (int cb = 0; cb < WG_BN; cb += 32) {
-      uint32_t r[32];
-      tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + cb, r);
-      tmem_ld_wait();
-      if (d < p.Cd) {
+    for (int mt = 0; mt < MT; ++mt) {
+      const int d = d0 + mt * WG_BM + warp * 32 + lane;
+      float* orow = p.out + ((size_t)d * p.T + p.widx[tap]) * p.Cg + n0;
+#pragma unroll 1
+      for (int cb = 0; cb < WG_BN; cb += 32) {
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + mt * WG_BN + cb, r);
+        tmem_ld_wait();
+        if (d < p.Cd) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          red_add_v4(orow + cb + 4 * j, __uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                     __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+          for (int j = 0; j < 8; ++j)
+            red_add_v4(orow + cb + 4 * j, __uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                       __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+        }
       }
     }
   } else if (warp == 4) {
-    // ============ dense operand by TMA: two [64 px][64 ch] boxes per K block ============
+    // ============ dense operand by TMA: 2*MT [64 px][64 ch] boxes per K block ============
     if (lane == 0) {
       int stage = 0, phase = 0;
       for (int kb = 0; kb < nkb; ++kb) {
@@ -123,8 +138,9 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
         mbar_arrive_expect_tx(&full_bar[stage], WG_A_BYTES);
         const int pix0 = (kb_begin + kb) * WG_BK;
         const uint32_t sa = smem_base + stage * WG_STAGE_BYTES;
-        tma_load_2d(&p.tmapA, &full_bar[stage], sa, d0, pix0);
-        tma_load_2d(&p.tmapA, &full_bar[stage], sa + WG_SEG_BYTES, d0 + 64, pix0);
+#pragma unroll
+        for (int seg = 0; seg < 2 * MT; ++seg)
+          tma_load_2d(&p.tmapA, &full_bar[stage], sa + seg * WG_SEG_BYTES, d0 + 64 * seg, pix0);
         if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -141,9 +157,12 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
 #pragma unroll
         for (int k = 0; k < WG_BK / 16; ++k) {
           // K step of 16 pixel rows = 2 KB; LBO = next 64-channel segment, SBO = next 8 rows
-          const uint64_t ad = make_sdesc_sw128(sa + k * 2048, WG_SEG_BYTES, 1024);
           const uint64_t bd = make_sdesc_sw128(sb + k * 2048, WG_SEG_BYTES, 1024);
-          umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0);
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt) {
+            const uint64_t ad = make_sdesc_sw128(sa + mt * 2 * WG_SEG_BYTES + k * 2048, WG_SEG_BYTES, 1024);
+            umma_bf16(tmem_base + mt * WG_BN, ad, bd, idesc, (kb | k) != 0);
+          }
         }
         umma_commit(&empty_bar[stage]);
         if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
@@ -155,7 +174,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
   __syncthreads();
   if (warp == 5) {
     tc_fence_after();
-    tmem_dealloc<WG_BN>(tmem_base);
+    tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
   }
 }
 
@@ -167,20 +186,23 @@ int launch_wgrad(WgradParams& p, cudaStream_t stream) {
   LMSFC_CHECK_ARG(p.ntaps >= 1 && p.ntaps <= kMaxTaps && p.M > 0, "wgrad: ntaps=%d M=%d", p.ntaps, p.M);
   static bool attr_done = false;
   if (!attr_done) {
-    LMSFC_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES));
+    LMSFC_CUDA(cudaFuncSetAttribute(wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, WgCfg<1>::SMEM_BYTES));
+    LMSFC_CUDA(cudaFuncSetAttribute(wgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, WgCfg<2>::SMEM_BYTES));
     attr_done = true;
   }
   int rc = make_tmap_2d_bf16(&p.tmapA, p.dense, (uint64_t)p.M, (uint64_t)p.Cd, (uint64_t)p.Cd, 64, 64);
   if (rc) return rc;
+  const int mt = (p.Cd % 256 == 0) ? 2 : 1;
   p.kb_total = ceil_div(p.M, WG_BK);
-  const int tiles = p.ntaps * (p.Cg / WG_BN) * (p.Cd / WG_BM);
-  // split K (pixels) until the grid covers ~2 waves of the 148 SMs, keeping >= 4 K blocks per CTA
-  int ksplit = ceil_div(296, tiles);
-  ksplit = max(1, min(ksplit, ceil_div(p.kb_total, 4)));
+  const int tiles = p.ntaps * (p.Cg / WG_BN) * (p.Cd / (WG_BM * mt));
+  // split K (pixels) so that the grid fills, but does not exceed, one wave of the 148 SMs
+  int ksplit = max(1, 148 / tiles);
+  ksplit = max(1, min(ksplit, ceil_div(p.kb_total, 2)));
   p.kb_per_split = ceil_div(p.kb_total, ksplit);
   ksplit = ceil_div(p.kb_total, p.kb_per_split);
-  dim3 grid(p.ntaps * (p.Cg / WG_BN), p.Cd / WG_BM, ksplit);
-  wgrad_kernel<<<grid, WG_THREADS, WG_SMEM_BYTES, stream>>>(p);
+  dim3 grid(p.ntaps * (p.Cg / WG_BN), p.Cd / (WG_BM * mt), ksplit);
+  if (mt == 2) wgrad_kernel<2><<<grid, WG_THREADS, WgCfg<2>::SMEM_BYTES, stream>>>(p);
+  else         wgrad_kernel<1><<<grid, WG_THREADS, WgCfg<1>::SMEM_BYTES, stream>>>(p);
   LMSFC_LAUNCH_CHECK();
   return LMSFC_OK;
 }
