@@ -1,51 +1,16 @@
 // Integer pmf -> quantised CDF tables, bit-exact with the reference's C++ routine
 //   compressai/cpp_exts/ops/ops.cpp:40-109   (pmf_to_quantized_cdf)
 //   compressai/entropy_models/entropy_models.py:204-212 (_pmf_to_cdf: one row per channel/scale)
-// Host version (one row) and device version (one thread block per row: the argmin scan and the
-// range shift of the "steal" loop run block-parallel; the loop over zero-width bins keeps the
-// reference's order, so the result is identical).
+// One thread block per row: the argmin scan and the range shift of the "steal" loop run
+// block-parallel; the loop over zero-width bins keeps the reference's order, so the result is
+// identical.  The single-row entry point with HOST pointers (the signature of the reference's
+// pybind11 function) stages the row through the same device kernel: there is no CPU algorithm in
+// this library.
 #include <math.h>
 
 #include "kernels.cuh"
 
 namespace lmsfc {
-
-int pmf_to_quantized_cdf_host(const float* pmf, int n, int precision, uint32_t* cdf) {
-  for (int i = 0; i < n; ++i)
-    if (pmf[i] < 0 || !isfinite(pmf[i])) {
-      set_error("Invalid `pmf`, non-finite or negative element found");
-      return LMSFC_ERR_DOMAIN;
-    }
-  cdf[0] = 0;
-  const float scale = (float)(1 << precision);
-  for (int i = 0; i < n; ++i) cdf[i + 1] = (uint32_t)roundf(pmf[i] * scale);
-  int acc = 0;  // the reference accumulates into an int
-  for (int i = 0; i <= n; ++i) acc = (int)((uint32_t)acc + cdf[i]);
-  const uint32_t total = (uint32_t)acc;
-  if (total == 0) {
-    set_error("Invalid `pmf`: at least one element must have a non-zero probability.");
-    return LMSFC_ERR_DOMAIN;
-  }
-  for (int i = 0; i <= n; ++i) cdf[i] = (uint32_t)((((uint64_t)1 << precision) * cdf[i]) / total);
-  for (int i = 1; i <= n; ++i) cdf[i] += cdf[i - 1];
-  cdf[n] = 1u << precision;
-  for (int i = 0; i < n; ++i) {
-    if (cdf[i] != cdf[i + 1]) continue;
-    uint32_t best_freq = ~0u;
-    int best = -1;
-    for (int j = 0; j < n; ++j) {
-      const uint32_t f = cdf[j + 1] - cdf[j];
-      if (f > 1 && f < best_freq) { best_freq = f; best = j; }
-    }
-    if (best < 0) {
-      set_error("pmf_to_quantized_cdf: no symbol to steal from");
-      return LMSFC_ERR_DOMAIN;
-    }
-    if (best < i) for (int j = best + 1; j <= i; ++j) cdf[j]--;
-    else          for (int j = i + 1; j <= best; ++j) cdf[j]++;
-  }
-  return LMSFC_OK;
-}
 
 // status[row]: 0 ok, 1 bad element, 2 all-zero, 3 nothing to steal
 __global__ void __launch_bounds__(256) cdf_rows_kernel(const float* pmf, int pmf_stride, const float* tail,
@@ -131,6 +96,51 @@ int pmf_rows_to_cdf_device(const float* pmf, int pmf_stride, const float* tail, 
   cdf_rows_kernel<<<rows, 256, smem, s>>>(pmf, pmf_stride, tail, pmf_length, precision, cdf, cdf_stride, status);
   LMSFC_LAUNCH_CHECK();
   return LMSFC_OK;
+}
+
+// Host-pointer signature of the reference's `_CXX.pmf_to_quantized_cdf(list, precision)`: the row is
+// copied to the device, converted by cdf_rows_kernel and copied back (synchronous, like the original).
+int pmf_to_quantized_cdf_host(const float* pmf, int n, int precision, uint32_t* cdf) {
+  if (n <= 0) {
+    set_error("Invalid `pmf`: at least one element must have a non-zero probability.");
+    return LMSFC_ERR_DOMAIN;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    set_error("pmf_to_quantized_cdf: no CUDA device (this library has no CPU fallback)");
+    return LMSFC_ERR_CUDA;
+  }
+  const int len = n - 1;                       // kernel row = pmf[0:len] ++ tail
+  uint8_t* buf = nullptr;
+  const size_t off_cdf = (size_t)n * sizeof(float), off_len = off_cdf + (size_t)(n + 1) * sizeof(int32_t);
+  LMSFC_CUDA(cudaMalloc(&buf, off_len + 2 * sizeof(int)));
+  float* d_pmf = (float*)buf;
+  int32_t* d_cdf = (int32_t*)(buf + off_cdf);
+  int* d_len = (int*)(buf + off_len);
+  int host_meta[2] = {len, 0};
+  int rc = LMSFC_OK;
+  cudaError_t e = cudaMemcpy(d_pmf, pmf, (size_t)n * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_len, host_meta, sizeof(host_meta), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    rc = pmf_rows_to_cdf_device(d_pmf, n, d_pmf + len, d_len, 1, precision, d_cdf, n + 1, d_len + 1, 0);
+    if (rc == LMSFC_OK) {
+      e = cudaMemcpy(cdf, d_cdf, (size_t)(n + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess) e = cudaMemcpy(host_meta, d_len, sizeof(host_meta), cudaMemcpyDeviceToHost);
+    }
+  }
+  cudaFree(buf);
+  if (rc) return rc;
+  if (e != cudaSuccess) {
+    set_error("pmf_to_quantized_cdf: %s", cudaGetErrorString(e));
+    return LMSFC_ERR_CUDA;
+  }
+  switch (host_meta[1]) {
+    case 0: return LMSFC_OK;
+    case 1: set_error("Invalid `pmf`, non-finite or negative element found"); break;
+    case 2: set_error("Invalid `pmf`: at least one element must have a non-zero probability."); break;
+    default: set_error("pmf_to_quantized_cdf: no symbol to steal from"); break;
+  }
+  return LMSFC_ERR_DOMAIN;
 }
 
 }  // namespace lmsfc

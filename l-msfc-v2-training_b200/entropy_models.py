@@ -93,32 +93,28 @@ class EntropyModel(nn.Module):
         return outputs
 
     def _pmf_to_cdf(self, pmf, tail_mass, pmf_length, max_length):
-        """:204-212 -- one row per channel / scale; integer stage on the device when there is one."""
+        """:204-212 -- one row per channel / scale, one thread block per row on the device."""
         rows = len(pmf_length)
         pmf = pmf.detach().float().contiguous()
         tail = tail_mass.detach().float().reshape(rows).contiguous()
         plen = pmf_length.detach().int().contiguous()
         max_length = int(max_length)
         dev = self._offset.device
-        if dev.type == "cuda":
-            pmf_d, tail_d, plen_d = pmf.to(dev), tail.to(dev), plen.to(dev)
-            cdf = torch.empty((rows, max_length + 2), dtype=torch.int32, device=dev)
-            status = torch.zeros(rows, dtype=torch.int32, device=dev)
-            L.pmf_rows_to_cdf(ptr(pmf_d), pmf_d.stride(0), ptr(tail_d), ptr(plen_d), rows,
-                              self.entropy_coder_precision, ptr(cdf), max_length + 2, ptr(status), stream())
-            bad = int(status.max().item())
-            if bad == 1:
-                raise ValueError("Invalid `pmf`, non-finite or negative element found")
-            if bad == 2:
-                raise ValueError("Invalid `pmf`: at least one element must have a non-zero probability.")
-            if bad:
-                raise ValueError("pmf_to_quantized_cdf: no symbol to steal from")
-            return cdf
-        cdf = torch.zeros((rows, max_length + 2), dtype=torch.int32)
-        for i in range(rows):
-            prob = torch.cat((pmf[i, : int(plen[i])].cpu(), tail[i:i + 1].cpu()), dim=0)
-            c = pmf_to_quantized_cdf(prob, self.entropy_coder_precision)
-            cdf[i, : c.size(0)] = c
+        if dev.type != "cuda":
+            raise RuntimeError("EntropyModel._pmf_to_cdf: move the module to a CUDA device first "
+                               "(l-msfc-v2-training_b200 has no CPU fallback)")
+        pmf_d, tail_d, plen_d = pmf.to(dev), tail.to(dev), plen.to(dev)
+        cdf = torch.empty((rows, max_length + 2), dtype=torch.int32, device=dev)
+        status = torch.zeros(rows, dtype=torch.int32, device=dev)
+        L.pmf_rows_to_cdf(ptr(pmf_d), pmf_d.stride(0), ptr(tail_d), ptr(plen_d), rows,
+                          self.entropy_coder_precision, ptr(cdf), max_length + 2, ptr(status), stream())
+        bad = int(status.max().item())
+        if bad == 1:
+            raise ValueError("Invalid `pmf`, non-finite or negative element found")
+        if bad == 2:
+            raise ValueError("Invalid `pmf`: at least one element must have a non-zero probability.")
+        if bad:
+            raise ValueError("pmf_to_quantized_cdf: no symbol to steal from")
         return cdf
 
     def _check_cdf_size(self):
