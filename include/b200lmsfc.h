@@ -30,7 +30,8 @@ uint64_t lmsfc_launch_count(void);
  * deconv = nn.ConvTranspose2d(k, stride, padding=k/2, output_padding=stride-1), and their autograd.
  * Weights live in "GEMM layout" [D0][T][D1] with T = k*k taps: conv D0=Cout, D1=Cin (torch
  * [Cout][Cin][kh][kw] permuted (0,2,3,1)); deconv D0=Cin, D1=Cout (torch [Cin][Cout][kh][kw] permuted).
- * `w_direct` is the bf16 copy in that layout, `w_transposed` the bf16 copy as [D1][T][D0]. */
+ * `w` is always the ONE bf16 copy in that layout: forward and data-gradient kernels read it either as a
+ * K-major or as an MN-major tensor-core operand, so no transposed copy exists. */
 typedef struct {
   int kind;          /* 0 conv, 1 deconv */
   int k, stride;     /* 5/2 or 3/1 in L-MSFC */
@@ -41,11 +42,10 @@ typedef struct {
 } lmsfc_conv_desc;
 
 /* out = act(conv(cat[src0,src1]) + bias).  Any of out_bf16 / out_f32 / out_abs (|.| as bf16, the
- * abs(y) fed to h_a, models/google.py:294) may be null.  conv needs w_direct, deconv w_transposed. */
+ * abs(y) fed to h_a, models/google.py:294) may be null. */
 int lmsfc_conv_forward(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* w,
                        const float* bias, int relu, void* out_bf16, float* out_f32, void* out_abs, void* stream);
-/* grad wrt the first n_in input channels (n_in <= c0; source 1 is data and gets none).
- * conv needs w_transposed, deconv w_direct. */
+/* grad wrt the first n_in input channels (n_in <= c0; source 1 is data and gets none). */
 int lmsfc_conv_dgrad(const lmsfc_conv_desc* d, const void* gout, const void* w, int n_in, void* gin_bf16,
                      void* stream);
 /* gw (fp32, GEMM layout, caller-zeroed) += weight gradient; gbias (fp32 [Cout], nullable) += column sums. */
@@ -58,9 +58,8 @@ int lmsfc_conv_wgrad(const lmsfc_conv_desc* d, const void* src0, const void* src
  * saved (bf16) for backward; x2 / t are caller scratch of P*C bf16. */
 int lmsfc_gdn_forward(const void* x, const void* gamma_eff, const float* beta_eff, int inverse, int64_t P, int C,
                       void* x2_scratch, void* y, void* rn, void* stream);
-/* gx written; g_gamma_eff fp32 [C][C] and g_beta_eff fp32 [C] accumulated (caller-zeroed).
- * gamma_eff_t is gamma_eff transposed ([in][out], bf16). */
-int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void* gamma_eff_t, int inverse, int64_t P,
+/* gx written; g_gamma_eff fp32 [C][C] and g_beta_eff fp32 [C] accumulated (caller-zeroed). */
+int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void* gamma_eff, int inverse, int64_t P,
                        int C, void* x2_scratch, void* t_scratch, void* gx, float* g_gamma_eff, float* g_beta_eff,
                        void* stream);
 /* NonNegativeParametrizer (ops/parametrizers.py:38-64) with LowerBound's gradient (ops/bound_ops.py:40-42):
@@ -109,8 +108,6 @@ int lmsfc_colsum(const void* g_bf16, int64_t P, int C, float* out, void* stream)
 int lmsfc_cast_f32_bf16(const float* in, void* out, int64_t n, void* stream);
 int lmsfc_cast_bf16_f32(const void* in, float* out, int64_t n, void* stream);
 int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C, int HW, void* stream);
-/* fp32 [D0][T][D1] -> bf16 [D1][T][D0] */
-int lmsfc_transpose_weight(const float* in, void* out, int D0, int T, int D1, void* stream);
 
 /* ------------------------------------------------------------------ optimiser (examples/train.py:100-107) */
 int lmsfc_sumsq(const float* g, int64_t n, float* accum, void* stream);

@@ -9,7 +9,8 @@ import os
 from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int64, c_uint64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200lmsfc.so")
+# LMSFC_LIB selects an alternative build of the same library (e.g. the TIMELINE=1 debug build)
+LIB_PATH = os.environ.get("LMSFC_LIB") or os.path.join(_HERE, "libb200lmsfc.so")
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -47,7 +48,6 @@ _SIGS = {
     "lmsfc_cast_f32_bf16": [P, P, c_int64, P],
     "lmsfc_cast_bf16_f32": [P, P, c_int64, P],
     "lmsfc_nchw_to_nhwc_bf16": [P, P, c_int, c_int, c_int, P],
-    "lmsfc_transpose_weight": [P, P, c_int, c_int, c_int, P],
     "lmsfc_sumsq": [P, c_int64, P, P],
     "lmsfc_adam_step": [P, P, P, P, P, c_int64, c_float, c_float, c_float, c_float, c_float, P, P, P, P],
     "lmsfc_pmf_to_quantized_cdf": [P, c_int, c_int, P],

@@ -65,17 +65,18 @@ static int run_regular(const bf16* s0, const bf16* s1, int c0, int c1, int B, in
   p.ph[0].Hg = Hg; p.ph[0].Wg = Wg; p.ph[0].M = B * Hg * Wg; p.ph[0].oy = 0; p.ph[0].ox = 0; p.ph[0].tap_begin = 0;
   taps_regular(k, k / 2, &p.ph[0].ntaps, p.dy, p.dx, p.widx);
   p.Hout = Hg; p.Wout = Wg; p.sout = 1; p.N = N;
-  p.w = w; p.w_rows = w_rows; p.w_cols = k * k * (c0 + c1);
+  p.w = w; p.w_rows = w_rows; p.w_cols = k * k * (c0 + c1); p.w_mn = 0;
   return launch_igemm(p, st);
 }
 // "transposed" structure: out[s*h+py][s*w+px] = sum_{taps of phase} src[h+dy][w+dx] . W[tap];
 // the s*s sub-pixel phases partition the k*k taps and run as blockIdx.z slices of ONE launch
+// The weight block is the layer's direct [D0 = c0][T][D1 = w_d1] copy, consumed as an MN-major B operand.
 static int run_transposed(const bf16* s0, int c0, int B, int Hs, int Ws, int Ho, int Wo, int k, int s, const bf16* w,
-                          int w_rows, int N, IgemmParams& p, cudaStream_t st) {
+                          int w_d1, int N, IgemmParams& p, cudaStream_t st) {
   p.src0 = s0; p.src1 = nullptr; p.c0 = c0; p.c1 = 0;
   p.B = B; p.Hin = Hs; p.Win = Ws; p.sin = 1;
   p.Hout = Ho; p.Wout = Wo; p.sout = s; p.N = N;
-  p.w = w; p.w_rows = w_rows; p.w_cols = k * k * c0;
+  p.w = w; p.w_rows = c0; p.w_cols = k * k * w_d1; p.w_mn = 1; p.w_ld_tap = w_d1;
   int np = 0, tb = 0;
   for (int py = 0; py < s; ++py)
     for (int px = 0; px < s; ++px) {
@@ -180,10 +181,10 @@ extern "C" int lmsfc_gdn_forward(const void* x, const void* gamma_eff, const flo
   return launch_igemm(p, ST(stream));
 }
 
-extern "C" int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void* gamma_eff_t, int inverse,
+extern "C" int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void* gamma_eff, int inverse,
                                   int64_t P, int C, void* x2_scratch, void* t_scratch, void* gx, float* g_gamma_eff,
                                   float* g_beta_eff, void* stream) {
-  LMSFC_CHECK_ARG(gy && x && rn && gamma_eff_t && x2_scratch && t_scratch && gx && g_gamma_eff && g_beta_eff,
+  LMSFC_CHECK_ARG(gy && x && rn && gamma_eff && x2_scratch && t_scratch && gx && g_gamma_eff && g_beta_eff,
                   "gdn_backward: null operand");
   LMSFC_CHECK_ARG(C % 256 == 0 && P > 0 && P < (1ll << 31), "gdn_backward: P=%lld C=%d", (long long)P, C);
   int rc = gdn_t((const bf16*)gy, (const bf16*)x, (const bf16*)rn, inverse, P, C, (bf16*)t_scratch, g_beta_eff, ST(stream));
@@ -191,7 +192,8 @@ extern "C" int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn,
   rc = square_bf16((const bf16*)x, (bf16*)x2_scratch, P * C, ST(stream));
   if (rc) return rc;
   IgemmParams p;
-  gdn_gemm_params(p, (const bf16*)t_scratch, (const bf16*)gamma_eff_t, P, C);
+  gdn_gemm_params(p, (const bf16*)t_scratch, (const bf16*)gamma_eff, P, C);
+  p.w_mn = 1; p.w_ld_tap = C;      // s_j = sum_i gamma[i][j] t_i: gamma read as an MN-major operand
   p.epi = EPI_GDN_BWD; p.inverse = inverse; p.aux_x = (const bf16*)x; p.aux_gy = (const bf16*)gy; p.aux_rn = (const bf16*)rn;
   p.out_bf16 = (bf16*)gx;
   rc = launch_igemm(p, ST(stream));
@@ -280,9 +282,6 @@ extern "C" int lmsfc_cast_bf16_f32(const void* in, float* out, int64_t n, void* 
 }
 extern "C" int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C, int HW, void* stream) {
   return nchw_to_nhwc_bf16(in, (bf16*)out, B, C, HW, ST(stream));
-}
-extern "C" int lmsfc_transpose_weight(const float* in, void* out, int D0, int T, int D1, void* stream) {
-  return transpose_weight(in, (bf16*)out, D0, T, D1, ST(stream));
 }
 extern "C" int lmsfc_sumsq(const float* g, int64_t n, float* accum, void* stream) { return sumsq_f32(g, n, accum, ST(stream)); }
 extern "C" int lmsfc_adam_step(float* p, float* m, float* v, const float* g, void* p_bf16, int64_t n, float lr, float beta1,

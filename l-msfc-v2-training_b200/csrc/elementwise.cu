@@ -73,7 +73,7 @@ int loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist,
 // (device counter, self-resetting) adds the column totals to `out`.
 __device__ __forceinline__ void colsum_finish(const float (&acc)[8], int c8, int C8, float* out, float* scratch,
                                               unsigned int* counter) {
-  __shared__ float red[8][32][9];
+  __shared__ __align__(16) float red[8][32][9];
   __shared__ unsigned int is_last;
   const int C = C8 * 8;
 #pragma unroll
@@ -97,12 +97,34 @@ __device__ __forceinline__ void colsum_finish(const float (&acc)[8], int c8, int
   }
   __syncthreads();
   if (is_last) {
+    // 256 threads = 4 row slices x 64 float4 column groups of this block's 256 columns; 8 independent
+    // L2 loads in flight per thread (a serial loop over the partial rows was latency-bound)
     __threadfence();
-    const int col = (blockIdx.x * 32 + threadIdx.x) * 8 + threadIdx.y;
+    const int tid = threadIdx.y * 32 + threadIdx.x;
+    const int q = tid & 63, sl = tid >> 6;
+    const int col = blockIdx.x * 256 + q * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (col < C) {
-      float v = 0.f;
-      for (unsigned int b = 0; b < gridDim.y; ++b) v += __ldcg(scratch + (size_t)b * C + col);
-      out[col] += v;
+      const int nb = (int)gridDim.y;
+#pragma unroll 8
+      for (int b2 = sl; b2 < nb; b2 += 4) {
+        const float4 t = __ldcg(reinterpret_cast<const float4*>(scratch + (size_t)b2 * C + col));
+        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+      }
+    }
+    float4* fin = reinterpret_cast<float4*>(&red[0][0][0]);      // reuse (all reads of red are done)
+    fin[tid] = v;
+    __syncthreads();
+    if (sl == 0 && col < C) {
+#pragma unroll
+      for (int k = 1; k < 4; ++k) {
+        const float4 t = fin[k * 64 + q];
+        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+      }
+      float4* o = reinterpret_cast<float4*>(out + col);
+      float4 cur = *o;
+      cur.x += v.x; cur.y += v.y; cur.z += v.z; cur.w += v.w;
+      *o = cur;
     }
   }
 }
@@ -196,7 +218,7 @@ __global__ void __launch_bounds__(256) colsum_kernel(const uint4* __restrict__ g
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
   if (c8 < C8) {
-#pragma unroll 4
+#pragma unroll 8
     for (int64_t p = (int64_t)blockIdx.y * 8 + threadIdx.y; p < P; p += (int64_t)gridDim.y * 8) {
       const uint4 a = __ldg(g + p * C8 + c8);
       const uint32_t av[4] = {a.x, a.y, a.z, a.w};
@@ -209,10 +231,11 @@ __global__ void __launch_bounds__(256) colsum_kernel(const uint4* __restrict__ g
 int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream_t s) {
   LMSFC_CHECK_ARG(C % 8 == 0, "colsum: C must be a multiple of 8");
   LMSFC_CHECK_ARG(C <= kRedMaxC, "column reduction: C=%d too large", C);
+  LMSFC_CHECK_ARG(((uintptr_t)out & 15) == 0, "colsum: out must be 16-byte aligned");
   if (int rc = ensure_reduce_scratch()) return rc;
   if (P == 0) return LMSFC_OK;
   const int C8 = C / 8, bx = (C8 + 31) / 32;
-  int64_t by = (148 * 2 + bx - 1) / bx;   // ~2 blocks per SM: few same-address atomics, 4 loads in flight per thread
+  int64_t by = (148 * 2 + bx - 1) / bx;   // ~2 blocks per SM, 8 x 16 B loads in flight per thread
   const int64_t maxy = (P + 7) / 8;
   if (by > maxy) by = maxy;
   colsum_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)g, P, C8, out, g_red_scratch, g_red_count);

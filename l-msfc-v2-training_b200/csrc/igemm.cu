@@ -104,9 +104,26 @@ __device__ __forceinline__ void epilogue_chunk(const IgemmParams& p, float (&v)[
   if (p.out_bf16) store_bf16x32(p.out_bf16 + o, v);
 }
 
+#ifdef LMSFC_TIMELINE
+// debug build only (make TIMELINE=1): %globaltimer stamps of CTA 0 / last CTA, read back by profiles/timeline.py
+__device__ unsigned long long g_timeline[64 * 16];
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define TL(slot)                                                                                   \
+  do {                                                                                             \
+    const int _c = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                 \
+    if (_c < 64) g_timeline[_c * 16 + (slot)] = gtimer();                                          \
+  } while (0)
+#else
+#define TL(slot) do {} while (0)
+#endif
+
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool B_MN>
 __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_constant__ IgemmParams p) {
   using Cfg = FwdCfg<BLOCK_N>;
   constexpr int STAGES = Cfg::STAGES;
@@ -119,6 +136,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   uint32_t* last_flag = tmem_slot + 1;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) TL(0);
   const int phase_id = blockIdx.z / p.ksplit, ks = blockIdx.z % p.ksplit;
   const IgemmPhase ph = p.ph[phase_id];
   const int m0 = blockIdx.x * BLOCK_M;
@@ -146,6 +164,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (tid == 0) TL(1);
 
   if (warp < 4) {
     // ================= activation gather (producer) =================
@@ -187,13 +206,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       if (++kc == kc_per_tap) { kc = 0; ++tap; }
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
+    if (tid == 0) TL(2);
     cp_async_wait_all();
+    if (tid == 0) TL(3);
 
     // ================= epilogue: TMEM -> registers -> global =================
     if (nkb > 0) {
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
     }
+    if (tid == 0) TL(4);
     const int row = warp * 32 + lane;
     const int m = m0 + row;
     bool ok = m < ph.M;
@@ -234,8 +256,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
                        "f"(__uint_as_float(r[4 * j + 2])), "f"(__uint_as_float(r[4 * j + 3]))
                        : "memory");
       }
+      if (tid == 0) TL(5);
       __threadfence();
       epi_bar_sync();
+      if (tid == 0) TL(6);
       if (tid == 0) {
         const unsigned prev = atomicAdd(p.ws_count + tile, 1u);
         *last_flag = (prev == (unsigned)p.ksplit - 1) ? 1u : 0u;
@@ -266,8 +290,17 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         mbar_arrive_expect_tx(&full_bar[stage], Cfg::B_STAGE_BYTES);
-        const int kcoord = (int)p.widx[tap] * ctot + kc * BLOCK_K;
-        tma_load_2d(&p.tmapB, &full_bar[stage], smem_base + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES, kcoord, n0);
+        const uint32_t sb = smem_base + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES;
+        if (!B_MN) {
+          const int kcoord = (int)p.widx[tap] * ctot + kc * BLOCK_K;
+          tma_load_2d(&p.tmapB, &full_bar[stage], sb, kcoord, n0);
+        } else {
+          // rows = k channel, cols = tap*N + n: BLOCK_N/64 boxes of [64 k][64 n], one 8 KB segment each
+          const int ncoord = (int)p.widx[tap] * p.w_ld_tap + n0;
+#pragma unroll
+          for (int seg = 0; seg < BLOCK_N / 64; ++seg)
+            tma_load_2d(&p.tmapB, &full_bar[stage], sb + seg * (BLOCK_K * 128), ncoord + 64 * seg, kc * BLOCK_K);
+        }
         if (++kc == kc_per_tap) { kc = 0; ++tap; }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
@@ -275,32 +308,45 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   } else {
     // ================= MMA issuer (one thread) =================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N, 0, 0);
+      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N, 0, B_MN ? 1 : 0);
       int stage = 0, phase = 0;
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
+        if (kb == 0) TL(9);
         const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
         const uint32_t sb = sa + A_STAGE_BYTES;
 #pragma unroll
         for (int k = 0; k < BLOCK_K / 16; ++k) {
           const uint64_t ad = make_sdesc_sw128(sa + k * 32, 16, 1024);
-          const uint64_t bd = make_sdesc_sw128(sb + k * 32, 16, 1024);
+          // K-major: 32 B per 16-k step inside the 128 B row; MN-major: 16 k rows = 2 KB per step,
+          // LBO = next 64-n segment, SBO = next 8 k rows (same image as wgrad.cu's gathered operand)
+          const uint64_t bd = B_MN ? make_sdesc_sw128(sb + k * 2048, BLOCK_K * 128, 1024)
+                                   : make_sdesc_sw128(sb + k * 32, 16, 1024);
           umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0);
         }
         umma_commit(&empty_bar[stage]);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
       if (nkb > 0) umma_commit(tmem_full_bar);
+      TL(10);
     }
   }
+  if (tid == 0) TL(7);
   tc_fence_before();
   __syncthreads();
   if (warp == 5) {
     tc_fence_after();
     tmem_dealloc<BLOCK_N>(tmem_base);
   }
+  if (tid == 0) TL(8);
 }
+
+#ifdef LMSFC_TIMELINE
+extern "C" int lmsfc_debug_read_timeline(unsigned long long* host64x16) {
+  return (int)cudaMemcpyFromSymbol(host64x16, g_timeline, sizeof(unsigned long long) * 64 * 16);
+}
+#endif
 
 // ---------------------------------------------------------------- host side
 namespace {
@@ -321,16 +367,16 @@ int ensure_workspace() {
 }
 }  // namespace
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool B_MN>
 static int launch_fwd_t(const IgemmParams& p, dim3 grid, cudaStream_t stream) {
   using Cfg = FwdCfg<BLOCK_N>;
   static bool attr_done = false;
   if (!attr_done) {
-    LMSFC_CUDA(cudaFuncSetAttribute(igemm_fwd_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    LMSFC_CUDA(cudaFuncSetAttribute(igemm_fwd_kernel<BLOCK_N, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::SMEM_BYTES));
     attr_done = true;
   }
-  igemm_fwd_kernel<BLOCK_N><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(p);
+  igemm_fwd_kernel<BLOCK_N, B_MN><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(p);
   LMSFC_LAUNCH_CHECK();
   return LMSFC_OK;
 }
@@ -340,7 +386,8 @@ int launch_igemm(IgemmParams& p, cudaStream_t stream) {
   LMSFC_CHECK_ARG(p.c0 % 64 == 0 && p.c1 % 64 == 0 && p.c0 > 0, "igemm: channels (%d,%d) must be multiples of 64",
                   p.c0, p.c1);
   LMSFC_CHECK_ARG(p.nphase >= 1 && p.nphase <= kMaxPhases, "igemm: nphase=%d", p.nphase);
-  LMSFC_CHECK_ARG(p.w_rows >= p.N && p.w_cols % 64 == 0, "igemm: weight matrix %dx%d", p.w_rows, p.w_cols);
+  LMSFC_CHECK_ARG(p.w_cols % 64 == 0 && (p.w_mn ? p.w_rows >= p.c0 + p.c1 : p.w_rows >= p.N),
+                  "igemm: weight matrix %dx%d", p.w_rows, p.w_cols);
   int maxM = 0, min_taps = kMaxTaps, max_taps = 0;
   int64_t tiles128 = 0;
   for (int i = 0; i < p.nphase; ++i) {
@@ -381,10 +428,11 @@ int launch_igemm(IgemmParams& p, cudaStream_t stream) {
   p.ksplit = ksplit;
   p.ws = g_ws;
   p.ws_count = g_ws_count;
-  int rc = make_tmap_2d_bf16(&p.tmapB, p.w, (uint64_t)p.w_rows, (uint64_t)p.w_cols, (uint64_t)p.w_cols, bn, 64);
+  int rc = make_tmap_2d_bf16(&p.tmapB, p.w, (uint64_t)p.w_rows, (uint64_t)p.w_cols, (uint64_t)p.w_cols,
+                             p.w_mn ? 64 : bn, 64);
   if (rc) return rc;
-  if (bn == 256) return launch_fwd_t<256>(p, grid, stream);
-  return launch_fwd_t<128>(p, grid, stream);
+  if (p.w_mn) return bn == 256 ? launch_fwd_t<256, true>(p, grid, stream) : launch_fwd_t<128, true>(p, grid, stream);
+  return bn == 256 ? launch_fwd_t<256, false>(p, grid, stream) : launch_fwd_t<128, false>(p, grid, stream);
 }
 
 }  // namespace lmsfc

@@ -23,9 +23,11 @@ struct IgemmPhase {
   int tap_begin, ntaps;     // slice of the tap table
 };
 struct IgemmParams {
-  CUtensorMap tmapB;        // filled by launch_igemm: box {64, BLOCK_N}, SWIZZLE_128B
-  const __nv_bfloat16* w;   // weights, bf16 [w_rows][w_cols], K (= tap*Ctot + c) contiguous
-  int w_rows, w_cols;
+  CUtensorMap tmapB;        // filled by launch_igemm, SWIZZLE_128B: box {64 k, BLOCK_N n} or, w_mn = 1, {64 n, 64 k}
+  const __nv_bfloat16* w;   // weights, bf16 [w_rows][w_cols]
+  int w_rows, w_cols;       //   w_mn = 0: rows = n, cols = k = widx(tap)*Ctot + c     (K-major B operand)
+  int w_mn;                 //   w_mn = 1: rows = k-channel c, cols = widx(tap)*w_ld_tap + n  (MN-major B operand:
+  int w_ld_tap;             //             the SAME [D0][T][D1] weight block read "transposed", no second copy)
   const __nv_bfloat16* src0;  // NHWC bf16 [B][Hin][Win][c0]
   const __nv_bfloat16* src1;  // optional second source (channel concat), [B][Hin][Win][c1]
   int c0, c1;

@@ -64,7 +64,6 @@ int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, i
             cudaStream_t s);
 int cast_f32_bf16(const float* in, __nv_bfloat16* out, int64_t n, cudaStream_t s);
 int cast_bf16_f32(const __nv_bfloat16* in, float* out, int64_t n, cudaStream_t s);
-int transpose_weight(const float* in, __nv_bfloat16* out, int D0, int T, int D1, cudaStream_t s);
 int nchw_to_nhwc_bf16(const float* in, __nv_bfloat16* out, int B, int C, int HW, cudaStream_t s);
 int sumsq_f32(const float* g, int64_t n, float* accum, cudaStream_t s);
 struct AdamArgs {

@@ -73,30 +73,7 @@ int adam_step(const AdamArgs& a, cudaStream_t s) {
   return LMSFC_OK;
 }
 
-// ---------------------------------------------------------------- weight repack
-// fp32 [D0][T][D1] -> bf16 [D1][T][D0]  (the "other side" GEMM operand of a conv / deconv)
-__global__ void __launch_bounds__(256) transpose_weight_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
-                                                               int D0, int T, int D1) {
-  __shared__ float tile[32][33];
-  const int t = blockIdx.z;
-  const int d1b = blockIdx.x * 32, d0b = blockIdx.y * 32;
-  for (int r = threadIdx.y; r < 32; r += 8) {
-    const int d0 = d0b + r, d1 = d1b + threadIdx.x;
-    tile[r][threadIdx.x] = (d0 < D0 && d1 < D1) ? in[((size_t)d0 * T + t) * D1 + d1] : 0.f;
-  }
-  __syncthreads();
-  for (int r = threadIdx.y; r < 32; r += 8) {
-    const int d1 = d1b + r, d0 = d0b + threadIdx.x;
-    if (d0 < D0 && d1 < D1) out[((size_t)d1 * T + t) * D0 + d0] = __float2bfloat16(tile[threadIdx.x][r]);
-  }
-}
-int transpose_weight(const float* in, __nv_bfloat16* out, int D0, int T, int D1, cudaStream_t s) {
-  dim3 grid((D1 + 31) / 32, (D0 + 31) / 32, T);
-  transpose_weight_kernel<<<grid, dim3(32, 8), 0, s>>>(in, out, D0, T, D1);
-  LMSFC_LAUNCH_CHECK();
-  return LMSFC_OK;
-}
-
+// ---------------------------------------------------------------- layout
 // fp32 NCHW -> bf16 NHWC (feature ingest for callers that hand over the reference's layout)
 __global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int C,
                                                            int HW) {

@@ -59,8 +59,9 @@ def grad_view(param, layout_perm=None):
 
 # ====================================================================== conv / deconv
 class ConvState:
-    """Per-layer device state shared by forward and backward: geometry, bf16 weight shadows
-    ([D0][T][D1] "direct" and [D1][T][D0] "transposed") and the parameters they shadow."""
+    """Per-layer device state shared by forward and backward: geometry and the bf16 weight shadow
+    ([D0][T][D1]; read K-major by conv-forward / deconv-dgrad and MN-major by conv-dgrad /
+    deconv-forward, so there is no transposed copy)."""
 
     def __init__(self, kind, k, stride, c0, c1, cout):
         self.kind, self.k, self.stride, self.c0, self.c1, self.cout = kind, k, stride, c0, c1, cout
@@ -68,7 +69,6 @@ class ConvState:
         cin = c0 + c1
         self.D0, self.D1 = (cout, cin) if kind == 0 else (cin, cout)
         self.w_direct = None
-        self.w_trans = None
         self._version = -1
         self.grad_ready = None     # callable(list_of_params) set by the DP wrapper
 
@@ -88,7 +88,7 @@ class ConvState:
         return w if w.is_contiguous() else None
 
     def refresh(self, weight, force=False):
-        """(Re)build the bf16 shadows when the fp32 parameter changed."""
+        """(Re)build the bf16 shadow when the fp32 parameter changed."""
         v = weight._version
         if not force and self.w_direct is not None and v == self._version:
             return
@@ -97,10 +97,8 @@ class ConvState:
             wg = weight.detach().permute(0, 2, 3, 1).contiguous()
         if self.w_direct is None:
             self.w_direct = torch.empty((self.D0, self.T, self.D1), dtype=BF16, device=weight.device)
-            self.w_trans = torch.empty((self.D1, self.T, self.D0), dtype=BF16, device=weight.device)
         st = stream()
         L.cast_f32_bf16(ptr(wg), ptr(self.w_direct), wg.numel(), st)
-        L.transpose_weight(ptr(wg), ptr(self.w_trans), self.D0, self.T, self.D1, st)
         self._version = v
 
 
@@ -114,7 +112,7 @@ class _ConvFn(torch.autograd.Function):
         Ho, Wo = state.out_hw(H, W, out_hw)
         state.refresh(weight)
         d = state.desc(B, H, W, Ho, Wo)
-        w = state.w_direct if state.kind == 0 else state.w_trans
+        w = state.w_direct
         dev = x0.device
         out_b = out_f = out_a = None
         if mode == 0:
@@ -168,9 +166,8 @@ class _ConvFn(torch.autograd.Function):
         # ---- data gradient (only source 0 is differentiable: source 1 is input data)
         gx = None
         if ctx.need_dx:
-            w = state.w_trans if state.kind == 0 else state.w_direct
             gx = empty_nhwc(B, state.c0, H, W, BF16, g.device)
-            L.conv_dgrad(d, ptr(g), ptr(w), state.c0, ptr(gx), st)
+            L.conv_dgrad(d, ptr(g), ptr(state.w_direct), state.c0, ptr(gx), st)
         if state.grad_ready is not None and ready:
             state.grad_ready(ready)
         return gx, None, None, None, None, None, None, None
@@ -217,25 +214,23 @@ class _GDNFn(torch.autograd.Function):
         rn = torch.empty_like(x)
         L.gdn_forward(ptr(x), ptr(gamma_bf), ptr(beta_eff), int(state.inverse), P, C, ptr(x2), ptr(y), ptr(rn), st)
         ctx.state, ctx.beta, ctx.gamma = state, beta, gamma
-        ctx.save_for_backward(x, rn, gamma_eff)
+        ctx.save_for_backward(x, rn, gamma_bf)
         return y
 
     @staticmethod
     def backward(ctx, gy):
         state = ctx.state
-        x, rn, gamma_eff = ctx.saved_tensors
+        x, rn, gamma_bf = ctx.saved_tensors
         B, C, H, W = x.shape
         P = B * H * W
         dev, st = x.device, stream()
         gy = nhwc(gy, BF16)
-        gamma_t = torch.empty((C, C), dtype=BF16, device=dev)
-        L.transpose_weight(ptr(gamma_eff), ptr(gamma_t), C, 1, C, st)
         x2 = torch.empty_like(x)
         t = torch.empty_like(x)
         gx = torch.empty_like(x)
         g_gamma_eff = torch.zeros((C, C), dtype=F32, device=dev)
         g_beta_eff = torch.zeros(C, dtype=F32, device=dev)
-        L.gdn_backward(ptr(gy), ptr(x), ptr(rn), ptr(gamma_t), int(state.inverse), P, C, ptr(x2), ptr(t), ptr(gx),
+        L.gdn_backward(ptr(gy), ptr(x), ptr(rn), ptr(gamma_bf), int(state.inverse), P, C, ptr(x2), ptr(t), ptr(gx),
                        ptr(g_gamma_eff), ptr(g_beta_eff), st)
         beta, gamma = ctx.beta, ctx.gamma
         gb, gg = grad_view(beta), grad_view(gamma)

@@ -67,7 +67,6 @@ class _ConvBase(nn.Module):
         # nn.Module._apply may re-create parameters; drop the bf16 shadows so they are rebuilt
         out = super()._apply(fn, recurse)
         self._state.w_direct = None
-        self._state.w_trans = None
         self._state._version = -1
         return out
 

@@ -6,8 +6,8 @@ models/google.py:292-303: `forward(x) -> {"x_hat": ..., "likelihoods": {...}}`, 
 Here `x` and `x_hat` are dicts of the pyramid levels (p2..p5, [B,F,H,W]).
 
 ParamArena packs every fp32 parameter (and its gradient) into one flat allocation so that
-clip+Adam is one launch, the bf16 GEMM shadows of all conv weights are one contiguous block
-written by the same launch, and gradient all-reduce buckets are plain slices.
+clip+Adam is one launch, the bf16 GEMM operands of all conv weights are one contiguous block
+written by the same launch (each is read K-major or MN-major by the kernels: no transposed copies), and gradient all-reduce buckets are plain slices.
 """
 import math
 
@@ -186,7 +186,6 @@ class ParamArena:
             o = self.offsets[name]
             st = m._state
             st.w_direct = self.net_bf16[o:o + m.weight.numel()].view(st.D0, st.T, st.D1)
-            st.w_trans = torch.empty((st.D1, st.T, st.D0), dtype=torch.bfloat16, device=dev)
         self.refresh_shadows(cast=True)
 
     def names(self, group="net"):
@@ -199,14 +198,12 @@ class ParamArena:
         return base[o:o + p.numel()]
 
     def refresh_shadows(self, cast=True):
-        st = stream()
+        """bf16 GEMM operands of all conv weights = one cast of the flat arena (Adam writes the same
+        block in its own pass, so the train step never calls this)."""
         if cast:
-            L.cast_f32_bf16(ptr(self.net_params), ptr(self.net_bf16), self.net_params.numel(), st)
+            L.cast_f32_bf16(ptr(self.net_params), ptr(self.net_bf16), self.net_params.numel(), stream())
         for m in self.model.conv_layers():
-            s = m._state
-            wg = m.weight.detach().permute(0, 2, 3, 1)
-            L.transpose_weight(ptr(wg), ptr(s.w_trans), s.D0, s.T, s.D1, st)
-            s._version = m.weight._version
+            m._state._version = m.weight._version
 
     def zero_grad(self):
         self.net_grads.zero_()

@@ -1,7 +1,7 @@
 """The L-MSFC train step: one iteration of train_one_epoch (compressai/examples/train.py:85-118)
 
     zero_grad x2 -> forward -> RD loss -> backward -> [DP all-reduce] -> clip(1.0) + Adam(1e-4)
-    -> aux loss -> backward -> Adam(1e-3) on quantiles -> refresh bf16 GEMM operands
+    -> aux loss -> backward -> Adam(1e-3) on quantiles   (Adam also writes the bf16 GEMM operands)
 
 `TrainStep.step(feats)` runs it eagerly; `TrainStep.capture(feats)` records the same launch sequence
 once into a CUDA graph (static shapes, device-side RNG counter and Adam step counter) so later
@@ -49,7 +49,6 @@ class TrainStep:
         aux = model.aux_loss()
         aux.backward()
         opt["aux"].step()
-        model.refresh_shadows(cast=False)       # transposed GEMM operands of the updated weights
         return {"loss": crit["loss"].detach(), "mse_loss": crit["mse_loss"].detach(),
                 "bpp_loss": crit["bpp_loss"].detach(), "aux_loss": aux.detach()}
 

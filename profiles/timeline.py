@@ -1,0 +1,38 @@
+"""%globaltimer timeline of the implicit-GEMM kernel (debug build: make -C .../csrc TIMELINE=1).
+  LMSFC_LIB=l-msfc-v2-training_b200/libb200lmsfc_tl.so python profiles/timeline.py
+Prints, for a few layer shapes, per-CTA stage times (us since the first CTA started)."""
+import ctypes, importlib, os, sys
+import numpy as np, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+os.environ.setdefault("LMSFC_LIB", os.path.join(ROOT, "l-msfc-v2-training_b200", "libb200lmsfc_tl.so"))
+PKG = "l-msfc-v2-training_b200"
+L = importlib.import_module(PKG + "._lib")
+layers = importlib.import_module(PKG + ".layers")
+Fn = importlib.import_module(PKG + ".functional")
+dev = torch.device("cuda", 0)
+NAMES = ["start", "setup", "gather-issued", "gather-landed", "tmem-full", "reds-issued", "fence+bar", "epi-done", "exit", "mma-first", "mma-last"]
+bf = lambda *s: (torch.randn(*s, device=dev) * 0.5).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+P = L.ptr
+CASES = [("h_a.4 16x2x2->1x1 k5", 0, 5, 2, 256, 16, 2, 2, 1, 1), ("h_a.0 16x4x4 k3", 0, 3, 1, 256, 16, 4, 4, 4, 4),
+         ("head5 16x8x8 k3", 0, 3, 1, 256, 16, 8, 8, 8, 8), ("conv4 16x16x16->8x8 k5 (256 in)", 0, 5, 2, 256, 16, 16, 16, 8, 8),
+         ("conv2 16x64x64->32x32 k5", 0, 5, 2, 256, 16, 64, 64, 32, 32)]
+for (name, kind, k, s, c, B, hi, wi, ho, wo) in CASES:
+    m = layers.Conv(c, 256, k, s).to(dev)
+    st = m._state
+    st.refresh(m.weight)
+    x, y = bf(B, c, hi, wi), Fn.empty_nhwc(B, 256, ho, wo, torch.bfloat16, dev)
+    d = st.desc(B, hi, wi, ho, wo)
+    for _ in range(3):
+        L.conv_forward(d, P(x), None, P(st.w_direct), P(m.bias), 0, P(y), None, None, L.stream())
+    torch.cuda.synchronize()
+    buf = np.zeros((64, 16), dtype=np.uint64)
+    L.lib.lmsfc_debug_read_timeline(ctypes.c_void_p(buf.ctypes.data))
+    t0 = buf[:, 0][buf[:, 0] > 0].min()
+    print(f"== {name}")
+    for cta in (0, 1, 31, 63):
+        if buf[cta, 0] == 0:
+            continue
+        r = buf[cta]
+        print(f"  cta {cta:2d}: " + "  ".join(f"{NAMES[i]} {((int(r[i]) - int(t0)) / 1e3):.2f}" for i in (0, 1, 9, 2, 3, 10, 4, 5, 6, 7, 8) if r[i] >= t0))
+    print(f"  last exit over recorded CTAs: {(int(buf[:, 8].max()) - int(t0)) / 1e3:.2f} us")
