@@ -67,24 +67,34 @@ int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void
 int lmsfc_reparam_forward(const float* p, int64_t n, float bound, float pedestal, float* out_f32, void* out_bf16,
                           void* stream);
 int lmsfc_reparam_backward(const float* g_out, const float* p, int64_t n, float bound, float* g_p, void* stream);
+/* The same two maps over a device table of segments (every GDN layer of a model in one launch):
+ * table[s] = {param offset, n, out_f32 offset or -1, out_bf16 offset or -1, g_eff offset} (int64, offsets in
+ * elements from params / out_f32 / out_bf16 / g_eff); bounds[s] fp32; max_n = largest n. */
+int lmsfc_reparam_forward_multi(const float* params, const int64_t* table, const float* bounds, int nseg, int64_t max_n,
+                                float pedestal, float* out_f32, void* out_bf16, void* stream);
+int lmsfc_reparam_backward_multi(const float* g_eff, const float* params, const int64_t* table, const float* bounds,
+                                 int nseg, int64_t max_n, float* g_params, void* stream);
 
 /* ------------------------------------------------------------------ entropy models (entropy_models/entropy_models.py)
  * mode: 0 "noise" (:161-165), 1 "dequantize" (:167-176).  noise: injected U(-.5,.5) draw (parity
  * tests) or null -> in-kernel Philox keyed by (seed, offset [+ rng_state[1]]).  sum_ln (nullable):
- * += sum(ln likelihood), the rate term of losses/rate_distortion.py:52-55. */
+ * += sum(ln likelihood), the rate term of losses/rate_distortion.py:52-55.  y_hat_bf16 (nullable): bf16
+ * copy of y_hat, the operand of the next conv.  Backward: g_yhat (fp32) or g_yhat_bf16 (a dgrad output),
+ * either nullable. */
 int lmsfc_gc_forward(const float* y, const float* scales, const float* means, const float* noise, int64_t n, int mode,
                      float scale_bound, float lik_bound, uint64_t seed, uint64_t offset, const uint64_t* rng_state,
-                     float* y_hat, float* lik, float* sum_ln, void* stream);            /* :650-682 */
+                     float* y_hat, void* y_hat_bf16, float* lik, float* sum_ln, void* stream);   /* :650-682 */
 /* g_lik null -> g = rate_coef / lik (fused rate gradient).  g_yhat nullable.  g_means nullable. */
 int lmsfc_gc_backward(const float* y_hat, const float* scales, const float* means, const float* g_lik,
-                      const float* g_yhat, int64_t n, int mode, float scale_bound, float lik_bound, float rate_coef,
-                      float* g_y, float* g_scales, float* g_means, void* stream);
+                      const float* g_yhat, const void* g_yhat_bf16, int64_t n, int mode, float scale_bound,
+                      float lik_bound, float rate_coef, float* g_y, float* g_scales, float* g_means, void* stream);
 /* EntropyBottleneck (:436-516).  x [P][C] fp32 NHWC; params [C][58] packed per channel as
  * M0(3) b0(3) f0(3) | (M(9) b(3) f(3)) x3 | M4(3) b4(1); medians [C] (quantiles[:,0,1]) for mode 1. */
 int lmsfc_eb_forward(const float* x, const float* params, const float* medians, const float* noise, int64_t P, int C,
                      int mode, float lik_bound, uint64_t seed, uint64_t offset, const uint64_t* rng_state, float* y_hat,
-                     float* lik, float* sum_ln, void* stream);
-int lmsfc_eb_backward(const float* y_hat, const float* params, const float* g_lik, const float* g_yhat, int64_t P, int C,
+                     void* y_hat_bf16, float* lik, float* sum_ln, void* stream);
+int lmsfc_eb_backward(const float* y_hat, const float* params, const float* g_lik, const float* g_yhat,
+                      const void* g_yhat_bf16, int64_t P, int C,
                       int mode, float lik_bound, float rate_coef, float* g_x, float* g_params, void* stream);
 /* aux loss (:431-434): loss += sum |logits(quantiles) - target| ; g_quantiles [C][3] written. */
 int lmsfc_eb_aux_loss(const float* params, const float* quantiles, const float* target, int C, float* loss,

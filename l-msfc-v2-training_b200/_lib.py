@@ -34,10 +34,12 @@ _SIGS = {
     "lmsfc_gdn_backward": [P, P, P, P, c_int, c_int64, c_int, P, P, P, P, P, P],
     "lmsfc_reparam_forward": [P, c_int64, c_float, c_float, P, P, P],
     "lmsfc_reparam_backward": [P, P, c_int64, c_float, P, P],
-    "lmsfc_gc_forward": [P, P, P, P, c_int64, c_int, c_float, c_float, c_uint64, c_uint64, P, P, P, P, P],
-    "lmsfc_gc_backward": [P, P, P, P, P, c_int64, c_int, c_float, c_float, c_float, P, P, P, P],
-    "lmsfc_eb_forward": [P, P, P, P, c_int64, c_int, c_int, c_float, c_uint64, c_uint64, P, P, P, P, P],
-    "lmsfc_eb_backward": [P, P, P, P, c_int64, c_int, c_int, c_float, c_float, P, P, P],
+    "lmsfc_reparam_forward_multi": [P, P, P, c_int, c_int64, c_float, P, P, P],
+    "lmsfc_reparam_backward_multi": [P, P, P, P, c_int, c_int64, P, P],
+    "lmsfc_gc_forward": [P, P, P, P, c_int64, c_int, c_float, c_float, c_uint64, c_uint64, P, P, P, P, P, P],
+    "lmsfc_gc_backward": [P, P, P, P, P, P, c_int64, c_int, c_float, c_float, c_float, P, P, P, P],
+    "lmsfc_eb_forward": [P, P, P, P, c_int64, c_int, c_int, c_float, c_uint64, c_uint64, P, P, P, P, P, P],
+    "lmsfc_eb_backward": [P, P, P, P, P, c_int64, c_int, c_int, c_float, c_float, P, P, P],
     "lmsfc_eb_aux_loss": [P, P, P, c_int, P, P, P],
     "lmsfc_rng_advance": [P, P],
     "lmsfc_mse_forward_backward": [P, P, c_int64, c_float, P, P, P],

@@ -214,37 +214,51 @@ extern "C" int lmsfc_reparam_backward(const float* g_out, const float* p, int64_
   return reparam_bwd(g_out, p, n, bound, g_p, ST(stream));
 }
 
+extern "C" int lmsfc_reparam_forward_multi(const float* params, const int64_t* table, const float* bounds, int nseg,
+                                           int64_t max_n, float pedestal, float* out_f32, void* out_bf16, void* stream) {
+  LMSFC_CHECK_ARG(nseg == 0 || (params && table && bounds), "reparam_forward_multi: null operand");
+  return reparam_fwd_multi(params, table, bounds, nseg, max_n, pedestal, out_f32, (bf16*)out_bf16, ST(stream));
+}
+extern "C" int lmsfc_reparam_backward_multi(const float* g_eff, const float* params, const int64_t* table,
+                                            const float* bounds, int nseg, int64_t max_n, float* g_params, void* stream) {
+  LMSFC_CHECK_ARG(nseg == 0 || (g_eff && params && table && bounds && g_params), "reparam_backward_multi: null operand");
+  return reparam_bwd_multi(g_eff, params, table, bounds, nseg, max_n, g_params, ST(stream));
+}
+
 // ---------------------------------------------------------------- entropy models
 extern "C" int lmsfc_gc_forward(const float* y, const float* scales, const float* means, const float* noise, int64_t n,
                                 int mode, float scale_bound, float lik_bound, uint64_t seed, uint64_t offset,
-                                const uint64_t* rng_state, float* y_hat, float* lik, float* sum_ln, void* stream) {
+                                const uint64_t* rng_state, float* y_hat, void* y_hat_bf16, float* lik, float* sum_ln,
+                                void* stream) {
   LMSFC_CHECK_ARG(mode == 0 || mode == 1, "Invalid quantization mode: \"%d\"", mode);   // entropy_models.py:158-159
   LMSFC_CHECK_ARG(n == 0 || (y && scales && y_hat && lik), "gc_forward: null operand");
-  GcArgs a{y, scales, means, noise, y_hat, lik, sum_ln, n, mode, scale_bound, lik_bound, seed, offset, rng_state};
+  GcArgs a{y, scales, means, noise, y_hat, lik, sum_ln, (bf16*)y_hat_bf16, n, mode, scale_bound, lik_bound, seed, offset, rng_state};
   return gc_forward(a, ST(stream));
 }
 extern "C" int lmsfc_gc_backward(const float* y_hat, const float* scales, const float* means, const float* g_lik,
-                                 const float* g_yhat, int64_t n, int mode, float scale_bound, float lik_bound,
-                                 float rate_coef, float* g_y, float* g_scales, float* g_means, void* stream) {
+                                 const float* g_yhat, const void* g_yhat_bf16, int64_t n, int mode, float scale_bound,
+                                 float lik_bound, float rate_coef, float* g_y, float* g_scales, float* g_means,
+                                 void* stream) {
   LMSFC_CHECK_ARG(mode == 0 || mode == 1, "Invalid quantization mode: \"%d\"", mode);
   LMSFC_CHECK_ARG(n == 0 || (y_hat && scales && g_y && g_scales), "gc_backward: null operand");
-  GcBwdArgs a{y_hat, scales, means, g_lik, g_yhat, g_y, g_scales, g_means, n, mode, scale_bound, lik_bound, rate_coef};
+  GcBwdArgs a{y_hat, scales, means, g_lik, g_yhat, (const bf16*)g_yhat_bf16, g_y, g_scales, g_means, n, mode, scale_bound, lik_bound, rate_coef};
   return gc_backward(a, ST(stream));
 }
 extern "C" int lmsfc_eb_forward(const float* x, const float* params, const float* medians, const float* noise, int64_t P,
                                 int C, int mode, float lik_bound, uint64_t seed, uint64_t offset,
-                                const uint64_t* rng_state, float* y_hat, float* lik, float* sum_ln, void* stream) {
+                                const uint64_t* rng_state, float* y_hat, void* y_hat_bf16, float* lik, float* sum_ln,
+                                void* stream) {
   LMSFC_CHECK_ARG(mode == 0 || mode == 1, "Invalid quantization mode: \"%d\"", mode);
   LMSFC_CHECK_ARG(P == 0 || (x && params && y_hat && lik), "eb_forward: null operand");
   LMSFC_CHECK_ARG(mode == 0 || medians, "eb_forward: dequantize mode needs medians");
-  EbArgs a{x, params, medians, noise, y_hat, lik, sum_ln, P, C, mode, lik_bound, seed, offset, rng_state};
+  EbArgs a{x, params, medians, noise, y_hat, lik, sum_ln, (bf16*)y_hat_bf16, P, C, mode, lik_bound, seed, offset, rng_state};
   return eb_forward(a, ST(stream));
 }
 extern "C" int lmsfc_eb_backward(const float* y_hat, const float* params, const float* g_lik, const float* g_yhat,
-                                 int64_t P, int C, int mode, float lik_bound, float rate_coef, float* g_x, float* g_params,
+                                 const void* g_yhat_bf16, int64_t P, int C, int mode, float lik_bound, float rate_coef, float* g_x, float* g_params,
                                  void* stream) {
   LMSFC_CHECK_ARG(P == 0 || (y_hat && params && g_x && g_params), "eb_backward: null operand");
-  EbBwdArgs a{y_hat, params, g_lik, g_yhat, g_x, g_params, P, C, mode, lik_bound, rate_coef};
+  EbBwdArgs a{y_hat, params, g_lik, g_yhat, (const bf16*)g_yhat_bf16, g_x, g_params, P, C, mode, lik_bound, rate_coef};
   return eb_backward(a, ST(stream));
 }
 extern "C" int lmsfc_eb_aux_loss(const float* params, const float* quantiles, const float* target, int C, float* loss,

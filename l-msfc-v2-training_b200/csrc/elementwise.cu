@@ -273,6 +273,50 @@ int reparam_bwd(const float* g_out, const float* p, int64_t n, float bound, floa
   return LMSFC_OK;
 }
 
+// Batched form over a table of segments (all GDN layers of a model in ONE launch per direction).
+// table row s = {param offset, n, out_f32 offset | -1, out_bf16 offset | -1, g_eff offset}.
+__global__ void reparam_fwd_multi_kernel(const float* params, const int64_t* table, const float* bounds, float ped,
+                                         float* o32, __nv_bfloat16* o16) {
+  const int64_t* t = table + 5 * blockIdx.y;
+  const float* p = params + t[0];
+  const int64_t n = t[1], a32 = t[2], a16 = t[3];
+  const float bound = bounds[blockIdx.y];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = fmaxf(p[i], bound);
+    const float r = v * v - ped;
+    if (a32 >= 0) o32[a32 + i] = r;
+    if (a16 >= 0) o16[a16 + i] = __float2bfloat16(r);
+  }
+}
+__global__ void reparam_bwd_multi_kernel(const float* g_eff, const float* params, const int64_t* table,
+                                         const float* bounds, float* g_params) {
+  const int64_t* t = table + 5 * blockIdx.y;
+  const float* p = params + t[0];
+  float* gp = g_params + t[0];
+  const float* ge = g_eff + t[4];
+  const int64_t n = t[1];
+  const float bound = bounds[blockIdx.y];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = p[i];
+    const float g = ge[i] * 2.f * fmaxf(v, bound);
+    gp[i] += (v >= bound || g < 0.f) ? g : 0.f;
+  }
+}
+int reparam_fwd_multi(const float* params, const int64_t* table, const float* bounds, int nseg, int64_t max_n,
+                      float pedestal, float* out_f32, __nv_bfloat16* out_bf16, cudaStream_t s) {
+  if (nseg == 0) return LMSFC_OK;
+  reparam_fwd_multi_kernel<<<dim3(grid1d(max_n), nseg), TPB, 0, s>>>(params, table, bounds, pedestal, out_f32, out_bf16);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+int reparam_bwd_multi(const float* g_eff, const float* params, const int64_t* table, const float* bounds, int nseg,
+                      int64_t max_n, float* g_params, cudaStream_t s) {
+  if (nseg == 0) return LMSFC_OK;
+  reparam_bwd_multi_kernel<<<dim3(grid1d(max_n), nseg), TPB, 0, s>>>(g_eff, params, table, bounds, g_params);
+  LMSFC_LAUNCH_CHECK();
+  return LMSFC_OK;
+}
+
 // ---------------------------------------------------------------- small activation gradients
 __global__ void relu_bwd_kernel(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)

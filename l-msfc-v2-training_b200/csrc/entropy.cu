@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(256) gc_forward_kernel(GcArgs a) {
     const float L = std_cumulative((0.5f - v) / s) - std_cumulative((-0.5f - v) / s);
     const float lik = fmaxf(L, a.lik_bound);
     a.y_hat[i] = yh;
+    if (a.y_hat_bf16) a.y_hat_bf16[i] = __float2bfloat16(yh);
     a.lik[i] = lik;
     local += __logf(lik);
   }
@@ -88,7 +89,7 @@ __global__ void __launch_bounds__(256) gc_backward_kernel(GcBwdArgs a) {
     float gs = g * (tb * pb - ta * pa) / s;
     if (!(sraw >= a.scale_bound || gs < 0.f)) gs = 0.f;
     const float sgn = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);
-    const float gyh = a.g_yhat ? a.g_yhat[i] : 0.f;
+    const float gyh = a.g_yhat ? a.g_yhat[i] : (a.g_yhat_bf16 ? __bfloat162float(a.g_yhat_bf16[i]) : 0.f);
     if (a.mode == QUANT_NOISE) {
       a.g_y[i] = gyh + gv * sgn;
       if (a.g_means) a.g_means[i] = -gv * sgn;
@@ -208,6 +209,7 @@ __global__ void __launch_bounds__(128) eb_forward_kernel(EbArgs a) {
       const float up = eb_logits<false>(ch, yh + 0.5f, nullptr);
       const float lik = fmaxf(eb_lik_raw(lo, up), a.lik_bound);
       a.y_hat[i] = yh;
+      if (a.y_hat_bf16) a.y_hat_bf16[i] = __float2bfloat16(yh);
       a.lik[i] = lik;
       local += __logf(lik);
     }
@@ -281,7 +283,7 @@ __global__ void __launch_bounds__(128) eb_backward_kernel(EbBwdArgs a) {
     const float gl = -g * sd * sl * (1.f - sl) * sg;
     float gx = eb_logits_bwd(ch, tl, yh - 0.5f, gl, G);
     gx += eb_logits_bwd(ch, tu, yh + 0.5f, gu, G);
-    const float gyh = a.g_yhat ? a.g_yhat[i] : 0.f;
+    const float gyh = a.g_yhat ? a.g_yhat[i] : (a.g_yhat_bf16 ? __bfloat162float(a.g_yhat_bf16[i]) : 0.f);
     a.g_x[i] = (a.mode == QUANT_NOISE) ? gx + gyh : 0.f;
   }
   // chain through softplus / tanh of the raw parameters, then one atomic per (channel, param)

@@ -9,6 +9,7 @@ enum : int { QUANT_NOISE = 0, QUANT_DEQUANTIZE = 1 };
 struct GcArgs {
   const float *y, *scales, *means, *noise;   // means / noise nullable
   float *y_hat, *lik, *sum_ln;               // sum_ln nullable (atomicAdd of sum ln L)
+  __nv_bfloat16* y_hat_bf16;                 // nullable: bf16 copy of y_hat (operand of the next conv)
   int64_t n;
   int mode;
   float scale_bound, lik_bound;
@@ -17,6 +18,7 @@ struct GcArgs {
 };
 struct GcBwdArgs {
   const float *y_hat, *scales, *means, *g_lik, *g_yhat;   // means / g_lik / g_yhat nullable
+  const __nv_bfloat16* g_yhat_bf16;                       // alternative to g_yhat (dgrad output), nullable
   float *g_y, *g_scales, *g_means;                        // g_means nullable
   int64_t n;
   int mode;
@@ -25,6 +27,7 @@ struct GcBwdArgs {
 struct EbArgs {
   const float *x, *params, *medians, *noise;  // x: [P][C] (NHWC); params: [C][58]
   float *y_hat, *lik, *sum_ln;
+  __nv_bfloat16* y_hat_bf16;                  // nullable
   int64_t P;
   int C, mode;
   float lik_bound;
@@ -33,6 +36,7 @@ struct EbArgs {
 };
 struct EbBwdArgs {
   const float *y_hat, *params, *g_lik, *g_yhat;
+  const __nv_bfloat16* g_yhat_bf16;           // alternative to g_yhat, nullable
   float *g_x, *g_params;                      // g_params [C][58], accumulated with atomicAdd
   int64_t P;
   int C, mode;
@@ -58,6 +62,10 @@ int gdn_t(const __nv_bfloat16* gy, const __nv_bfloat16* x, const __nv_bfloat16* 
 int reparam_fwd(const float* p, int64_t n, float bound, float pedestal, float* out_f32, __nv_bfloat16* out_bf16,
                 cudaStream_t s);
 int reparam_bwd(const float* g_out, const float* p, int64_t n, float bound, float* g_p, cudaStream_t s);
+int reparam_fwd_multi(const float* params, const int64_t* table, const float* bounds, int nseg, int64_t max_n,
+                      float pedestal, float* out_f32, __nv_bfloat16* out_bf16, cudaStream_t s);
+int reparam_bwd_multi(const float* g_eff, const float* params, const int64_t* table, const float* bounds, int nseg,
+                      int64_t max_n, float* g_params, cudaStream_t s);
 int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream_t s);
 int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, cudaStream_t s);
 int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, int64_t n, int relu, __nv_bfloat16* g_out,

@@ -45,8 +45,9 @@ class EntropyModel(nn.Module):
         self.register_buffer("_offset", torch.IntTensor())
         self.register_buffer("_quantized_cdf", torch.IntTensor())
         self.register_buffer("_cdf_length", torch.IntTensor())
-        self.rng = None          # Fn.RNG, created lazily on the module's device
+        self.rng = None          # Fn.RNG, created lazily on the module's device (a model may share one)
         self.rng_offset = 0      # distinguishes the draws of different modules within one step
+        self.rng_auto_advance = True   # False when the owning model advances a shared RNG once per step
 
     @property
     def offset(self):
@@ -209,9 +210,21 @@ class EntropyBottleneck(EntropyModel):
     def _get_medians(self):
         return self.quantiles[:, :, 1:2]
 
+    # column ranges of the 14 reference-named parameters inside the per-channel block of 58 floats
+    PACK_COLUMNS = (("_matrix0", 0, 3), ("_bias0", 3, 6), ("_factor0", 6, 9),
+                    ("_matrix1", 9, 18), ("_bias1", 18, 21), ("_factor1", 21, 24),
+                    ("_matrix2", 24, 33), ("_bias2", 33, 36), ("_factor2", 36, 39),
+                    ("_matrix3", 39, 48), ("_bias3", 48, 51), ("_factor3", 51, 54),
+                    ("_matrix4", 54, 57), ("_bias4", 57, 58))
+    PACK_WIDTH = 58
+
     def packed_parameters(self):
-        """[C,58] per-channel parameter block read by the kernels (autograd routes its gradient
-        back onto the 13 reference-named parameters)."""
+        """[C,58] per-channel parameter block read by the kernels.  Once the model's ParamArena is
+        built the 14 reference-named parameters ARE strided views of that block (and their .grad of
+        `_packed_grad`), so this is free; stand-alone modules concatenate (autograd routes the
+        gradient back)."""
+        if getattr(self, "_packed", None) is not None:
+            return self._packed
         C = self.channels
         parts = []
         for i in range(len(self.filters) + 1):
@@ -293,14 +306,14 @@ class EntropyBottleneck(EntropyModel):
         medians = self.quantiles[:, 0, 1].detach().contiguous()
         out, lik = Fn.eb_apply(x4, self.packed_parameters(), medians, n4, mode,
                                self.likelihood_bound if self.use_likelihood_bound else 0.0,
-                               self._rng(x.device) if noise is None and training else None, self.rng_offset)
-        if noise is None and training:
+                               self._rng(x.device) if noise is None and training else None, self.rng_offset,
+                               packed_grad=getattr(self, "_packed_grad", None))
+        if noise is None and training and self.rng_auto_advance:
             self.rng.advance()
-        sum_ln = getattr(lik, Fn._SUM_LN_ATTR, None)
-        out, lik = out.reshape(shape), lik.reshape(shape)
-        if sum_ln is not None:
-            setattr(lik, Fn._SUM_LN_ATTR, sum_ln)
-        return out, lik
+        out_r, lik_r = out.reshape(shape), lik.reshape(shape)
+        b16 = getattr(out, Fn._BF16_ATTR)
+        setattr(out_r, Fn._BF16_ATTR, b16.reshape(shape))
+        return out_r, Fn.carry_attrs(lik, lik_r)
 
     @staticmethod
     def _build_indexes(size):
@@ -403,13 +416,12 @@ class GaussianConditional(EntropyModel):
         out, lik = Fn.gc_apply(as4(inputs), as4(scales), as4(means), as4(noise), mode, self.scale_bound_value,
                                self.likelihood_bound if self.use_likelihood_bound else 0.0,
                                self._rng(inputs.device) if noise is None and training else None, self.rng_offset)
-        if noise is None and training:
+        if noise is None and training and self.rng_auto_advance:
             self.rng.advance()
-        sum_ln = getattr(lik, Fn._SUM_LN_ATTR, None)
         if out.shape != shape:
-            out, lik = out.reshape(shape), lik.reshape(shape)
-            if sum_ln is not None:
-                setattr(lik, Fn._SUM_LN_ATTR, sum_ln)
+            out_r, lik_r = out.reshape(shape), lik.reshape(shape)
+            setattr(out_r, Fn._BF16_ATTR, getattr(out, Fn._BF16_ATTR).reshape(shape))
+            out, lik = out_r, Fn.carry_attrs(lik, lik_r)
         return out, lik
 
     def build_indexes(self, scales):

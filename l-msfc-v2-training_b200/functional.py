@@ -189,10 +189,17 @@ PEDESTAL = 2.0 ** -36   # reparam_offset**2, compressai/ops/parametrizers.py:47-
 
 
 class GDNState:
+    """Per-layer GDN state.  Stand-alone modules reparametrise beta / gamma on every call; inside a
+    model's ParamArena the effective values (`beta_eff` fp32, `gamma_bf` bf16) and the buffers that
+    receive their gradients (`g_beta_eff`, `g_gamma_eff`) are persistent views filled for ALL GDN
+    layers by one batched launch per direction (ParamArena.prepare / finish_backward)."""
+
     def __init__(self, C, inverse, beta_bound, gamma_bound):
         self.C, self.inverse = C, bool(inverse)
         self.beta_bound, self.gamma_bound = float(beta_bound), float(gamma_bound)
         self.grad_ready = None
+        self.arena = None
+        self.beta_eff = self.gamma_bf = self.g_beta_eff = self.g_gamma_eff = None
 
 
 class _GDNFn(torch.autograd.Function):
@@ -204,11 +211,15 @@ class _GDNFn(torch.autograd.Function):
         B, C, H, W = x.shape
         P = B * H * W
         dev, st = x.device, stream()
-        beta_eff = torch.empty(C, dtype=F32, device=dev)
-        gamma_eff = torch.empty((C, C), dtype=F32, device=dev)
-        gamma_bf = torch.empty((C, C), dtype=BF16, device=dev)
-        L.reparam_forward(ptr(beta), C, state.beta_bound, PEDESTAL, ptr(beta_eff), None, st)
-        L.reparam_forward(ptr(gamma), C * C, state.gamma_bound, PEDESTAL, ptr(gamma_eff), ptr(gamma_bf), st)
+        arena = state.arena
+        if arena is not None:
+            arena.ensure_prepared(beta, gamma)
+            beta_eff, gamma_bf = state.beta_eff, state.gamma_bf
+        else:
+            beta_eff = torch.empty(C, dtype=F32, device=dev)
+            gamma_bf = torch.empty((C, C), dtype=BF16, device=dev)
+            L.reparam_forward(ptr(beta), C, state.beta_bound, PEDESTAL, ptr(beta_eff), None, st)
+            L.reparam_forward(ptr(gamma), C * C, state.gamma_bound, PEDESTAL, None, ptr(gamma_bf), st)
         x2 = torch.empty_like(x)
         y = torch.empty_like(x)
         rn = torch.empty_like(x)
@@ -228,16 +239,23 @@ class _GDNFn(torch.autograd.Function):
         x2 = torch.empty_like(x)
         t = torch.empty_like(x)
         gx = torch.empty_like(x)
-        g_gamma_eff = torch.zeros((C, C), dtype=F32, device=dev)
-        g_beta_eff = torch.zeros(C, dtype=F32, device=dev)
+        arena = state.arena
+        if arena is not None:
+            g_gamma_eff, g_beta_eff = state.g_gamma_eff, state.g_beta_eff
+        else:
+            g_gamma_eff = torch.zeros((C, C), dtype=F32, device=dev)
+            g_beta_eff = torch.zeros(C, dtype=F32, device=dev)
         L.gdn_backward(ptr(gy), ptr(x), ptr(rn), ptr(gamma_bf), int(state.inverse), P, C, ptr(x2), ptr(t), ptr(gx),
                        ptr(g_gamma_eff), ptr(g_beta_eff), st)
         beta, gamma = ctx.beta, ctx.gamma
-        gb, gg = grad_view(beta), grad_view(gamma)
-        L.reparam_backward(ptr(g_beta_eff), ptr(beta), C, state.beta_bound, ptr(gb), st)
-        L.reparam_backward(ptr(g_gamma_eff), ptr(gamma), C * C, state.gamma_bound, ptr(gg), st)
-        if state.grad_ready is not None:
-            state.grad_ready([beta, gamma])
+        if arena is not None:
+            arena.queue_finish_backward()       # one batched reparam-backward at the end of this backward pass
+        else:
+            gb, gg = grad_view(beta), grad_view(gamma)
+            L.reparam_backward(ptr(g_beta_eff), ptr(beta), C, state.beta_bound, ptr(gb), st)
+            L.reparam_backward(ptr(g_gamma_eff), ptr(gamma), C * C, state.gamma_bound, ptr(gg), st)
+            if state.grad_ready is not None:
+                state.grad_ready([beta, gamma])
         return (gx if ctx.needs_input_grad[0] else None), None, None, None
 
 
@@ -267,41 +285,73 @@ class RNG:
         L.rng_advance(ptr(self.state), stream())
 
 
-_SUM_LN_ATTR = "_lmsfc_sum_ln"
+_SUM_LN_ATTR = "_lmsfc_sum_ln"        # [1] fp32: sum(ln likelihood), reduced inside the likelihood kernel
+_BF16_ATTR = "_lmsfc_bf16"            # bf16 copy of the quantised latent (operand of the next conv)
+_RATE_ATTR = "_lmsfc_rate_hook"       # RateHook shared between the likelihood op and the RD loss
+_CARRIED = (_SUM_LN_ATTR, _BF16_ATTR, _RATE_ATTR)
+
+
+def carry_attrs(src, dst):
+    """Views created by reshape() drop Python attributes: copy the side-band ones over."""
+    for a in _CARRIED:
+        v = getattr(src, a, None)
+        if v is not None:
+            setattr(dst, a, v)
+    return dst
+
+
+class RateHook:
+    """Lets RateDistortionLoss hand d loss / d likelihood = coef / L to the likelihood op's own
+    backward kernel (no reciprocal / scale passes, no gradient tensor)."""
+    __slots__ = ("coef",)
+
+    def __init__(self):
+        self.coef = None
 
 
 class _GCFn(torch.autograd.Function):
-    """GaussianConditional.forward, entropy_models.py:650-682."""
+    """GaussianConditional.forward, entropy_models.py:650-682.
+    Returns (y_hat fp32, likelihood fp32, y_hat bf16)."""
 
     @staticmethod
     def forward(ctx, y, scales, means, noise, mode, scale_bound, lik_bound, rng, offset):
         n = y.numel()
         y_hat = torch.empty_like(y)
+        y_hat_b = torch.empty_like(y, dtype=BF16)
         lik = torch.empty_like(y)
         sum_ln = torch.zeros(1, dtype=F32, device=y.device)
         L.gc_forward(ptr(y), ptr(scales), ptr(means), ptr(noise), n, mode, scale_bound, lik_bound,
                      rng.seed if rng is not None else 0, offset, ptr(rng.state) if rng is not None else None,
-                     ptr(y_hat), ptr(lik), ptr(sum_ln), stream())
+                     ptr(y_hat), ptr(y_hat_b), ptr(lik), ptr(sum_ln), stream())
         ctx.save_for_backward(y_hat, scales, means)
         ctx.cfg = (mode, scale_bound, lik_bound)
+        ctx.hook = RateHook()
+        ctx.set_materialize_grads(False)      # unused outputs arrive as None, not as zero tensors
         setattr(lik, _SUM_LN_ATTR, sum_ln)
-        return y_hat, lik
+        setattr(lik, _RATE_ATTR, ctx.hook)
+        return y_hat, lik, y_hat_b
 
     @staticmethod
-    def backward(ctx, g_yhat, g_lik):
+    def backward(ctx, g_yhat, g_lik, g_yhat_b):
         y_hat, scales, means = ctx.saved_tensors
         mode, scale_bound, lik_bound = ctx.cfg
         n = y_hat.numel()
         g_y = torch.empty_like(y_hat)
         g_s = torch.empty_like(y_hat)
         g_m = torch.empty_like(y_hat) if means is not None else None
-        if g_lik is None:
+        rate_coef, ctx.hook.coef = (ctx.hook.coef or 0.0), None
+        if g_lik is None and rate_coef == 0.0:
             g_lik = torch.zeros_like(y_hat)
-        g_lik = g_lik.to(dtype=F32).contiguous(memory_format=CL)
+        if g_lik is not None:
+            g_lik = g_lik.to(dtype=F32).contiguous(memory_format=CL)
+        if g_yhat is not None and g_yhat_b is not None:
+            g_yhat, g_yhat_b = g_yhat.to(F32) + g_yhat_b.to(F32), None
         if g_yhat is not None:
             g_yhat = g_yhat.to(dtype=F32).contiguous(memory_format=CL)
-        L.gc_backward(ptr(y_hat), ptr(scales), ptr(means), ptr(g_lik), ptr(g_yhat), n, mode, scale_bound, lik_bound,
-                      0.0, ptr(g_y), ptr(g_s), ptr(g_m), stream())
+        if g_yhat_b is not None:
+            g_yhat_b = g_yhat_b.to(dtype=BF16).contiguous(memory_format=CL)
+        L.gc_backward(ptr(y_hat), ptr(scales), ptr(means), ptr(g_lik), ptr(g_yhat), ptr(g_yhat_b), n, mode, scale_bound,
+                      lik_bound, rate_coef, ptr(g_y), ptr(g_s), ptr(g_m), stream())
         return g_y, g_s, g_m, None, None, None, None, None, None
 
 
@@ -312,48 +362,66 @@ def gc_apply(y, scales, means, noise, mode, scale_bound, lik_bound, rng=None, of
         means = nhwc(means, F32)
     if noise is not None:
         noise = nhwc(noise, F32)
-    return _GCFn.apply(y, scales, means, noise, _mode_id(mode), float(scale_bound), float(lik_bound), rng, offset)
+    out, lik, out_b = _GCFn.apply(y, scales, means, noise, _mode_id(mode), float(scale_bound), float(lik_bound), rng, offset)
+    setattr(out, _BF16_ATTR, out_b)
+    return out, lik
 
 
 class _EBFn(torch.autograd.Function):
-    """EntropyBottleneck.forward, entropy_models.py:436-516, on the NHWC view [P][C]."""
+    """EntropyBottleneck.forward, entropy_models.py:436-516, on the NHWC view [P][C].
+    Returns (y_hat fp32, likelihood fp32, y_hat bf16).  `packed_grad` (optional, [C,58] fp32 view of
+    the gradient arena): the backward kernel accumulates the parameter gradients straight into it."""
 
     @staticmethod
-    def forward(ctx, x, packed, medians, noise, mode, lik_bound, rng, offset):
+    def forward(ctx, x, packed, medians, noise, mode, lik_bound, rng, offset, packed_grad):
         B, C, H, W = x.shape
         P = B * H * W
         y_hat = torch.empty_like(x)
+        y_hat_b = torch.empty_like(x, dtype=BF16)
         lik = torch.empty_like(x)
         sum_ln = torch.zeros(1, dtype=F32, device=x.device)
         L.eb_forward(ptr(x), ptr(packed), ptr(medians), ptr(noise), P, C, mode, lik_bound,
                      rng.seed if rng is not None else 0, offset, ptr(rng.state) if rng is not None else None,
-                     ptr(y_hat), ptr(lik), ptr(sum_ln), stream())
+                     ptr(y_hat), ptr(y_hat_b), ptr(lik), ptr(sum_ln), stream())
         ctx.save_for_backward(y_hat, packed)
         ctx.cfg = (mode, lik_bound, P, C)
+        ctx.packed_grad = packed_grad
+        ctx.hook = RateHook()
+        ctx.set_materialize_grads(False)      # unused outputs arrive as None, not as zero tensors
         setattr(lik, _SUM_LN_ATTR, sum_ln)
-        return y_hat, lik
+        setattr(lik, _RATE_ATTR, ctx.hook)
+        return y_hat, lik, y_hat_b
 
     @staticmethod
-    def backward(ctx, g_yhat, g_lik):
+    def backward(ctx, g_yhat, g_lik, g_yhat_b):
         y_hat, packed = ctx.saved_tensors
         mode, lik_bound, P, C = ctx.cfg
         g_x = torch.empty_like(y_hat)
-        g_p = torch.zeros_like(packed)
-        if g_lik is None:
+        g_p = ctx.packed_grad if ctx.packed_grad is not None else torch.zeros_like(packed)
+        rate_coef, ctx.hook.coef = (ctx.hook.coef or 0.0), None
+        if g_lik is None and rate_coef == 0.0:
             g_lik = torch.zeros_like(y_hat)
-        g_lik = g_lik.to(dtype=F32).contiguous(memory_format=CL)
+        if g_lik is not None:
+            g_lik = g_lik.to(dtype=F32).contiguous(memory_format=CL)
+        if g_yhat is not None and g_yhat_b is not None:
+            g_yhat, g_yhat_b = g_yhat.to(F32) + g_yhat_b.to(F32), None
         if g_yhat is not None:
             g_yhat = g_yhat.to(dtype=F32).contiguous(memory_format=CL)
-        L.eb_backward(ptr(y_hat), ptr(packed), ptr(g_lik), ptr(g_yhat), P, C, mode, lik_bound, 0.0, ptr(g_x), ptr(g_p),
-                      stream())
-        return g_x, g_p, None, None, None, None, None, None
+        if g_yhat_b is not None:
+            g_yhat_b = g_yhat_b.to(dtype=BF16).contiguous(memory_format=CL)
+        L.eb_backward(ptr(y_hat), ptr(packed), ptr(g_lik), ptr(g_yhat), ptr(g_yhat_b), P, C, mode, lik_bound, rate_coef,
+                      ptr(g_x), ptr(g_p), stream())
+        return g_x, (None if ctx.packed_grad is not None else g_p), None, None, None, None, None, None, None
 
 
-def eb_apply(x, packed, medians, noise, mode, lik_bound, rng=None, offset=0):
+def eb_apply(x, packed, medians, noise, mode, lik_bound, rng=None, offset=0, packed_grad=None):
     x = nhwc(x, F32)
     if noise is not None:
         noise = nhwc(noise, F32)
-    return _EBFn.apply(x, packed.contiguous(), medians, noise, _mode_id(mode), float(lik_bound), rng, offset)
+    out, lik, out_b = _EBFn.apply(x, packed.contiguous(), medians, noise, _mode_id(mode), float(lik_bound), rng, offset,
+                                  packed_grad)
+    setattr(out, _BF16_ATTR, out_b)
+    return out, lik
 
 
 class _EBAuxFn(torch.autograd.Function):
@@ -424,14 +492,22 @@ class _RDLossFn(torch.autograd.Function):
         coef_t = _const_tensor(tuple(coef), dev)
         out = torch.empty(3, dtype=F32, device=dev)
         L.loss_finalize(ptr(accum), ptr(coef_t), n_lik, n_lev, lmbda_scale, ptr(out), st)
+        # likelihoods produced by the fused entropy kernels take d loss / d L = rate_c / L inside their
+        # own backward (RateHook); any other likelihood tensor gets an explicit gradient
+        ctx.fused = []
+        for lk in liks:
+            hook = getattr(lk, _RATE_ATTR, None)
+            ctx.fused.append(hook is not None)
+            if hook is not None:
+                hook.coef = rate_c
         ctx.grads, ctx.rate_c, ctx.n_lev = grads, rate_c, n_lev
-        ctx.save_for_backward(*liks)
+        ctx.save_for_backward(*[lk for lk, f in zip(liks, ctx.fused) if not f])
         return out[2], out[0], out[1]
 
     @staticmethod
     def backward(ctx, g_loss, g_bpp, g_mse):
-        liks = ctx.saved_tensors
-        g_liks = [ctx.rate_c / lk for lk in liks]
+        plain = iter(ctx.saved_tensors)
+        g_liks = [None if f else ctx.rate_c / next(plain) for f in ctx.fused]
         return (None, None, None, None, None, *ctx.grads, *([None] * ctx.n_lev), *g_liks)
 
 

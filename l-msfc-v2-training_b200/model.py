@@ -53,6 +53,12 @@ class LMSFC(nn.Module):
         g_s.up2 = Deconv(N, Fc)
         self.g_s = g_s
         self.arena = None
+        self.entropy_bottleneck.rng_auto_advance = False
+        self.gaussian_conditional.rng_auto_advance = False
+
+    def _share_rng(self, device):
+        eb, gc = self.entropy_bottleneck, self.gaussian_conditional
+        gc.rng = eb._rng(device)
 
     # ------------------------------------------------------------------ forward
     def forward(self, feats, noise_z=None, noise_y=None):
@@ -60,6 +66,7 @@ class LMSFC(nn.Module):
         the U(-.5,.5) draws for parity tests; RNG order is EB then GC (google.py:295-297)."""
         lv = self.spec.levels
         p2, p3, p4, p5 = (Fn.nhwc(feats[k], Fn.BF16) for k in lv)
+        self._share_rng(p2.device)
         a, s = self.g_a, self.g_s
         e2 = a.gdn2(a.conv2(p2))
         e3 = a.gdn3(a.conv3(e2, p3))
@@ -69,11 +76,13 @@ class LMSFC(nn.Module):
         z2 = self.h_a["2"](z1, relu=True)
         z, _ = self.h_a["4"](z2, latent_head=True)
         z_hat, z_lik = self.entropy_bottleneck(z, noise=noise_z)
-        t = self.h_s["0"](z_hat.to(Fn.BF16), relu=True, out_hw=z2.shape[2:])
+        t = self.h_s["0"](getattr(z_hat, Fn._BF16_ATTR), relu=True, out_hw=z2.shape[2:])
         t = self.h_s["2"](t, relu=True, out_hw=y.shape[2:])
         scales, _ = self.h_s["4"](t, relu=True, latent_head=True)
         y_hat, y_lik = self.gaussian_conditional(y, scales, noise=noise_y)
-        d5 = s.igdn5(s.up5(y_hat.to(Fn.BF16), out_hw=p5.shape[2:]))
+        if self.training and noise_z is None and noise_y is None:
+            self.entropy_bottleneck.rng.advance()      # ONE shared counter bump per step (EB and GC share the RNG)
+        d5 = s.igdn5(s.up5(getattr(y_hat, Fn._BF16_ATTR), out_hw=p5.shape[2:]))
         p5h = s.head5(d5)
         d4 = s.igdn4(s.up4(d5, out_hw=p4.shape[2:]))
         p4h = s.head4(d4)
@@ -146,8 +155,17 @@ class ParamArena:
     """Flat fp32 storage for parameters / gradients (+ one bf16 shadow block).
 
     "net" holds every parameter except `*.quantiles`, "aux" holds those -- the split of
-    compressai/optimizers/net_aux.py:46-57.  Every parameter keeps its logical shape and strides
-    (conv weights stay GEMM-layout permuted views), only its storage moves."""
+    compressai/optimizers/net_aux.py:46-57.  Every parameter keeps its logical shape (conv weights
+    stay GEMM-layout permuted views), only its storage moves.  Physical order of the net arena:
+
+        [GDN beta/gamma of every layer] [EntropyBottleneck blocks, C x 58 interleaved] [the rest]
+
+    * the EntropyBottleneck's 14 reference-named parameters become strided views of the per-channel
+      block of 58 floats the kernels read, and their .grad of the block the backward kernel writes;
+    * the GDN group is reparametrised (forward) and its gradient mapped back (backward) by ONE
+      batched launch each per step; its "effective" gradient scratch sits behind the parameter
+      gradients in the same allocation so one fill zeroes everything.
+    """
 
     ALIGN = 64   # floats: 256-byte aligned slices (TMA bases, float4 kernels)
 
@@ -157,33 +175,99 @@ class ParamArena:
             raise RuntimeError("build_arena(): move the model to a CUDA device first (no CPU fallback)")
         dev = named[0][1].device
         self.device = dev
-        self.net = [(n, p) for n, p in named if not n.endswith(".quantiles")]
+        self.model = model
+        name_of = {id(p): n for n, p in named}
+        gdns = [m for m in model.modules() if isinstance(m, GDN)]
+        ebs = [m for m in model.modules() if isinstance(m, EntropyBottleneck)]
+        gdn_ids = {id(p) for m in gdns for p in (m.beta, m.gamma)}
+        eb_ids = {id(getattr(m, pn)) for m in ebs for pn, _, _ in m.PACK_COLUMNS}
+        rest = [(n, p) for n, p in named if id(p) not in gdn_ids and id(p) not in eb_ids and not n.endswith(".quantiles")]
         self.aux = [(n, p) for n, p in named if n.endswith(".quantiles")]
         self.offsets = {}
-
-        def pack(group):
-            off = 0
-            for n, p in group:
-                self.offsets[n] = off
+        # ---- plan the net arena
+        off = 0
+        plan = []            # (name, param, offset, shape, stride)
+        gdn_plan = []
+        for m in gdns:
+            for p in (m.beta, m.gamma):
+                plan.append((name_of[id(p)], p, off, p.shape, p.stride()))
+                gdn_plan.append((m, p, off))
                 off += _round_up(p.numel(), self.ALIGN)
-            flat = torch.zeros(max(off, self.ALIGN), dtype=torch.float32, device=dev)
-            grad = torch.zeros_like(flat)
-            for n, p in group:
-                o = self.offsets[n]
-                view = flat.as_strided(p.shape, p.stride(), o)
+        eb_blocks = []
+        for m in ebs:
+            C, W = m.channels, m.PACK_WIDTH
+            eb_blocks.append((m, off))
+            for pn, a, b in m.PACK_COLUMNS:
+                p = getattr(m, pn)
+                cols = p.shape[2]
+                plan.append((name_of[id(p)], p, off + a, p.shape, (W, cols, 1)))
+            off += _round_up(C * W, self.ALIGN)
+        for n, p in rest:
+            plan.append((n, p, off, p.shape, p.stride()))
+            off += _round_up(p.numel(), self.ALIGN)
+        n_net = max(off, self.ALIGN)
+        # ---- effective-gradient scratch of the GDN group behind the parameter gradients
+        g_off, o32, o16 = n_net, 0, 0
+        rows, bounds = [], []
+        for m, p, poff in gdn_plan:
+            is_beta = p is m.beta
+            rows.append([poff, p.numel(), o32 if is_beta else -1, -1 if is_beta else o16, g_off - 0])
+            bounds.append(m._state.beta_bound if is_beta else m._state.gamma_bound)
+            if is_beta:
+                o32 += _round_up(p.numel(), self.ALIGN)
+            else:
+                o16 += _round_up(p.numel(), self.ALIGN)
+            g_off += _round_up(p.numel(), self.ALIGN)
+        with torch.no_grad():
+            self.net_params = torch.zeros(n_net, dtype=torch.float32, device=dev)
+            self._grads_all = torch.zeros(g_off, dtype=torch.float32, device=dev)
+            self.net_grads = self._grads_all[:n_net]
+            self.net = []
+            for n, p, o, shape, stride in plan:
+                self.offsets[n] = o
+                view = self.net_params.as_strided(shape, stride, o)
                 view.copy_(p.data)
                 p.data = view
-                p.grad = grad.as_strided(p.shape, p.stride(), o)
-            return flat, grad
-
-        with torch.no_grad():
-            self.net_params, self.net_grads = pack(self.net)
-            self.aux_params, self.aux_grads = pack(self.aux)
+                p.grad = self.net_grads.as_strided(shape, stride, o)
+                self.net.append((n, p))
+            aoff = 0
+            for n, p in self.aux:
+                self.offsets[n] = aoff
+                aoff += _round_up(p.numel(), self.ALIGN)
+            self.aux_params = torch.zeros(max(aoff, self.ALIGN), dtype=torch.float32, device=dev)
+            self.aux_grads = torch.zeros_like(self.aux_params)
+            for n, p in self.aux:
+                o = self.offsets[n]
+                view = self.aux_params.as_strided(p.shape, p.stride(), o)
+                view.copy_(p.data)
+                p.data = view
+                p.grad = self.aux_grads.as_strided(p.shape, p.stride(), o)
+        for m, o in eb_blocks:
+            C, W = m.channels, m.PACK_WIDTH
+            m._packed = self.net_params[o:o + C * W].view(C, W)
+            m._packed_grad = self.net_grads[o:o + C * W].view(C, W)
+        # ---- GDN group: effective values, gradient scratch, segment table
+        self.gdn_layers = gdns
+        self.eff32 = torch.zeros(max(o32, 1), dtype=torch.float32, device=dev)
+        self.eff16 = torch.zeros(max(o16, 1), dtype=torch.bfloat16, device=dev)
+        self.gdn_table = torch.tensor(rows, dtype=torch.int64, device=dev).reshape(-1, 5)
+        self.gdn_bounds = torch.tensor(bounds, dtype=torch.float32, device=dev)
+        self.gdn_max_n = max([r[1] for r in rows], default=0)
+        for (m, p, poff), r in zip(gdn_plan, rows):
+            st, C = m._state, m.in_channels
+            st.arena = self
+            if p is m.beta:
+                st.beta_eff = self.eff32[r[2]:r[2] + C]
+                st.g_beta_eff = self._grads_all[r[4]:r[4] + C]
+            else:
+                st.gamma_bf = self.eff16[r[3]:r[3] + C * C].view(C, C)
+                st.g_gamma_eff = self._grads_all[r[4]:r[4] + C * C].view(C, C)
+        self._gdn_versions = None
+        self._finish_queued = False
+        # ---- bf16 GEMM operands of the conv weights: slices of one shadow of the whole arena
         self.net_bf16 = torch.empty(self.net_params.numel(), dtype=torch.bfloat16, device=dev)
-        self.model = model
         for m in model.conv_layers():
-            name = next(n for n, p in self.net if p is m.weight)
-            o = self.offsets[name]
+            o = self.offsets[name_of[id(m.weight)]]
             st = m._state
             st.w_direct = self.net_bf16[o:o + m.weight.numel()].view(st.D0, st.T, st.D1)
         self.refresh_shadows(cast=True)
@@ -191,20 +275,47 @@ class ParamArena:
     def names(self, group="net"):
         return [n for n, _ in (self.net if group == "net" else self.aux)]
 
-    def slice_of(self, name, what="grad"):
-        base = {"grad": self.net_grads, "param": self.net_params}[what]
-        p = dict(self.net)[name]
-        o = self.offsets[name]
-        return base[o:o + p.numel()]
-
+    # ------------------------------------------------------------------ derived operands
     def refresh_shadows(self, cast=True):
-        """bf16 GEMM operands of all conv weights = one cast of the flat arena (Adam writes the same
-        block in its own pass, so the train step never calls this)."""
+        """bf16 GEMM operands of all conv weights = one cast of the flat arena, and the GDN group's
+        effective beta / gamma (Adam writes the bf16 block in its own pass and calls prepare())."""
         if cast:
             L.cast_f32_bf16(ptr(self.net_params), ptr(self.net_bf16), self.net_params.numel(), stream())
         for m in self.model.conv_layers():
             m._state._version = m.weight._version
+        self.prepare()
+
+    def _versions(self):
+        return tuple(p._version for m in self.gdn_layers for p in (m.beta, m.gamma))
+
+    def prepare(self):
+        """NonNegativeParametrizer forward of every GDN layer, one launch (ops/parametrizers.py:60-63)."""
+        if self.gdn_layers:
+            L.reparam_forward_multi(ptr(self.net_params), ptr(self.gdn_table), ptr(self.gdn_bounds), self.gdn_table.shape[0],
+                                    self.gdn_max_n, Fn.PEDESTAL, ptr(self.eff32), ptr(self.eff16), stream())
+        self._gdn_versions = self._versions()
+
+    def ensure_prepared(self, beta, gamma):
+        if self._gdn_versions != self._versions():      # someone wrote the parameters through torch
+            self.prepare()
+
+    def queue_finish_backward(self):
+        if not self._finish_queued:
+            self._finish_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self.finish_backward)
+
+    def finish_backward(self):
+        """End of a backward pass: map the GDN group's effective gradients onto beta / gamma
+        (LowerBound gradient rule, ops/bound_ops.py:40-42), one launch; then report them ready."""
+        self._finish_queued = False
+        if not self.gdn_layers:
+            return
+        L.reparam_backward_multi(ptr(self._grads_all), ptr(self.net_params), ptr(self.gdn_table), ptr(self.gdn_bounds),
+                                 self.gdn_table.shape[0], self.gdn_max_n, ptr(self.net_grads), stream())
+        for m in self.gdn_layers:
+            if m._state.grad_ready is not None:
+                m._state.grad_ready([m.beta, m.gamma])
 
     def zero_grad(self):
-        self.net_grads.zero_()
+        self._grads_all.zero_()
         self.aux_grads.zero_()

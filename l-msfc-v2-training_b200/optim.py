@@ -14,8 +14,11 @@ class FusedAdam:
     the squared-gradient sum is one reduction launch, the clip coefficient is computed on the
     device (no host sync, so the step stays capturable)."""
 
-    def __init__(self, params, grads, lr, betas=(0.9, 0.999), eps=1e-8, bf16_shadow=None, clip_max_norm=0.0):
+    def __init__(self, params, grads, lr, betas=(0.9, 0.999), eps=1e-8, bf16_shadow=None, clip_max_norm=0.0,
+                 zero_buffer=None, after_step=None):
         self.params, self.grads = params, grads
+        self.zero_buffer = grads if zero_buffer is None else zero_buffer    # may extend past `grads` (GDN scratch)
+        self.after_step = after_step                                        # e.g. ParamArena.prepare
         self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
         self.clip_max_norm = float(clip_max_norm)
         self.m = torch.zeros_like(params)
@@ -27,7 +30,7 @@ class FusedAdam:
         self.scratch = torch.zeros(4, dtype=torch.float32, device=dev)   # clip, bc1, bc2, grad norm
 
     def zero_grad(self, set_to_none=False):
-        self.grads.zero_()
+        self.zero_buffer.zero_()
 
     def step(self):
         st = stream()
@@ -39,6 +42,8 @@ class FusedAdam:
         L.adam_step(ptr(self.params), ptr(self.m), ptr(self.v), ptr(self.grads), ptr(self.bf16_shadow), n, self.lr,
                     self.betas[0], self.betas[1], self.eps, self.clip_max_norm, ptr(self.sumsq) if clip else None,
                     ptr(self.step_count), ptr(self.scratch), st)
+        if self.after_step is not None:
+            self.after_step()
 
     @property
     def grad_norm(self):
@@ -60,6 +65,6 @@ def net_aux_optimizer(model, conf=None, clip_max_norm=1.0):
             raise ValueError(f"only Adam is implemented on the fused path, got {conf[k]['type']}")
     arena = model.arena or model.build_arena()
     net = FusedAdam(arena.net_params, arena.net_grads, conf["net"]["lr"], bf16_shadow=arena.net_bf16,
-                    clip_max_norm=clip_max_norm)
+                    clip_max_norm=clip_max_norm, zero_buffer=arena._grads_all, after_step=arena.prepare)
     aux = FusedAdam(arena.aux_params, arena.aux_grads, conf["aux"]["lr"])
     return {"net": net, "aux": aux}

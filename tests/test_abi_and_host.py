@@ -50,7 +50,7 @@ def test_argument_errors_are_reported_without_a_device():
     entropy_models.py:158-159)."""
     L = importlib.import_module(PKG + "._lib")
     with pytest.raises(ValueError, match="Invalid quantization mode"):
-        L.gc_forward(None, None, None, None, 0, 7, 0.11, 1e-9, 0, 0, None, None, None, None, None)
+        L.gc_forward(None, None, None, None, 0, 7, 0.11, 1e-9, 0, 0, None, None, None, None, None, None)
     d = L.ConvDesc(0, 4, 2, 1, 8, 8, 4, 4, 256, 0, 256)          # k = 4 is not an L-MSFC kernel size
     with pytest.raises(ValueError, match="conv: k=4"):
         L.conv_forward(d, None, None, None, None, 0, None, None, None, None)
