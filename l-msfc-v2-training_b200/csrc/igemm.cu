@@ -13,8 +13,11 @@
 //   warp 4     TMA producer for the weight operand (cp.async.bulk.tensor, SWIZZLE_128B)
 //   warp 5     TMEM allocator + single-thread tcgen05.mma issuer
 // Pipelines: smem full/empty mbarrier ring (STAGES deep) and one TMEM-full barrier.
-// Small grids (latent-resolution layers) split K over blockIdx.z: partial tiles are summed with
-// red.global.add into a self-cleaning fp32 workspace and the last CTA to arrive runs the epilogue.
+// Small grids (latent-resolution layers) split K over a thread-block cluster (cluster dims 1x1xS,
+// S <= 8): every CTA keeps its partial tile in TMEM, then scatters it column-slice-wise into the
+// owning CTA's shared memory (st.shared::cluster), and after one cluster barrier each CTA sums the S
+// partials of its own BLOCK_N/S columns and runs the epilogue for them -- no global atomics, no
+// workspace, no counters (the atomic version queued ~10 us of same-address reductions in L2).
 #include "igemm.cuh"
 
 namespace lmsfc {
@@ -35,73 +38,95 @@ struct FwdCfg {
 
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
-__device__ __forceinline__ void load_bf16x32(const __nv_bfloat16* p, uint32_t (&r)[16]) {
+template <int W>
+__device__ __forceinline__ void load_bf16(const __nv_bfloat16* p, uint32_t (&r)[W / 2]) {
   const uint4* s = reinterpret_cast<const uint4*>(p);
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
+  for (int j = 0; j < W / 8; ++j) {
     const uint4 q = __ldg(s + j);
     r[4 * j] = q.x; r[4 * j + 1] = q.y; r[4 * j + 2] = q.z; r[4 * j + 3] = q.w;
   }
 }
-__device__ __forceinline__ void store_bf16x32(__nv_bfloat16* p, const float (&v)[32]) {
+template <int W>
+__device__ __forceinline__ void store_bf16(__nv_bfloat16* p, const float (&v)[W]) {
   uint4* d = reinterpret_cast<uint4*>(p);
 #pragma unroll
-  for (int j = 0; j < 4; ++j)
+  for (int j = 0; j < W / 8; ++j)
     d[j] = make_uint4(pack_bf16(v[8 * j], v[8 * j + 1]), pack_bf16(v[8 * j + 2], v[8 * j + 3]),
                       pack_bf16(v[8 * j + 4], v[8 * j + 5]), pack_bf16(v[8 * j + 6], v[8 * j + 7]));
 }
-__device__ __forceinline__ float pick(const uint32_t (&r)[16], int j) {
+template <int H>
+__device__ __forceinline__ float pick(const uint32_t (&r)[H], int j) {
   return (j & 1) ? bf16_hi(r[j >> 1]) : bf16_lo(r[j >> 1]);
 }
 
-// epilogue maths for 32 consecutive output channels [nb, nb+32) of one output pixel at offset o
-__device__ __forceinline__ void epilogue_chunk(const IgemmParams& p, float (&v)[32], size_t o, int nb) {
+// epilogue maths for W consecutive output channels [nb, nb+W) of one output pixel at offset o
+template <int W>
+__device__ __forceinline__ void epilogue_chunk(const IgemmParams& p, float (&v)[W], size_t o, int nb) {
   if (p.epi == EPI_BIAS) {
     if (p.bias) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + nb + j);
+      for (int j = 0; j < W; ++j) v[j] += __ldg(p.bias + nb + j);
     }
     if (p.relu) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+      for (int j = 0; j < W; ++j) v[j] = fmaxf(v[j], 0.f);
     }
     if (p.out_f32) {
       float4* d = reinterpret_cast<float4*>(p.out_f32 + o);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) d[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      for (int j = 0; j < W / 4; ++j) d[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
     }
     if (p.out_abs) {
-      float a[32];
+      float a[W];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) a[j] = fabsf(v[j]);
-      store_bf16x32(p.out_abs + o, a);
+      for (int j = 0; j < W; ++j) a[j] = fabsf(v[j]);
+      store_bf16<W>(p.out_abs + o, a);
     }
   } else {
-    uint32_t xr[16];
-    load_bf16x32(p.aux_x + o, xr);
+    uint32_t xr[W / 2];
+    load_bf16<W>(p.aux_x + o, xr);
     if (p.epi == EPI_GDN) {
-      float rn[32];
+      float rn[W];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
+      for (int j = 0; j < W; ++j) {
         const float nrm = v[j] + __ldg(p.bias + nb + j);
         rn[j] = rsqrtf(nrm);
         const float x = pick(xr, j);
         v[j] = p.inverse ? x * (nrm * rn[j]) : x * rn[j];
       }
-      if (p.out_rn) store_bf16x32(p.out_rn + o, rn);
+      if (p.out_rn) store_bf16<W>(p.out_rn + o, rn);
     } else {  // EPI_GDN_BWD
-      uint32_t gr[16], rr[16];
-      load_bf16x32(p.aux_gy + o, gr);
-      load_bf16x32(p.aux_rn + o, rr);
+      uint32_t gr[W / 2], rr[W / 2];
+      load_bf16<W>(p.aux_gy + o, gr);
+      load_bf16<W>(p.aux_rn + o, rr);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
+      for (int j = 0; j < W; ++j) {
         const float rn = pick(rr, j);
         const float f = p.inverse ? 1.f / rn : rn;
         v[j] = pick(gr, j) * f + 2.f * pick(xr, j) * v[j];
       }
     }
   }
-  if (p.out_bf16) store_bf16x32(p.out_bf16 + o, v);
+  if (p.out_bf16) store_bf16<W>(p.out_bf16 + o, v);
+}
+
+// ---- thread-block cluster helpers (split-K reduction through distributed shared memory)
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_v4(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
 #ifdef LMSFC_TIMELINE
@@ -133,11 +158,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
-  uint32_t* last_flag = tmem_slot + 1;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) TL(0);
-  const int phase_id = blockIdx.z / p.ksplit, ks = blockIdx.z % p.ksplit;
+  const int phase_id = blockIdx.z / p.ksplit, ks = blockIdx.z % p.ksplit;   // ks == %cluster_ctarank (cluster 1x1xksplit)
   const IgemmPhase ph = p.ph[phase_id];
   const int m0 = blockIdx.x * BLOCK_M;
   if (m0 >= ph.M) return;                       // phases differ in size: whole CTA exits together
@@ -165,6 +189,22 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if (tid == 0) TL(1);
+
+  // output row of this thread (meaningful for the 128 gather/epilogue threads)
+  const int row = (warp & 3) * 32 + lane;
+  bool ok = false;
+  size_t obase = 0;
+  {
+    const int m = m0 + row;
+    if (m < ph.M) {
+      const int wg = m % ph.Wg, t = m / ph.Wg;
+      const int hg = t % ph.Hg, b = t / ph.Hg;
+      const int ho = hg * p.sout + ph.oy, wo = wg * p.sout + ph.ox;
+      ok = ho < p.Hout && wo < p.Wout;
+      obase = ((size_t)(b * p.Hout + ho) * p.Wout + wo) * p.N + n0;
+    }
+  }
+  const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
 
   if (warp < 4) {
     // ================= activation gather (producer) =================
@@ -216,18 +256,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       tc_fence_after();
     }
     if (tid == 0) TL(4);
-    const int row = warp * 32 + lane;
-    const int m = m0 + row;
-    bool ok = m < ph.M;
-    size_t obase = 0;
-    if (ok) {
-      const int wg = m % ph.Wg, t = m / ph.Wg;
-      const int hg = t % ph.Hg, b = t / ph.Hg;
-      const int ho = hg * p.sout + ph.oy, wo = wg * p.sout + ph.ox;
-      ok = ho < p.Hout && wo < p.Wout;
-      obase = ((size_t)(b * p.Hout + ho) * p.Wout + wo) * p.N + n0;
-    }
-    const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16);
     if (p.ksplit == 1) {
 #pragma unroll 1
       for (int cb = 0; cb < BLOCK_N; cb += 32) {
@@ -238,48 +266,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
         float v[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        epilogue_chunk(p, v, obase + cb, n0 + cb);
-      }
-    } else {
-      // split K: add the partial tile into the workspace; the last slice to arrive finishes it
-      const int tile = (phase_id * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-      float* wrow = p.ws + ((size_t)tile * BLOCK_M + row) * BLOCK_N;
-#pragma unroll 1
-      for (int cb = 0; cb < BLOCK_N && nkb > 0; cb += 32) {
-        uint32_t r[32];
-        tmem_ld32(trow + cb, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(wrow + cb + 4 * j),
-                       "f"(__uint_as_float(r[4 * j])), "f"(__uint_as_float(r[4 * j + 1])),
-                       "f"(__uint_as_float(r[4 * j + 2])), "f"(__uint_as_float(r[4 * j + 3]))
-                       : "memory");
-      }
-      if (tid == 0) TL(5);
-      __threadfence();
-      epi_bar_sync();
-      if (tid == 0) TL(6);
-      if (tid == 0) {
-        const unsigned prev = atomicAdd(p.ws_count + tile, 1u);
-        *last_flag = (prev == (unsigned)p.ksplit - 1) ? 1u : 0u;
-        if (prev == (unsigned)p.ksplit - 1) p.ws_count[tile] = 0;    // self-cleaning
-      }
-      epi_bar_sync();
-      if (*last_flag) {
-        __threadfence();
-#pragma unroll 1
-        for (int cb = 0; cb < BLOCK_N; cb += 32) {
-          float v[32];
-          float4* w4 = reinterpret_cast<float4*>(wrow + cb);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 q = __ldcg(w4 + j);
-            v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
-            __stcg(w4 + j, make_float4(0.f, 0.f, 0.f, 0.f));
-          }
-          if (ok) epilogue_chunk(p, v, obase + cb, n0 + cb);
-        }
+        epilogue_chunk<32>(p, v, obase + cb, n0 + cb);
       }
     }
   } else if (warp == 4) {
@@ -332,6 +319,77 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       TL(10);
     }
   }
+  if (p.ksplit > 1) {
+    // ================= split K: reduce the cluster's partial tiles through DSMEM =================
+    // recv[src rank][w/4][row] float4 overlays the (now idle) pipeline stages of every CTA; CTA r owns
+    // output columns [r*w, (r+1)*w), w = BLOCK_N / ksplit.  Row-fastest, so the 32 lanes (= rows) of a
+    // warp write / read 512 contiguous bytes per instruction.
+    const int S = p.ksplit, w = BLOCK_N / S;
+    __syncwarp();
+    cluster_sync_all();                 // every CTA of the cluster has retired its MMAs: stage smem is free
+    if (tid == 0) TL(5);
+    if (warp < 4) {
+#pragma unroll 1
+      for (int cb = 0; cb < BLOCK_N; cb += 32) {
+        uint32_t r[32];
+        if (nkb > 0) {                   // warp-uniform: tcgen05.ld is .sync.aligned
+          tmem_ld32(trow + cb, r);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) r[j] = 0u;
+        }
+        if (!ok) continue;               // rows past M / cropped outputs are never stored
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int col = cb + 16 * h;
+          const int owner = col / w, cin = col - owner * w;
+          const uint32_t dst = map_to_cta(smem_base + (uint32_t)(((ks * (w >> 2) + (cin >> 2)) * BLOCK_M + row) * 16),
+                                          (uint32_t)owner);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            st_cluster_v4(dst + j * (BLOCK_M * 16), __uint_as_float(r[16 * h + 4 * j]), __uint_as_float(r[16 * h + 4 * j + 1]),
+                          __uint_as_float(r[16 * h + 4 * j + 2]), __uint_as_float(r[16 * h + 4 * j + 3]));
+        }
+      }
+    }
+    cluster_sync_all();                 // all partials have landed
+    if (tid == 0) TL(6);
+    if (warp < 4 && ok) {
+      const float4* mine = reinterpret_cast<const float4*>(smem) + row;     // [src][w/4][row]
+      const int w4 = w >> 2;
+      if (w >= 32) {
+#pragma unroll 1
+        for (int c = 0; c < w; c += 32) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+          for (int src = 0; src < S; ++src) {
+            const float4* q = mine + (size_t)(src * w4 + (c >> 2)) * BLOCK_M;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 t = q[j * BLOCK_M];
+              v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
+            }
+          }
+          epilogue_chunk<32>(p, v, obase + ks * w + c, n0 + ks * w + c);
+        }
+      } else {                          // w == 16
+        float v[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = 0.f;
+        for (int src = 0; src < S; ++src) {
+          const float4* q = mine + (size_t)(src * w4) * BLOCK_M;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 t = q[j * BLOCK_M];
+            v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
+          }
+        }
+        epilogue_chunk<16>(p, v, obase + ks * w, n0 + ks * w);
+      }
+    }
+  }
   if (tid == 0) TL(7);
   tc_fence_before();
   __syncthreads();
@@ -349,23 +407,33 @@ extern "C" int lmsfc_debug_read_timeline(unsigned long long* host64x16) {
 #endif
 
 // ---------------------------------------------------------------- host side
-namespace {
-constexpr size_t kWsFloats = 8u << 20;     // 32 MB fp32 split-K workspace
-constexpr int kWsTiles = 4096;
-float* g_ws = nullptr;
-unsigned int* g_ws_count = nullptr;
-
-int ensure_workspace() {
-  if (g_ws) return LMSFC_OK;
-  // first use happens in an eager (un-captured) step; cudaMalloc is not capturable
-  LMSFC_CUDA(cudaMalloc(&g_ws, kWsFloats * sizeof(float)));
-  LMSFC_CUDA(cudaMalloc(&g_ws_count, kWsTiles * sizeof(unsigned int)));
-  LMSFC_CUDA(cudaMemset(g_ws, 0, kWsFloats * sizeof(float)));
-  LMSFC_CUDA(cudaMemset(g_ws_count, 0, kWsTiles * sizeof(unsigned int)));
-  LMSFC_CUDA(cudaDeviceSynchronize());
-  return LMSFC_OK;
+// how many clusters of `ks` CTAs of this kernel can be resident at once (1 CTA per SM; a cluster
+// must fit inside one GPC), queried once per configuration
+template <int BLOCK_N, bool B_MN>
+static int max_active_clusters_t(int ks) {
+  static int cache[9] = {0};
+  if (cache[ks]) return cache[ks];
+  using Cfg = FwdCfg<BLOCK_N>;
+  cudaFuncSetAttribute(igemm_fwd_kernel<BLOCK_N, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1, 1, ks * 64);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)ks;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, igemm_fwd_kernel<BLOCK_N, B_MN>, &cfg) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    n = 148 / ks / 2;                      // conservative guess
+  }
+  return cache[ks] = n;
 }
-}  // namespace
+static int max_active_clusters(int bn, bool mn, int ks) {
+  if (bn == 256) return mn ? max_active_clusters_t<256, true>(ks) : max_active_clusters_t<256, false>(ks);
+  return mn ? max_active_clusters_t<128, true>(ks) : max_active_clusters_t<128, false>(ks);
+}
 
 template <int BLOCK_N, bool B_MN>
 static int launch_fwd_t(const IgemmParams& p, dim3 grid, cudaStream_t stream) {
@@ -376,7 +444,21 @@ static int launch_fwd_t(const IgemmParams& p, dim3 grid, cudaStream_t stream) {
                                     Cfg::SMEM_BYTES));
     attr_done = true;
   }
-  igemm_fwd_kernel<BLOCK_N, B_MN><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  if (p.ksplit > 1) {                    // the K slices of one output tile form a cluster along z
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = (unsigned)p.ksplit;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  LMSFC_CUDA(cudaLaunchKernelEx(&cfg, igemm_fwd_kernel<BLOCK_N, B_MN>, p));
   LMSFC_LAUNCH_CHECK();
   return LMSFC_OK;
 }
@@ -399,35 +481,34 @@ int launch_igemm(IgemmParams& p, cudaStream_t stream) {
     tiles128 += ceil_div(p.ph[i].M, BLOCK_M);
   }
   // Tile width / split-K choice from a small cost model (us): waves * (K blocks * t_kb + fixed).
-  // 256-wide tiles halve the gather traffic per flop; splitting K fills the 148 SMs when the
-  // output has few tiles (latent-resolution layers); measured t_kb: 0.5 us (N=256), 0.3 us (N=128).
+  // 256-wide tiles halve the gather traffic per flop; splitting K over a cluster fills more of the
+  // 148 SMs when the output has few tiles (latent-resolution layers).  t_kb: tensor-pipe time of one
+  // 64-deep K block (0.38 / 0.19 us), stretched to 0.5 / 0.3 us when a full-chip grid saturates L2.
   const int kc = (p.c0 + p.c1) / BLOCK_K;
   const int grid_x = ceil_div(maxM, BLOCK_M);
   int bn = 128, ksplit = 1;
   double best = 1e30;
-  static const int ks_opts[] = {1, 2, 3, 4, 5, 6, 8, 10, 12, 16, 20, 25, 32};
+  static const int ks_opts[] = {1, 2, 4, 8};
   for (int cand_bn = 128; cand_bn <= 256; cand_bn += 128) {
     if (p.N % cand_bn != 0) continue;
     const int64_t tiles = tiles128 * (p.N / cand_bn);
     for (int ks : ks_opts) {
       if (ks > 1) {
-        if (min_taps * kc / ks < 2) continue;
-        if ((size_t)p.nphase * grid_x * (p.N / cand_bn) * BLOCK_M * cand_bn > kWsFloats) continue;
-        if ((size_t)p.nphase * grid_x * (p.N / cand_bn) > (size_t)kWsTiles) continue;
+        if (cand_bn / ks < 16) continue;
+        const int kb_per = ceil_div(min_taps * kc, ks);
+        if ((ks - 1) * kb_per >= min_taps * kc) continue;      // no empty K slice in any phase
       }
-      const double waves = (double)ceil_div(tiles * ks, 148);
-      const double t = waves * (ceil_div(max_taps * kc, ks) * (cand_bn == 256 ? 0.5 : 0.3) + 5.0) + (ks > 1 ? 3.0 : 0.0);
+      const int64_t ctas = tiles * ks;
+      const double waves = ks == 1 ? (double)ceil_div(ctas, 148)
+                                   : (double)ceil_div(tiles, max_active_clusters(cand_bn, p.w_mn != 0, ks));
+      const bool busy = ctas >= 100;
+      const double t_kb = cand_bn == 256 ? (busy ? 0.5 : 0.38) : (busy ? 0.3 : 0.19);
+      const double t = waves * (ceil_div(max_taps * kc, ks) * t_kb + 4.0) + (ks > 1 ? 1.5 : 0.0);
       if (t < best) { best = t; bn = cand_bn; ksplit = ks; }
     }
   }
   dim3 grid(grid_x, p.N / bn, p.nphase * ksplit);
-  if (ksplit > 1) {
-    int rc = ensure_workspace();
-    if (rc) return rc;
-  }
   p.ksplit = ksplit;
-  p.ws = g_ws;
-  p.ws_count = g_ws_count;
   int rc = make_tmap_2d_bf16(&p.tmapB, p.w, (uint64_t)p.w_rows, (uint64_t)p.w_cols, (uint64_t)p.w_cols,
                              p.w_mn ? 64 : bn, 64);
   if (rc) return rc;

@@ -15,7 +15,7 @@ enum : int {
 
 // Gathered-A x weight-B GEMM:  D[m][n] = sum_{tap,c} A[pixel(m)+tap][c] * W[n][widx(tap)*Ctot + c]
 // A launch covers up to 4 sub-pixel phases of a transposed conv (blockIdx.z / ksplit) and, for
-// small grids, `ksplit` slices of the K loop whose fp32 partials meet in a workspace.
+// small grids, `ksplit` slices of the K loop (one thread-block cluster) reduced through DSMEM.
 constexpr int kMaxPhases = 4;
 struct IgemmPhase {
   int Hg, Wg, M;            // GEMM row grid of this phase: m = (b*Hg + hg)*Wg + wg
@@ -40,9 +40,7 @@ struct IgemmParams {
   int Hout, Wout, sout;
   int N;                    // output channels (row pitch of every output / aux tensor)
   int epi, relu, inverse;
-  int ksplit;               // filled by launch_igemm
-  float* ws;                // split-K workspace (zero between launches), filled by launch_igemm
-  unsigned int* ws_count;   // per-tile arrival counters (zero between launches)
+  int ksplit;               // filled by launch_igemm: K slices per output tile = cluster size along z
   const float* bias;        // [N] or null
   __nv_bfloat16* out_bf16;  // nullable
   float* out_f32;           // nullable
