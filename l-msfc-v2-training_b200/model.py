@@ -65,9 +65,24 @@ class LMSFC(nn.Module):
         """feats: {"p2": [B,F,H,W], ...}.  noise_z / noise_y (optional, shaped like z / y) inject
         the U(-.5,.5) draws for parity tests; RNG order is EB then GC (google.py:295-297)."""
         lv = self.spec.levels
-        p2, p3, p4, p5 = (Fn.nhwc(feats[k], Fn.BF16) for k in lv)
-        self._share_rng(p2.device)
-        a, s = self.g_a, self.g_s
+        ps = tuple(Fn.nhwc(feats[k], Fn.BF16) for k in lv)
+        self._share_rng(ps[0].device)
+        y, z, z2_hw = self.analysis(ps)
+        z_hat, z_lik = self.entropy_bottleneck(z, noise=noise_z)
+        scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
+        y_hat, y_lik = self.gaussian_conditional(y, scales, noise=noise_y)
+        if self.training and noise_z is None and noise_y is None:
+            self.entropy_bottleneck.rng.advance()      # ONE shared counter bump per step (EB and GC share the RNG)
+        x_hat = self.synthesis(getattr(y_hat, Fn._BF16_ATTR), [p.shape[2:] for p in ps])
+        return {"x_hat": dict(zip(lv, x_hat)),
+                "likelihoods": {"y": y_lik, "z": z_lik},
+                "latents": {"y": y, "z": z, "y_hat": y_hat, "z_hat": z_hat, "scales": scales},
+                "inputs_nhwc": dict(zip(lv, ps))}
+
+    def analysis(self, ps):
+        """g_a + h_a: (p2..p5 bf16 NHWC) -> y fp32, z fp32, spatial size of h_a's middle activation."""
+        p2, p3, p4, p5 = ps
+        a = self.g_a
         e2 = a.gdn2(a.conv2(p2))
         e3 = a.gdn3(a.conv3(e2, p3))
         e4 = a.gdn4(a.conv4(e3, p4))
@@ -75,24 +90,27 @@ class LMSFC(nn.Module):
         z1 = self.h_a["0"](y_abs, relu=True)
         z2 = self.h_a["2"](z1, relu=True)
         z, _ = self.h_a["4"](z2, latent_head=True)
-        z_hat, z_lik = self.entropy_bottleneck(z, noise=noise_z)
-        t = self.h_s["0"](getattr(z_hat, Fn._BF16_ATTR), relu=True, out_hw=z2.shape[2:])
-        t = self.h_s["2"](t, relu=True, out_hw=y.shape[2:])
+        return y, z, z2.shape[2:]
+
+    def hyper_synthesis(self, z_hat_bf16, mid_hw, y_hw):
+        """h_s: z_hat -> scales (fp32, ReLU'd as models/google.py:275-282)."""
+        t = self.h_s["0"](z_hat_bf16, relu=True, out_hw=mid_hw)
+        t = self.h_s["2"](t, relu=True, out_hw=y_hw)
         scales, _ = self.h_s["4"](t, relu=True, latent_head=True)
-        y_hat, y_lik = self.gaussian_conditional(y, scales, noise=noise_y)
-        if self.training and noise_z is None and noise_y is None:
-            self.entropy_bottleneck.rng.advance()      # ONE shared counter bump per step (EB and GC share the RNG)
-        d5 = s.igdn5(s.up5(getattr(y_hat, Fn._BF16_ATTR), out_hw=p5.shape[2:]))
+        return scales
+
+    def synthesis(self, y_hat_bf16, level_hw):
+        """g_s: y_hat -> (p2_hat, p3_hat, p4_hat, p5_hat), each cropped to its level's H x W."""
+        s = self.g_s
+        hw2, hw3, hw4, hw5 = level_hw
+        d5 = s.igdn5(s.up5(y_hat_bf16, out_hw=hw5))
         p5h = s.head5(d5)
-        d4 = s.igdn4(s.up4(d5, out_hw=p4.shape[2:]))
+        d4 = s.igdn4(s.up4(d5, out_hw=hw4))
         p4h = s.head4(d4)
-        d3 = s.igdn3(s.up3(d4, out_hw=p3.shape[2:]))
+        d3 = s.igdn3(s.up3(d4, out_hw=hw3))
         p3h = s.head3(d3)
-        p2h = s.up2(d3, out_hw=p2.shape[2:])
-        return {"x_hat": dict(zip(lv, (p2h, p3h, p4h, p5h))),
-                "likelihoods": {"y": y_lik, "z": z_lik},
-                "latents": {"y": y, "z": z, "y_hat": y_hat, "z_hat": z_hat, "scales": scales},
-                "inputs_nhwc": dict(zip(lv, (p2, p3, p4, p5)))}
+        p2h = s.up2(d3, out_hw=hw2)
+        return p2h, p3h, p4h, p5h
 
     # ------------------------------------------------------------------ CompressionModel contract
     def aux_loss(self):
