@@ -16,6 +16,7 @@ namespace lmsfc {
 __global__ void __launch_bounds__(256) cdf_rows_kernel(const float* pmf, int pmf_stride, const float* tail,
                                                        const int* pmf_length, int precision, int32_t* cdf_out,
                                                        int cdf_stride, int* status) {
+  pdl_sync();
   extern __shared__ uint32_t sm[];       // n + 1 entries
   __shared__ unsigned long long best_key;
   __shared__ int flag;
@@ -93,8 +94,7 @@ int pmf_rows_to_cdf_device(const float* pmf, int pmf_stride, const float* tail, 
     LMSFC_CUDA(cudaFuncSetAttribute(cdf_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr = smem;
   }
-  cdf_rows_kernel<<<rows, 256, smem, s>>>(pmf, pmf_stride, tail, pmf_length, precision, cdf, cdf_stride, status);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(cdf_rows_kernel, dim3(rows), dim3(256), smem, s, pmf, pmf_stride, tail, pmf_length, precision, cdf, cdf_stride, status);
   return LMSFC_OK;
 }
 

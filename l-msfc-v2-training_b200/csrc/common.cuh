@@ -45,7 +45,48 @@ extern unsigned long long g_launch_count;
 
 static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every kernel of this library is launched with cudaLaunchAttributeProgrammaticStreamSerialization and
+// runs   <prologue without global-memory traffic> ; pdl_wait() ; pdl_trigger() ; <body>.
+// pdl_wait() returns once the preceding kernel in the stream has completed and flushed, so data
+// dependences are exactly those of a plain stream; what overlaps is the launch latency, CTA rasterisation
+// and prologue (barrier init, TMEM allocation, descriptor prefetch) of the NEXT kernel with the tail of this
+// one -- the train step is a chain of ~170 short kernels inside one CUDA graph.
+#include <utility>
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                     unsigned cluster_z, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[n].val.programmaticStreamSerializationAllowed = 1;
+  ++n;
+  if (cluster_z > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = 1;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = cluster_z;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+#define LMSFC_LAUNCH(kernel, grid, block, smem, stream, ...)                                      \
+  do {                                                                                            \
+    LMSFC_CUDA(::lmsfc::launch_pdl(kernel, grid, block, smem, stream, 1u, __VA_ARGS__));          \
+    ++::lmsfc::g_launch_count;                                                                    \
+  } while (0)
+
 #ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() { pdl_wait(); pdl_trigger(); }
 // ---------------------------------------------------------------- device util
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);

@@ -24,6 +24,7 @@ __device__ __forceinline__ float hi(uint32_t v) { return __uint_as_float(v & 0xf
 // sse += sum (xhat-x)^2 ; grad = grad_coef * (xhat - x).  5 bytes/element at bf16 (2 reads + 1 write).
 __global__ void __launch_bounds__(TPB) mse_kernel(const uint4* __restrict__ xh, const uint4* __restrict__ x, int64_t n8,
                                                   float coef, float* sse, uint4* __restrict__ grad) {
+  pdl_sync();
   float local = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n8; i += (int64_t)gridDim.x * TPB) {
     const uint4 a = __ldg(xh + i), b = __ldg(x + i);
@@ -46,8 +47,7 @@ int mse_fwd_bwd(const __nv_bfloat16* xhat, const __nv_bfloat16* x, int64_t n, fl
                 __nv_bfloat16* grad, cudaStream_t s) {
   LMSFC_CHECK_ARG(n % 8 == 0, "mse: n=%lld must be a multiple of 8", (long long)n);
   if (n == 0) return LMSFC_OK;
-  mse_kernel<<<grid1d(n / 8), TPB, 0, s>>>((const uint4*)xhat, (const uint4*)x, n / 8, grad_coef, sse, (uint4*)grad);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(mse_kernel, dim3(grid1d(n / 8)), dim3(TPB), 0, s, (const uint4*)xhat, (const uint4*)x, n / 8, grad_coef, sse, (uint4*)grad);
   return LMSFC_OK;
 }
 
@@ -55,6 +55,7 @@ int mse_fwd_bwd(const __nv_bfloat16* xhat, const __nv_bfloat16* x, int64_t n, fl
 // D = sum_{n_rate<=i<n_rate+n_dist} accum[i]*coef[i]; loss = lambda_scale*D + bpp.
 __global__ void loss_finalize_kernel(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale,
                                      float* out) {
+  pdl_sync();
   float bpp = 0.f, d = 0.f;
   for (int i = 0; i < n_rate; ++i) bpp += accum[i] * coef[i];
   for (int i = 0; i < n_dist; ++i) d += accum[n_rate + i] * coef[n_rate + i];
@@ -62,8 +63,7 @@ __global__ void loss_finalize_kernel(const float* accum, const float* coef, int 
 }
 int loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale, float* out,
                   cudaStream_t s) {
-  loss_finalize_kernel<<<1, 1, 0, s>>>(accum, coef, n_rate, n_dist, lambda_scale, out);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(loss_finalize_kernel, dim3(1), dim3(1), 0, s, accum, coef, n_rate, n_dist, lambda_scale, out);
   return LMSFC_OK;
 }
 
@@ -145,6 +145,7 @@ int ensure_reduce_scratch() {
 
 // ---------------------------------------------------------------- GDN helper passes
 __global__ void __launch_bounds__(TPB) square_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int64_t n8) {
+  pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n8; i += (int64_t)gridDim.x * TPB) {
     const uint4 a = __ldg(x + i);
     const uint32_t av[4] = {a.x, a.y, a.z, a.w};
@@ -157,8 +158,7 @@ __global__ void __launch_bounds__(TPB) square_kernel(const uint4* __restrict__ x
 int square_bf16(const __nv_bfloat16* x, __nv_bfloat16* x2, int64_t n, cudaStream_t s) {
   LMSFC_CHECK_ARG(n % 8 == 0, "square: n must be a multiple of 8");
   if (n == 0) return LMSFC_OK;
-  square_kernel<<<grid1d(n / 8), TPB, 0, s>>>((const uint4*)x, (uint4*)x2, n / 8);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(square_kernel, dim3(grid1d(n / 8)), dim3(TPB), 0, s, (const uint4*)x, (uint4*)x2, n / 8);
   return LMSFC_OK;
 }
 
@@ -168,6 +168,7 @@ __global__ void __launch_bounds__(256) gdn_t_kernel(const uint4* __restrict__ gy
                                                     const uint4* __restrict__ rn, int inverse, int64_t P, int C8,
                                                     uint4* __restrict__ t, float* g_beta, float* scratch,
                                                     unsigned int* counter) {
+  pdl_sync();
   const int c8 = blockIdx.x * 32 + threadIdx.x;
   float acc[8];
 #pragma unroll
@@ -203,16 +204,16 @@ int gdn_t(const __nv_bfloat16* gy, const __nv_bfloat16* x, const __nv_bfloat16* 
   int64_t by = (148 * 2 + bx - 1) / bx;   // ~2 blocks per SM: few same-address atomics, 4 loads in flight per thread
   const int64_t maxy = (P + 7) / 8;
   if (by > maxy) by = maxy;
-  gdn_t_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)gy, (const uint4*)x, (const uint4*)rn,
+  LMSFC_LAUNCH(gdn_t_kernel, dim3(dim3(bx, (unsigned)by)), dim3(dim3(32, 8)), 0, s, (const uint4*)gy, (const uint4*)x, (const uint4*)rn,
                                                                 inverse, P, C8, (uint4*)t, g_beta, g_red_scratch,
                                                                 g_red_count);
-  LMSFC_LAUNCH_CHECK();
   return LMSFC_OK;
 }
 
 // column sums of a bf16 [P][C] matrix (conv bias gradients)
 __global__ void __launch_bounds__(256) colsum_kernel(const uint4* __restrict__ g, int64_t P, int C8, float* out,
                                                      float* scratch, unsigned int* counter) {
+  pdl_sync();
   const int c8 = blockIdx.x * 32 + threadIdx.x;
   float acc[8];
 #pragma unroll
@@ -238,13 +239,13 @@ int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream
   int64_t by = (148 * 2 + bx - 1) / bx;   // ~2 blocks per SM, 8 x 16 B loads in flight per thread
   const int64_t maxy = (P + 7) / 8;
   if (by > maxy) by = maxy;
-  colsum_kernel<<<dim3(bx, (unsigned)by), dim3(32, 8), 0, s>>>((const uint4*)g, P, C8, out, g_red_scratch, g_red_count);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(colsum_kernel, dim3(dim3(bx, (unsigned)by)), dim3(dim3(32, 8)), 0, s, (const uint4*)g, P, C8, out, g_red_scratch, g_red_count);
   return LMSFC_OK;
 }
 
 // ---------------------------------------------------------------- NonNegativeParametrizer
 __global__ void reparam_fwd_kernel(const float* p, int64_t n, float bound, float ped, float* o32, __nv_bfloat16* o16) {
+  pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float v = fmaxf(p[i], bound);
     const float r = v * v - ped;
@@ -255,11 +256,11 @@ __global__ void reparam_fwd_kernel(const float* p, int64_t n, float bound, float
 int reparam_fwd(const float* p, int64_t n, float bound, float pedestal, float* out_f32, __nv_bfloat16* out_bf16,
                 cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
-  reparam_fwd_kernel<<<grid1d(n), TPB, 0, s>>>(p, n, bound, pedestal, out_f32, out_bf16);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(reparam_fwd_kernel, dim3(grid1d(n)), dim3(TPB), 0, s, p, n, bound, pedestal, out_f32, out_bf16);
   return LMSFC_OK;
 }
 __global__ void reparam_bwd_kernel(const float* g_out, const float* p, int64_t n, float bound, float* g_p) {
+  pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float v = p[i];
     const float g = g_out[i] * 2.f * fmaxf(v, bound);
@@ -268,8 +269,7 @@ __global__ void reparam_bwd_kernel(const float* g_out, const float* p, int64_t n
 }
 int reparam_bwd(const float* g_out, const float* p, int64_t n, float bound, float* g_p, cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
-  reparam_bwd_kernel<<<grid1d(n), TPB, 0, s>>>(g_out, p, n, bound, g_p);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(reparam_bwd_kernel, dim3(grid1d(n)), dim3(TPB), 0, s, g_out, p, n, bound, g_p);
   return LMSFC_OK;
 }
 
@@ -277,6 +277,7 @@ int reparam_bwd(const float* g_out, const float* p, int64_t n, float bound, floa
 // table row s = {param offset, n, out_f32 offset | -1, out_bf16 offset | -1, g_eff offset}.
 __global__ void reparam_fwd_multi_kernel(const float* params, const int64_t* table, const float* bounds, float ped,
                                          float* o32, __nv_bfloat16* o16) {
+  pdl_sync();
   const int64_t* t = table + 5 * blockIdx.y;
   const float* p = params + t[0];
   const int64_t n = t[1], a32 = t[2], a16 = t[3];
@@ -290,6 +291,7 @@ __global__ void reparam_fwd_multi_kernel(const float* params, const int64_t* tab
 }
 __global__ void reparam_bwd_multi_kernel(const float* g_eff, const float* params, const int64_t* table,
                                          const float* bounds, float* g_params) {
+  pdl_sync();
   const int64_t* t = table + 5 * blockIdx.y;
   const float* p = params + t[0];
   float* gp = g_params + t[0];
@@ -305,33 +307,32 @@ __global__ void reparam_bwd_multi_kernel(const float* g_eff, const float* params
 int reparam_fwd_multi(const float* params, const int64_t* table, const float* bounds, int nseg, int64_t max_n,
                       float pedestal, float* out_f32, __nv_bfloat16* out_bf16, cudaStream_t s) {
   if (nseg == 0) return LMSFC_OK;
-  reparam_fwd_multi_kernel<<<dim3(grid1d(max_n), nseg), TPB, 0, s>>>(params, table, bounds, pedestal, out_f32, out_bf16);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(reparam_fwd_multi_kernel, dim3(dim3(grid1d(max_n), nseg)), dim3(TPB), 0, s, params, table, bounds, pedestal, out_f32, out_bf16);
   return LMSFC_OK;
 }
 int reparam_bwd_multi(const float* g_eff, const float* params, const int64_t* table, const float* bounds, int nseg,
                       int64_t max_n, float* g_params, cudaStream_t s) {
   if (nseg == 0) return LMSFC_OK;
-  reparam_bwd_multi_kernel<<<dim3(grid1d(max_n), nseg), TPB, 0, s>>>(g_eff, params, table, bounds, g_params);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(reparam_bwd_multi_kernel, dim3(dim3(grid1d(max_n), nseg)), dim3(TPB), 0, s, g_eff, params, table, bounds, g_params);
   return LMSFC_OK;
 }
 
 // ---------------------------------------------------------------- small activation gradients
 __global__ void relu_bwd_kernel(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n) {
+  pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     if (!(__bfloat162float(out[i]) > 0.f)) g[i] = __float2bfloat16(0.f);
 }
 int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
-  relu_bwd_kernel<<<grid1d(n), TPB, 0, s>>>(g, out, n);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(relu_bwd_kernel, dim3(grid1d(n)), dim3(TPB), 0, s, g, out, n);
   return LMSFC_OK;
 }
 // g_out = bf16(g_direct + sign(y) * g_abs): gradient of y feeding both GaussianConditional and h_a(|y|)
 // relu != 0: y is a ReLU output, both branches are masked by (y > 0)
 __global__ void abs_bwd_kernel(const float* gd, const __nv_bfloat16* ga, const float* y, int64_t n, int relu,
                                __nv_bfloat16* o) {
+  pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float yv = y[i];
     const float sg = (yv > 0.f) ? 1.f : ((yv < 0.f) ? -1.f : 0.f);
@@ -342,29 +343,28 @@ __global__ void abs_bwd_kernel(const float* gd, const __nv_bfloat16* ga, const f
 int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, int64_t n, int relu, __nv_bfloat16* g_out,
             cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
-  abs_bwd_kernel<<<grid1d(n), TPB, 0, s>>>(g_direct, g_abs, y, n, relu, g_out);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(abs_bwd_kernel, dim3(grid1d(n)), dim3(TPB), 0, s, g_direct, g_abs, y, n, relu, g_out);
   return LMSFC_OK;
 }
 
 __global__ void cast_f32_bf16_kernel(const float* in, __nv_bfloat16* out, int64_t n) {
+  pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     out[i] = __float2bfloat16(in[i]);
 }
 int cast_f32_bf16(const float* in, __nv_bfloat16* out, int64_t n, cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
-  cast_f32_bf16_kernel<<<grid1d(n), TPB, 0, s>>>(in, out, n);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(cast_f32_bf16_kernel, dim3(grid1d(n)), dim3(TPB), 0, s, in, out, n);
   return LMSFC_OK;
 }
 __global__ void cast_bf16_f32_kernel(const __nv_bfloat16* in, float* out, int64_t n) {
+  pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     out[i] = __bfloat162float(in[i]);
 }
 int cast_bf16_f32(const __nv_bfloat16* in, float* out, int64_t n, cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
-  cast_bf16_f32_kernel<<<grid1d(n), TPB, 0, s>>>(in, out, n);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(cast_bf16_f32_kernel, dim3(grid1d(n)), dim3(TPB), 0, s, in, out, n);
   return LMSFC_OK;
 }
 

@@ -30,11 +30,11 @@ __device__ __forceinline__ float philox_uniform(uint64_t seed, uint64_t offset, 
   return (float)(c[idx & 3] >> 8) * (1.0f / 16777216.0f) - 0.5f;
 }
 
-__global__ void rng_advance_kernel(uint64_t* state) { state[1] += 1; }
+__global__ void rng_advance_kernel(uint64_t* state) {
+  pdl_sync(); state[1] += 1; }
 
 int rng_advance(uint64_t* state, cudaStream_t s) {
-  rng_advance_kernel<<<1, 1, 0, s>>>(state);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(rng_advance_kernel, dim3(1), dim3(1), 0, s, state);
   return LMSFC_OK;
 }
 
@@ -45,6 +45,7 @@ __device__ __forceinline__ float std_cumulative(float x) {  // entropy_models.py
 __device__ __forceinline__ float normal_pdf(float t) { return 0.3989422804014327f * __expf(-0.5f * t * t); }
 
 __global__ void __launch_bounds__(256) gc_forward_kernel(GcArgs a) {
+  pdl_sync();
   float local = 0.f;
   // key = seed perturbed per module (`offset`), counter = device step count
   const uint64_t seed = (a.rng_state ? a.rng_state[0] : a.seed) + a.offset * 0x9E3779B97F4A7C15ull;
@@ -75,6 +76,7 @@ __global__ void __launch_bounds__(256) gc_forward_kernel(GcArgs a) {
 }
 
 __global__ void __launch_bounds__(256) gc_backward_kernel(GcBwdArgs a) {
+  pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * blockDim.x) {
     const float yh = a.y_hat[i], mu = a.means ? a.means[i] : 0.f;
     const float d = yh - mu, v = fabsf(d);
@@ -109,14 +111,12 @@ static int grid_for(int64_t n, int threads) {
 
 int gc_forward(const GcArgs& a, cudaStream_t s) {
   if (a.n <= 0) return LMSFC_OK;
-  gc_forward_kernel<<<grid_for(a.n, 256), 256, 0, s>>>(a);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(gc_forward_kernel, dim3(grid_for(a.n, 256)), dim3(256), 0, s, a);
   return LMSFC_OK;
 }
 int gc_backward(const GcBwdArgs& a, cudaStream_t s) {
   if (a.n <= 0) return LMSFC_OK;
-  gc_backward_kernel<<<grid_for(a.n, 256), 256, 0, s>>>(a);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(gc_backward_kernel, dim3(grid_for(a.n, 256)), dim3(256), 0, s, a);
   return LMSFC_OK;
 }
 
@@ -186,6 +186,7 @@ __device__ __forceinline__ float eb_lik_raw(float lower, float upper) {  // entr
 
 // x is NHWC-flattened [P][C]; thread <-> channel, grid.y strides over pixels.
 __global__ void __launch_bounds__(128) eb_forward_kernel(EbArgs a) {
+  pdl_sync();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   float local = 0.f;
   if (c < a.C) {
@@ -258,6 +259,7 @@ __device__ __forceinline__ float eb_logits_bwd(const EbChan& c, const EbTape& tp
 }
 
 __global__ void __launch_bounds__(128) eb_backward_kernel(EbBwdArgs a) {
+  pdl_sync();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= a.C) return;
   EbChan ch;
@@ -302,6 +304,7 @@ __global__ void __launch_bounds__(128) eb_backward_kernel(EbBwdArgs a) {
 // aux loss (entropy_models.py:431-434): value and d/d quantiles in one pass; parameters detached.
 __global__ void __launch_bounds__(128) eb_aux_kernel(const float* params, const float* quantiles, const float* target,
                                                      int C, float* loss, float* g_quantiles) {
+  pdl_sync();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   float local = 0.f;
   if (c < C) {
@@ -336,20 +339,17 @@ static dim3 eb_grid(int C, int64_t P) {
 
 int eb_forward(const EbArgs& a, cudaStream_t s) {
   if (a.P <= 0 || a.C <= 0) return LMSFC_OK;
-  eb_forward_kernel<<<eb_grid(a.C, a.P), 128, 0, s>>>(a);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(eb_forward_kernel, dim3(eb_grid(a.C, a.P)), dim3(128), 0, s, a);
   return LMSFC_OK;
 }
 int eb_backward(const EbBwdArgs& a, cudaStream_t s) {
   if (a.P <= 0 || a.C <= 0) return LMSFC_OK;
-  eb_backward_kernel<<<eb_grid(a.C, a.P), 128, 0, s>>>(a);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(eb_backward_kernel, dim3(eb_grid(a.C, a.P)), dim3(128), 0, s, a);
   return LMSFC_OK;
 }
 int eb_aux(const float* params, const float* quantiles, const float* target, int C, float* loss, float* g_quantiles,
            cudaStream_t s) {
-  eb_aux_kernel<<<(C + 127) / 128, 128, 0, s>>>(params, quantiles, target, C, loss, g_quantiles);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(eb_aux_kernel, dim3((C + 127) / 128), dim3(128), 0, s, params, quantiles, target, C, loss, g_quantiles);
   return LMSFC_OK;
 }
 

@@ -188,6 +188,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_sync();                            // everything above touched no global memory
   if (tid == 0) TL(1);
 
   // output row of this thread (meaningful for the 128 gather/epilogue threads)
@@ -444,22 +445,10 @@ static int launch_fwd_t(const IgemmParams& p, dim3 grid, cudaStream_t stream) {
                                     Cfg::SMEM_BYTES));
     attr_done = true;
   }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = grid;
-  cfg.blockDim = dim3(NUM_THREADS);
-  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  if (p.ksplit > 1) {                    // the K slices of one output tile form a cluster along z
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 1;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = (unsigned)p.ksplit;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-  }
-  LMSFC_CUDA(cudaLaunchKernelEx(&cfg, igemm_fwd_kernel<BLOCK_N, B_MN>, p));
-  LMSFC_LAUNCH_CHECK();
+  // the K slices of one output tile form a cluster along z
+  LMSFC_CUDA(launch_pdl(igemm_fwd_kernel<BLOCK_N, B_MN>, grid, dim3(NUM_THREADS), (size_t)Cfg::SMEM_BYTES, stream,
+                        (unsigned)p.ksplit, p));
+  ++g_launch_count;
   return LMSFC_OK;
 }
 

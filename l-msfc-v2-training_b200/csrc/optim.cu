@@ -18,6 +18,7 @@ inline int grid1d(int64_t work_items) {
 // ---------------------------------------------------------------- sum of squares (grad norm)
 __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g, int64_t n4, const float* tail, int ntail,
                                                     float* accum) {
+  pdl_sync();
   float local = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n4; i += (int64_t)gridDim.x * TPB) {
     const float4 v = __ldg(g + i);
@@ -32,14 +33,14 @@ int sumsq_f32(const float* g, int64_t n, float* accum, cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
   LMSFC_CHECK_ARG(((uintptr_t)g & 15) == 0, "sumsq: pointer must be 16-byte aligned");
   const int64_t n4 = n / 4;
-  sumsq_kernel<<<grid1d(n4 > 0 ? n4 : 1), TPB, 0, s>>>((const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(sumsq_kernel, dim3(grid1d(n4 > 0 ? n4 : 1)), dim3(TPB), 0, s, (const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum);
   return LMSFC_OK;
 }
 
 // ---------------------------------------------------------------- Adam
 // prep: one thread bumps the step counter and derives {clip_coef, bias_corr1, bias_corr2, norm}
 __global__ void adam_prep_kernel(AdamArgs a) {
+  pdl_sync();
   const int step = *a.step + 1;
   *a.step = step;
   float clip = 1.f, norm = 0.f;
@@ -53,6 +54,7 @@ __global__ void adam_prep_kernel(AdamArgs a) {
   a.scratch[3] = norm;
 }
 __global__ void __launch_bounds__(TPB) adam_kernel(AdamArgs a) {
+  pdl_sync();
   const float clip = a.scratch[0], bc1 = a.scratch[1], bc2 = a.scratch[2];
   const float step_size = a.lr / bc1, rs_bc2 = rsqrtf(bc2);
   for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * TPB) {
@@ -66,10 +68,8 @@ __global__ void __launch_bounds__(TPB) adam_kernel(AdamArgs a) {
 }
 int adam_step(const AdamArgs& a, cudaStream_t s) {
   if (a.n == 0) return LMSFC_OK;
-  adam_prep_kernel<<<1, 1, 0, s>>>(a);
-  LMSFC_LAUNCH_CHECK();
-  adam_kernel<<<grid1d(a.n), TPB, 0, s>>>(a);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(adam_prep_kernel, dim3(1), dim3(1), 0, s, a);
+  LMSFC_LAUNCH(adam_kernel, dim3(grid1d(a.n)), dim3(TPB), 0, s, a);
   return LMSFC_OK;
 }
 
@@ -77,6 +77,7 @@ int adam_step(const AdamArgs& a, cudaStream_t s) {
 // fp32 NCHW -> bf16 NHWC (feature ingest for callers that hand over the reference's layout)
 __global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int C,
                                                            int HW) {
+  pdl_sync();
   __shared__ float tile[32][33];
   const int b = blockIdx.z;
   const int pb = blockIdx.x * 32, cb = blockIdx.y * 32;
@@ -93,8 +94,7 @@ __global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const float* __restri
 int nchw_to_nhwc_bf16(const float* in, __nv_bfloat16* out, int B, int C, int HW, cudaStream_t s) {
   if (B == 0 || C == 0 || HW == 0) return LMSFC_OK;
   dim3 grid((HW + 31) / 32, (C + 31) / 32, B);
-  nchw_to_nhwc_kernel<<<grid, dim3(32, 8), 0, s>>>(in, out, C, HW);
-  LMSFC_LAUNCH_CHECK();
+  LMSFC_LAUNCH(nchw_to_nhwc_kernel, dim3(grid), dim3(dim3(32, 8)), 0, s, in, out, C, HW);
   return LMSFC_OK;
 }
 

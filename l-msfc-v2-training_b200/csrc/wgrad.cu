@@ -73,6 +73,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_sync();                            // everything above touched no global memory
 
   if (warp < 4) {
     // ============ gather of the shifted operand: 64 pixel rows x 256 channels per K block ============
@@ -201,9 +202,9 @@ int launch_wgrad(WgradParams& p, cudaStream_t stream) {
   p.kb_per_split = ceil_div(p.kb_total, ksplit);
   ksplit = ceil_div(p.kb_total, p.kb_per_split);
   dim3 grid(p.ntaps * (p.Cg / WG_BN), p.Cd / (WG_BM * mt), ksplit);
-  if (mt == 2) wgrad_kernel<2><<<grid, WG_THREADS, WgCfg<2>::SMEM_BYTES, stream>>>(p);
-  else         wgrad_kernel<1><<<grid, WG_THREADS, WgCfg<1>::SMEM_BYTES, stream>>>(p);
-  LMSFC_LAUNCH_CHECK();
+  if (mt == 2) LMSFC_CUDA(launch_pdl(wgrad_kernel<2>, grid, dim3(WG_THREADS), (size_t)WgCfg<2>::SMEM_BYTES, stream, 1u, p));
+  else         LMSFC_CUDA(launch_pdl(wgrad_kernel<1>, grid, dim3(WG_THREADS), (size_t)WgCfg<1>::SMEM_BYTES, stream, 1u, p));
+  ++g_launch_count;
   return LMSFC_OK;
 }
 
