@@ -35,20 +35,30 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
+static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int esize, const void* base, uint64_t rows, uint64_t cols,
+                        uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols);
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_elems,
                       uint32_t box_rows, uint32_t box_cols) {
+  return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, rows, cols, row_stride_elems, box_rows, box_cols);
+}
+int make_tmap_2d_f32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_stride_elems,
+                     uint32_t box_rows, uint32_t box_cols) {
+  return make_tmap_2d(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, rows, cols, row_stride_elems, box_rows, box_cols);
+}
+static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int esize, const void* base, uint64_t rows, uint64_t cols,
+                        uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols) {
   EncodeTiledFn enc = get_encode();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled not available (no CUDA driver?)");
     return LMSFC_ERR_CUDA;
   }
-  LMSFC_CHECK_ARG(((uintptr_t)base & 15) == 0 && (row_stride_elems * 2) % 16 == 0,
+  LMSFC_CHECK_ARG(((uintptr_t)base & 15) == 0 && (row_stride_elems * esize) % 16 == 0,
                   "tensor map: base/stride must be 16-byte aligned");
   cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstr[1] = {row_stride_elems * 2};
+  cuuint64_t gstr[1] = {row_stride_elems * (uint64_t)esize};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+  CUresult r = enc(out, dt, 2, const_cast<void*>(base), gdim, gstr, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {

@@ -55,6 +55,7 @@ struct IgemmParams {
 //   G[d][widx(tap)][g] += sum_pix dense[pix][d] * gath[pixel(pix)+tap][g]
 struct WgradParams {
   CUtensorMap tmapA;        // filled by launch_wgrad: box {64 ch, 64 px}, SWIZZLE_128B
+  CUtensorMap tmapOut;      // filled by launch_wgrad: fp32 [Cd][T*Cg], box {32 cols, 128 rows}, SWIZZLE_128B
   const __nv_bfloat16* dense;  // dense operand, NHWC bf16 viewed as [M][Cd]
   const __nv_bfloat16* g0;  // gathered NHWC bf16 [B][Hin][Win][gc0]
   const __nv_bfloat16* g1;  // optional concat source [B][Hin][Win][gc1]
@@ -65,7 +66,7 @@ struct WgradParams {
   int ntaps;
   int8_t dy[kMaxTaps], dx[kMaxTaps];
   int16_t widx[kMaxTaps];
-  float* out;               // fp32 [Cd][T][Cg], accumulated with red.global.add
+  float* out;               // fp32 [Cd][T][Cg], accumulated by TMA reduce-add (cp.reduce.async.bulk.tensor ... .add)
   int Cd, Cg, T;
   int kb_total, kb_per_split;
 };
