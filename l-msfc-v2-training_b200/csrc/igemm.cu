@@ -18,6 +18,8 @@
 // owning CTA's shared memory (st.shared::cluster), and after one cluster barrier each CTA sums the S
 // partials of its own BLOCK_N/S columns and runs the epilogue for them -- no global atomics, no
 // workspace, no counters (the atomic version queued ~10 us of same-address reductions in L2).
+#include <stdlib.h>
+
 #include "igemm.cuh"
 
 namespace lmsfc {
@@ -189,6 +191,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_sync();                            // everything above touched no global memory
+#ifdef LMSFC_TIMELINE
+  const int dbg = p.dbg;                 // bit0: skip the gather, bit1: skip the TMA loads (timing experiments)
+#else
+  constexpr int dbg = 0;
+#endif
   if (tid == 0) TL(1);
 
   // output row of this thread (meaningful for the 128 gather/epilogue threads)
@@ -241,7 +248,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
         const int hi = hi0[i] + dy, wi = wi0[i] + dx;
         const bool ok = (unsigned)hi < (unsigned)p.Hin && (unsigned)wi < (unsigned)p.Win;
         const __nv_bfloat16* g = ok ? src + ((size_t)(pixbase[i] + hi * p.Win + wi) * C + coff) : src;
-        cp_async16(dst + i * 2048, g, ok ? 16u : 0u);
+        if (!(dbg & 1)) cp_async16(dst + i * 2048, g, ok ? 16u : 0u);
       }
       cp_async_mbar_arrive_noinc(&full_bar[stage]);
       if (++kc == kc_per_tap) { kc = 0; ++tap; }
@@ -277,9 +284,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       int tap = ph.tap_begin + kb_begin / kc_per_tap, kc = kb_begin % kc_per_tap;
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full_bar[stage], Cfg::B_STAGE_BYTES);
+        mbar_arrive_expect_tx(&full_bar[stage], (dbg & 2) ? 0 : Cfg::B_STAGE_BYTES);
         const uint32_t sb = smem_base + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES;
-        if (!B_MN) {
+        if (dbg & 2) {
+        } else if (!B_MN) {
           const int kcoord = (int)p.widx[tap] * ctot + kc * BLOCK_K;
           tma_load_2d(&p.tmapB, &full_bar[stage], sb, kcoord, n0);
         } else {
@@ -498,6 +506,9 @@ int launch_igemm(IgemmParams& p, cudaStream_t stream) {
   }
   dim3 grid(grid_x, p.N / bn, p.nphase * ksplit);
   p.ksplit = ksplit;
+#ifdef LMSFC_TIMELINE
+  { const char* e = getenv("LMSFC_WG_DBG"); p.dbg = e ? atoi(e) : 0; }
+#endif
   int rc = make_tmap_2d_bf16(&p.tmapB, p.w, (uint64_t)p.w_rows, (uint64_t)p.w_cols, (uint64_t)p.w_cols,
                              p.w_mn ? 64 : bn, 64);
   if (rc) return rc;

@@ -41,6 +41,7 @@ struct IgemmParams {
   int N;                    // output channels (row pitch of every output / aux tensor)
   int epi, relu, inverse;
   int ksplit;               // filled by launch_igemm: K slices per output tile = cluster size along z
+  int dbg;                  // TIMELINE builds only
   const float* bias;        // [N] or null
   __nv_bfloat16* out_bf16;  // nullable
   float* out_f32;           // nullable
@@ -69,6 +70,7 @@ struct WgradParams {
   float* out;               // fp32 [Cd][T][Cg], accumulated by TMA reduce-add (cp.reduce.async.bulk.tensor ... .add)
   int Cd, Cg, T;
   int kb_total, kb_per_split;
+  int dbg;                  // TIMELINE builds only
 };
 
 int launch_igemm(IgemmParams& p, cudaStream_t stream);

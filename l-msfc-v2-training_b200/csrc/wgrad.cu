@@ -9,6 +9,8 @@
 // the same 128-byte-row swizzled image.  One CTA = 128 dense channels x 256 gathered channels of
 // one filter tap over one K split; fp32 partials leave TMEM through shared-memory boxes and TMA
 // reduce-add (cp.reduce.async.bulk.tensor.2d ... .add.f32).
+#include <stdlib.h>
+
 #include "igemm.cuh"
 
 namespace lmsfc {
@@ -73,6 +75,11 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_sync();                            // everything above touched no global memory
+#ifdef LMSFC_TIMELINE
+  const int dbg = p.dbg;                 // bit0: skip the gather, bit1: skip the TMA loads (timing experiments)
+#else
+  constexpr int dbg = 0;
+#endif
 
   if (warp < 4) {
     // ============ gather of the shifted operand: 64 pixel rows x 256 channels per K block ============
@@ -100,6 +107,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
           ok = (unsigned)hi < (unsigned)p.Hin && (unsigned)wi < (unsigned)p.Win;
           if (ok) g = src + ((size_t)((b * p.Hin + hi) * p.Win + wi) * C + coff);
         }
+        if (dbg & 1) continue;
 #pragma unroll
         for (int seg = 0; seg < 4; ++seg)
           cp_async16(dst + seg * WG_SEG_BYTES + i * 2048, g + seg * 64, ok ? 16u : 0u);
@@ -151,7 +159,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
       int stage = 0, phase = 0;
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full_bar[stage], WG_A_BYTES);
+        mbar_arrive_expect_tx(&full_bar[stage], (dbg & 2) ? 0 : WG_A_BYTES);
+        if (dbg & 2) { if (++stage == WG_STAGES) { stage = 0; phase ^= 1; } continue; }
         const int pix0 = (kb_begin + kb) * WG_BK;
         const uint32_t sa = smem_base + stage * WG_STAGE_BYTES;
 #pragma unroll
@@ -212,6 +221,9 @@ int launch_wgrad(WgradParams& p, cudaStream_t stream) {
   if (rc) return rc;
   const int mt = (p.Cd % 256 == 0) ? 2 : 1;
   p.kb_total = ceil_div(p.M, WG_BK);
+#ifdef LMSFC_TIMELINE
+  { const char* e = getenv("LMSFC_WG_DBG"); p.dbg = e ? atoi(e) : 0; }
+#endif
   const int tiles = p.ntaps * (p.Cg / WG_BN) * (p.Cd / (WG_BM * mt));
   // split K (pixels) so that the grid fills, but does not exceed, one wave of the 148 SMs
   int ksplit = max(1, 148 / tiles);
