@@ -130,17 +130,32 @@ __device__ __forceinline__ void colsum_finish(const float (&acc)[8], int c8, int
 }
 
 namespace {
+// One scratch slot per CUDA stream: kernels of one stream serialise, kernels of different streams (the
+// weight-gradient side stream, the hyperprior side stream) may overlap and must not share partial sums.
+constexpr int kRedBlocksY = 296, kRedMaxC = 2048, kRedSlots = 16;
 float* g_red_scratch = nullptr;
 unsigned int* g_red_count = nullptr;
-constexpr int kRedBlocksY = 296, kRedMaxC = 2048;
+cudaStream_t g_red_streams[kRedSlots];
+int g_red_nstreams = 0;
 int ensure_reduce_scratch() {
   if (g_red_scratch) return LMSFC_OK;
-  LMSFC_CUDA(cudaMalloc(&g_red_scratch, sizeof(float) * kRedBlocksY * kRedMaxC));
-  LMSFC_CUDA(cudaMalloc(&g_red_count, sizeof(unsigned int) * 64));
-  LMSFC_CUDA(cudaMemset(g_red_count, 0, sizeof(unsigned int) * 64));
+  LMSFC_CUDA(cudaMalloc(&g_red_scratch, sizeof(float) * kRedSlots * kRedBlocksY * kRedMaxC));
+  LMSFC_CUDA(cudaMalloc(&g_red_count, sizeof(unsigned int) * kRedSlots * 64));
+  LMSFC_CUDA(cudaMemset(g_red_count, 0, sizeof(unsigned int) * kRedSlots * 64));
   LMSFC_CUDA(cudaDeviceSynchronize());
   return LMSFC_OK;
 }
+int red_slot(cudaStream_t s) {
+  for (int i = 0; i < g_red_nstreams; ++i)
+    if (g_red_streams[i] == s) return i;
+  if (g_red_nstreams < kRedSlots) {
+    g_red_streams[g_red_nstreams] = s;
+    return g_red_nstreams++;
+  }
+  return (int)(((uintptr_t)s >> 4) % kRedSlots);
+}
+float* red_scratch(cudaStream_t s) { return g_red_scratch + (size_t)red_slot(s) * kRedBlocksY * kRedMaxC; }
+unsigned int* red_count(cudaStream_t s) { return g_red_count + red_slot(s) * 64; }
 }  // namespace
 
 // ---------------------------------------------------------------- GDN helper passes
@@ -205,8 +220,8 @@ int gdn_t(const __nv_bfloat16* gy, const __nv_bfloat16* x, const __nv_bfloat16* 
   const int64_t maxy = (P + 7) / 8;
   if (by > maxy) by = maxy;
   LMSFC_LAUNCH(gdn_t_kernel, dim3(dim3(bx, (unsigned)by)), dim3(dim3(32, 8)), 0, s, (const uint4*)gy, (const uint4*)x, (const uint4*)rn,
-                                                                inverse, P, C8, (uint4*)t, g_beta, g_red_scratch,
-                                                                g_red_count);
+                                                                inverse, P, C8, (uint4*)t, g_beta, red_scratch(s),
+                                                                red_count(s));
   return LMSFC_OK;
 }
 
@@ -239,7 +254,7 @@ int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream
   int64_t by = (148 * 2 + bx - 1) / bx;   // ~2 blocks per SM, 8 x 16 B loads in flight per thread
   const int64_t maxy = (P + 7) / 8;
   if (by > maxy) by = maxy;
-  LMSFC_LAUNCH(colsum_kernel, dim3(dim3(bx, (unsigned)by)), dim3(dim3(32, 8)), 0, s, (const uint4*)g, P, C8, out, g_red_scratch, g_red_count);
+  LMSFC_LAUNCH(colsum_kernel, dim3(dim3(bx, (unsigned)by)), dim3(dim3(32, 8)), 0, s, (const uint4*)g, P, C8, out, red_scratch(s), red_count(s));
   return LMSFC_OK;
 }
 

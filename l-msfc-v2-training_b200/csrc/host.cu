@@ -47,6 +47,13 @@ int make_tmap_2d_f32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
 }
 static int make_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int esize, const void* base, uint64_t rows, uint64_t cols,
                         uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols) {
+  // cuTensorMapEncodeTiled is a driver entry point: make sure this thread (e.g. autograd's backward worker)
+  // has the primary context bound before the first call
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(0);
+    ctx_bound = true;
+  }
   EncodeTiledFn enc = get_encode();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled not available (no CUDA driver?)");

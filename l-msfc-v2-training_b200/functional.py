@@ -20,6 +20,43 @@ BF16, F32 = torch.bfloat16, torch.float32
 CL = torch.channels_last
 
 
+class SideStreams:
+    """Concurrency inside one train step (CUDA streams forked / joined inside the captured graph):
+
+    * `wgrad`: weight-gradient GEMMs (+ bias column sums) are off the backward critical path -- only the
+      optimiser needs them -- so they run beside the data-gradient chain; the latency-bound latent-resolution
+      layers (a few CTAs each) overlap almost entirely.
+    * `hyper`: in noise mode y_hat = y + U does not depend on the hyperprior, so h_a -> EntropyBottleneck ->
+      h_s -> Gaussian likelihood runs beside the synthesis transform (and its backward beside g_s's backward;
+      autograd replays every node on the stream it was recorded on).
+    Disabled (None) by default: stand-alone modules run on the caller's stream."""
+    wgrad = None
+    hyper = None
+    _join_queued = False
+
+    @classmethod
+    def enable(cls, device, wgrad=True, hyper=True):
+        cls.wgrad = torch.cuda.Stream(device=device) if wgrad else None
+        cls.hyper = torch.cuda.Stream(device=device) if hyper else None
+
+    @classmethod
+    def disable(cls):
+        cls.wgrad = cls.hyper = None
+
+    @classmethod
+    def queue_join(cls):
+        """Join the weight-gradient stream at the end of the running backward pass."""
+        if not cls._join_queued:
+            cls._join_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(cls._join)
+
+    @classmethod
+    def _join(cls):
+        cls._join_queued = False
+        if cls.wgrad is not None:
+            torch.cuda.current_stream().wait_stream(cls.wgrad)
+
+
 def _require_cuda(t):
     if not t.is_cuda:
         raise RuntimeError("l-msfc-v2-training_b200 runs on CUDA tensors only (no CPU fallback)")
@@ -148,29 +185,46 @@ class _ConvFn(torch.autograd.Function):
             ga = None if g_abs is None else nhwc(g_abs, BF16)
             L.abs_backward(ptr(gd), ptr(ga), ptr(y_f32), g.numel(), int(ctx.relu), ptr(g), st)
         d = state.desc(B, H, W, Ho, Wo)
-        # ---- weight / bias gradients, straight into param.grad
-        weight, bias = ctx.weight, ctx.bias
-        ready = []
-        if weight.requires_grad:
-            gw = grad_view(weight, (0, 2, 3, 1))
-            gb = grad_view(bias) if (bias is not None and bias.requires_grad) else None
-            if gw is not None:
-                L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(gw), ptr(gb), st)
-            else:  # foreign (non GEMM-layout) parameter: stage and add
-                tmp = torch.zeros((state.D0, state.T, state.D1), dtype=F32, device=g.device)
-                L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(tmp), ptr(gb), st)
-                weight.grad.add_(tmp.view(state.D0, state.k, state.k, state.D1).permute(0, 3, 1, 2))
-            ready.append(weight)
-            if gb is not None:
-                ready.append(bias)
-        # ---- data gradient (only source 0 is differentiable: source 1 is input data)
+        # ---- data gradient first: it is the critical path (only source 0 is differentiable: source 1 is input data)
         gx = None
         if ctx.need_dx:
             gx = empty_nhwc(B, state.c0, H, W, BF16, g.device)
             L.conv_dgrad(d, ptr(g), ptr(state.w_direct), state.c0, ptr(gx), st)
-        if state.grad_ready is not None and ready:
-            state.grad_ready(ready)
+        # ---- weight / bias gradients, straight into param.grad; on the side stream when one is enabled
+        weight, bias = ctx.weight, ctx.bias
+        if weight.requires_grad:
+            ws = SideStreams.wgrad
+            if ws is not None:
+                ev = torch.cuda.Event()
+                ev.record()                      # g is complete on the current stream
+                for t in (g, x0, x1):
+                    if t is not None:
+                        t.record_stream(ws)
+                with torch.cuda.stream(ws):
+                    ws.wait_event(ev)
+                    _ConvFn._wgrad(ctx, state, d, x0, x1, g, weight, bias)
+                SideStreams.queue_join()
+            else:
+                _ConvFn._wgrad(ctx, state, d, x0, x1, g, weight, bias)
         return gx, None, None, None, None, None, None, None
+
+    @staticmethod
+    def _wgrad(ctx, state, d, x0, x1, g, weight, bias):
+        st = stream()
+        ready = []
+        gw = grad_view(weight, (0, 2, 3, 1))
+        gb = grad_view(bias) if (bias is not None and bias.requires_grad) else None
+        if gw is not None:
+            L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(gw), ptr(gb), st)
+        else:  # foreign (non GEMM-layout) parameter: stage and add
+            tmp = torch.zeros((state.D0, state.T, state.D1), dtype=F32, device=g.device)
+            L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(tmp), ptr(gb), st)
+            weight.grad.add_(tmp.view(state.D0, state.k, state.k, state.D1).permute(0, 3, 1, 2))
+        ready.append(weight)
+        if gb is not None:
+            ready.append(bias)
+        if state.grad_ready is not None:
+            state.grad_ready(ready)        # the DP reducer records its event on the stream the gradient was produced on
 
 
 def conv_apply(state, x0, x1, weight, bias, relu=False, mode=0, out_hw=None):

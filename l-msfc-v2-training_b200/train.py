@@ -18,7 +18,7 @@ from .parallel import BucketedGradReducer
 
 class TrainStep:
     def __init__(self, model: LMSFC, lmbda=0.0130, lr=1e-4, aux_lr=1e-3, clip_max_norm=1.0, distributed=False,
-                 bucket_mb=16.0):
+                 bucket_mb=16.0, side_streams=True):
         self.model = model
         if model.arena is None:
             model.build_arena()
@@ -27,6 +27,8 @@ class TrainStep:
         self.opt = net_aux_optimizer(model, {"net": {"type": "Adam", "lr": lr}, "aux": {"type": "Adam", "lr": aux_lr}},
                                      clip_max_norm=clip_max_norm)
         self.reducer = BucketedGradReducer(model, bucket_mb=bucket_mb) if distributed else None
+        if side_streams:
+            Fn.SideStreams.enable(self.arena.device)
         self.graph = None
         self.static_in = None
         self.static_out = None
