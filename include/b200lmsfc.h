@@ -76,7 +76,9 @@ int lmsfc_reparam_backward_multi(const float* g_eff, const float* params, const 
                                  int nseg, int64_t max_n, float* g_params, void* stream);
 
 /* ------------------------------------------------------------------ entropy models (entropy_models/entropy_models.py)
- * mode: 0 "noise" (:161-165), 1 "dequantize" (:167-176).  noise: injected U(-.5,.5) draw (parity
+ * mode: 0 "noise" (:161-165), 1 "dequantize" (:167-176); lmsfc_gc_* also 2 "given" (input already quantised).
+ * lmsfc_gc_forward with scales == NULL only quantises (y_hat / y_hat_bf16), so the likelihood can run later / on
+ * another stream from the quantised values.  noise: injected U(-.5,.5) draw (parity
  * tests) or null -> in-kernel Philox keyed by (seed, offset [+ rng_state[1]]).  sum_ln (nullable):
  * += sum(ln likelihood), the rate term of losses/rate_distortion.py:52-55.  y_hat_bf16 (nullable): bf16
  * copy of y_hat, the operand of the next conv.  Backward: g_yhat (fp32) or g_yhat_bf16 (a dgrad output),

@@ -230,8 +230,8 @@ extern "C" int lmsfc_gc_forward(const float* y, const float* scales, const float
                                 int mode, float scale_bound, float lik_bound, uint64_t seed, uint64_t offset,
                                 const uint64_t* rng_state, float* y_hat, void* y_hat_bf16, float* lik, float* sum_ln,
                                 void* stream) {
-  LMSFC_CHECK_ARG(mode == 0 || mode == 1, "Invalid quantization mode: \"%d\"", mode);   // entropy_models.py:158-159
-  LMSFC_CHECK_ARG(n == 0 || (y && scales && y_hat && lik), "gc_forward: null operand");
+  LMSFC_CHECK_ARG(mode >= 0 && mode <= 2, "Invalid quantization mode: \"%d\"", mode);   // entropy_models.py:158-159
+  LMSFC_CHECK_ARG(n == 0 || (y && (scales ? (lik != nullptr) : (y_hat || y_hat_bf16))), "gc_forward: null operand");
   GcArgs a{y, scales, means, noise, y_hat, lik, sum_ln, (bf16*)y_hat_bf16, n, mode, scale_bound, lik_bound, seed, offset, rng_state};
   return gc_forward(a, ST(stream));
 }
@@ -239,7 +239,7 @@ extern "C" int lmsfc_gc_backward(const float* y_hat, const float* scales, const 
                                  const float* g_yhat, const void* g_yhat_bf16, int64_t n, int mode, float scale_bound,
                                  float lik_bound, float rate_coef, float* g_y, float* g_scales, float* g_means,
                                  void* stream) {
-  LMSFC_CHECK_ARG(mode == 0 || mode == 1, "Invalid quantization mode: \"%d\"", mode);
+  LMSFC_CHECK_ARG(mode >= 0 && mode <= 2, "Invalid quantization mode: \"%d\"", mode);
   LMSFC_CHECK_ARG(n == 0 || (y_hat && scales && g_y && g_scales), "gc_backward: null operand");
   GcBwdArgs a{y_hat, scales, means, g_lik, g_yhat, (const bf16*)g_yhat_bf16, g_y, g_scales, g_means, n, mode, scale_bound, lik_bound, rate_coef};
   return gc_backward(a, ST(stream));

@@ -56,17 +56,21 @@ __global__ void __launch_bounds__(256) gc_forward_kernel(GcArgs a) {
     if (a.mode == QUANT_NOISE) {
       const float u = a.noise ? a.noise[i] : philox_uniform(seed, off, (uint64_t)i);
       yh = y + u;                                  // entropy_models.py:161-165
-    } else {
+    } else if (a.mode == QUANT_DEQUANTIZE) {
       yh = rintf(y - mu) + mu;                     // :167-176 (torch.round = half to even)
+    } else {
+      yh = y;                                      // QUANT_GIVEN: the caller quantised already
     }
-    const float v = fabsf(yh - mu);
-    const float s = fmaxf(a.scales[i], a.scale_bound);
-    const float L = std_cumulative((0.5f - v) / s) - std_cumulative((-0.5f - v) / s);
-    const float lik = fmaxf(L, a.lik_bound);
-    a.y_hat[i] = yh;
+    if (a.y_hat) a.y_hat[i] = yh;
     if (a.y_hat_bf16) a.y_hat_bf16[i] = __float2bfloat16(yh);
-    a.lik[i] = lik;
-    local += __logf(lik);
+    if (a.scales) {                                // null: quantise only (the likelihood runs elsewhere)
+      const float v = fabsf(yh - mu);
+      const float s = fmaxf(a.scales[i], a.scale_bound);
+      const float L = std_cumulative((0.5f - v) / s) - std_cumulative((-0.5f - v) / s);
+      const float lik = fmaxf(L, a.lik_bound);
+      a.lik[i] = lik;
+      local += __logf(lik);
+    }
   }
   if (a.sum_ln) {
     __shared__ float red[32];
@@ -92,7 +96,7 @@ __global__ void __launch_bounds__(256) gc_backward_kernel(GcBwdArgs a) {
     if (!(sraw >= a.scale_bound || gs < 0.f)) gs = 0.f;
     const float sgn = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);
     const float gyh = a.g_yhat ? a.g_yhat[i] : (a.g_yhat_bf16 ? __bfloat162float(a.g_yhat_bf16[i]) : 0.f);
-    if (a.mode == QUANT_NOISE) {
+    if (a.mode != QUANT_DEQUANTIZE) {              // noise, or an already quantised input: identity path
       a.g_y[i] = gyh + gv * sgn;
       if (a.g_means) a.g_means[i] = -gv * sgn;
     } else {

@@ -4,7 +4,7 @@
 
 namespace lmsfc {
 
-enum : int { QUANT_NOISE = 0, QUANT_DEQUANTIZE = 1 };
+enum : int { QUANT_NOISE = 0, QUANT_DEQUANTIZE = 1, QUANT_GIVEN = 2 };
 
 struct GcArgs {
   const float *y, *scales, *means, *noise;   // means / noise nullable

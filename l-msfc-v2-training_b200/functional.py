@@ -421,6 +421,42 @@ def gc_apply(y, scales, means, noise, mode, scale_bound, lik_bound, rng=None, of
     return out, lik
 
 
+class _QuantNoiseFn(torch.autograd.Function):
+    """y_hat = y + U(-.5, .5) (entropy_models.py:161-165) as its own node: in noise mode the quantised
+    latent does not depend on the hyperprior, so the synthesis transform can start while the hyper path
+    (and later the likelihood) runs on another stream.  Returns (y_hat fp32, y_hat bf16)."""
+
+    @staticmethod
+    def forward(ctx, y, noise, rng, offset):
+        y_hat = torch.empty_like(y)
+        y_hat_b = torch.empty_like(y, dtype=BF16)
+        L.gc_forward(ptr(y), None, None, ptr(noise), y.numel(), 0, 0.0, 0.0, rng.seed if rng is not None else 0, offset,
+                     ptr(rng.state) if rng is not None else None, ptr(y_hat), ptr(y_hat_b), None, None, stream())
+        ctx.set_materialize_grads(False)
+        return y_hat, y_hat_b
+
+    @staticmethod
+    def backward(ctx, g, g_b):
+        if g is None:
+            out = None if g_b is None else g_b.to(F32)
+        else:
+            out = g if g_b is None else torch.add(g, g_b)      # fp32 + bf16 -> fp32, one pass
+        return out, None, None, None
+
+
+def quant_noise_apply(y, noise=None, rng=None, offset=1):
+    y = nhwc(y, F32)
+    if noise is not None:
+        noise = nhwc(noise, F32)
+    return _QuantNoiseFn.apply(y, noise, rng, offset)
+
+
+def gc_likelihood_apply(y_hat, scales, scale_bound, lik_bound):
+    """Gaussian likelihood of an already quantised latent (mode "given"); same node type as gc_apply."""
+    _, lik, _ = _GCFn.apply(nhwc(y_hat, F32), nhwc(scales, F32), None, None, 2, float(scale_bound), float(lik_bound), None, 0)
+    return lik
+
+
 class _EBFn(torch.autograd.Function):
     """EntropyBottleneck.forward, entropy_models.py:436-516, on the NHWC view [P][C].
     Returns (y_hat fp32, likelihood fp32, y_hat bf16).  `packed_grad` (optional, [C,58] fp32 view of

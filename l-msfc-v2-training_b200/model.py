@@ -67,30 +67,65 @@ class LMSFC(nn.Module):
         lv = self.spec.levels
         ps = tuple(Fn.nhwc(feats[k], Fn.BF16) for k in lv)
         self._share_rng(ps[0].device)
-        y, z, z2_hw = self.analysis(ps)
-        z_hat, z_lik = self.entropy_bottleneck(z, noise=noise_z)
-        scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
-        y_hat, y_lik = self.gaussian_conditional(y, scales, noise=noise_y)
+        level_hw = [p.shape[2:] for p in ps]
+        hs = Fn.SideStreams.hyper if self.training else None
+        if hs is None:
+            y, z, z2_hw = self.analysis(ps)
+            z_hat, z_lik = self.entropy_bottleneck(z, noise=noise_z)
+            scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
+            y_hat, y_lik = self.gaussian_conditional(y, scales, noise=noise_y)
+            x_hat = self.synthesis(getattr(y_hat, Fn._BF16_ATTR), level_hw)
+        else:
+            # noise mode: y_hat = y + U needs no hyperprior -> g_s starts right away on this stream while
+            # h_a -> EntropyBottleneck -> h_s -> Gaussian likelihood run on the hyper stream; autograd replays
+            # each node on the stream it was recorded on, so the two backward chains overlap as well.
+            eb, gc = self.entropy_bottleneck, self.gaussian_conditional
+            y, y_abs = self.encode_y(ps)
+            y_hat, y_hat_b = Fn.quant_noise_apply(y, noise_y, gc._rng(y.device) if noise_y is None else None, gc.rng_offset)
+            main = torch.cuda.current_stream()
+            ev = torch.cuda.Event()
+            ev.record(main)
+            for t in (y_abs, y_hat):
+                t.record_stream(hs)
+            with torch.cuda.stream(hs):
+                hs.wait_event(ev)
+                z, z2_hw = self.hyper_analysis(y_abs)
+                z_hat, z_lik = eb(z, noise=noise_z)
+                scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
+                y_lik = Fn.gc_likelihood_apply(y_hat, scales, gc.scale_bound_value,
+                                               gc.likelihood_bound if gc.use_likelihood_bound else 0.0)
+            x_hat = self.synthesis(y_hat_b, level_hw)
+            main.wait_stream(hs)
+            for t in (z, z_hat, z_lik, scales, y_lik, getattr(z_lik, Fn._SUM_LN_ATTR), getattr(y_lik, Fn._SUM_LN_ATTR)):
+                t.record_stream(main)
         if self.training and noise_z is None and noise_y is None:
             self.entropy_bottleneck.rng.advance()      # ONE shared counter bump per step (EB and GC share the RNG)
-        x_hat = self.synthesis(getattr(y_hat, Fn._BF16_ATTR), [p.shape[2:] for p in ps])
         return {"x_hat": dict(zip(lv, x_hat)),
                 "likelihoods": {"y": y_lik, "z": z_lik},
                 "latents": {"y": y, "z": z, "y_hat": y_hat, "z_hat": z_hat, "scales": scales},
                 "inputs_nhwc": dict(zip(lv, ps))}
 
-    def analysis(self, ps):
-        """g_a + h_a: (p2..p5 bf16 NHWC) -> y fp32, z fp32, spatial size of h_a's middle activation."""
+    def encode_y(self, ps):
+        """g_a: (p2..p5 bf16 NHWC) -> y fp32 and |y| bf16 (the input of h_a, models/google.py:294)."""
         p2, p3, p4, p5 = ps
         a = self.g_a
         e2 = a.gdn2(a.conv2(p2))
         e3 = a.gdn3(a.conv3(e2, p3))
         e4 = a.gdn4(a.conv4(e3, p4))
-        y, y_abs = a.conv5(e4, p5, latent_head=True)
+        return a.conv5(e4, p5, latent_head=True)
+
+    def hyper_analysis(self, y_abs):
+        """h_a: |y| -> z fp32 and the spatial size of its middle activation."""
         z1 = self.h_a["0"](y_abs, relu=True)
         z2 = self.h_a["2"](z1, relu=True)
         z, _ = self.h_a["4"](z2, latent_head=True)
-        return y, z, z2.shape[2:]
+        return z, z2.shape[2:]
+
+    def analysis(self, ps):
+        """g_a + h_a: (p2..p5 bf16 NHWC) -> y fp32, z fp32, spatial size of h_a's middle activation."""
+        y, y_abs = self.encode_y(ps)
+        z, z2_hw = self.hyper_analysis(y_abs)
+        return y, z, z2_hw
 
     def hyper_synthesis(self, z_hat_bf16, mid_hw, y_hw):
         """h_s: z_hat -> scales (fp32, ReLU'd as models/google.py:275-282)."""
