@@ -151,6 +151,10 @@ extern "C" int lmsfc_conv_wgrad(const lmsfc_conv_desc* d, const void* src0, cons
     p.Hin = d->Hout; p.Win = d->Wout;
   }
   p.M = p.B * p.Hg * p.Wg;
+  if (gbias && d->Cout == 256) {   // bias gradient by the spare CTAs of the weight-gradient wave
+    p.bias_src = (const bf16*)gout; p.bias_P = (long long)d->B * d->Hout * d->Wout; p.gbias = gbias;
+    return launch_wgrad(p, ST(stream));
+  }
   rc = launch_wgrad(p, ST(stream));
   if (rc) return rc;
   if (gbias) return colsum_bf16((const bf16*)gout, (int64_t)d->B * d->Hout * d->Wout, d->Cout, gbias, ST(stream));
@@ -182,26 +186,34 @@ extern "C" int lmsfc_gdn_forward(const void* x, const void* gamma_eff, const flo
 }
 
 extern "C" int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void* gamma_eff, int inverse,
-                                  int64_t P, int C, void* x2_scratch, void* t_scratch, void* gx, float* g_gamma_eff,
-                                  float* g_beta_eff, void* stream) {
-  LMSFC_CHECK_ARG(gy && x && rn && gamma_eff && x2_scratch && t_scratch && gx && g_gamma_eff && g_beta_eff,
+                                  int64_t P, int C, void* x2, int x2_ready, void* t_scratch, void* gx,
+                                  float* g_gamma_eff, float* g_beta_eff, void* stream) {
+  LMSFC_CHECK_ARG(gy && x && rn && gamma_eff && t_scratch && gx && g_beta_eff && (x2 || !g_gamma_eff),
                   "gdn_backward: null operand");
   LMSFC_CHECK_ARG(C % 256 == 0 && P > 0 && P < (1ll << 31), "gdn_backward: P=%lld C=%d", (long long)P, C);
   int rc = gdn_t((const bf16*)gy, (const bf16*)x, (const bf16*)rn, inverse, P, C, (bf16*)t_scratch, g_beta_eff, ST(stream));
   if (rc) return rc;
-  rc = square_bf16((const bf16*)x, (bf16*)x2_scratch, P * C, ST(stream));
-  if (rc) return rc;
+  if (x2 && !x2_ready) {
+    rc = square_bf16((const bf16*)x, (bf16*)x2, P * C, ST(stream));
+    if (rc) return rc;
+  }
   IgemmParams p;
   gdn_gemm_params(p, (const bf16*)t_scratch, (const bf16*)gamma_eff, P, C);
   p.w_mn = 1; p.w_ld_tap = C;      // s_j = sum_i gamma[i][j] t_i: gamma read as an MN-major operand
   p.epi = EPI_GDN_BWD; p.inverse = inverse; p.aux_x = (const bf16*)x; p.aux_gy = (const bf16*)gy; p.aux_rn = (const bf16*)rn;
   p.out_bf16 = (bf16*)gx;
   rc = launch_igemm(p, ST(stream));
-  if (rc) return rc;
+  if (rc || !g_gamma_eff) return rc;
+  return lmsfc_gdn_wgrad(t_scratch, x2, P, C, g_gamma_eff, stream);
+}
+
+extern "C" int lmsfc_gdn_wgrad(const void* t, const void* x2, int64_t P, int C, float* g_gamma_eff, void* stream) {
+  LMSFC_CHECK_ARG(t && x2 && g_gamma_eff, "gdn_wgrad: null operand");
+  LMSFC_CHECK_ARG(C % 256 == 0 && P > 0 && P < (1ll << 31), "gdn_wgrad: P=%lld C=%d", (long long)P, C);
   WgradParams q;
   memset(&q, 0, sizeof(q));
-  q.dense = (const bf16*)t_scratch; q.Cd = C; q.B = 1; q.Hg = 1; q.Wg = (int)P; q.M = (int)P;
-  q.g0 = (const bf16*)x2_scratch; q.gc0 = C; q.Cg = C; q.Hin = 1; q.Win = (int)P; q.sin = 1;
+  q.dense = (const bf16*)t; q.Cd = C; q.B = 1; q.Hg = 1; q.Wg = (int)P; q.M = (int)P;
+  q.g0 = (const bf16*)x2; q.gc0 = C; q.Cg = C; q.Hin = 1; q.Win = (int)P; q.sin = 1;
   q.ntaps = 1; q.T = 1; q.out = g_gamma_eff;
   return launch_wgrad(q, ST(stream));
 }

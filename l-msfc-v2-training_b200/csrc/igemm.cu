@@ -143,6 +143,7 @@ __device__ __forceinline__ unsigned long long gtimer() {
   do {                                                                                             \
     const int _c = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                 \
     if (_c < 64) g_timeline[_c * 16 + (slot)] = gtimer();                                          \
+    if (_c < 64 && (slot) >= 9) g_timeline[_c * 16 + (slot) + 2] = (unsigned long long)clock64();  \
   } while (0)
 #else
 #define TL(slot) do {} while (0)

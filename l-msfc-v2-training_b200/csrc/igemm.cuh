@@ -70,6 +70,15 @@ struct WgradParams {
   float* out;               // fp32 [Cd][T][Cg], accumulated by TMA reduce-add (cp.reduce.async.bulk.tensor ... .add)
   int Cd, Cg, T;
   int kb_total, kb_per_split;
+  // pixel index -> (b, hg, wg) by multiply-shift (filled by launch_wgrad): the gather recomputes it for every
+  // K block, and hardware integer division there bounded the whole main loop
+  uint32_t wg_mul, wg_shr, hg_mul, hg_shr;
+  int grid_x, grid_y, gemm_ctas;   // the launch is 1-D: GEMM CTAs (x fastest, then y, then K split) + bias CTAs
+  // optional bias gradient (column sums of grad_out [bias_P][256]) computed by the spare CTAs of the same wave
+  const __nv_bfloat16* bias_src;
+  long long bias_P;
+  float* gbias;
+  int bias_ctas;
   int dbg;                  // TIMELINE builds only
 };
 

@@ -33,7 +33,57 @@ struct WgCfg {
 };
 
 __device__ __forceinline__ void wg_epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+#ifdef LMSFC_TIMELINE
+// debug build only (make TIMELINE=1): %globaltimer stamps of the first 64 CTAs, read back by profiles/timeline.py
+__device__ unsigned long long g_wg_timeline[64 * 16];
+#define WTL(slot)                                                                                  \
+  do {                                                                                             \
+    const int _c = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                 \
+    unsigned long long _t;                                                                         \
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(_t));                                          \
+    if (_c < 64) g_wg_timeline[_c * 16 + (slot)] = _t;                                             \
+    if (_c < 64 && (slot) >= 9) g_wg_timeline[_c * 16 + (slot) + 2] = (unsigned long long)clock64(); \
+  } while (0)
+#else
+#define WTL(slot) do {} while (0)
+#endif
 }  // namespace
+
+__device__ __forceinline__ int fast_div(int n, uint32_t mul, uint32_t shr) {
+  return mul ? (int)(__umulhi((uint32_t)n, mul) >> shr) : n;
+}
+
+// Bias gradient = column sums of grad_out [P][256] (bf16), by CTA `idx` of `n` spare CTAs riding in the GEMM's wave:
+// 32 channel groups x 6 row lanes of 16-byte loads, lanes combined in shared memory, 256 float atomics per CTA.
+__device__ __forceinline__ void wg_bias_cta(const WgradParams& p, int idx, int n, float* red) {
+  const int tid = threadIdx.x, c8 = tid & 31, rl = tid >> 5;
+  const long long per = (p.bias_P + n - 1) / n;
+  const long long r0 = (long long)idx * per, r1 = min(p.bias_P, r0 + per);
+  const uint4* __restrict__ g = reinterpret_cast<const uint4*>(p.bias_src);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll 16
+  for (long long r = r0 + rl; r < r1; r += WG_THREADS / 32) {
+    const uint4 a = __ldg(g + r * 32 + c8);
+    const uint32_t av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      acc[2 * j] += __uint_as_float(av[j] << 16);
+      acc[2 * j + 1] += __uint_as_float(av[j] & 0xffff0000u);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[rl * 256 + c8 * 8 + j] = acc[j];
+  __syncthreads();
+  for (int c = tid; c < 256; c += WG_THREADS) {
+    float v = 0.f;
+#pragma unroll
+    for (int k = 0; k < WG_THREADS / 32; ++k) v += red[k * 256 + c];
+    atomicAdd(p.gbias + c, v);
+  }
+}
 
 template <int MT>
 __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_constant__ WgradParams p) {
@@ -48,16 +98,24 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
   uint64_t* tmem_full_bar = empty_bar + WG_STAGES;
   uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
 
+  const uint32_t smem_base = smem_u32(smem);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if ((int)blockIdx.x >= p.gemm_ctas) {    // spare CTA of the wave: bias gradient
+    pdl_sync();
+    wg_bias_cta(p, (int)blockIdx.x - p.gemm_ctas, p.bias_ctas, reinterpret_cast<float*>(smem));
+    return;
+  }
+  const int bx = (int)blockIdx.x % p.grid_x, byz = (int)blockIdx.x / p.grid_x;
+  const int by = byz % p.grid_y, bz = byz / p.grid_y;
   const int ntile_per_tap = p.Cg / WG_BN;
-  const int tap = blockIdx.x / ntile_per_tap;
-  const int n0 = (blockIdx.x % ntile_per_tap) * WG_BN;   // gathered-channel offset
-  const int d0 = blockIdx.y * WG_BM * MT;                 // dense-channel offset
-  const int kb_begin = blockIdx.z * p.kb_per_split;
+  const int tap = bx / ntile_per_tap;
+  const int n0 = (bx % ntile_per_tap) * WG_BN;            // gathered-channel offset
+  const int d0 = by * WG_BM * MT;                         // dense-channel offset
+  const int kb_begin = bz * p.kb_per_split;
   const int kb_end = min(kb_begin + p.kb_per_split, p.kb_total);
   const int nkb = kb_end - kb_begin;
   if (nkb <= 0) return;
-  const uint32_t smem_base = smem_u32(smem);
+  if (tid == 0) WTL(0);
 
   if (warp == 4 && lane == 0) {
     tma_prefetch_desc(&p.tmapA);
@@ -75,6 +133,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_sync();                            // everything above touched no global memory
+  if (tid == 0) WTL(1);
 #ifdef LMSFC_TIMELINE
   const int dbg = p.dbg;                 // bit0: skip the gather, bit1: skip the TMA loads (timing experiments)
 #else
@@ -101,8 +160,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
         bool ok = m < p.M;
         const __nv_bfloat16* g = src;
         if (ok) {
-          const int wg = m % p.Wg, t = m / p.Wg;
-          const int hg = t % p.Hg, b = t / p.Hg;
+          const int t = fast_div(m, p.wg_mul, p.wg_shr), wg = m - t * p.Wg;
+          const int b = fast_div(t, p.hg_mul, p.hg_shr), hg = t - b * p.Hg;
           const int hi = hg * p.sin + dy, wi = wg * p.sin + dx;
           ok = (unsigned)hi < (unsigned)p.Hin && (unsigned)wi < (unsigned)p.Win;
           if (ok) g = src + ((size_t)((b * p.Hin + hi) * p.Win + wi) * C + coff);
@@ -123,6 +182,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
     // L2 traffic instead of 32 scattered 16-byte atomics per warp instruction.  4 boxes rotate.
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
+    if (tid == 0) WTL(4);
     const int row = warp * 32 + lane;
     const int out_col0 = (int)p.widx[tap] * p.Cg + n0;
     int it = 0;
@@ -152,7 +212,9 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
         }
       }
     }
+    if (tid == 0) WTL(5);
     if (tid == 0) bulk_wait_group<0>();
+    if (tid == 0) WTL(7);
   } else if (warp == 4) {
     // ============ dense operand by TMA: 2*MT [64 px][64 ch] boxes per K block ============
     if (lane == 0) {
@@ -172,27 +234,36 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
   } else {
     // ============ MMA issuer: both operands MN-major (channels contiguous, K = pixel rows) ============
     if (lane == 0) {
+#ifdef LMSFC_TIMELINE
+      // timing experiment (results are garbage): bit2 / bit3 read the A / B stage image as a K-major tile
+      const uint32_t idesc = make_idesc_bf16(WG_BM, WG_BN, (dbg & 4) ? 0 : 1, (dbg & 8) ? 0 : 1);
+#else
       constexpr uint32_t idesc = make_idesc_bf16(WG_BM, WG_BN, 1, 1);
+#endif
       int stage = 0, phase = 0;
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
+        if (kb == 0) WTL(9);
         const uint32_t sa = smem_base + stage * WG_STAGE_BYTES;
         const uint32_t sb = sa + WG_A_BYTES;
 #pragma unroll
-        for (int k = 0; k < WG_BK / 16; ++k) {
-          // K step of 16 pixel rows = 2 KB; LBO = next 64-channel segment, SBO = next 8 rows
-          const uint64_t bd = make_sdesc_sw128(sb + k * 2048, WG_SEG_BYTES, 1024);
+        for (int mt = 0; mt < MT; ++mt) {
 #pragma unroll
-          for (int mt = 0; mt < MT; ++mt) {
-            const uint64_t ad = make_sdesc_sw128(sa + mt * 2 * WG_SEG_BYTES + k * 2048, WG_SEG_BYTES, 1024);
-            umma_bf16(tmem_base + mt * WG_BN, ad, bd, idesc, (kb | k) != 0);
+          for (int k = 0; k < WG_BK / 16; ++k) {
+            // K step of 16 pixel rows = 2 KB; LBO = next 64-channel segment, SBO = next 8 rows
+            uint64_t bd = make_sdesc_sw128(sb + k * 2048, WG_SEG_BYTES, 1024);
+            if (dbg & 8) bd = make_sdesc_sw128(sb + k * 32, 16, 1024);
+            uint64_t ad = make_sdesc_sw128(sa + mt * 2 * WG_SEG_BYTES + k * 2048, WG_SEG_BYTES, 1024);
+            if (dbg & 4) ad = make_sdesc_sw128(sa + mt * 2 * WG_SEG_BYTES + k * 32, 16, 1024);
+            umma_bf16(tmem_base + ((dbg & 16) ? 0 : mt * WG_BN), ad, bd, idesc, (kb | k) != 0);
           }
         }
         umma_commit(&empty_bar[stage]);
         if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
       }
       umma_commit(tmem_full_bar);
+      WTL(10);
     }
   }
   tc_fence_before();
@@ -201,6 +272,22 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
     tc_fence_after();
     tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
   }
+  if (tid == 0) WTL(8);
+}
+
+#ifdef LMSFC_TIMELINE
+extern "C" int lmsfc_debug_read_wg_timeline(unsigned long long* host64x16) {
+  return (int)cudaMemcpyFromSymbol(host64x16, g_wg_timeline, sizeof(unsigned long long) * 64 * 16);
+}
+#endif
+
+static void fast_div_magic(int d, uint32_t* mul, uint32_t* shr) {   // n / d == umulhi(n, mul) >> shr for 0 <= n < 2^31
+  if (d == 1) { *mul = 0; *shr = 0; return; }
+  int l = 0;
+  while ((1ll << l) < d) ++l;
+  const int pw = 31 + l;
+  *mul = (uint32_t)(((1ull << pw) + (uint64_t)d - 1) / (uint64_t)d);
+  *shr = (uint32_t)(pw - 32);
 }
 
 int launch_wgrad(WgradParams& p, cudaStream_t stream) {
@@ -219,18 +306,33 @@ int launch_wgrad(WgradParams& p, cudaStream_t stream) {
   if (rc) return rc;
   rc = make_tmap_2d_f32(&p.tmapOut, p.out, (uint64_t)p.Cd, (uint64_t)p.T * p.Cg, (uint64_t)p.T * p.Cg, WG_BM, 32);
   if (rc) return rc;
-  const int mt = (p.Cd % 256 == 0) ? 2 : 1;
+  int mt = (p.Cd % 256 == 0) ? 2 : 1;
+#ifdef LMSFC_TIMELINE
+  { const char* e = getenv("LMSFC_WG_MT"); if (e) mt = atoi(e); }
+#endif
   p.kb_total = ceil_div(p.M, WG_BK);
 #ifdef LMSFC_TIMELINE
   { const char* e = getenv("LMSFC_WG_DBG"); p.dbg = e ? atoi(e) : 0; }
 #endif
   const int tiles = p.ntaps * (p.Cg / WG_BN) * (p.Cd / (WG_BM * mt));
+  fast_div_magic(p.Wg, &p.wg_mul, &p.wg_shr);
+  fast_div_magic(p.Hg, &p.hg_mul, &p.hg_shr);
+  // bias CTAs: about one per 512 KB of grad_out (a lone SM streams ~0.1 TB/s), at most 16, inside the same wave
+  int spare = 0;
+  if (p.gbias) spare = (int)max(1ll, min(16ll, (p.bias_P * 512 + (512 << 10) - 1) / (512 << 10)));
   // split K (pixels) so that the grid fills, but does not exceed, one wave of the 148 SMs
-  int ksplit = max(1, 148 / tiles);
+  int ksplit = max(1, (148 - spare) / tiles);
   ksplit = max(1, min(ksplit, ceil_div(p.kb_total, 4)));   // >= 4 K blocks per CTA: amortise its 256 KB reduce-add
+#ifdef LMSFC_TIMELINE
+  { const char* e = getenv("LMSFC_WG_KSPLIT"); if (e) ksplit = atoi(e); }
+#endif
   p.kb_per_split = ceil_div(p.kb_total, ksplit);
   ksplit = ceil_div(p.kb_total, p.kb_per_split);
-  dim3 grid(p.ntaps * (p.Cg / WG_BN), p.Cd / (WG_BM * mt), ksplit);
+  p.grid_x = p.ntaps * (p.Cg / WG_BN);
+  p.grid_y = p.Cd / (WG_BM * mt);
+  p.gemm_ctas = p.grid_x * p.grid_y * ksplit;
+  p.bias_ctas = p.gbias ? max(spare, min(148 - p.gemm_ctas, 32)) : 0;
+  dim3 grid(p.gemm_ctas + p.bias_ctas);
   if (mt == 2) LMSFC_CUDA(launch_pdl(wgrad_kernel<2>, grid, dim3(WG_THREADS), (size_t)WgCfg<2>::SMEM_BYTES, stream, 1u, p));
   else         LMSFC_CUDA(launch_pdl(wgrad_kernel<1>, grid, dim3(WG_THREADS), (size_t)WgCfg<1>::SMEM_BYTES, stream, 1u, p));
   ++g_launch_count;

@@ -279,18 +279,17 @@ class _GDNFn(torch.autograd.Function):
         rn = torch.empty_like(x)
         L.gdn_forward(ptr(x), ptr(gamma_bf), ptr(beta_eff), int(state.inverse), P, C, ptr(x2), ptr(y), ptr(rn), st)
         ctx.state, ctx.beta, ctx.gamma = state, beta, gamma
-        ctx.save_for_backward(x, rn, gamma_bf)
+        ctx.save_for_backward(x, rn, gamma_bf, x2)       # x^2 is kept: 180 GB of HBM, no recompute pass in backward
         return y
 
     @staticmethod
     def backward(ctx, gy):
         state = ctx.state
-        x, rn, gamma_bf = ctx.saved_tensors
+        x, rn, gamma_bf, x2 = ctx.saved_tensors
         B, C, H, W = x.shape
         P = B * H * W
         dev, st = x.device, stream()
         gy = nhwc(gy, BF16)
-        x2 = torch.empty_like(x)
         t = torch.empty_like(x)
         gx = torch.empty_like(x)
         arena = state.arena
@@ -299,8 +298,17 @@ class _GDNFn(torch.autograd.Function):
         else:
             g_gamma_eff = torch.zeros((C, C), dtype=F32, device=dev)
             g_beta_eff = torch.zeros(C, dtype=F32, device=dev)
-        L.gdn_backward(ptr(gy), ptr(x), ptr(rn), ptr(gamma_bf), int(state.inverse), P, C, ptr(x2), ptr(t), ptr(gx),
-                       ptr(g_gamma_eff), ptr(g_beta_eff), st)
+        ws = SideStreams.wgrad if arena is not None else None
+        L.gdn_backward(ptr(gy), ptr(x), ptr(rn), ptr(gamma_bf), int(state.inverse), P, C, ptr(x2), 1, ptr(t), ptr(gx),
+                       None if ws is not None else ptr(g_gamma_eff), ptr(g_beta_eff), st)
+        if ws is not None:                       # gamma's gradient GEMM is off the critical path
+            ev = torch.cuda.Event()
+            ev.record()
+            t.record_stream(ws)
+            x2.record_stream(ws)
+            with torch.cuda.stream(ws):
+                ws.wait_event(ev)
+                L.gdn_wgrad(ptr(t), ptr(x2), P, C, ptr(g_gamma_eff), stream())
         beta, gamma = ctx.beta, ctx.gamma
         if arena is not None:
             arena.queue_finish_backward()       # one batched reparam-backward at the end of this backward pass

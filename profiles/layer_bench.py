@@ -72,7 +72,7 @@ def main():
             gg, gbt = torch.zeros(ci, ci, device=dev), torch.zeros(ci, device=dev)
             Pn = B * hi * wi
             fw = lambda: L.gdn_forward(P(x), P(gam), P(beta), inv, Pn, ci, P(x2), P(y), P(rn), L.stream())
-            bw = lambda: L.gdn_backward(P(gy), P(x), P(rn), P(gam), inv, Pn, ci, P(x2), P(t), P(gx), P(gg), P(gbt), L.stream())
+            bw = lambda: L.gdn_backward(P(gy), P(x), P(rn), P(gam), inv, Pn, ci, P(x2), 1, P(t), P(gx), P(gg), P(gbt), L.stream())
             fw()
             t_f, t_fc, t_b = timeit(fw), timeit(fw, cold=True, n=1), timeit(bw)
             fl = 2.0 * ci * co * hi * wi * B

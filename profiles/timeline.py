@@ -35,4 +35,30 @@ for (name, kind, k, s, c, B, hi, wi, ho, wo) in CASES:
             continue
         r = buf[cta]
         print(f"  cta {cta:2d}: " + "  ".join(f"{NAMES[i]} {((int(r[i]) - int(t0)) / 1e3):.2f}" for i in (0, 1, 9, 2, 3, 10, 4, 5, 6, 7, 8) if r[i] >= t0))
-    print(f"  last exit over recorded CTAs: {(int(buf[:, 8].max()) - int(t0)) / 1e3:.2f} us")
+    print(f"  last exit over recorded CTAs: {(int(buf[:, 8].max()) - int(t0)) / 1e3:.2f} us;  SM clock over cta 0's MMA loop "
+          f"{(int(buf[0, 12]) - int(buf[0, 11])) / max(1, int(buf[0, 10]) - int(buf[0, 9])) * 1e3:.0f} MHz")
+
+# ---- weight-gradient kernel (same debug build): stage stamps of a few CTAs
+WNAMES = {0: "start", 1: "setup", 9: "mma-first", 10: "mma-last-issued", 4: "tmem-full", 5: "reds-issued", 7: "reds-done", 8: "exit"}
+for (name, k, s, B, hi, wi, ho, wo) in [("conv2 wgrad", 5, 2, 16, 64, 64, 32, 32), ("head3 wgrad", 3, 1, 16, 32, 32, 32, 32),
+                                        ("head5 wgrad", 3, 1, 16, 8, 8, 8, 8)]:
+    m = layers.Conv(256, 256, k, s).to(dev)
+    st = m._state
+    st.refresh(m.weight)
+    d = st.desc(B, hi, wi, ho, wo)
+    x, gy = bf(B, 256, hi, wi), bf(B, 256, ho, wo)
+    gw = torch.zeros((st.D0, st.T, st.D1), device=dev)
+    for _ in range(3):
+        L.conv_wgrad(d, P(x), None, P(gy), P(gw), None, L.stream())
+    torch.cuda.synchronize()
+    buf = np.zeros((64, 16), dtype=np.uint64)
+    L.lib.lmsfc_debug_read_wg_timeline(ctypes.c_void_p(buf.ctypes.data))
+    t0 = buf[:, 0][buf[:, 0] > 0].min()
+    print(f"== {name}")
+    for cta in (0, 1, 31, 63):
+        r = buf[cta]
+        if r[0] == 0:
+            continue
+        print(f"  cta {cta:2d}: " + "  ".join(f"{WNAMES[i]} {((int(r[i]) - int(t0)) / 1e3):.2f}" for i in (0, 1, 9, 10, 4, 5, 7, 8) if r[i] >= t0))
+    print(f"  last exit over recorded CTAs: {(int(buf[:, 8].max()) - int(t0)) / 1e3:.2f} us;  SM clock over cta 0's MMA loop "
+          f"{(int(buf[0, 12]) - int(buf[0, 11])) / max(1, int(buf[0, 10]) - int(buf[0, 9])) * 1e3:.0f} MHz")

@@ -31,3 +31,13 @@ for (name, k, s, B, hi, wi, ho, wo) in [("conv2", 5, 2, 16, 64, 64, 32, 32), ("h
     tf = t(lambda: L.conv_forward(d, P(x), None, P(st.w_direct), P(m.bias), 0, P(y), None, None, L.stream()))
     td = t(lambda: L.conv_dgrad(d, P(gy), P(st.w_direct), 256, P(gx), L.stream()))
     print(f"LMSFC_WG_DBG={os.environ.get('LMSFC_WG_DBG','0')} {name}: wgrad {tw:.1f} us  fwd {tf:.1f} us  dgrad {td:.1f} us (graph-timed, per launch)")
+    import ctypes, numpy as np
+    def loop(fn_read):        # cta 0: MMA loop duration in ns and SM cycles (stamps of the last launch)
+        buf = np.zeros((64, 16), dtype=np.uint64); fn_read(ctypes.c_void_p(buf.ctypes.data)); r = buf[0]
+        return int(r[10]) - int(r[9]), int(r[12]) - int(r[11])
+    L.conv_wgrad(d, P(x), None, P(gy), P(gw), None, L.stream()); torch.cuda.synchronize()
+    ns, cyc = loop(L.lib.lmsfc_debug_read_wg_timeline)
+    print(f"   wgrad cta0 MMA loop after sustained run: {ns/1e3:.1f} us, {cyc} cyc ({cyc/ns*1e3:.0f} MHz)")
+    L.conv_forward(d, P(x), None, P(st.w_direct), P(m.bias), 0, P(y), None, None, L.stream()); torch.cuda.synchronize()
+    ns, cyc = loop(L.lib.lmsfc_debug_read_timeline)
+    print(f"   fwd   cta0 MMA loop after sustained run: {ns/1e3:.1f} us, {cyc} cyc ({cyc/ns*1e3:.0f} MHz)")
