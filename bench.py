@@ -189,9 +189,8 @@ def run_b200(args):
     feats = {k: v.to(dev, non_blocking=True) for k, v in host[0].items()}
     h2d = sum(v.numel() * 2 for v in host[0].values())
     ts.step(feats)                           # eager once (lazy init), then capture the graph
-    c0 = L.launch_count()
-    ts.capture(feats, warmup=1)
-    launches_per_step = (L.launch_count() - c0) // 2       # 1 warm-up + 1 captured iteration
+    ts.capture(feats, warmup=1, pipelined=not args.sequential)
+    launches_per_step = ts.launches_per_step               # launches of this library recorded into the graph
 
     def barrier():
         if world > 1:
@@ -241,6 +240,7 @@ def run_b200(args):
     f1.record()
     barrier()
     ms_e2e = f0.elapsed_time(f1)
+    ts.flush()                               # pipelined order: apply the update of the last backward pass
     if sampler:
         sampler.stop = True
         sampler.join()
@@ -259,6 +259,8 @@ def run_b200(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": "L-MSFC training, batch 16/GPU synthetic P2-P5 feature crops (256x256 input), bf16, one lambda",
                        "lambda": LMBDA, "spec": "N=M=F=256 (spec.py)", "cuda_graph": True,
+                       "step_order": "sequential" if args.sequential else
+                                     "pipelined: each step = [Adam of the previous backward || forward] -> backward (train.py)",
                        "l2": "per-step working set (weights+Adam state+activations ~0.9 GB) exceeds the 126 MB L2",
                        "parallelism": f"dp{world}"},
             "e2e": {"value": world * BATCH * args.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
@@ -287,6 +289,8 @@ if __name__ == "__main__":
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--sequential", action="store_true",
+                    help="capture the eager order (update at the end of the step) instead of the rotated, pipelined one")
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)

@@ -133,6 +133,14 @@ int lmsfc_adam_step(float* p, float* m, float* v, const float* g, void* p_bf16, 
                     float beta2, float eps, float max_norm, const float* sumsq, int* step, float* scratch,
                     void* stream);
 
+/* The same step in two parts, so that the element-wise pass can run slice by slice (in the order the next forward
+ * pass needs the weights) on a stream of its own: adam_prep bumps `step` and fills scratch from sumsq; adam_update
+ * applies it to one 16-byte aligned slice and, with zero_g, clears the slice's gradient in the same pass. */
+int lmsfc_adam_prep(float beta1, float beta2, float max_norm, const float* sumsq, int* step, float* scratch,
+                    void* stream);
+int lmsfc_adam_update(float* p, float* m, float* v, float* g, void* p_bf16, int64_t n, float lr, float beta1,
+                      float beta2, float eps, const float* scratch, int zero_g, void* stream);
+
 /* ------------------------------------------------------------------ CDF tables (cpp_exts/ops/ops.cpp:40-109) */
 /* host pointers; cdf must hold n+1 entries.  Errors mirror the reference's ValueError cases. */
 int lmsfc_pmf_to_quantized_cdf(const float* pmf_host, int n, int precision, uint32_t* cdf_host);

@@ -53,6 +53,8 @@ _SIGS = {
     "lmsfc_nchw_to_nhwc_bf16": [P, P, c_int, c_int, c_int, P],
     "lmsfc_sumsq": [P, c_int64, P, P],
     "lmsfc_adam_step": [P, P, P, P, P, c_int64, c_float, c_float, c_float, c_float, c_float, P, P, P, P],
+    "lmsfc_adam_prep": [c_float, c_float, c_float, P, P, P, P],
+    "lmsfc_adam_update": [P, P, P, P, P, c_int64, c_float, c_float, c_float, c_float, P, c_int, P],
     "lmsfc_pmf_to_quantized_cdf": [P, c_int, c_int, P],
     "lmsfc_pmf_rows_to_cdf": [P, c_int, P, P, c_int, c_int, P, c_int, P, P],
 }

@@ -314,8 +314,20 @@ extern "C" int lmsfc_adam_step(float* p, float* m, float* v, const float* g, voi
                                float beta2, float eps, float max_norm, const float* sumsq, int* step, float* scratch,
                                void* stream) {
   LMSFC_CHECK_ARG(n == 0 || (p && m && v && g && step && scratch), "adam_step: null operand");
-  AdamArgs a{p, m, v, g, (bf16*)p_bf16, n, lr, beta1, beta2, eps, max_norm, sumsq, step, scratch};
+  AdamArgs a{p, m, v, const_cast<float*>(g), (bf16*)p_bf16, n, lr, beta1, beta2, eps, max_norm, sumsq, step, scratch, 0};
   return adam_step(a, ST(stream));
+}
+extern "C" int lmsfc_adam_prep(float beta1, float beta2, float max_norm, const float* sumsq, int* step, float* scratch,
+                               void* stream) {
+  LMSFC_CHECK_ARG(step && scratch, "adam_prep: null operand");
+  AdamArgs a{nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0.f, beta1, beta2, 0.f, max_norm, sumsq, step, scratch, 0};
+  return adam_prep(a, ST(stream));
+}
+extern "C" int lmsfc_adam_update(float* p, float* m, float* v, float* g, void* p_bf16, int64_t n, float lr, float beta1,
+                                 float beta2, float eps, const float* scratch, int zero_g, void* stream) {
+  LMSFC_CHECK_ARG(n == 0 || (p && m && v && g && scratch), "adam_update: null operand");
+  AdamArgs a{p, m, v, g, (bf16*)p_bf16, n, lr, beta1, beta2, eps, 0.f, nullptr, nullptr, const_cast<float*>(scratch), zero_g};
+  return adam_update(a, ST(stream));
 }
 extern "C" int lmsfc_pmf_to_quantized_cdf(const float* pmf_host, int n, int precision, uint32_t* cdf_host) {
   LMSFC_CHECK_ARG(pmf_host && cdf_host && n >= 0, "pmf_to_quantized_cdf: null operand");

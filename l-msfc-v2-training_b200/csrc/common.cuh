@@ -77,6 +77,10 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
   cfg.numAttrs = n;
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
+// Note (measured, profiles/trace_step.py): an SM only changes its L1 / shared split when it is empty, so a GEMM CTA
+// (200 KB of pipeline) of a concurrent stream joins an SM running one of the element-wise kernels only after that
+// grid drains.  Forcing the max-shared carve-out on them lets the CTAs co-reside -- and made the step SLOWER (the
+// convolutions already use most of the L2 -> SM bandwidth; sharing it with Adam doubled both run times).
 #define LMSFC_LAUNCH(kernel, grid, block, smem, stream, ...)                                      \
   do {                                                                                            \
     LMSFC_CUDA(::lmsfc::launch_pdl(kernel, grid, block, smem, stream, 1u, __VA_ARGS__));          \

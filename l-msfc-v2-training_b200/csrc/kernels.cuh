@@ -76,15 +76,18 @@ int nchw_to_nhwc_bf16(const float* in, __nv_bfloat16* out, int B, int C, int HW,
 int sumsq_f32(const float* g, int64_t n, float* accum, cudaStream_t s);
 struct AdamArgs {
   float *p, *m, *v;
-  const float* g;
+  float* g;                  // read; zeroed in the same pass when zero_g
   __nv_bfloat16* p_bf16;     // nullable: bf16 shadow written in the same pass
   int64_t n;
   float lr, beta1, beta2, eps, max_norm;   // max_norm <= 0: no clipping
   const float* sumsq;        // device scalar with sum(g^2) (clip_grad_norm_); nullable
   int* step;                 // device step counter, incremented by the prep kernel
   float* scratch;            // >= 4 floats: {clip_coef, bias_corr1, bias_corr2, grad_norm}
+  int zero_g;
 };
 int adam_step(const AdamArgs& a, cudaStream_t s);
+int adam_prep(const AdamArgs& a, cudaStream_t s);     // step counter + clip / bias-correction scalars
+int adam_update(const AdamArgs& a, cudaStream_t s);   // the element-wise pass, given a prepared scratch
 
 // ---- cdf.cu
 int pmf_to_quantized_cdf_host(const float* pmf, int n, int precision, uint32_t* cdf);

@@ -53,24 +53,86 @@ __global__ void adam_prep_kernel(AdamArgs a) {
   a.scratch[2] = 1.f - powf(a.beta2, (float)step);
   a.scratch[3] = norm;
 }
-__global__ void __launch_bounds__(TPB) adam_kernel(AdamArgs a) {
+__device__ __forceinline__ void adam_one(float g, float& m, float& v, float& p, float clip, float b1, float b2,
+                                         float step_size, float rs_bc2, float eps) {
+  g *= clip;
+  m = b1 * m + (1.f - b1) * g;
+  v = b2 * v + (1.f - b2) * g * g;
+  p = p - step_size * m / (sqrtf(v) * rs_bc2 + eps);
+}
+// 30 B of HBM traffic per parameter (34 with zero_g).  2 CTAs of 256 threads per SM, 2 x 4 independent 16-byte
+// loads per thread in flight: a small footprint on purpose -- in the pipelined step this kernel shares the SMs with
+// the forward convolutions (a grid that fills every thread slot would hold their CTAs back until it ends).
+constexpr int ADAM_CTAS_PER_SM = 2;
+__device__ __forceinline__ void adam_quad(const float4& g, float4& m, float4& v, float4& p, float clip, float b1, float b2,
+                                          float step_size, float rs_bc2, float eps) {
+  adam_one(g.x, m.x, v.x, p.x, clip, b1, b2, step_size, rs_bc2, eps);
+  adam_one(g.y, m.y, v.y, p.y, clip, b1, b2, step_size, rs_bc2, eps);
+  adam_one(g.z, m.z, v.z, p.z, clip, b1, b2, step_size, rs_bc2, eps);
+  adam_one(g.w, m.w, v.w, p.w, clip, b1, b2, step_size, rs_bc2, eps);
+}
+__global__ void __launch_bounds__(TPB, 4) adam_kernel(AdamArgs a) {
   pdl_sync();
   const float clip = a.scratch[0], bc1 = a.scratch[1], bc2 = a.scratch[2];
   const float step_size = a.lr / bc1, rs_bc2 = rsqrtf(bc2);
-  for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * TPB) {
-    const float g = a.g[i] * clip;
-    const float m = a.beta1 * a.m[i] + (1.f - a.beta1) * g;
-    const float v = a.beta2 * a.v[i] + (1.f - a.beta2) * g * g;
-    const float p = a.p[i] - step_size * m / (sqrtf(v) * rs_bc2 + a.eps);
+  const int64_t n4 = a.n >> 2, stride = (int64_t)gridDim.x * TPB;
+  float4* __restrict__ p4 = reinterpret_cast<float4*>(a.p);
+  float4* __restrict__ m4 = reinterpret_cast<float4*>(a.m);
+  float4* __restrict__ v4 = reinterpret_cast<float4*>(a.v);
+  float4* __restrict__ g4 = reinterpret_cast<float4*>(a.g);
+  uint2* __restrict__ s4 = reinterpret_cast<uint2*>(a.p_bf16);
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  for (; i + stride < n4; i += 2 * stride) {
+    const int64_t j = i + stride;
+    const float4 g0 = __ldcs(g4 + i), g1 = __ldcs(g4 + j);
+    float4 m0 = __ldcs(m4 + i), m1 = __ldcs(m4 + j);
+    float4 v0 = __ldcs(v4 + i), v1 = __ldcs(v4 + j);
+    float4 p0 = __ldcs(p4 + i), p1 = __ldcs(p4 + j);
+    adam_quad(g0, m0, v0, p0, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
+    adam_quad(g1, m1, v1, p1, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
+    __stcs(m4 + i, m0); __stcs(v4 + i, v0); __stcs(p4 + i, p0);
+    __stcs(m4 + j, m1); __stcs(v4 + j, v1); __stcs(p4 + j, p1);
+    if (a.p_bf16) {                                            // read again by the next forward: default caching
+      s4[i] = make_uint2(pack_bf16(p0.x, p0.y), pack_bf16(p0.z, p0.w));
+      s4[j] = make_uint2(pack_bf16(p1.x, p1.y), pack_bf16(p1.z, p1.w));
+    }
+    if (a.zero_g) { g4[i] = zero; g4[j] = zero; }
+  }
+  if (i < n4) {
+    const float4 g0 = __ldcs(g4 + i);
+    float4 m0 = __ldcs(m4 + i), v0 = __ldcs(v4 + i), p0 = __ldcs(p4 + i);
+    adam_quad(g0, m0, v0, p0, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
+    __stcs(m4 + i, m0); __stcs(v4 + i, v0); __stcs(p4 + i, p0);
+    if (a.p_bf16) s4[i] = make_uint2(pack_bf16(p0.x, p0.y), pack_bf16(p0.z, p0.w));
+    if (a.zero_g) g4[i] = zero;
+  }
+  if (blockIdx.x == 0 && (int64_t)threadIdx.x < a.n - n4 * 4) {   // scalar tail
+    const int64_t i = n4 * 4 + threadIdx.x;
+    float m = a.m[i], v = a.v[i], p = a.p[i];
+    adam_one(a.g[i], m, v, p, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
     a.m[i] = m; a.v[i] = v; a.p[i] = p;
     if (a.p_bf16) a.p_bf16[i] = __float2bfloat16(p);
+    if (a.zero_g) a.g[i] = 0.f;
   }
+}
+int adam_prep(const AdamArgs& a, cudaStream_t s) {
+  LMSFC_LAUNCH(adam_prep_kernel, dim3(1), dim3(1), 0, s, a);
+  return LMSFC_OK;
+}
+int adam_update(const AdamArgs& a, cudaStream_t s) {
+  if (a.n == 0) return LMSFC_OK;
+  LMSFC_CHECK_ARG((((uintptr_t)a.p | (uintptr_t)a.m | (uintptr_t)a.v | (uintptr_t)a.g) & 15) == 0 &&
+                      ((uintptr_t)a.p_bf16 & 7) == 0, "adam: arena slices must be 16-byte aligned");
+  const int64_t quads = (a.n + 3) / 4, want = (quads + 2 * TPB - 1) / (2 * TPB);
+  const int grid = (int)max((int64_t)1, min(want, (int64_t)148 * ADAM_CTAS_PER_SM));
+  LMSFC_LAUNCH(adam_kernel, dim3(grid), dim3(TPB), 0, s, a);
+  return LMSFC_OK;
 }
 int adam_step(const AdamArgs& a, cudaStream_t s) {
   if (a.n == 0) return LMSFC_OK;
-  LMSFC_LAUNCH(adam_prep_kernel, dim3(1), dim3(1), 0, s, a);
-  LMSFC_LAUNCH(adam_kernel, dim3(grid1d(a.n)), dim3(TPB), 0, s, a);
-  return LMSFC_OK;
+  if (int rc = adam_prep(a, s)) return rc;
+  return adam_update(a, s);
 }
 
 // ---------------------------------------------------------------- layout

@@ -29,19 +29,24 @@ class SideStreams:
     * `hyper`: in noise mode y_hat = y + U does not depend on the hyperprior, so h_a -> EntropyBottleneck ->
       h_s -> Gaussian likelihood runs beside the synthesis transform (and its backward beside g_s's backward;
       autograd replays every node on the stream it was recorded on).
+    * `opt`: the pipelined train step (train.TrainStep.capture(pipelined=True)) runs clip + Adam of the PREVIOUS
+      backward pass here, slice by slice in the order the forward pass consumes the weights, so the HBM-bound
+      update hides under the tensor-bound forward convolutions.
     Disabled (None) by default: stand-alone modules run on the caller's stream."""
     wgrad = None
     hyper = None
+    opt = None
     _join_queued = False
 
     @classmethod
-    def enable(cls, device, wgrad=True, hyper=True):
+    def enable(cls, device, wgrad=True, hyper=True, opt=True):
         cls.wgrad = torch.cuda.Stream(device=device) if wgrad else None
         cls.hyper = torch.cuda.Stream(device=device) if hyper else None
+        cls.opt = torch.cuda.Stream(device=device) if opt else None
 
     @classmethod
     def disable(cls):
-        cls.wgrad = cls.hyper = None
+        cls.wgrad = cls.hyper = cls.opt = None
 
     @classmethod
     def queue_join(cls):

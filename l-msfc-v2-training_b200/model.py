@@ -110,12 +110,21 @@ class LMSFC(nn.Module):
         p2, p3, p4, p5 = ps
         a = self.g_a
         e2 = a.gdn2(a.conv2(p2))
+        self._gate("g_a.conv3.weight")
         e3 = a.gdn3(a.conv3(e2, p3))
         e4 = a.gdn4(a.conv4(e3, p4))
         return a.conv5(e4, p5, latent_head=True)
 
+    def _gate(self, name):
+        """Pipelined train step: wait (on the current stream) for the optimiser slice that starts at this parameter."""
+        if self.arena is not None and self.arena.gates:
+            ev = self.arena.gates.get(name)
+            if ev is not None:
+                torch.cuda.current_stream().wait_event(ev)
+
     def hyper_analysis(self, y_abs):
         """h_a: |y| -> z fp32 and the spatial size of its middle activation."""
+        self._gate("h_a.0.weight")
         z1 = self.h_a["0"](y_abs, relu=True)
         z2 = self.h_a["2"](z1, relu=True)
         z, _ = self.h_a["4"](z2, latent_head=True)
@@ -138,6 +147,7 @@ class LMSFC(nn.Module):
         """g_s: y_hat -> (p2_hat, p3_hat, p4_hat, p5_hat), each cropped to its level's H x W."""
         s = self.g_s
         hw2, hw3, hw4, hw5 = level_hw
+        self._gate("h_a.0.weight")
         d5 = s.igdn5(s.up5(y_hat_bf16, out_hw=hw5))
         p5h = s.head5(d5)
         d4 = s.igdn4(s.up4(d5, out_hw=hw4))
@@ -317,6 +327,8 @@ class ParamArena:
                 st.g_gamma_eff = self._grads_all[r[4]:r[4] + C * C].view(C, C)
         self._gdn_versions = None
         self._finish_queued = False
+        self.gates = {}            # parameter name -> event of the optimiser slice starting there (train.TrainStep)
+        self.n_net = n_net
         # ---- bf16 GEMM operands of the conv weights: slices of one shadow of the whole arena
         self.net_bf16 = torch.empty(self.net_params.numel(), dtype=torch.bfloat16, device=dev)
         for m in model.conv_layers():

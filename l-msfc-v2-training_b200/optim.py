@@ -33,17 +33,31 @@ class FusedAdam:
         self.zero_buffer.zero_()
 
     def step(self):
-        st = stream()
-        n = self.params.numel()
-        clip = self.clip_max_norm > 0
-        if clip:
-            self.sumsq.zero_()
-            L.sumsq(ptr(self.grads), n, ptr(self.sumsq), st)
-        L.adam_step(ptr(self.params), ptr(self.m), ptr(self.v), ptr(self.grads), ptr(self.bf16_shadow), n, self.lr,
-                    self.betas[0], self.betas[1], self.eps, self.clip_max_norm, ptr(self.sumsq) if clip else None,
-                    ptr(self.step_count), ptr(self.scratch), st)
+        self.accumulate_norm()
+        self.prep()
+        self.update(0, self.params.numel())
         if self.after_step is not None:
             self.after_step()
+
+    # ---- the same step in parts (pipelined train step: norm at the end of backward, update slices next replay)
+    def accumulate_norm(self):
+        """sum(g^2) of the whole arena -> self.sumsq (clip_grad_norm_'s total norm, squared)."""
+        if self.clip_max_norm > 0:
+            self.sumsq.zero_()
+            L.sumsq(ptr(self.grads), self.params.numel(), ptr(self.sumsq), stream())
+
+    def prep(self):
+        """step += 1; clip coefficient and bias corrections -> device scratch."""
+        L.adam_prep(self.betas[0], self.betas[1], self.clip_max_norm, ptr(self.sumsq) if self.clip_max_norm > 0 else None,
+                    ptr(self.step_count), ptr(self.scratch), stream())
+
+    def update(self, lo, hi, zero_grad=False):
+        """Element-wise Adam on arena slice [lo, hi) (multiples of 4 floats); optionally clears its gradient."""
+        if hi <= lo:
+            return
+        sh = self.bf16_shadow[lo:hi] if self.bf16_shadow is not None else None
+        L.adam_update(ptr(self.params[lo:hi]), ptr(self.m[lo:hi]), ptr(self.v[lo:hi]), ptr(self.grads[lo:hi]), ptr(sh),
+                      hi - lo, self.lr, self.betas[0], self.betas[1], self.eps, ptr(self.scratch), int(zero_grad), stream())
 
     @property
     def grad_norm(self):

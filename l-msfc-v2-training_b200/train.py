@@ -6,9 +6,21 @@
 `TrainStep.step(feats)` runs it eagerly; `TrainStep.capture(feats)` records the same launch sequence
 once into a CUDA graph (static shapes, device-side RNG counter and Adam step counter) so later
 steps are a single graph launch with no Python or launch latency on the critical path.
+
+`capture(feats, pipelined=True)` records the SAME iteration rotated by half a step:
+
+    [clip + Adam of the previous backward pass, slice by slice on its own stream  ||  forward] -> RD loss
+    -> backward -> [DP all-reduce] -> squared gradient norm (kept on the device for the next replay)
+
+Every replay still does exactly one forward, one backward and one optimiser update, on the same weights in
+the same order as the eager loop (forward k sees the weights after k updates); only the graph boundary moves,
+so the HBM-bound update hides under the tensor-bound analysis convolutions.  The forward pass waits per slice
+(model.LMSFC._gate), in the order it consumes the weights.  `flush()` applies the update still pending after
+the last replay (call it before reading / saving the weights).
 """
 import torch
 
+from . import _lib as L
 from . import functional as Fn
 from .losses import RateDistortionLoss
 from .model import LMSFC
@@ -33,6 +45,8 @@ class TrainStep:
         self.static_in = None
         self.static_out = None
         self.launches_per_step = None
+        self.pipelined = False
+        self.pending = False        # pipelined mode: gradients (and their norm) of the last backward await their update
 
     # ------------------------------------------------------------------ one eager iteration
     def _iteration(self, feats, noise_z=None, noise_y=None):
@@ -57,12 +71,86 @@ class TrainStep:
     def step(self, feats, noise_z=None, noise_y=None):
         if self.graph is not None and noise_z is None and noise_y is None:
             return self.replay(feats)
+        self.flush()
         return self._iteration(feats, noise_z, noise_y)
 
+    # ------------------------------------------------------------------ the iteration rotated by half a step
+    def _slices(self):
+        """Arena slices in the order the forward pass consumes them: [GDN group, EntropyBottleneck, g_a.conv2],
+        [g_a.conv3..5], [h_a, h_s, g_s].  Each later slice opens a gate the forward pass waits on."""
+        off, n = self.arena.offsets, self.arena.n_net
+        names = ["start"] + [k for k in ("g_a.conv3.weight", "h_a.0.weight") if k in off]
+        edges = [0] + [off[k] for k in names[1:]] + [n]
+        assert edges == sorted(edges), "arena order no longer follows the forward pass"
+        return [(edges[i], edges[i + 1], names[i]) for i in range(len(names))]
+
+    def _apply_pending(self):
+        """clip + Adam of the pending gradients (on SideStreams.opt when enabled), gradient cleared in the same pass;
+        then the aux step (examples/train.py:104-107).  Returns the aux loss."""
+        model, opt, arena = self.model, self.opt, self.arena
+        net, aux_opt = opt["net"], opt["aux"]
+        main = torch.cuda.current_stream()
+        os_ = Fn.SideStreams.opt
+        ctx = torch.cuda.stream(os_) if os_ is not None else _Null()
+        if os_ is not None:
+            os_.wait_stream(main)
+        arena.gates = {}
+        with ctx:
+            net.prep()
+            for i, (lo, hi, gate) in enumerate(self._slices()):
+                net.update(lo, hi, zero_grad=True)
+                if i == 0:
+                    arena._grads_all[arena.n_net:].zero_()     # GDN effective-gradient scratch
+                    arena.prepare()                            # GDN group (first in the arena) -> effective beta / gamma
+                if os_ is not None:
+                    ev = torch.cuda.Event()
+                    ev.record()
+                    arena.gates[gate] = ev
+            aux_opt.zero_grad()
+            aux = model.aux_loss()
+            aux.backward()
+            aux_opt.step()
+        if os_ is not None:
+            main.wait_event(arena.gates.pop("start"))          # the later gates are waited on inside model.forward
+        self.pending = False
+        return aux.detach()
+
+    def _grad_pass(self, feats):
+        """forward -> RD loss -> backward -> [DP all-reduce] -> squared gradient norm; leaves the update pending."""
+        model, opt = self.model, self.opt
+        if self.reducer is not None:
+            self.reducer.begin()
+        out = model(feats)
+        if Fn.SideStreams.opt is not None:       # gradient buffers are cleared by the update pass: join before backward
+            torch.cuda.current_stream().wait_stream(Fn.SideStreams.opt)
+        self.arena.gates = {}
+        crit = self.criterion(out, feats)
+        crit["loss"].backward()
+        if self.reducer is not None:
+            self.reducer.mark_ready(self.reducer.eb_names)
+            self.reducer.finish()
+        opt["net"].accumulate_norm()
+        self.pending = True
+        return crit
+
+    def _iteration_pipelined(self, feats):
+        aux = self._apply_pending()
+        crit = self._grad_pass(feats)
+        return {"loss": crit["loss"].detach(), "mse_loss": crit["mse_loss"].detach(),
+                "bpp_loss": crit["bpp_loss"].detach(), "aux_loss": aux}
+
+    def flush(self):
+        """Apply the update left pending by the last pipelined replay."""
+        if self.pending:
+            self._apply_pending()
+            if Fn.SideStreams.opt is not None:
+                torch.cuda.current_stream().wait_stream(Fn.SideStreams.opt)
+            self.arena.gates = {}
+
     # ------------------------------------------------------------------ CUDA graph
-    def capture(self, feats, warmup=2):
+    def capture(self, feats, warmup=2, pipelined=False):
         """Record one iteration.  `feats` fixes the shapes; its values are copied into static
-        input buffers on every replay."""
+        input buffers on every replay.  pipelined: see the module docstring (call flush() at the end)."""
         lv = self.model.spec.levels
         dev = self.arena.device
         self.static_in = {k: Fn.nhwc(feats[k], Fn.BF16).clone(memory_format=torch.channels_last) for k in lv}
@@ -71,12 +159,23 @@ class TrainStep:
         with torch.cuda.stream(side):
             for _ in range(warmup):             # allocator / lazy-init warm-up outside capture
                 self._iteration(self.static_in)
+            if pipelined:                       # prime the pipeline: gradients of one pass, update pending
+                self._iteration_pipelined_warm(self.static_in)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
+        self.pipelined = bool(pipelined)
+        c0 = L.launch_count()
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
-            self.static_out = self._iteration(self.static_in)
+            self.static_out = (self._iteration_pipelined if pipelined else self._iteration)(self.static_in)
+        self.launches_per_step = L.launch_count() - c0
         return self
+
+    def _iteration_pipelined_warm(self, feats):
+        """Eager rotated iterations before capture: allocator warm-up of the rotated order, and the pipeline primed."""
+        self.opt["net"].zero_grad()
+        self._grad_pass(feats)
+        self._iteration_pipelined(feats)
 
     def replay(self, feats=None):
         if feats is not None:
@@ -86,3 +185,11 @@ class TrainStep:
                     buf.copy_(src, non_blocking=True)
         self.graph.replay()
         return self.static_out
+
+
+class _Null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False

@@ -20,7 +20,7 @@ ts = train_m.TrainStep(net, lmbda=0.013)
 f = OL.synth_features(sp, 16, 64, 64, seed=1234)
 feats = {k: v.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).to(dev) for k, v in f.items()}
 ts.step(feats)
-ts.capture(feats, warmup=1)
+ts.capture(feats, warmup=1, pipelined=os.environ.get("LMSFC_SEQUENTIAL", "0") != "1")
 for _ in range(5):
     ts.replay()
 torch.cuda.synchronize()

@@ -117,3 +117,41 @@ def test_cuda_graph_step_matches_eager_and_trains():
     assert all(l == l and l < 1e6 for l in losses)
     assert losses[-1] < first                     # it trains
     assert len(set(losses)) > 10                  # fresh noise / weights every replay
+
+
+def test_pipelined_graph_step_equals_the_sequential_order():
+    """capture(pipelined=True) rotates the iteration ([Adam of the previous backward || forward] -> backward); after
+    flush() the weights and the loss sequence must be those of the eager loop with the same number of iterations
+    (differences: float atomics order in the gradient reductions only)."""
+    spec_m, model_m, train_m = _mods()
+    from oracle import lmsfc as OL
+    spec = spec_m.DEFAULT_SPEC
+    feats = OL.synth_features(spec, 2, 32, 32, device=DEV)
+    runs = []
+    for pipelined in (False, True):
+        torch.manual_seed(11)
+        net = model_m.LMSFC(spec).to(DEV)
+        ts = train_m.TrainStep(net, lmbda=0.013)
+        losses = []
+        if pipelined:
+            ts.capture(feats, warmup=1, pipelined=True)      # 1 eager iteration + 2 forward passes (priming), 1 update pending
+            for _ in range(3):
+                losses.append(float(ts.replay()["loss"]))
+            assert ts.pending
+            ts.flush()
+            assert not ts.pending
+        else:
+            for i in range(6):
+                l = float(ts.step(feats)["loss"])
+                if i >= 3:
+                    losses.append(l)
+        torch.cuda.synchronize()
+        runs.append((losses, net.arena.net_params.clone(), net.arena.aux_params.clone(), int(ts.opt["net"].step_count)))
+    (la, pa, qa, sa), (lb, pb, qb, sb) = runs
+    print("sequential", la, "pipelined", lb)
+    assert sa == sb == 6
+    for x, y in zip(la, lb):
+        assert abs(x - y) <= 2e-3 * abs(x), (la, lb)
+    rel = float((pa - pb).norm() / pa.norm())
+    assert rel < 1e-4, rel
+    torch.testing.assert_close(qa, qb, rtol=1e-3, atol=1e-4)
