@@ -32,21 +32,25 @@ class SideStreams:
     * `opt`: the pipelined train step (train.TrainStep.capture(pipelined=True)) runs clip + Adam of the PREVIOUS
       backward pass here, slice by slice in the order the forward pass consumes the weights, so the HBM-bound
       update hides under the tensor-bound forward convolutions.
+    * `heads`: the 3x3 output heads of g_s (p5, p4, p3 reconstructions) only feed the distortion term, so they run
+      beside the next up-sampling stage; in backward their data gradients run beside the up-sampling stage's.
     Disabled (None) by default: stand-alone modules run on the caller's stream."""
     wgrad = None
     hyper = None
     opt = None
+    heads = None
     _join_queued = False
 
     @classmethod
-    def enable(cls, device, wgrad=True, hyper=True, opt=True):
+    def enable(cls, device, wgrad=True, hyper=True, opt=True, heads=True):
         cls.wgrad = torch.cuda.Stream(device=device) if wgrad else None
         cls.hyper = torch.cuda.Stream(device=device) if hyper else None
         cls.opt = torch.cuda.Stream(device=device) if opt else None
+        cls.heads = torch.cuda.Stream(device=device) if heads else None
 
     @classmethod
     def disable(cls):
-        cls.wgrad = cls.hyper = cls.opt = None
+        cls.wgrad = cls.hyper = cls.opt = cls.heads = None
 
     @classmethod
     def queue_join(cls):

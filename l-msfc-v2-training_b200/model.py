@@ -148,13 +148,30 @@ class LMSFC(nn.Module):
         s = self.g_s
         hw2, hw3, hw4, hw5 = level_hw
         self._gate("h_a.0.weight")
+        hs = Fn.SideStreams.heads if (self.training and torch.is_grad_enabled()) else None
+        main = torch.cuda.current_stream()
+
+        def head(layer, d):
+            if hs is None:
+                return layer(d)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            d.record_stream(hs)
+            with torch.cuda.stream(hs):
+                hs.wait_event(ev)
+                out = layer(d)
+            out.record_stream(main)
+            return out
+
         d5 = s.igdn5(s.up5(y_hat_bf16, out_hw=hw5))
-        p5h = s.head5(d5)
+        p5h = head(s.head5, d5)
         d4 = s.igdn4(s.up4(d5, out_hw=hw4))
-        p4h = s.head4(d4)
+        p4h = head(s.head4, d4)
         d3 = s.igdn3(s.up3(d4, out_hw=hw3))
-        p3h = s.head3(d3)
+        p3h = head(s.head3, d3)
         p2h = s.up2(d3, out_hw=hw2)
+        if hs is not None:
+            main.wait_stream(hs)
         return p2h, p3h, p4h, p5h
 
     # ------------------------------------------------------------------ CompressionModel contract
