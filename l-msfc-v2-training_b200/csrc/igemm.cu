@@ -28,7 +28,7 @@ constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;            // 64 bf16 = one 128-byte swizzle row
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
 constexpr int NUM_GATHER_THREADS = 128;
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 256;   // warps 0-3 gather, 4 weight TMA, 5 MMA issue; all 8 run the direct epilogue
 
 template <int BLOCK_N>
 struct FwdCfg {
@@ -62,6 +62,52 @@ __device__ __forceinline__ float pick(const uint32_t (&r)[H], int j) {
   return (j & 1) ? bf16_hi(r[j >> 1]) : bf16_lo(r[j >> 1]);
 }
 
+// GDN forward / backward maths on W channels of one pixel; xr / gr / rr = x, grad_out, rsqrt(norm) as packed bf16
+template <int W>
+__device__ __forceinline__ void gdn_math(const IgemmParams& p, float (&v)[W], const uint32_t (&xr)[W / 2],
+                                         const uint32_t (&gr)[W / 2], const uint32_t (&rr)[W / 2], float (&rn)[W], int nb) {
+  if (p.epi == EPI_GDN) {
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      const float nrm = v[j] + __ldg(p.bias + nb + j);
+      rn[j] = rsqrtf(nrm);
+      const float x = pick(xr, j);
+      v[j] = p.inverse ? x * (nrm * rn[j]) : x * rn[j];
+    }
+  } else {  // EPI_GDN_BWD
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      const float r1 = pick(rr, j);
+      const float f = p.inverse ? 1.f / r1 : r1;
+      v[j] = pick(gr, j) * f + 2.f * pick(xr, j) * v[j];
+    }
+  }
+}
+// 32 bf16 of this thread's staged row (shared memory, 16-byte aligned)
+__device__ __forceinline__ void load_bf16_smem32(uint32_t saddr, uint32_t (&r)[16]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[4 * j]), "=r"(r[4 * j + 1]), "=r"(r[4 * j + 2]), "=r"(r[4 * j + 3])
+                 : "r"(saddr + 16 * j));
+}
+
+// 32 values of this thread's row -> its staging row in shared memory, as bf16 (64 B) or fp32 (128 B)
+__device__ __forceinline__ void stage_bf16_32(uint32_t saddr, const float (&v)[32]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr + 16 * j), "r"(pack_bf16(v[8 * j], v[8 * j + 1])),
+                 "r"(pack_bf16(v[8 * j + 2], v[8 * j + 3])), "r"(pack_bf16(v[8 * j + 4], v[8 * j + 5])),
+                 "r"(pack_bf16(v[8 * j + 6], v[8 * j + 7]))
+                 : "memory");
+}
+__device__ __forceinline__ void stage_f32_32(uint32_t saddr, const float (&v)[32]) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(saddr + 16 * j), "f"(v[4 * j]), "f"(v[4 * j + 1]),
+                 "f"(v[4 * j + 2]), "f"(v[4 * j + 3])
+                 : "memory");
+}
 // epilogue maths for W consecutive output channels [nb, nb+W) of one output pixel at offset o
 template <int W>
 __device__ __forceinline__ void epilogue_chunk(const IgemmParams& p, float (&v)[W], size_t o, int nb) {
@@ -86,29 +132,15 @@ __device__ __forceinline__ void epilogue_chunk(const IgemmParams& p, float (&v)[
       store_bf16<W>(p.out_abs + o, a);
     }
   } else {
-    uint32_t xr[W / 2];
+    uint32_t xr[W / 2], gr[W / 2], rr[W / 2];
     load_bf16<W>(p.aux_x + o, xr);
-    if (p.epi == EPI_GDN) {
-      float rn[W];
-#pragma unroll
-      for (int j = 0; j < W; ++j) {
-        const float nrm = v[j] + __ldg(p.bias + nb + j);
-        rn[j] = rsqrtf(nrm);
-        const float x = pick(xr, j);
-        v[j] = p.inverse ? x * (nrm * rn[j]) : x * rn[j];
-      }
-      if (p.out_rn) store_bf16<W>(p.out_rn + o, rn);
-    } else {  // EPI_GDN_BWD
-      uint32_t gr[W / 2], rr[W / 2];
+    if (p.epi == EPI_GDN_BWD) {
       load_bf16<W>(p.aux_gy + o, gr);
       load_bf16<W>(p.aux_rn + o, rr);
-#pragma unroll
-      for (int j = 0; j < W; ++j) {
-        const float rn = pick(rr, j);
-        const float f = p.inverse ? 1.f / rn : rn;
-        v[j] = pick(gr, j) * f + 2.f * pick(xr, j) * v[j];
-      }
     }
+    float rn[W];
+    gdn_math<W>(p, v, xr, gr, rr, rn, nb);
+    if (p.epi == EPI_GDN && p.out_rn) store_bf16<W>(p.out_rn + o, rn);
   }
   if (p.out_bf16) store_bf16<W>(p.out_bf16 + o, v);
 }
@@ -143,7 +175,7 @@ __device__ __forceinline__ unsigned long long gtimer() {
   do {                                                                                             \
     const int _c = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                 \
     if (_c < 64) g_timeline[_c * 16 + (slot)] = gtimer();                                          \
-    if (_c < 64 && (slot) >= 9) g_timeline[_c * 16 + (slot) + 2] = (unsigned long long)clock64();  \
+    if (_c < 64 && ((slot) == 9 || (slot) == 10)) g_timeline[_c * 16 + (slot) + 2] = (unsigned long long)clock64();  \
   } while (0)
 #else
 #define TL(slot) do {} while (0)
@@ -265,19 +297,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       tc_fence_after();
     }
     if (tid == 0) TL(4);
-    if (p.ksplit == 1) {
-#pragma unroll 1
-      for (int cb = 0; cb < BLOCK_N; cb += 32) {
-        uint32_t r[32];
-        tmem_ld32(trow + cb, r);
-        tmem_ld_wait();
-        if (!ok) continue;
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        epilogue_chunk<32>(p, v, obase + cb, n0 + cb);
-      }
-    }
   } else if (warp == 4) {
     // ================= weight TMA producer =================
     if (lane == 0) {
@@ -302,7 +321,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
-  } else {
+  } else if (warp == 5) {
     // ================= MMA issuer (one thread) =================
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N, 0, B_MN ? 1 : 0);
@@ -327,6 +346,122 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       }
       if (nkb > 0) umma_commit(tmem_full_bar);
       TL(10);
+    }
+  }
+  if (p.ksplit == 1) {
+    // ================= direct epilogue: all 8 warps =================
+    // Warp w reads TMEM lanes 32*(w%4)...: warps w and w+4 share a row quarter and split the columns in halves
+    // (two warps per scheduler instead of one: the epilogue is instruction / latency bound).  Thread-per-row
+    // GLOBAL accesses (16-byte pieces at a 512-byte stride) are avoided altogether: all tile traffic goes through
+    // the idle pipeline memory in 64-column passes -- a warp copies the aux rows of ITS 32 pixels in with coalesced
+    // cp.async (all in flight at once), every thread computes its own row from / to shared memory (row stride
+    // 128 + 16 B resp. 256 + 16 B: conflict-free for 16-byte accesses), the warp copies the results out as whole
+    // row segments.  Only __syncwarp is needed: a warp touches its own rows of its own column half.
+    __syncwarp();
+    if (nkb > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    if (tid == 0) TL(4);
+    constexpr int PW = 64, ROWB = PW * 2 + 16, ROWF = PW * 4 + 16, HALF = BLOCK_N / 2, PASSES = HALF / PW;
+    constexpr int SLOT_B = BLOCK_M * ROWB, SLOT_F = BLOCK_M * ROWF, GROUP = 3 * SLOT_B + SLOT_F;
+    static_assert(2 * GROUP <= Cfg::STAGES * Cfg::STAGE_BYTES, "staging slots");
+    const int half = warp >> 2, wrow0 = (warp & 3) * 32;
+    const bool gdn_f = p.epi == EPI_GDN, gdn_b = p.epi == EPI_GDN_BWD;
+    // per column half: bf16 slots 0..2 and one fp32 slot.  GDN forward {x -> y in place, rn}; GDN backward
+    // {x -> grad_in in place, grad_out, rn}; conv {y, |y|, -, fp32}
+    const uint32_t sgroup = smem_base + (uint32_t)half * GROUP;
+    const uint32_t srow_b = sgroup + (uint32_t)row * ROWB, swarp_b = sgroup + (uint32_t)wrow0 * ROWB;
+    const uint32_t srow_f = sgroup + 3 * SLOT_B + (uint32_t)row * ROWF, swarp_f = sgroup + 3 * SLOT_B + (uint32_t)wrow0 * ROWF;
+    const long long orow = ok ? (long long)obase : -1ll;      // element offset of this row (column n0), -1: not stored
+    auto issue = [&](const __nv_bfloat16* src, int col, int slot) {   // 4 rows x 128 B per instruction
+      const uint32_t sdst = swarp_b + (uint32_t)slot * SLOT_B + (lane & 7) * 16;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int rr = 4 * i + (lane >> 3);
+        const long long o = __shfl_sync(0xffffffffu, orow, rr);
+        if (o >= 0) cp_async16(sdst + (uint32_t)rr * ROWB, src + o + col + (lane & 7) * 8, 16u);
+      }
+    };
+    auto copy_out = [&](uint32_t swarp, int stride, void* dst, int col, int esize) {
+      const int lpr = (PW * esize) >> 4, sub = lane / lpr, cb16 = (lane % lpr) * 16;   // lanes per row: 8 (bf16) / 16 (fp32)
+      for (int i = 0; i < 32; i += 32 / lpr) {
+        const int rr = i + sub;
+        const long long o = __shfl_sync(0xffffffffu, orow, rr);
+        if (o >= 0) {
+          uint32_t a, b, c, d;
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(swarp + rr * stride + cb16));
+          *reinterpret_cast<uint4*>((uint8_t*)dst + (size_t)(o + col) * esize + cb16) = make_uint4(a, b, c, d);
+        }
+      }
+    };
+#pragma unroll 1
+    for (int ps = 0; ps < PASSES; ++ps) {
+      const int col = half * HALF + ps * PW;                // first column of this pass inside the tile
+      if (gdn_f || gdn_b) {
+        issue(p.aux_x, col, 0);
+        if (gdn_b) {
+          issue(p.aux_gy, col, 1);
+          issue(p.aux_rn, col, 2);
+        }
+        cp_async_wait_all();
+        __syncwarp();
+      }
+      if (tid == 0 && ps == 0) TL(13);
+#pragma unroll 1
+      for (int cb = 0; cb < PW; cb += 32) {
+        uint32_t r[32];
+        if (nkb > 0) {                   // warp-uniform: tcgen05.ld is .sync.aligned
+          tmem_ld32(trow + col + cb, r);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) r[j] = 0u;
+        }
+        if (!ok) continue;               // rows past M / cropped outputs are never stored
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        const uint32_t coff = (uint32_t)cb * 2;
+        if (gdn_f || gdn_b) {
+          uint32_t xr[16], gr[16], rr[16];
+          float rn[32];
+          load_bf16_smem32(srow_b + coff, xr);
+          if (gdn_b) {
+            load_bf16_smem32(srow_b + SLOT_B + coff, gr);
+            load_bf16_smem32(srow_b + 2 * SLOT_B + coff, rr);
+          }
+          gdn_math<32>(p, v, xr, gr, rr, rn, n0 + col + cb);
+          if (gdn_f && p.out_rn) stage_bf16_32(srow_b + SLOT_B + coff, rn);
+          if (p.out_bf16) stage_bf16_32(srow_b + coff, v);
+        } else {
+          if (p.bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + n0 + col + cb + j);
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          }
+          if (p.out_bf16) stage_bf16_32(srow_b + coff, v);
+          if (p.out_f32) stage_f32_32(srow_f + coff * 2, v);
+          if (p.out_abs) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fabsf(v[j]);
+            stage_bf16_32(srow_b + SLOT_B + coff, v);
+          }
+        }
+      }
+      __syncwarp();
+      if (tid == 0 && ps == 0) TL(14);
+      if (p.out_bf16) copy_out(swarp_b, ROWB, p.out_bf16, col, 2);
+      if (gdn_f && p.out_rn) copy_out(swarp_b + SLOT_B, ROWB, p.out_rn, col, 2);
+      if (!gdn_f && !gdn_b) {
+        if (p.out_f32) copy_out(swarp_f, ROWF, p.out_f32, col, 4);
+        if (p.out_abs) copy_out(swarp_b + SLOT_B, ROWB, p.out_abs, col, 2);
+      }
+      if (tid == 0 && ps == 0) TL(15);
+      __syncwarp();                      // staging rows are reused by the next pass
     }
   }
   if (p.ksplit > 1) {

@@ -62,3 +62,29 @@ for (name, k, s, B, hi, wi, ho, wo) in [("conv2 wgrad", 5, 2, 16, 64, 64, 32, 32
         print(f"  cta {cta:2d}: " + "  ".join(f"{WNAMES[i]} {((int(r[i]) - int(t0)) / 1e3):.2f}" for i in (0, 1, 9, 10, 4, 5, 7, 8) if r[i] >= t0))
     print(f"  last exit over recorded CTAs: {(int(buf[:, 8].max()) - int(t0)) / 1e3:.2f} us;  SM clock over cta 0's MMA loop "
           f"{(int(buf[0, 12]) - int(buf[0, 11])) / max(1, int(buf[0, 10]) - int(buf[0, 9])) * 1e3:.0f} MHz")
+
+# ---- GDN forward / backward GEMMs (same implicit-GEMM kernel, EPI_GDN_FWD / EPI_GDN_BWD)
+for (name, B, h, w) in [("gdn 16x32x32", 16, 32, 32), ("gdn 16x8x8", 16, 8, 8)]:
+    C, Pn = 256, B * h * w
+    x, gy = bf(B, C, h, w), bf(B, C, h, w)
+    gam = (torch.rand(C, C, device=dev) * 0.01).to(torch.bfloat16)
+    beta = torch.ones(C, device=dev)
+    x2, y, rn, t, gx = (torch.empty_like(x) for _ in range(5))
+    gg, gb = torch.zeros(C, C, device=dev), torch.zeros(C, device=dev)
+    for which in ("fwd", "bwd"):
+        for _ in range(3):
+            if which == "fwd":
+                L.gdn_forward(P(x), P(gam), P(beta), 0, Pn, C, P(x2), P(y), P(rn), L.stream())
+            else:
+                L.gdn_backward(P(gy), P(x), P(rn), P(gam), 0, Pn, C, P(x2), 1, P(t), P(gx), None, P(gb), L.stream())
+        torch.cuda.synchronize()
+        buf = np.zeros((64, 16), dtype=np.uint64)
+        L.lib.lmsfc_debug_read_timeline(ctypes.c_void_p(buf.ctypes.data))
+        t0 = buf[:, 0][buf[:, 0] > 0].min()
+        print(f"== {name} {which}")
+        EN = dict(enumerate(NAMES)); EN.update({13: "epi:inputs-staged", 14: "epi:slab0-computed", 15: "epi:slab0-stored", 3: "epi:bwd-issued", 5: "epi:bwd-landed", 2: "epi:tmem0", 6: "epi:tmem1"})
+        for cta in (0, 7):
+            r = buf[cta]
+            if r[0] == 0:
+                continue
+            print(f"  cta {cta:2d}: " + "  ".join(f"{EN[i]} {((int(r[i]) - int(t0)) / 1e3):.2f}" for i in (0, 1, 9, 10, 4, 13, 3, 5, 2, 6, 14, 15, 7, 8) if r[i] >= t0))
