@@ -50,6 +50,15 @@ __device__ __forceinline__ void load_bf16(const __nv_bfloat16* p, uint32_t (&r)[
   }
 }
 template <int W>
+__device__ __forceinline__ void load_f32(const float* p, float (&r)[W]) {   // 16-byte aligned, warp-uniform address
+  const float4* s = reinterpret_cast<const float4*>(p);
+#pragma unroll
+  for (int j = 0; j < W / 4; ++j) {
+    const float4 q = __ldg(s + j);
+    r[4 * j] = q.x; r[4 * j + 1] = q.y; r[4 * j + 2] = q.z; r[4 * j + 3] = q.w;
+  }
+}
+template <int W>
 __device__ __forceinline__ void store_bf16(__nv_bfloat16* p, const float (&v)[W]) {
   uint4* d = reinterpret_cast<uint4*>(p);
 #pragma unroll
@@ -66,21 +75,34 @@ __device__ __forceinline__ float pick(const uint32_t (&r)[H], int j) {
 template <int W>
 __device__ __forceinline__ void gdn_math(const IgemmParams& p, float (&v)[W], const uint32_t (&xr)[W / 2],
                                          const uint32_t (&gr)[W / 2], const uint32_t (&rr)[W / 2], float (&rn)[W], int nb) {
+  // norm >= beta_min > 0 and rn is a bf16 value: the approximate rsqrt / reciprocal (2 ulp) lose nothing here,
+  // while the IEEE division of the inverse backward was a call per element
   if (p.epi == EPI_GDN) {
+    float beta[W];
+    load_f32<W>(p.bias + nb, beta);
 #pragma unroll
     for (int j = 0; j < W; ++j) {
-      const float nrm = v[j] + __ldg(p.bias + nb + j);
-      rn[j] = rsqrtf(nrm);
-      const float x = pick(xr, j);
-      v[j] = p.inverse ? x * (nrm * rn[j]) : x * rn[j];
+      const float nrm = v[j] + beta[j];
+      asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rn[j]) : "f"(nrm));
+      v[j] = nrm;
     }
-  } else {  // EPI_GDN_BWD
+    if (p.inverse) {
+#pragma unroll
+      for (int j = 0; j < W; ++j) v[j] = pick(xr, j) * (v[j] * rn[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < W; ++j) v[j] = pick(xr, j) * rn[j];
+    }
+  } else if (p.inverse) {  // EPI_GDN_BWD of y = x * sqrt(norm)
 #pragma unroll
     for (int j = 0; j < W; ++j) {
-      const float r1 = pick(rr, j);
-      const float f = p.inverse ? 1.f / r1 : r1;
+      float f;
+      asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(f) : "f"(pick(rr, j)));
       v[j] = pick(gr, j) * f + 2.f * pick(xr, j) * v[j];
     }
+  } else {                 // EPI_GDN_BWD of y = x * rsqrt(norm)
+#pragma unroll
+    for (int j = 0; j < W; ++j) v[j] = pick(gr, j) * pick(rr, j) + 2.f * pick(xr, j) * v[j];
   }
 }
 // 32 bf16 of this thread's staged row (shared memory, 16-byte aligned)
@@ -113,8 +135,10 @@ template <int W>
 __device__ __forceinline__ void epilogue_chunk(const IgemmParams& p, float (&v)[W], size_t o, int nb) {
   if (p.epi == EPI_BIAS) {
     if (p.bias) {
+      float bv[W];
+      load_f32<W>(p.bias + nb, bv);
 #pragma unroll
-      for (int j = 0; j < W; ++j) v[j] += __ldg(p.bias + nb + j);
+      for (int j = 0; j < W; ++j) v[j] += bv[j];
     }
     if (p.relu) {
 #pragma unroll
@@ -436,8 +460,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
           if (p.out_bf16) stage_bf16_32(srow_b + coff, v);
         } else {
           if (p.bias) {
+            float bv[32];
+            load_f32<32>(p.bias + n0 + col + cb, bv);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + n0 + col + cb + j);
+            for (int j = 0; j < 32; ++j) v[j] += bv[j];
           }
           if (p.relu) {
 #pragma unroll
