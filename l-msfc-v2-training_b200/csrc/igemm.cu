@@ -38,6 +38,9 @@ struct FwdCfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
+__device__ __forceinline__ int fast_div(int n, uint32_t mul, uint32_t shr) {   // n / d, d's magic from fast_div_magic
+  return mul ? (int)(__umulhi((uint32_t)n, mul) >> shr) : n;
+}
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 template <int W>
@@ -233,6 +236,38 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   const int nkb = min(kb_per, nkb_total - kb_begin);   // host guarantees >= 1
   const uint32_t smem_base = smem_u32(smem);
 
+  // Row decode (no global memory): before the barrier / pdl_sync, so it overlaps the previous kernel's tail.
+  // output row of this thread (warp w and w + 4 share a row quarter in the epilogue)
+  const int row = (warp & 3) * 32 + lane;
+  bool ok = false;
+  size_t obase = 0;
+  {
+    const int m = m0 + row;
+    if (m < ph.M) {
+      const int t = fast_div(m, ph.wg_mul, ph.wg_shr), wg = m - t * ph.Wg;
+      const int b = fast_div(t, ph.hg_mul, ph.hg_shr), hg = t - b * ph.Hg;
+      const int ho = hg * p.sout + ph.oy, wo = wg * p.sout + ph.ox;
+      ok = ho < p.Hout && wo < p.Wout;
+      obase = ((size_t)(b * p.Hout + ho) * p.Wout + wo) * p.N + n0;
+    }
+  }
+  // gather rows of this thread (producer warps): r0 + 16*i
+  const int chunk = tid & 7, r0 = (tid >> 3) & 15;
+  int pixbase[8], hi0[8], wi0[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int m = m0 + r0 + 16 * i;
+    if (m < ph.M) {
+      const int t = fast_div(m, ph.wg_mul, ph.wg_shr), wg = m - t * ph.Wg;
+      const int b = fast_div(t, ph.hg_mul, ph.hg_shr), hg = t - b * ph.Hg;
+      pixbase[i] = b * p.Hin * p.Win;
+      hi0[i] = hg * p.sin;
+      wi0[i] = wg * p.sin;
+    } else {
+      pixbase[i] = 0; hi0[i] = -100000; wi0[i] = -100000;
+    }
+  }
+
   if (warp == 4 && lane == 0) {
     tma_prefetch_desc(&p.tmapB);
     for (int s = 0; s < STAGES; ++s) {
@@ -255,39 +290,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
 #endif
   if (tid == 0) TL(1);
 
-  // output row of this thread (meaningful for the 128 gather/epilogue threads)
-  const int row = (warp & 3) * 32 + lane;
-  bool ok = false;
-  size_t obase = 0;
-  {
-    const int m = m0 + row;
-    if (m < ph.M) {
-      const int wg = m % ph.Wg, t = m / ph.Wg;
-      const int hg = t % ph.Hg, b = t / ph.Hg;
-      const int ho = hg * p.sout + ph.oy, wo = wg * p.sout + ph.ox;
-      ok = ho < p.Hout && wo < p.Wout;
-      obase = ((size_t)(b * p.Hout + ho) * p.Wout + wo) * p.N + n0;
-    }
-  }
   const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
 
   if (warp < 4) {
     // ================= activation gather (producer) =================
-    const int chunk = tid & 7, r0 = tid >> 3;
-    int pixbase[8], hi0[8], wi0[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int m = m0 + r0 + 16 * i;
-      if (m < ph.M) {
-        const int wg = m % ph.Wg, t = m / ph.Wg;
-        const int hg = t % ph.Hg, b = t / ph.Hg;
-        pixbase[i] = b * p.Hin * p.Win;
-        hi0[i] = hg * p.sin;
-        wi0[i] = wg * p.sin;
-      } else {
-        pixbase[i] = 0; hi0[i] = -100000; wi0[i] = -100000;
-      }
-    }
     const uint32_t dst_thread = smem_base + r0 * 128 + ((chunk ^ (r0 & 7)) << 4);
     int stage = 0, phase = 0;
     int tap = ph.tap_begin + kb_begin / kc_per_tap, kc = kb_begin % kc_per_tap;
@@ -634,6 +640,8 @@ int launch_igemm(IgemmParams& p, cudaStream_t stream) {
   for (int i = 0; i < p.nphase; ++i) {
     LMSFC_CHECK_ARG(p.ph[i].M > 0 && p.ph[i].ntaps >= 1 && p.ph[i].tap_begin + p.ph[i].ntaps <= kMaxTaps,
                     "igemm: phase %d M=%d ntaps=%d", i, p.ph[i].M, p.ph[i].ntaps);
+    fast_div_magic(p.ph[i].Wg, &p.ph[i].wg_mul, &p.ph[i].wg_shr);
+    fast_div_magic(p.ph[i].Hg, &p.ph[i].hg_mul, &p.ph[i].hg_shr);
     maxM = max(maxM, p.ph[i].M);
     min_taps = min(min_taps, p.ph[i].ntaps);
     max_taps = max(max_taps, p.ph[i].ntaps);

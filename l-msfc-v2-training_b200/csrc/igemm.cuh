@@ -21,6 +21,7 @@ struct IgemmPhase {
   int Hg, Wg, M;            // GEMM row grid of this phase: m = (b*Hg + hg)*Wg + wg
   int oy, ox;               // output pixel = (hg*sout + oy, wg*sout + ox)
   int tap_begin, ntaps;     // slice of the tap table
+  uint32_t wg_mul, wg_shr, hg_mul, hg_shr;   // m -> (b, hg, wg) by multiply-shift (filled by launch_igemm)
 };
 struct IgemmParams {
   CUtensorMap tmapB;        // filled by launch_igemm, SWIZZLE_128B: box {64 k, BLOCK_N n} or, w_mn = 1, {64 n, 64 k}
@@ -81,6 +82,16 @@ struct WgradParams {
   int bias_ctas;
   int dbg;                  // TIMELINE builds only
 };
+
+// n / d == umulhi(n, mul) >> shr for 0 <= n < 2^31 (mul == 0: d == 1); the kernels decode pixel indices with it
+inline void fast_div_magic(int d, uint32_t* mul, uint32_t* shr) {
+  if (d == 1) { *mul = 0; *shr = 0; return; }
+  int l = 0;
+  while ((1ll << l) < d) ++l;
+  const int pw = 31 + l;
+  *mul = (uint32_t)(((1ull << pw) + (uint64_t)d - 1) / (uint64_t)d);
+  *shr = (uint32_t)(pw - 32);
+}
 
 int launch_igemm(IgemmParams& p, cudaStream_t stream);
 int launch_wgrad(WgradParams& p, cudaStream_t stream);

@@ -281,15 +281,6 @@ extern "C" int lmsfc_debug_read_wg_timeline(unsigned long long* host64x16) {
 }
 #endif
 
-static void fast_div_magic(int d, uint32_t* mul, uint32_t* shr) {   // n / d == umulhi(n, mul) >> shr for 0 <= n < 2^31
-  if (d == 1) { *mul = 0; *shr = 0; return; }
-  int l = 0;
-  while ((1ll << l) < d) ++l;
-  const int pw = 31 + l;
-  *mul = (uint32_t)(((1ull << pw) + (uint64_t)d - 1) / (uint64_t)d);
-  *shr = (uint32_t)(pw - 32);
-}
-
 int launch_wgrad(WgradParams& p, cudaStream_t stream) {
   LMSFC_CHECK_ARG(p.Cd % 128 == 0 && p.Cg % 256 == 0, "wgrad: Cd=%d must be a multiple of 128, Cg=%d of 256", p.Cd,
                   p.Cg);
