@@ -63,7 +63,6 @@ __device__ __forceinline__ void adam_one(float g, float& m, float& v, float& p, 
 // 30 B of HBM traffic per parameter (34 with zero_g).  2 CTAs of 256 threads per SM, 2 x 4 independent 16-byte
 // loads per thread in flight: a small footprint on purpose -- in the pipelined step this kernel shares the SMs with
 // the forward convolutions (a grid that fills every thread slot would hold their CTAs back until it ends).
-constexpr int ADAM_CTAS_PER_SM = 2;
 __device__ __forceinline__ void adam_quad(const float4& g, float4& m, float4& v, float4& p, float clip, float b1, float b2,
                                           float step_size, float rs_bc2, float eps) {
   adam_one(g.x, m.x, v.x, p.x, clip, b1, b2, step_size, rs_bc2, eps);
@@ -124,8 +123,10 @@ int adam_update(const AdamArgs& a, cudaStream_t s) {
   if (a.n == 0) return LMSFC_OK;
   LMSFC_CHECK_ARG((((uintptr_t)a.p | (uintptr_t)a.m | (uintptr_t)a.v | (uintptr_t)a.g) & 15) == 0 &&
                       ((uintptr_t)a.p_bf16 & 7) == 0, "adam: arena slices must be 16-byte aligned");
-  const int64_t quads = (a.n + 3) / 4, want = (quads + 2 * TPB - 1) / (2 * TPB);
-  const int grid = (int)max((int64_t)1, min(want, (int64_t)148 * ADAM_CTAS_PER_SM));
+  // short-lived CTAs (8 quads per thread): in the pipelined step the forward convolutions run on a higher-priority
+  // stream and take every SM an Adam CTA leaves (a GEMM CTA cannot join an SM in the L1-heavy split)
+  const int64_t quads = (a.n + 3) / 4, want = (quads + 8 * TPB - 1) / (8 * TPB);
+  const int grid = (int)max((int64_t)1, want);
   LMSFC_LAUNCH(adam_kernel, dim3(grid), dim3(TPB), 0, s, a);
   return LMSFC_OK;
 }

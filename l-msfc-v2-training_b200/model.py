@@ -112,8 +112,13 @@ class LMSFC(nn.Module):
         e2 = a.gdn2(a.conv2(p2))
         self._gate("g_a.conv3.weight")
         e3 = a.gdn3(a.conv3(e2, p3))
+        self._gate("g_a.conv4.weight")
         e4 = a.gdn4(a.conv4(e3, p4))
+        self._gate("g_a.conv5.weight")
         return a.conv5(e4, p5, latent_head=True)
+
+    # first parameter of every optimiser slice of the pipelined train step, in arena (= forward) order
+    GATES = ("g_a.conv3.weight", "g_a.conv4.weight", "g_a.conv5.weight", "h_a.0.weight", "g_s.up5.weight")
 
     def _gate(self, name):
         """Pipelined train step: wait (on the current stream) for the optimiser slice that starts at this parameter."""
@@ -147,7 +152,7 @@ class LMSFC(nn.Module):
         """g_s: y_hat -> (p2_hat, p3_hat, p4_hat, p5_hat), each cropped to its level's H x W."""
         s = self.g_s
         hw2, hw3, hw4, hw5 = level_hw
-        self._gate("h_a.0.weight")
+        self._gate("g_s.up5.weight")
         hs = Fn.SideStreams.heads if (self.training and torch.is_grad_enabled()) else None
         main = torch.cuda.current_stream()
 

@@ -77,9 +77,10 @@ class TrainStep:
     # ------------------------------------------------------------------ the iteration rotated by half a step
     def _slices(self):
         """Arena slices in the order the forward pass consumes them: [GDN group, EntropyBottleneck, g_a.conv2],
-        [g_a.conv3..5], [h_a, h_s, g_s].  Each later slice opens a gate the forward pass waits on."""
+        [g_a.conv3], [g_a.conv4], [g_a.conv5], [h_a, h_s], [g_s].  Each slice opens a gate the forward pass waits on
+        (model.LMSFC.GATES)."""
         off, n = self.arena.offsets, self.arena.n_net
-        names = ["start"] + [k for k in ("g_a.conv3.weight", "h_a.0.weight") if k in off]
+        names = ["start"] + [k for k in self.model.GATES if k in off]
         edges = [0] + [off[k] for k in names[1:]] + [n]
         assert edges == sorted(edges), "arena order no longer follows the forward pass"
         return [(edges[i], edges[i + 1], names[i]) for i in range(len(names))]
@@ -166,7 +167,10 @@ class TrainStep:
         self.pipelined = bool(pipelined)
         c0 = L.launch_count()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        # the critical path (forward / data-gradient chain) is captured on a high-priority stream: its CTAs are
+        # dispatched before those of the weight-gradient / optimiser / hyper / head streams whenever SMs free up
+        cap = torch.cuda.Stream(device=dev, priority=-1)
+        with torch.cuda.graph(self.graph, stream=cap):
             self.static_out = (self._iteration_pipelined if pipelined else self._iteration)(self.static_in)
         self.launches_per_step = L.launch_count() - c0
         return self
