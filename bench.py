@@ -188,9 +188,18 @@ def run_b200(args):
         host.append({k: v.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).pin_memory() for k, v in f.items()})
     feats = {k: v.to(dev, non_blocking=True) for k, v in host[0].items()}
     h2d = sum(v.numel() * 2 for v in host[0].values())
+    def note(msg):
+        if args.verbose:
+            print(f"[bench rank {rank}] {msg}", file=sys.stderr, flush=True)
+
+    note("model built")
     ts.step(feats)                           # eager once (lazy init), then capture the graph
+    torch.cuda.synchronize()
+    note("eager step done")
     ts.capture(feats, warmup=1, pipelined=not args.sequential)
     launches_per_step = ts.launches_per_step               # launches of this library recorded into the graph
+    torch.cuda.synchronize()
+    note("graph captured")
 
     def barrier():
         if world > 1:
@@ -200,6 +209,8 @@ def run_b200(args):
     # ---- device-resident throughput ("value")
     for _ in range(max(args.warmup, 3)):
         ts.replay()
+    torch.cuda.synchronize()
+    note("warm replays done")
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
@@ -273,14 +284,27 @@ def run_b200(args):
             "clocks": sampler.summary() if sampler else None,
             "final_loss": float(loss_host[-1, 0]),
         }
-        try:
-            line["cpu_baseline"] = cpu_baseline(sp)
-        except Exception as e:  # the baseline is reported, never a dependency
-            line["cpu_baseline"] = {"value": None, "error": str(e)}
-        print(json.dumps(line))
+        if world == 1:                       # the CPU baseline is measured at N=1 only (rank 0, idle host cores)
+            try:
+                line["cpu_baseline"] = cpu_baseline(sp)
+            except Exception as e:  # the baseline is reported, never a dependency
+                line["cpu_baseline"] = {"value": None, "error": str(e)}
+        else:
+            line["cpu_baseline"] = None
+        print(json.dumps(line), flush=True)
     if world > 1:
+        # Tear down in order: the captured graph holds NCCL kernels, and destroying the communicator under a live
+        # graph hung (measured, 2 GPUs).  Drop the graph first; exit hard if the teardown still does not return.
         dist.barrier()
+        torch.cuda.synchronize()
+        ts.graph = None
+        del ts
+        torch.cuda.synchronize()
+        killer = threading.Timer(20.0, lambda: os._exit(0))
+        killer.daemon = True
+        killer.start()
         dist.destroy_process_group()
+        killer.cancel()
 
 
 if __name__ == "__main__":
@@ -289,6 +313,7 @@ if __name__ == "__main__":
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--verbose", action="store_true", help="progress notes on stderr")
     ap.add_argument("--sequential", action="store_true",
                     help="capture the eager order (update at the end of the step) instead of the rotated, pipelined one")
     a = ap.parse_args()
