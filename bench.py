@@ -133,14 +133,34 @@ def kernel_rooflines(torch, L, layers, dev):
     M, N, K = BATCH * (H2 // 2) * (W2 // 2), 256, 25 * 256
     flops = 2.0 * M * N * K
 
-    def timeit(fn, n=20):
-        for _ in range(3):
-            fn()
-        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
-        for a, b in evs:
-            a.record(stream); fn(); b.record(stream)
+    def timeit(fn, n=10, reps=20):
+        """Average launch duration: n launches recorded into a CUDA graph (the host side of one eager call -- ctypes,
+        tensor-map encode -- is longer than the kernel), replayed `reps` times between CUDA events on the launching
+        stream; the median replay / n."""
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(stream)
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                fn()
+        stream.wait_stream(side)
         torch.cuda.synchronize()
-        return sum(a.elapsed_time(b) for a, b in evs) / n
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(n):
+                fn()
+        ts = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); g.replay(); b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b) / n)
+        ts.sort()
+        return ts[len(ts) // 2]
+
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+    except Exception:
+        traffic = {}
 
     st = conv._state
     d = st.desc(BATCH, H2, W2, H2 // 2, W2 // 2)
@@ -153,7 +173,7 @@ def kernel_rooflines(torch, L, layers, dev):
     for name, ms in (("igemm_fwd_kernel<256>", ms_f), ("wgrad_kernel", ms_w)):
         a = flops / (ms * 1e-3) / 1e12
         res[name] = {"bound": "tensor", "achieved": a, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                     "frac": a / pk["bf16_tflops"], "traffic": None, "ms_per_launch": ms,
+                     "frac": a / pk["bf16_tflops"], "traffic": (traffic.get(name) or {}).get("bytes"), "ms_per_launch": ms,
                      "flops_per_launch": flops, "peak_source": f"bf16_tflops (burst) of {which}",
                      "shape": f"M={M} N={N} K={K} (g_a.conv2 at batch 16)"}
     return res
@@ -180,7 +200,7 @@ def run_b200(args):
     sp = model_m.DEFAULT_SPEC
     torch.manual_seed(1234)
     net = model_m.LMSFC(sp).to(dev)
-    ts = train_m.TrainStep(net, lmbda=LMBDA, distributed=world > 1)
+    ts = train_m.TrainStep(net, lmbda=LMBDA, distributed=world > 1, bucket_mb=float(os.environ.get("LMSFC_BUCKET_MB", "32")))
     nbuf = 4
     host = []
     for i in range(nbuf):                    # pinned bf16 NHWC feature shards, one per buffered step

@@ -15,4 +15,8 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'igemm_fwd_kernel|wgrad_kernel' -s 20 -c 8 \
   -f -o $OUT/${TAG}_gemm_full python bench.py --steps 2 --warmup 3 > $OUT/${TAG}_ncu_full.log 2>&1
 fi
+timeout 300 python profiles/layer_bench.py > $OUT/${TAG}_layers.txt 2>&1
+timeout 300 python profiles/trace_step.py $OUT/${TAG}_trace.txt > /dev/null 2>&1
+LMSFC_SEQUENTIAL=1 timeout 300 python profiles/trace_step.py $OUT/${TAG}_trace_seq.txt > /dev/null 2>&1
+timeout 300 python profiles/timeline.py > $OUT/${TAG}_timeline.txt 2>&1
 tail -3 $OUT/${TAG}_pytest.log; cat $OUT/${TAG}_bench.json; tail -2 $OUT/${TAG}_bench.err
