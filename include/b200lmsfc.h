@@ -55,16 +55,18 @@ int lmsfc_conv_wgrad(const lmsfc_conv_desc* d, const void* src0, const void* src
 /* ------------------------------------------------------------------ GDN / IGDN   (layers/gdn.py:77-92)
  * y = x * rsqrt(beta' + gamma' . x^2)  (inverse: * sqrt).  gamma_eff bf16 [C][C] ([out][in]) and
  * beta_eff fp32 [C] are the reparametrised values (lmsfc_reparam_forward).  rn = rsqrt(norm) is
- * saved (bf16) for backward; x2 / t are caller scratch of P*C bf16. */
+ * saved (bf16) for backward.  x2_scratch (P*C bf16) receives x^2, which the backward pass's gamma gradient reads again;
+ * NULL (inference): x^2 is formed inside the GEMM by its producer warps and nothing is kept. */
 int lmsfc_gdn_forward(const void* x, const void* gamma_eff, const float* beta_eff, int inverse, int64_t P, int C,
                       void* x2_scratch, void* y, void* rn, void* stream);
-/* gx written; g_beta_eff fp32 [C] accumulated (caller-zeroed).  x2 = x^2 (bf16): x2_ready != 0 -> kept from the forward
- * pass, else recomputed into it.  t_scratch receives t = d loss / d norm (bf16).  g_gamma_eff fp32 [C][C] (nullable):
- * accumulated here, or later / on another stream by lmsfc_gdn_wgrad(t, x2) -- it is off the critical path. */
+/* gx written.  x2 = x^2 (bf16): x2_ready != 0 -> kept from the forward pass, else recomputed into it.  t_scratch receives
+ * t = d loss / d norm (bf16), formed by the GEMM's producer warps.  The parameter gradients g_gamma_eff fp32 [C][C] and
+ * g_beta_eff fp32 [C] (accumulated, caller-zeroed) are either both given -- computed here -- or both NULL and computed
+ * later / on another stream by lmsfc_gdn_wgrad(t, x2): they are off the critical path. */
 int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void* gamma_eff, int inverse, int64_t P,
                        int C, void* x2, int x2_ready, void* t_scratch, void* gx, float* g_gamma_eff, float* g_beta_eff,
                        void* stream);
-int lmsfc_gdn_wgrad(const void* t, const void* x2, int64_t P, int C, float* g_gamma_eff, void* stream);
+int lmsfc_gdn_wgrad(const void* t, const void* x2, int64_t P, int C, float* g_gamma_eff, float* g_beta_eff, void* stream);
 /* NonNegativeParametrizer (ops/parametrizers.py:38-64) with LowerBound's gradient (ops/bound_ops.py:40-42):
  * out = max(p, bound)^2 - pedestal ; g_p += g_out * 2 max(p,bound) * [(p >= bound) | (g < 0)]. */
 int lmsfc_reparam_forward(const float* p, int64_t n, float bound, float pedestal, float* out_f32, void* out_bf16,

@@ -32,7 +32,7 @@ _SIGS = {
     "lmsfc_conv_wgrad": [POINTER(ConvDesc), P, P, P, P, P, P],
     "lmsfc_gdn_forward": [P, P, P, c_int, c_int64, c_int, P, P, P, P],
     "lmsfc_gdn_backward": [P, P, P, P, c_int, c_int64, c_int, P, c_int, P, P, P, P, P],
-    "lmsfc_gdn_wgrad": [P, P, c_int64, c_int, P, P],
+    "lmsfc_gdn_wgrad": [P, P, c_int64, c_int, P, P, P],
     "lmsfc_reparam_forward": [P, c_int64, c_float, c_float, P, P, P],
     "lmsfc_reparam_backward": [P, P, c_int64, c_float, P, P],
     "lmsfc_reparam_forward_multi": [P, P, P, c_int, c_int64, c_float, P, P, P],

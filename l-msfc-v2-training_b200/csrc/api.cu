@@ -174,12 +174,18 @@ static void gdn_gemm_params(IgemmParams& p, const bf16* a, const bf16* w, int64_
 
 extern "C" int lmsfc_gdn_forward(const void* x, const void* gamma_eff, const float* beta_eff, int inverse, int64_t P, int C,
                                  void* x2_scratch, void* y, void* rn, void* stream) {
-  LMSFC_CHECK_ARG(x && gamma_eff && beta_eff && x2_scratch && y, "gdn_forward: null operand");
+  LMSFC_CHECK_ARG(x && gamma_eff && beta_eff && y, "gdn_forward: null operand");
   LMSFC_CHECK_ARG(C % 128 == 0 && P > 0 && P < (1ll << 31), "gdn_forward: P=%lld C=%d", (long long)P, C);
-  int rc = square_bf16((const bf16*)x, (bf16*)x2_scratch, P * C, ST(stream));
-  if (rc) return rc;
   IgemmParams p;
-  gdn_gemm_params(p, (const bf16*)x2_scratch, (const bf16*)gamma_eff, P, C);
+  if (!x2_scratch) {   // inference: x^2 is formed by the GEMM's producer warps, nothing is kept
+    gdn_gemm_params(p, (const bf16*)x, (const bf16*)gamma_eff, P, C);
+    p.a_mode = 1;
+  } else {             // training: a streaming kernel writes x^2 (kept for the gamma gradient); A/B-measured 0.5 %
+                       // faster in the step than the fused producer (synchronous loads vs. the cp.async pipeline)
+    int rc = square_bf16((const bf16*)x, (bf16*)x2_scratch, P * C, ST(stream));
+    if (rc) return rc;
+    gdn_gemm_params(p, (const bf16*)x2_scratch, (const bf16*)gamma_eff, P, C);
+  }
   p.epi = EPI_GDN; p.inverse = inverse; p.bias = beta_eff; p.aux_x = (const bf16*)x;
   p.out_bf16 = (bf16*)y; p.out_rn = (bf16*)rn;
   return launch_igemm(p, ST(stream));
@@ -188,15 +194,19 @@ extern "C" int lmsfc_gdn_forward(const void* x, const void* gamma_eff, const flo
 extern "C" int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn, const void* gamma_eff, int inverse,
                                   int64_t P, int C, void* x2, int x2_ready, void* t_scratch, void* gx,
                                   float* g_gamma_eff, float* g_beta_eff, void* stream) {
-  LMSFC_CHECK_ARG(gy && x && rn && gamma_eff && t_scratch && gx && g_beta_eff && (x2 || !g_gamma_eff),
-                  "gdn_backward: null operand");
+  LMSFC_CHECK_ARG(gy && x && rn && gamma_eff && t_scratch && gx && (x2 || !g_gamma_eff) && (!g_gamma_eff == !g_beta_eff),
+                  "gdn_backward: null operand (the two parameter gradients are computed together, or both deferred)");
   LMSFC_CHECK_ARG(C % 256 == 0 && P > 0 && P < (1ll << 31), "gdn_backward: P=%lld C=%d", (long long)P, C);
-  int rc = gdn_t((const bf16*)gy, (const bf16*)x, (const bf16*)rn, inverse, P, C, (bf16*)t_scratch, g_beta_eff, ST(stream));
-  if (rc) return rc;
+  int rc;
   if (x2 && !x2_ready) {
     rc = square_bf16((const bf16*)x, (bf16*)x2, P * C, ST(stream));
     if (rc) return rc;
   }
+  // t by a plain streaming kernel (its column sums = g_beta ride in the weight-gradient wave).  Forming t inside the
+  // GEMM's producer warps (a_mode 2) was measured slower in the step: three synchronous load round trips per K block
+  // from HBM-resident x / rn under contention, against one cp.async pipeline over L2-resident t.
+  rc = gdn_t((const bf16*)gy, (const bf16*)x, (const bf16*)rn, inverse, P, C, (bf16*)t_scratch, nullptr, ST(stream));
+  if (rc) return rc;
   IgemmParams p;
   gdn_gemm_params(p, (const bf16*)t_scratch, (const bf16*)gamma_eff, P, C);
   p.w_mn = 1; p.w_ld_tap = C;      // s_j = sum_i gamma[i][j] t_i: gamma read as an MN-major operand
@@ -204,18 +214,25 @@ extern "C" int lmsfc_gdn_backward(const void* gy, const void* x, const void* rn,
   p.out_bf16 = (bf16*)gx;
   rc = launch_igemm(p, ST(stream));
   if (rc || !g_gamma_eff) return rc;
-  return lmsfc_gdn_wgrad(t_scratch, x2, P, C, g_gamma_eff, stream);
+  return lmsfc_gdn_wgrad(t_scratch, x2, P, C, g_gamma_eff, g_beta_eff, stream);
 }
 
-extern "C" int lmsfc_gdn_wgrad(const void* t, const void* x2, int64_t P, int C, float* g_gamma_eff, void* stream) {
-  LMSFC_CHECK_ARG(t && x2 && g_gamma_eff, "gdn_wgrad: null operand");
+extern "C" int lmsfc_gdn_wgrad(const void* t, const void* x2, int64_t P, int C, float* g_gamma_eff, float* g_beta_eff,
+                               void* stream) {
+  LMSFC_CHECK_ARG(t && x2 && g_gamma_eff && g_beta_eff, "gdn_wgrad: null operand");
   LMSFC_CHECK_ARG(C % 256 == 0 && P > 0 && P < (1ll << 31), "gdn_wgrad: P=%lld C=%d", (long long)P, C);
   WgradParams q;
   memset(&q, 0, sizeof(q));
   q.dense = (const bf16*)t; q.Cd = C; q.B = 1; q.Hg = 1; q.Wg = (int)P; q.M = (int)P;
   q.g0 = (const bf16*)x2; q.gc0 = C; q.Cg = C; q.Hin = 1; q.Win = (int)P; q.sin = 1;
   q.ntaps = 1; q.T = 1; q.out = g_gamma_eff;
-  return launch_wgrad(q, ST(stream));
+  if (C == 256) {      // g_beta = column sums of t: by the spare CTAs of the same wave
+    q.bias_src = (const bf16*)t; q.bias_P = P; q.gbias = g_beta_eff;
+    return launch_wgrad(q, ST(stream));
+  }
+  int rc = launch_wgrad(q, ST(stream));
+  if (rc) return rc;
+  return colsum_bf16((const bf16*)t, P, C, g_beta_eff, ST(stream));
 }
 
 extern "C" int lmsfc_reparam_forward(const float* p, int64_t n, float bound, float pedestal, float* out_f32, void* out_bf16,

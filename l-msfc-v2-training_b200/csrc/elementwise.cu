@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(256) gdn_t_kernel(const uint4* __restrict__ gy
       t[i] = make_uint4(o[0], o[1], o[2], o[3]);
     }
   }
-  colsum_finish(acc, c8, C8, g_beta, scratch, counter);
+  if (g_beta) colsum_finish(acc, c8, C8, g_beta, scratch, counter);   // null: the caller sums t's columns elsewhere
 }
 int gdn_t(const __nv_bfloat16* gy, const __nv_bfloat16* x, const __nv_bfloat16* rn, int inverse, int64_t P, int C,
           __nv_bfloat16* t, float* g_beta, cudaStream_t s) {

@@ -297,7 +297,47 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
     const uint32_t dst_thread = smem_base + r0 * 128 + ((chunk ^ (r0 & 7)) << 4);
     int stage = 0, phase = 0;
     int tap = ph.tap_begin + kb_begin / kc_per_tap, kc = kb_begin % kc_per_tap;
-    for (int kb = 0; kb < nkb; ++kb) {
+    if (p.a_mode != 0) {
+      // ---- computed operand (GDN forward): load x -> x^2 in registers -> swizzled st.shared (+ optional global copy)
+      const bool writer = p.a_out != nullptr && blockIdx.y == 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int coff = kc * BLOCK_K + chunk * 8;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        const uint32_t dst = dst_thread + stage * Cfg::STAGE_BYTES;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint4 xv[4];
+          size_t off[4];
+          bool okr[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int hi = hi0[4 * h + i], wi = wi0[4 * h + i];
+            okr[i] = (unsigned)hi < (unsigned)p.Hin && (unsigned)wi < (unsigned)p.Win;
+            off[i] = (size_t)(pixbase[4 * h + i] + hi * p.Win + wi) * p.c0 + coff;
+            xv[i] = okr[i] ? __ldg(reinterpret_cast<const uint4*>(p.src0 + off[i])) : make_uint4(0u, 0u, 0u, 0u);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t xx[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w};
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float x0 = bf16_lo(xx[j]), x1 = bf16_hi(xx[j]);
+              o[j] = pack_bf16(x0 * x0, x1 * x1);
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (4 * h + i) * 2048), "r"(o[0]), "r"(o[1]),
+                         "r"(o[2]), "r"(o[3])
+                         : "memory");
+            if (writer && okr[i]) *reinterpret_cast<uint4*>(p.a_out + off[i]) = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+        }
+        fence_proxy_async_smem();          // generic-proxy stores -> visible to the tensor core's async proxy
+        mbar_arrive(&full_bar[stage]);
+        if (++kc == kc_per_tap) { kc = 0; ++tap; }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+    for (int kb = (p.a_mode != 0 ? nkb : 0); kb < nkb; ++kb) {
       const int cbase = kc * BLOCK_K;
       const bool first = cbase < p.c0;
       const __nv_bfloat16* src = first ? p.src0 : p.src1;

@@ -48,6 +48,11 @@ struct IgemmParams {
   float* out_f32;           // nullable
   __nv_bfloat16* out_abs;   // nullable, |v| (feeds h_a, models/google.py:294)
   __nv_bfloat16* out_rn;    // EPI_GDN: rsqrt(norm), saved for backward
+  // a_mode 1: the activation operand is COMPUTED by the producer warps instead of copied: A = src0^2 (GDN forward
+  // without a scratch buffer); a_out (nullable) also receives it ([M][c0] bf16).  Forming the backward operand
+  // t = grad_out * x * f(rn) the same way was measured slower in the step (see lmsfc_gdn_backward).
+  int a_mode;
+  __nv_bfloat16* a_out;
   const __nv_bfloat16* aux_x;   // EPI_GDN / EPI_GDN_BWD
   const __nv_bfloat16* aux_gy;  // EPI_GDN_BWD
   const __nv_bfloat16* aux_rn;  // EPI_GDN_BWD

@@ -283,12 +283,14 @@ class _GDNFn(torch.autograd.Function):
             gamma_bf = torch.empty((C, C), dtype=BF16, device=dev)
             L.reparam_forward(ptr(beta), C, state.beta_bound, PEDESTAL, ptr(beta_eff), None, st)
             L.reparam_forward(ptr(gamma), C * C, state.gamma_bound, PEDESTAL, None, ptr(gamma_bf), st)
-        x2 = torch.empty_like(x)
+        train = any(ctx.needs_input_grad[:3])
+        x2 = torch.empty_like(x) if train else None      # inference: x^2 never leaves the GEMM's producer warps
         y = torch.empty_like(x)
         rn = torch.empty_like(x)
         L.gdn_forward(ptr(x), ptr(gamma_bf), ptr(beta_eff), int(state.inverse), P, C, ptr(x2), ptr(y), ptr(rn), st)
         ctx.state, ctx.beta, ctx.gamma = state, beta, gamma
-        ctx.save_for_backward(x, rn, gamma_bf, x2)       # x^2 is kept: 180 GB of HBM, no recompute pass in backward
+        if train:
+            ctx.save_for_backward(x, rn, gamma_bf, x2)   # x^2 is kept: 180 GB of HBM, no recompute pass in backward
         return y
 
     @staticmethod
@@ -309,7 +311,7 @@ class _GDNFn(torch.autograd.Function):
             g_beta_eff = torch.zeros(C, dtype=F32, device=dev)
         ws = SideStreams.wgrad if arena is not None else None
         L.gdn_backward(ptr(gy), ptr(x), ptr(rn), ptr(gamma_bf), int(state.inverse), P, C, ptr(x2), 1, ptr(t), ptr(gx),
-                       None if ws is not None else ptr(g_gamma_eff), ptr(g_beta_eff), st)
+                       None if ws is not None else ptr(g_gamma_eff), None if ws is not None else ptr(g_beta_eff), st)
         if ws is not None:                       # gamma's gradient GEMM is off the critical path
             ev = torch.cuda.Event()
             ev.record()
@@ -317,7 +319,7 @@ class _GDNFn(torch.autograd.Function):
             x2.record_stream(ws)
             with torch.cuda.stream(ws):
                 ws.wait_event(ev)
-                L.gdn_wgrad(ptr(t), ptr(x2), P, C, ptr(g_gamma_eff), stream())
+                L.gdn_wgrad(ptr(t), ptr(x2), P, C, ptr(g_gamma_eff), ptr(g_beta_eff), stream())   # gamma and beta gradients
         beta, gamma = ctx.beta, ctx.gamma
         if arena is not None:
             arena.queue_finish_backward()       # one batched reparam-backward at the end of this backward pass
