@@ -35,6 +35,9 @@ class SideStreams:
     * `heads`: the 3x3 output heads of g_s (p5, p4, p3 reconstructions) only feed the distortion term, so they run
       beside the next up-sampling stage; in backward their data gradients run beside the up-sampling stage's.
     Disabled (None) by default: stand-alone modules run on the caller's stream."""
+    N_WGRAD = int(__import__("os").environ.get("LMSFC_N_WGRAD", "2"))
+    _wgrad_pool = []
+    _wgrad_next = 0
     wgrad = None
     hyper = None
     opt = None
@@ -44,6 +47,9 @@ class SideStreams:
     @classmethod
     def enable(cls, device, wgrad=True, hyper=True, opt=True, heads=True):
         cls.wgrad = torch.cuda.Stream(device=device) if wgrad else None
+        n = int(wgrad) if wgrad is not True else cls.N_WGRAD
+        cls._wgrad_pool = [cls.wgrad] + [torch.cuda.Stream(device=device) for _ in range(max(0, n - 1))] if wgrad else []
+        cls._wgrad_next = 0
         cls.hyper = torch.cuda.Stream(device=device) if hyper else None
         cls.opt = torch.cuda.Stream(device=device) if opt else None
         cls.heads = torch.cuda.Stream(device=device) if heads else None
@@ -51,6 +57,22 @@ class SideStreams:
     @classmethod
     def disable(cls):
         cls.wgrad = cls.hyper = cls.opt = cls.heads = None
+        cls._wgrad_pool = []
+
+    @classmethod
+    def next_wgrad(cls):
+        """Round-robin over the weight-gradient streams: consecutive layers' (latency-bound) gradient GEMMs overlap."""
+        if not cls._wgrad_pool:
+            return None
+        s = cls._wgrad_pool[cls._wgrad_next % len(cls._wgrad_pool)]
+        cls._wgrad_next += 1
+        return s
+
+    @classmethod
+    def join_wgrad(cls):
+        cur = torch.cuda.current_stream()
+        for s in cls._wgrad_pool:
+            cur.wait_stream(s)
 
     @classmethod
     def queue_join(cls):
@@ -62,8 +84,7 @@ class SideStreams:
     @classmethod
     def _join(cls):
         cls._join_queued = False
-        if cls.wgrad is not None:
-            torch.cuda.current_stream().wait_stream(cls.wgrad)
+        cls.join_wgrad()
 
 
 def _require_cuda(t):
@@ -202,7 +223,7 @@ class _ConvFn(torch.autograd.Function):
         # ---- weight / bias gradients, straight into param.grad; on the side stream when one is enabled
         weight, bias = ctx.weight, ctx.bias
         if weight.requires_grad:
-            ws = SideStreams.wgrad
+            ws = SideStreams.next_wgrad()
             if ws is not None:
                 ev = torch.cuda.Event()
                 ev.record()                      # g is complete on the current stream
@@ -309,7 +330,7 @@ class _GDNFn(torch.autograd.Function):
         else:
             g_gamma_eff = torch.zeros((C, C), dtype=F32, device=dev)
             g_beta_eff = torch.zeros(C, dtype=F32, device=dev)
-        ws = SideStreams.wgrad if arena is not None else None
+        ws = SideStreams.next_wgrad() if arena is not None else None
         L.gdn_backward(ptr(gy), ptr(x), ptr(rn), ptr(gamma_bf), int(state.inverse), P, C, ptr(x2), 1, ptr(t), ptr(gx),
                        None if ws is not None else ptr(g_gamma_eff), None if ws is not None else ptr(g_beta_eff), st)
         if ws is not None:                       # gamma's gradient GEMM is off the critical path

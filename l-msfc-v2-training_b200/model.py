@@ -397,8 +397,7 @@ class ParamArena:
         self._finish_queued = False
         if not self.gdn_layers:
             return
-        if Fn.SideStreams.wgrad is not None:     # gamma's gradient GEMMs ran on the weight-gradient stream
-            torch.cuda.current_stream().wait_stream(Fn.SideStreams.wgrad)
+        Fn.SideStreams.join_wgrad()              # gamma / beta gradient GEMMs ran on the weight-gradient streams
         L.reparam_backward_multi(ptr(self._grads_all), ptr(self.net_params), ptr(self.gdn_table), ptr(self.gdn_bounds),
                                  self.gdn_table.shape[0], self.gdn_max_n, ptr(self.net_grads), stream())
         for m in self.gdn_layers:

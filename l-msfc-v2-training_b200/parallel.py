@@ -84,10 +84,18 @@ class BucketedGradReducer:
         b = self.buckets[i]
         view = self.grads[b["lo"]:b["hi"]]
         if self.comm_stream is not None:
-            ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream())
+            # a bucket's gradients may come from any of the weight-gradient streams (round-robin) and from the
+            # current one: the exchange waits for what has been enqueued on each of them so far
+            from .functional import SideStreams
+            producers = {torch.cuda.current_stream()} | set(SideStreams._wgrad_pool)
+            evs = []
+            for s in producers:
+                ev = torch.cuda.Event()
+                ev.record(s)
+                evs.append(ev)
             with torch.cuda.stream(self.comm_stream):
-                self.comm_stream.wait_event(ev)
+                for ev in evs:
+                    self.comm_stream.wait_event(ev)
                 dist.all_reduce(view, op=dist.ReduceOp.AVG, group=self.pg)
         else:   # gloo (CPU tests of the host logic): no AVG op, no streams
             w = dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
