@@ -35,7 +35,7 @@ class SideStreams:
     * `heads`: the 3x3 output heads of g_s (p5, p4, p3 reconstructions) only feed the distortion term, so they run
       beside the next up-sampling stage; in backward their data gradients run beside the up-sampling stage's.
     Disabled (None) by default: stand-alone modules run on the caller's stream."""
-    N_WGRAD = int(__import__("os").environ.get("LMSFC_N_WGRAD", "2"))
+    N_WGRAD = int(__import__("os").environ.get("LMSFC_N_WGRAD", "3"))
     _wgrad_pool = []
     _wgrad_next = 0
     wgrad = None
