@@ -216,7 +216,7 @@ def run_b200(args):
     ts.step(feats)                           # eager once (lazy init), then capture the graph
     torch.cuda.synchronize()
     note("eager step done")
-    ts.capture(feats, warmup=1, pipelined=not args.sequential)
+    ts.capture(feats, warmup=1, pipelined=not args.sequential, n_buffers=2)
     launches_per_step = ts.launches_per_step               # launches of this library recorded into the graph
     torch.cuda.synchronize()
     note("graph captured")
@@ -244,7 +244,7 @@ def run_b200(args):
     ms = e0.elapsed_time(e1)
     # ---- end to end: pinned host features -> H2D (copy stream, double buffered) -> step -> D2H loss
     copy_stream = torch.cuda.Stream(device=dev)
-    dbuf = [{k: torch.empty_like(v, device=dev) for k, v in host[0].items()} for _ in range(2)]
+    dbuf = [ts.input_buffers(0), ts.input_buffers(1)]     # H2D lands directly in the buffers the two graphs read
     loss_host = torch.zeros(args.steps, 4).pin_memory()
     main = torch.cuda.current_stream()
     barrier()
@@ -264,10 +264,9 @@ def run_b200(args):
         if i >= 1:                           # run step i-1
             b = (i - 1) % 2
             main.wait_event(ready[b])
-            out = ts.replay(dbuf[b])
+            out = ts.replay(buffer=b)
             consumed[b].record(main)
-            loss_host[i - 1].copy_(torch.stack([out["loss"], out["bpp_loss"], out["mse_loss"], out["aux_loss"]]),
-                                   non_blocking=True)
+            loss_host[i - 1].copy_(out["scalars"], non_blocking=True)
     f1.record()
     barrier()
     ms_e2e = f0.elapsed_time(f1)
@@ -317,7 +316,7 @@ def run_b200(args):
         # graph hung (measured, 2 GPUs).  Drop the graph first; exit hard if the teardown still does not return.
         dist.barrier()
         torch.cuda.synchronize()
-        ts.graph = None
+        ts.release()
         del ts
         torch.cuda.synchronize()
         killer = threading.Timer(20.0, lambda: os._exit(0))

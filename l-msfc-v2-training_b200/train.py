@@ -149,12 +149,16 @@ class TrainStep:
             self.arena.gates = {}
 
     # ------------------------------------------------------------------ CUDA graph
-    def capture(self, feats, warmup=2, pipelined=False):
+    def capture(self, feats, warmup=2, pipelined=False, n_buffers=1):
         """Record one iteration.  `feats` fixes the shapes; its values are copied into static
-        input buffers on every replay.  pipelined: see the module docstring (call flush() at the end)."""
+        input buffers on every replay.  pipelined: see the module docstring (call flush() at the end).
+        n_buffers > 1 records the same iteration once per input buffer (`input_buffers(k)`, `replay(buffer=k)`):
+        a loader copies host features straight into buffer k+1 while the step on buffer k runs -- no staging copy."""
         lv = self.model.spec.levels
         dev = self.arena.device
-        self.static_in = {k: Fn.nhwc(feats[k], Fn.BF16).clone(memory_format=torch.channels_last) for k in lv}
+        self.static_ins = [{k: Fn.nhwc(feats[k], Fn.BF16).clone(memory_format=torch.channels_last) for k in lv}
+                           for _ in range(max(1, int(n_buffers)))]
+        self.static_in = self.static_ins[0]
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -165,15 +169,31 @@ class TrainStep:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.pipelined = bool(pipelined)
-        c0 = L.launch_count()
-        self.graph = torch.cuda.CUDAGraph()
         # the critical path (forward / data-gradient chain) is captured on a high-priority stream: its CTAs are
         # dispatched before those of the weight-gradient / optimiser / hyper / head streams whenever SMs free up
         cap = torch.cuda.Stream(device=dev, priority=-1)
-        with torch.cuda.graph(self.graph, stream=cap):
-            self.static_out = (self._iteration_pipelined if pipelined else self._iteration)(self.static_in)
-        self.launches_per_step = L.launch_count() - c0
+        self.graphs, self.static_outs = [], []
+        for buf in self.static_ins:
+            c0 = L.launch_count()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=cap):
+                out = (self._iteration_pipelined if pipelined else self._iteration)(buf)
+                # the four loss scalars packed for one device-to-host read per step
+                out["scalars"] = torch.stack([out["loss"], out["bpp_loss"], out["mse_loss"], out["aux_loss"]])
+            self.launches_per_step = L.launch_count() - c0
+            self.graphs.append(g)
+            self.static_outs.append(out)
+        self.graph, self.static_out = self.graphs[0], self.static_outs[0]
         return self
+
+    def release(self):
+        """Drop the captured graphs (before destroying an NCCL communicator whose kernels they hold)."""
+        self.graphs, self.static_outs = [], []
+        self.graph = self.static_out = None
+
+    def input_buffers(self, k=0):
+        """The static bf16 NHWC input tensors graph k reads ({level: tensor}); fill them before replay(buffer=k)."""
+        return self.static_ins[k]
 
     def _iteration_pipelined_warm(self, feats):
         """Eager rotated iterations before capture: allocator warm-up of the rotated order, and the pipeline primed."""
@@ -181,14 +201,14 @@ class TrainStep:
         self._grad_pass(feats)
         self._iteration_pipelined(feats)
 
-    def replay(self, feats=None):
+    def replay(self, feats=None, buffer=0):
         if feats is not None:
-            for k, buf in self.static_in.items():
+            for k, buf in self.static_ins[buffer].items():
                 src = feats[k]
                 if src.data_ptr() != buf.data_ptr():
                     buf.copy_(src, non_blocking=True)
-        self.graph.replay()
-        return self.static_out
+        self.graphs[buffer].replay()
+        return self.static_outs[buffer]
 
 
 class _Null:

@@ -74,7 +74,7 @@ def _worker(rank, world, port, out):
     out[f"losses_{rank}"] = losses
     dist.barrier()
     torch.cuda.synchronize()
-    ts.graph = None
+    ts.release()
     del ts
     torch.cuda.synchronize()
     dist.destroy_process_group()
