@@ -129,7 +129,6 @@ __device__ __forceinline__ void colsum_finish(const float (&acc)[8], int c8, int
   }
 }
 
-namespace {
 // One scratch slot per CUDA stream: kernels of one stream serialise, kernels of different streams (the
 // weight-gradient side stream, the hyperprior side stream) may overlap and must not share partial sums.
 constexpr int kRedBlocksY = 296, kRedMaxC = 2048, kRedSlots = 16;
@@ -156,7 +155,6 @@ int red_slot(cudaStream_t s) {
 }
 float* red_scratch(cudaStream_t s) { return g_red_scratch + (size_t)red_slot(s) * kRedBlocksY * kRedMaxC; }
 unsigned int* red_count(cudaStream_t s) { return g_red_count + red_slot(s) * 64; }
-}  // namespace
 
 // ---------------------------------------------------------------- GDN helper passes
 __global__ void __launch_bounds__(TPB) square_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int64_t n8) {

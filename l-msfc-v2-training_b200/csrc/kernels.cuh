@@ -85,6 +85,11 @@ struct AdamArgs {
   float* scratch;            // >= 4 floats: {clip_coef, bias_corr1, bias_corr2, grad_norm}
   int zero_g;
 };
+// reduction scratch shared by the two-stage reductions (elementwise.cu): one slot per stream, 296 x 2048 floats and 64
+// self-resetting counters each
+int ensure_reduce_scratch();
+float* red_scratch(cudaStream_t s);
+unsigned int* red_count(cudaStream_t s);
 int adam_step(const AdamArgs& a, cudaStream_t s);
 int adam_prep(const AdamArgs& a, cudaStream_t s);     // step counter + clip / bias-correction scalars
 int adam_update(const AdamArgs& a, cudaStream_t s);   // the element-wise pass, given a prepared scratch

@@ -16,8 +16,11 @@ inline int grid1d(int64_t work_items) {
 }  // namespace
 
 // ---------------------------------------------------------------- sum of squares (grad norm)
+// Deterministic: block partials are parked in scratch and the LAST block to arrive adds them up in index order, so two
+// ranks holding the same (all-reduced) gradient compute bit-identical norms -> identical clip coefficients -> replicas
+// never drift apart (float atomics made the norm differ in the last bits from run to run and rank to rank).
 __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g, int64_t n4, const float* tail, int ntail,
-                                                    float* accum) {
+                                                    float* accum, float* partial, unsigned int* counter) {
   pdl_sync();
   float local = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n4; i += (int64_t)gridDim.x * TPB) {
@@ -26,14 +29,31 @@ __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g
   }
   if (blockIdx.x == 0 && (int)threadIdx.x < ntail) local += tail[threadIdx.x] * tail[threadIdx.x];
   __shared__ float red[32];
+  __shared__ unsigned int is_last;
   local = block_sum(local, red);
-  if (threadIdx.x == 0) atomicAdd(accum, local);
+  if (threadIdx.x == 0) {
+    __stcg(partial + blockIdx.x, local);
+    __threadfence();
+    const unsigned int prev = atomicAdd(counter, 1u);
+    is_last = (prev == gridDim.x - 1) ? 1u : 0u;
+    if (is_last) *counter = 0;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    float v = 0.f;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += TPB) v += __ldcg(partial + i);   // fixed order per thread
+    v = block_sum(v, red);                                                               // fixed tree
+    if (threadIdx.x == 0) *accum += v;
+  }
 }
 int sumsq_f32(const float* g, int64_t n, float* accum, cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
   LMSFC_CHECK_ARG(((uintptr_t)g & 15) == 0, "sumsq: pointer must be 16-byte aligned");
+  if (int rc = ensure_reduce_scratch()) return rc;
   const int64_t n4 = n / 4;
-  LMSFC_LAUNCH(sumsq_kernel, dim3(grid1d(n4 > 0 ? n4 : 1)), dim3(TPB), 0, s, (const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum);
+  LMSFC_LAUNCH(sumsq_kernel, dim3(grid1d(n4 > 0 ? n4 : 1)), dim3(TPB), 0, s, (const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum,
+               red_scratch(s), red_count(s) + 63);
   return LMSFC_OK;
 }
 

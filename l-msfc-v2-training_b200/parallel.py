@@ -12,7 +12,7 @@ import torch.distributed as dist
 
 
 class BucketedGradReducer:
-    def __init__(self, model, bucket_mb=16.0, process_group=None):
+    def __init__(self, model, bucket_mb=32.0, process_group=None, tail_mb=8.0):
         if model.arena is None:
             model.build_arena()
         self.model, self.arena = model, model.arena
@@ -34,6 +34,21 @@ class BucketedGradReducer:
                 hi, cur_names = cur_lo, []
         if cur_names:
             self.buckets.append({"lo": cur_lo, "hi": hi, "names": set(cur_names)})
+        # The bucket at the START of the arena completes last (first conv layer, GDN group, EntropyBottleneck) and its
+        # exchange cannot overlap anything: keep it small by cutting it at the parameter boundary that leaves at most
+        # tail_mb in the final piece.
+        tail_cap = int(tail_mb * (1 << 20) / 4)
+        last = self.buckets[-1]
+        if tail_cap > 0 and last["hi"] - last["lo"] > tail_cap:
+            inside = sorted((self.arena.offsets[n], n) for n in last["names"])
+            cut = None
+            for o, n in inside:
+                if o - last["lo"] <= tail_cap and o > last["lo"]:
+                    cut = o
+            if cut is not None:
+                head = {n for o, n in inside if o >= cut}
+                self.buckets[-1] = {"lo": cut, "hi": last["hi"], "names": head}
+                self.buckets.append({"lo": last["lo"], "hi": cut, "names": last["names"] - head})
         self.bucket_of = {}
         for i, b in enumerate(self.buckets):
             for n in b["names"]:
