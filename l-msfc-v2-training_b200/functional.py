@@ -50,9 +50,9 @@ class SideStreams:
         n = int(wgrad) if wgrad is not True else cls.N_WGRAD
         cls._wgrad_pool = [cls.wgrad] + [torch.cuda.Stream(device=device) for _ in range(max(0, n - 1))] if wgrad else []
         cls._wgrad_next = 0
-        cls.hyper = torch.cuda.Stream(device=device) if hyper else None
+        cls.hyper = torch.cuda.Stream(device=device, priority=-1) if hyper else None   # on the forward's tail: A/B 1.036 -> 1.014 ms
         cls.opt = torch.cuda.Stream(device=device) if opt else None
-        cls.heads = torch.cuda.Stream(device=device) if heads else None
+        cls.heads = torch.cuda.Stream(device=device, priority=-1) if heads else None   # their outputs gate the loss: A/B 1.008 -> 1.000 ms
 
     @classmethod
     def disable(cls):
