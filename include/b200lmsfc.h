@@ -112,6 +112,10 @@ int lmsfc_rng_advance(uint64_t* rng_state, void* stream);
 /* sse += sum (xhat-x)^2 ; grad (nullable) = grad_coef*(xhat-x), bf16. */
 int lmsfc_mse_forward_backward(const void* xhat, const void* x, int64_t n, float grad_coef, float* sse, void* grad,
                                void* stream);
+/* The same for up to 8 tensors (pyramid levels) in one launch: HOST arrays of device pointers / sizes / coefficients,
+ * sse[l] += ..., grad (nullable array, nullable entries). */
+int lmsfc_mse_forward_backward_multi(int nlev, const void* const* xhat, const void* const* x, const int64_t* n,
+                                     const float* grad_coef, float* sse, void* const* grad, void* stream);
 /* out[0]=bpp=sum_{i<n_rate} accum[i]*coef[i]; out[1]=D=sum over the next n_dist; out[2]=lambda_scale*D+bpp */
 int lmsfc_loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale, float* out,
                         void* stream);

@@ -44,6 +44,7 @@ _SIGS = {
     "lmsfc_eb_aux_loss": [P, P, P, c_int, P, P, P],
     "lmsfc_rng_advance": [P, P],
     "lmsfc_mse_forward_backward": [P, P, c_int64, c_float, P, P, P],
+    "lmsfc_mse_forward_backward_multi": [c_int, P, P, P, P, P, P, P],
     "lmsfc_loss_finalize": [P, P, c_int, c_int, c_float, P, P],
     "lmsfc_relu_backward": [P, P, c_int64, P],
     "lmsfc_abs_backward": [P, P, P, c_int64, c_int, P, P],

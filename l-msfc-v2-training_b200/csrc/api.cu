@@ -303,6 +303,11 @@ extern "C" int lmsfc_mse_forward_backward(const void* xhat, const void* x, int64
   LMSFC_CHECK_ARG(n == 0 || (xhat && x && sse), "mse: null operand");
   return mse_fwd_bwd((const bf16*)xhat, (const bf16*)x, n, grad_coef, sse, (bf16*)grad, ST(stream));
 }
+extern "C" int lmsfc_mse_forward_backward_multi(int nlev, const void* const* xhat, const void* const* x, const int64_t* n,
+                                                const float* grad_coef, float* sse, void* const* grad, void* stream) {
+  LMSFC_CHECK_ARG(xhat && x && n && grad_coef && sse, "mse_multi: null operand");
+  return mse_fwd_bwd_multi(nlev, xhat, x, n, grad_coef, sse, grad, ST(stream));
+}
 extern "C" int lmsfc_loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale,
                                    float* out, void* stream) {
   return loss_finalize(accum, coef, n_rate, n_dist, lambda_scale, out, ST(stream));

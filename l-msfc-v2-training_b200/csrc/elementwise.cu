@@ -51,6 +51,67 @@ int mse_fwd_bwd(const __nv_bfloat16* xhat, const __nv_bfloat16* x, int64_t n, fl
   return LMSFC_OK;
 }
 
+// all pyramid levels in ONE launch (the loss sits on the step's critical path between forward and backward)
+struct MseMultiArgs {
+  const uint4* xh[kMseMaxLevels];
+  const uint4* x[kMseMaxLevels];
+  uint4* grad[kMseMaxLevels];
+  int64_t n8[kMseMaxLevels];
+  float coef[kMseMaxLevels];
+  int blk_end[kMseMaxLevels];     // blocks [blk_end[l-1], blk_end[l]) work on level l
+  int nlev;
+  float* sse;                     // [nlev]
+};
+__global__ void __launch_bounds__(TPB) mse_multi_kernel(const __grid_constant__ MseMultiArgs a) {
+  pdl_sync();
+  int l = 0;
+  while (l + 1 < a.nlev && (int)blockIdx.x >= a.blk_end[l]) ++l;
+  const int b0 = l ? a.blk_end[l - 1] : 0, nb = a.blk_end[l] - b0;
+  const uint4* __restrict__ xh = a.xh[l];
+  const uint4* __restrict__ x = a.x[l];
+  uint4* __restrict__ grad = a.grad[l];
+  const float coef = a.coef[l];
+  float local = 0.f;
+  for (int64_t i = (int64_t)(blockIdx.x - b0) * TPB + threadIdx.x; i < a.n8[l]; i += (int64_t)nb * TPB) {
+    const uint4 p = __ldg(xh + i), q = __ldg(x + i);
+    const uint32_t av[4] = {p.x, p.y, p.z, p.w}, bv[4] = {q.x, q.y, q.z, q.w};
+    uint32_t gv[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float d0 = lo(av[j]) - lo(bv[j]), d1 = hi(av[j]) - hi(bv[j]);
+      local += d0 * d0 + d1 * d1;
+      gv[j] = pack_bf16(coef * d0, coef * d1);
+    }
+    if (grad) grad[i] = make_uint4(gv[0], gv[1], gv[2], gv[3]);
+  }
+  __shared__ float red[32];
+  local = block_sum(local, red);
+  if (threadIdx.x == 0) atomicAdd(a.sse + l, local);
+}
+int mse_fwd_bwd_multi(int nlev, const void* const* xhat, const void* const* x, const int64_t* n, const float* grad_coef,
+                      float* sse, void* const* grad, cudaStream_t s) {
+  LMSFC_CHECK_ARG(nlev >= 1 && nlev <= kMseMaxLevels, "mse_multi: %d levels (max %d)", nlev, kMseMaxLevels);
+  MseMultiArgs a;
+  memset(&a, 0, sizeof(a));
+  int64_t total8 = 0;
+  for (int l = 0; l < nlev; ++l) {
+    LMSFC_CHECK_ARG(n[l] > 0 && n[l] % 8 == 0 && xhat[l] && x[l], "mse_multi: level %d n=%lld", l, (long long)n[l]);
+    total8 += n[l] / 8;
+  }
+  const int budget = 148 * 8;      // blocks shared out in proportion to the level sizes, at least one each
+  int end = 0;
+  for (int l = 0; l < nlev; ++l) {
+    a.xh[l] = (const uint4*)xhat[l]; a.x[l] = (const uint4*)x[l]; a.grad[l] = (uint4*)(grad ? grad[l] : nullptr);
+    a.n8[l] = n[l] / 8; a.coef[l] = grad_coef[l];
+    int64_t want = (a.n8[l] + TPB - 1) / TPB, share = (int64_t)budget * a.n8[l] / total8;
+    end += (int)max((int64_t)1, min(want, max(share, (int64_t)1)));
+    a.blk_end[l] = end;
+  }
+  a.nlev = nlev; a.sse = sse;
+  LMSFC_LAUNCH(mse_multi_kernel, dim3(end), dim3(TPB), 0, s, a);
+  return LMSFC_OK;
+}
+
 // out = {bpp, distortion, loss}: bpp = sum_{i<n_rate} accum[i]*coef[i];
 // D = sum_{n_rate<=i<n_rate+n_dist} accum[i]*coef[i]; loss = lambda_scale*D + bpp.
 __global__ void loss_finalize_kernel(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale,

@@ -611,14 +611,14 @@ class _RDLossFn(torch.autograd.Function):
         for i, lk in enumerate(liks):
             s = getattr(lk, _SUM_LN_ATTR, None)
             accum[i:i + 1] = s if s is not None else torch.log(lk.float()).sum()
-        grads = []
-        for i in range(n_lev):
-            n = xh[i].numel()
-            g = torch.empty_like(xh[i]) if ctx.needs_input_grad[5 + i] else None
-            L.mse_forward_backward(ptr(xh[i]), ptr(xt[i]), n, lmbda_scale * weights[i] * 2.0 / n, ptr(accum[n_lik + i:]),
-                                   ptr(g), st)
-            coef.append(weights[i] / n)
-            grads.append(g)
+        import ctypes
+        grads = [torch.empty_like(xh[i]) if ctx.needs_input_grad[5 + i] else None for i in range(n_lev)]
+        ns = [xh[i].numel() for i in range(n_lev)]
+        VP, I64, F32A = ctypes.c_void_p * n_lev, ctypes.c_int64 * n_lev, ctypes.c_float * n_lev
+        L.mse_forward_backward_multi(n_lev, VP(*[ptr(t) for t in xh]), VP(*[ptr(t) for t in xt]), I64(*ns),
+                                     F32A(*[lmbda_scale * weights[i] * 2.0 / ns[i] for i in range(n_lev)]),
+                                     ptr(accum[n_lik:]), VP(*[ptr(g) for g in grads]), st)   # all levels, one launch
+        coef += [weights[i] / ns[i] for i in range(n_lev)]
         coef_t = _const_tensor(tuple(coef), dev)
         out = torch.empty(3, dtype=F32, device=dev)
         L.loss_finalize(ptr(accum), ptr(coef_t), n_lik, n_lev, lmbda_scale, ptr(out), st)
