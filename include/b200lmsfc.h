@@ -155,6 +155,30 @@ int lmsfc_pmf_to_quantized_cdf(const float* pmf_host, int n, int precision, uint
 int lmsfc_pmf_rows_to_cdf(const float* pmf, int pmf_stride, const float* tail, const int* pmf_length, int rows,
                           int precision, int32_t* cdf, int cdf_stride, int* status, void* stream);
 
+/* ------------------------------------------------------------------ range-ANS entropy coding
+ * Replaces the pybind11 module `compressai.ans` (cpp_exts/rans/rans_interface.cpp:108-288, ryg rans64.h) behind
+ * EntropyModel.compress / decompress (entropy_models/entropy_models.py:235-325).  symbols / indexes are int32
+ * [items][n] (an item flattened in NCHW order, like `symbols[i].reshape(-1)`); cdfs int32 [rows][cdf_stride],
+ * sizes = `_cdf_length`, offsets = `_offset`.  Lane k of `lanes` codes symbols[item][k::lanes] as one reference
+ * string (lanes = 1: the reference's bytes).  16-bit probabilities, 4-bit bypass digits, as in the reference.
+ *
+ * encode: scratch holds items*lanes*lane_cap words (lane_cap >= lmsfc_rans_lane_cap(n, lanes)), lane_words
+ * [items*lanes], lane_offsets [items*lanes + 1] (word offset of every lane in `packed`, last = total words),
+ * packed [packed_cap] words; status (device int, caller-zeroed): 1 index outside the tables, 2 out of space. */
+int64_t lmsfc_rans_lane_cap(int64_t n, int lanes);
+int lmsfc_rans_encode(const int32_t* symbols, const int32_t* indexes, int items, int64_t n, int lanes,
+                      const int32_t* cdfs, int rows, int cdf_stride, const int32_t* sizes, const int32_t* offsets,
+                      uint32_t* scratch, int64_t lane_cap, uint32_t* lane_words, uint32_t* lane_offsets,
+                      uint32_t* packed, int64_t packed_cap, int* status, void* stream);
+/* decode: packed [packed_words] = the lanes' strings back to back, lane_offsets [items*lanes] their word offsets. */
+int lmsfc_rans_decode(const uint32_t* packed, int64_t packed_words, const uint32_t* lane_offsets,
+                      const int32_t* indexes, int items, int64_t n, int lanes, const int32_t* cdfs, int rows,
+                      int cdf_stride, const int32_t* sizes, const int32_t* offsets, int32_t* symbols_out, int* status,
+                      void* stream);
+/* GaussianConditional.build_indexes (entropy_models.py:684-689) */
+int lmsfc_gc_build_indexes(const float* scales, int64_t n, const float* scale_table, int table_len, float scale_bound,
+                           int32_t* indexes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,8 +58,11 @@ _SIGS = {
     "lmsfc_adam_update": [P, P, P, P, P, c_int64, c_float, c_float, c_float, c_float, P, c_int, P],
     "lmsfc_pmf_to_quantized_cdf": [P, c_int, c_int, P],
     "lmsfc_pmf_rows_to_cdf": [P, c_int, P, P, c_int, c_int, P, c_int, P, P],
+    "lmsfc_rans_encode": [P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, c_int64, P, P, P, c_int64, P, P],
+    "lmsfc_rans_decode": [P, c_int64, P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, P, P],
+    "lmsfc_gc_build_indexes": [P, c_int64, P, c_int, c_float, P, P],
 }
-EXPORTS = ["lmsfc_last_error", "lmsfc_version", "lmsfc_launch_count"] + list(_SIGS)
+EXPORTS = ["lmsfc_last_error", "lmsfc_version", "lmsfc_launch_count", "lmsfc_rans_lane_cap"] + list(_SIGS)
 
 lib.lmsfc_last_error.restype = c_char_p
 lib.lmsfc_last_error.argtypes = []
@@ -67,6 +70,8 @@ lib.lmsfc_version.restype = c_int
 lib.lmsfc_version.argtypes = []
 lib.lmsfc_launch_count.restype = c_uint64
 lib.lmsfc_launch_count.argtypes = []
+lib.lmsfc_rans_lane_cap.restype = c_int64
+lib.lmsfc_rans_lane_cap.argtypes = [c_int64, c_int]
 
 
 def launch_count():

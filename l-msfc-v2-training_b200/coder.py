@@ -1,0 +1,141 @@
+"""Host side of the device range coder (csrc/rans.cu), behind EntropyModel.compress / decompress.
+
+Replaces `compressai.ans.RansEncoder().encode_with_indexes` / `RansDecoder().decode_with_indexes` and the
+per-item `.tolist()` loops around them (compressai/entropy_models/entropy_models.py:256-268, :309-323): the whole
+batch is coded by one launch (one thread per string), and only the finished bytes cross PCIe.
+
+Strings
+  lanes = 1   the item's string is byte-identical to the reference's (one rANS string over the flattened item).
+  lanes = K   container: u32 K, K x u32 word counts, then the K lane strings back to back; lane k is the
+              reference string of symbols[k::K].  Costs 12 bytes per lane (length + the 8-byte final state) and
+              buys K-way parallelism inside one item; `decode_batch` reads K from the container.
+"""
+import struct
+from typing import List
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from ._lib import ptr, stream
+
+LANE_MAGIC = 0x4C414E45  # "LANE": first word of a multi-lane item string (a reference string never needs it: K = 1)
+
+
+def _tables(cdf, cdf_length, offset, dev):
+    cdf = cdf.to(dev, torch.int32).contiguous()
+    return cdf, cdf_length.to(dev, torch.int32).reshape(-1).contiguous(), offset.to(dev, torch.int32).reshape(-1).contiguous()
+
+
+def _check_status(status, who):
+    s = int(status.item())
+    if s == 1:
+        raise ValueError(f"{who}: index outside the CDF tables (or an empty / over-long CDF row)")
+    if s:
+        raise RuntimeError(f"{who}: out of string space (status {s})")
+
+
+def encode_device(symbols, indexes, cdf, cdf_length, offset, lanes: int = 1):
+    """-> (packed uint32 device tensor [total words], lane_offsets int64 numpy [items*lanes + 1]).
+    symbols / indexes: int32 [items, ...] on a CUDA device."""
+    if symbols.device.type != "cuda":
+        raise RuntimeError("coder: symbols must live on a CUDA device (l-msfc-v2-training_b200 has no CPU fallback)")
+    dev = symbols.device
+    items = symbols.shape[0]
+    sym = symbols.reshape(items, -1).to(torch.int32).contiguous()
+    idx = indexes.reshape(items, -1).to(dev, torch.int32).contiguous()
+    n = sym.shape[1] if items else 0
+    cdf, sizes, offs = _tables(cdf, cdf_length, offset, dev)
+    T = items * lanes
+    cap = int(L.lib.lmsfc_rans_lane_cap(n, lanes))
+    scratch = torch.empty(max(T * cap, 1), dtype=torch.int32, device=dev)
+    packed = torch.empty(max(T * cap, 1), dtype=torch.int32, device=dev)
+    meta = torch.zeros(2 * T + 2, dtype=torch.int32, device=dev)     # lane_words [T] | lane_offsets [T+1] | status
+    lane_words, lane_offsets, status = meta[:T], meta[T:2 * T + 1], meta[2 * T + 1:]
+    L.rans_encode(ptr(sym), ptr(idx), items, n, lanes, ptr(cdf), cdf.shape[0], cdf.shape[1], ptr(sizes), ptr(offs),
+                  ptr(scratch), cap, ptr(lane_words), ptr(lane_offsets), ptr(packed), T * cap, ptr(status), stream())
+    host = meta.cpu().numpy()
+    if host[-1] == 1:
+        raise ValueError("rans_encode: index outside the CDF tables (or an empty / over-long CDF row)")
+    if host[-1]:
+        raise RuntimeError(f"rans_encode: out of string space (status {host[-1]})")
+    off = host[T:2 * T + 1].astype(np.int64) & 0xFFFFFFFF
+    return packed[: int(off[-1])] if T else packed[:0], off
+
+
+def encode_batch(symbols, indexes, cdf, cdf_length, offset, precision: int = 16, lanes: int = 1) -> List[bytes]:
+    """One string per batch item (entropy_models.py:256-268)."""
+    if precision != 16:
+        raise ValueError("the range coder works at 16-bit precision (rans_interface.cpp:50)")
+    items = symbols.shape[0]
+    packed, off = encode_device(symbols, indexes, cdf, cdf_length, offset, lanes)
+    words = packed.cpu().numpy().view(np.uint32)
+    out = []
+    for i in range(items):
+        lo, hi = off[i * lanes], off[(i + 1) * lanes]
+        body = words[lo:hi].tobytes()
+        if lanes == 1:
+            out.append(body)
+        else:
+            counts = np.diff(off[i * lanes:(i + 1) * lanes + 1]).astype(np.uint32)
+            out.append(struct.pack("<2I", LANE_MAGIC, lanes) + counts.tobytes() + body)
+    return out
+
+
+def _split_item(s: bytes):
+    """-> (lanes, per-lane word counts, payload words)."""
+    w = np.frombuffer(s, dtype=np.uint32)
+    if len(s) % 4 or w.size < 2:
+        raise ValueError("Invalid strings or indexes parameters")
+    if w.size >= 3 and w[0] == LANE_MAGIC and 1 < int(w[1]) <= (w.size - 2) // 3 and \
+            int(w[2:2 + int(w[1])].astype(np.int64).sum()) == w.size - 2 - int(w[1]):
+        k = int(w[1])
+        return k, w[2:2 + k].astype(np.int64), w[2 + k:]
+    return 1, np.array([w.size], dtype=np.int64), w
+
+
+def decode_batch(strings, indexes, cdf, cdf_length, offset, precision: int = 16, lanes=None):
+    """strings: one per batch item -> int32 tensor shaped like `indexes` on its device (entropy_models.py:309-323).
+    lanes = 1 takes every string as a plain reference string; None reads the lane count from the container."""
+    if precision != 16:
+        raise ValueError("the range coder works at 16-bit precision (rans_interface.cpp:50)")
+    dev = cdf.device if indexes.device.type != "cuda" else indexes.device
+    if dev.type != "cuda":
+        raise RuntimeError("coder: CDF tables / indexes must live on a CUDA device (no CPU fallback)")
+    items = len(strings)
+    idx = indexes.reshape(items, -1).to(dev, torch.int32).contiguous()
+    n = idx.shape[1] if items else 0
+    if lanes == 1:
+        parts = [(1, np.array([len(s) // 4], dtype=np.int64), np.frombuffer(s, dtype=np.uint32)) for s in strings]
+        if any(len(s) % 4 or len(s) < 8 for s in strings):
+            raise ValueError("Invalid strings or indexes parameters")
+    else:
+        parts = [_split_item(s) for s in strings]
+    lanes = parts[0][0] if parts else 1
+    if any(p[0] != lanes for p in parts):
+        raise ValueError("decode_batch: items were coded with different lane counts")
+    counts = np.concatenate([p[1] for p in parts]) if parts else np.zeros(0, np.int64)
+    off = np.concatenate([[0], np.cumsum(counts)])
+    words = np.concatenate([p[2] for p in parts]) if parts else np.zeros(0, np.uint32)
+    out = torch.zeros(idx.shape, dtype=torch.int32, device=dev)
+    if items and n:
+        host = torch.from_numpy(np.concatenate([words.view(np.int32), off[:-1].astype(np.uint32).view(np.int32)]))
+        d = host.to(dev)
+        packed, lane_off = d[: words.size], d[words.size:]
+        cdf, sizes, offs = _tables(cdf, cdf_length, offset, dev)
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        L.rans_decode(ptr(packed), words.size, ptr(lane_off), ptr(idx), items, n, lanes, ptr(cdf), cdf.shape[0],
+                      cdf.shape[1], ptr(sizes), ptr(offs), ptr(out), ptr(status), stream())
+        _check_status(status, "rans_decode")
+    return out.reshape(indexes.shape)
+
+
+def gc_build_indexes(scales, scale_table, scale_bound: float):
+    """GaussianConditional.build_indexes (entropy_models.py:684-689) -> int32, same shape."""
+    if scales.device.type != "cuda":
+        raise RuntimeError("coder: scales must live on a CUDA device (no CPU fallback)")
+    s = scales.detach().float().contiguous()
+    table = scale_table.to(s.device, torch.float32).contiguous()
+    out = torch.empty(s.shape, dtype=torch.int32, device=s.device)
+    L.gc_build_indexes(ptr(s), s.numel(), ptr(table), table.numel(), float(scale_bound), ptr(out), stream())
+    return out

@@ -4,8 +4,8 @@ compressai/entropy_models/entropy_models.py:99-725) on fused sm_100a kernels.
 Constructor signatures, parameter / buffer names and shapes, `forward` return values, `update`,
 `loss`, error behaviour (ValueError cases) follow the reference; forward + backward run in
 lmsfc_eb_* / lmsfc_gc_* (quantise + likelihood + bound + sum-ln fused), the integer CDF tables in
-lmsfc_pmf_rows_to_cdf.  Entropy *coding* (compress/decompress, rANS) is the next scope row
- and lives in coder.py.
+lmsfc_pmf_rows_to_cdf.  Entropy *coding* (compress / decompress / build_indexes,
+SURVEY.md §8f-1) runs in csrc/rans.cu through coder.py: strings byte-identical to the reference's rANS.
 """
 import math
 from typing import Any, List, Optional, Tuple, Union
@@ -48,6 +48,7 @@ class EntropyModel(nn.Module):
         self.rng = None          # Fn.RNG, created lazily on the module's device (a model may share one)
         self.rng_offset = 0      # distinguishes the draws of different modules within one step
         self.rng_auto_advance = True   # False when the owning model advances a shared RNG once per step
+        self.coder_lanes = 1     # strings per item (coder.py): 1 = the reference's bytes, K > 1 = interleaved container
 
     @property
     def offset(self):
@@ -148,7 +149,7 @@ class EntropyModel(nn.Module):
         self._check_cdf_length()
         self._check_offsets_size()
         return coder.encode_batch(symbols, indexes, self._quantized_cdf, self._cdf_length, self._offset,
-                                  self.entropy_coder_precision)
+                                  self.entropy_coder_precision, lanes=int(self.coder_lanes))
 
     def decompress(self, strings, indexes, dtype: torch.dtype = torch.float, means=None):
         """:270-325."""
@@ -170,7 +171,7 @@ class EntropyModel(nn.Module):
                     if means.size(i) != 1:
                         raise ValueError("Invalid means parameters")
         outputs = coder.decode_batch(strings, indexes, self._quantized_cdf, self._cdf_length, self._offset,
-                                     self.entropy_coder_precision)
+                                     self.entropy_coder_precision, lanes=1 if int(self.coder_lanes) == 1 else None)
         return self.dequantize(outputs, means, dtype)
 
 
@@ -426,8 +427,5 @@ class GaussianConditional(EntropyModel):
 
     def build_indexes(self, scales):
         """:684-689."""
-        scales = torch.clamp(scales, min=self.scale_bound_value)
-        indexes = scales.new_full(scales.size(), len(self.scale_table) - 1).int()
-        for s in self.scale_table[:-1]:
-            indexes -= (scales <= s).int()
-        return indexes
+        from . import coder
+        return coder.gc_build_indexes(scales, self.scale_table, self.scale_bound_value)
