@@ -9,12 +9,11 @@ pipelines/base.py:219-245, split_inference/image_split_inference.py:100-175):
     decode(bitstream, codec_output_dir, file_prefix, org_img_size=None, img_input=False) -> {"data": {...}, ...}
     qp_value, eval_encode_type
 
-`encode` runs g_a / h_a and the quantiser on the B200 kernels and returns the integer symbols of (y, z) plus the
-side information needed to decode; `decode` runs h_s / g_s.  Entropy CODING (rANS, entropy_models.py:235-325) is the
-next scope row (§8f-1): until it lands the `.bin` written for decode-only runs carries the raw int16 symbols and
-`bytes` is the entropy-model estimate ceil(-sum log2 L / 8) per frame, which is what the rate term of training optimises.
+`encode` = ScaleHyperprior.compress (models/google.py:313-324) on the B200 kernels: g_a, h_a, the device range coder
+for z, h_s on the decoded z_hat, build_indexes, the range coder for y; `decode` = decompress (:326-333) + g_s.  The
+per-frame strings are the reference's rANS strings (coder.py; `coder_lanes` > 1 selects the interleaved container),
+`bytes` is their real length, and the `.bin` written for decode-only runs holds a small header and the strings.
 """
-import math
 import os
 import struct
 from typing import Dict
@@ -60,6 +59,10 @@ class LMSFCCodec(nn.Module):
         if ckpt:
             sd = torch.load(ckpt, map_location=self.device_name)
             self.model.load_state_dict(sd.get("state_dict", sd))
+        lanes = int(enc.get("coder_lanes", 1))
+        self.model.entropy_bottleneck.coder_lanes = lanes
+        self.model.gaussian_conditional.coder_lanes = lanes
+        self._tables_ready = False      # CDF tables are built on first use (after any checkpoint load)
         vm = kwargs.get("vision_model")
         self.layer_keys = list(getattr(vm, "split_layer_list", self.spec.levels))
 
@@ -72,6 +75,11 @@ class LMSFCCodec(nn.Module):
         return self.eval_encode
 
     # ------------------------------------------------------------------ encode
+    def _ensure_tables(self):
+        if not self._tables_ready:
+            self.model.update(force=True)          # CompressionModel.update (models/base.py:90-113)
+            self._tables_ready = True
+
     @torch.no_grad()
     def encode(self, input: Dict, codec_output_dir: str = "", bitstream_name: str = "", file_prefix: str = "",
                img_input=False) -> Dict:
@@ -81,20 +89,15 @@ class LMSFCCodec(nn.Module):
         keys = list(data.keys())
         if len(keys) != len(self.spec.levels):
             raise ValueError(f"expected {len(self.spec.levels)} pyramid levels, got {keys}")
+        self._ensure_tables()
         dev = self.device_name
-        ps = tuple(Fn.nhwc(data[k].to(dev, non_blocking=True).float(), Fn.BF16) for k in keys)   # video pipeline hands CPU tensors
-        m = self.model
-        y, z, mid_hw = m.analysis(ps)
-        z_hat, z_lik = m.entropy_bottleneck(z, training=False)
-        scales = m.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), mid_hw, y.shape[2:])
-        y_hat, y_lik = m.gaussian_conditional(y, scales, training=False)
-        med = m.entropy_bottleneck.quantiles[:, 0, 1].reshape(1, -1, 1, 1)
-        y_sym = torch.round(y_hat).to(torch.int16)
-        z_sym = torch.round(z_hat - med).to(torch.int16)
-        bits = -(torch.log2(y_lik).flatten(1).sum(1) + torch.log2(z_lik).flatten(1).sum(1))
-        nbytes = [int(math.ceil(float(b) / 8.0)) for b in bits.cpu()]
-        stream = {"y": y_sym, "z": z_sym, "keys": keys, "level_hw": [tuple(p.shape[2:]) for p in ps],
-                  "mid_hw": tuple(mid_hw), "input_size": input.get("input_size"), "org_input_size": input.get("org_input_size")}
+        feats = {lv: data[k].to(dev, non_blocking=True).float() for lv, k in zip(self.spec.levels, keys)}   # video pipeline hands CPU tensors
+        out = self.model.compress(feats)
+        y_strings, z_strings = out["strings"]
+        nbytes = [len(a) + len(b) for a, b in zip(y_strings, z_strings)]
+        stream = {"y_strings": y_strings, "z_strings": z_strings, "shape": out["shape"], "y_hw": out["y_hw"],
+                  "mid_hw": out["mid_hw"], "level_hw": out["level_hw"], "keys": keys,
+                  "input_size": input.get("input_size"), "org_input_size": input.get("org_input_size")}
         if codec_output_dir and bitstream_name:
             os.makedirs(codec_output_dir, exist_ok=True)
             path = os.path.join(codec_output_dir, f"{bitstream_name}-{file_prefix}.bin" if file_prefix else f"{bitstream_name}.bin")
@@ -109,50 +112,46 @@ class LMSFCCodec(nn.Module):
         if img_input:
             raise NotImplementedError("lmsfc codes feature pyramids (split inference), not images")
         stream = self._read_bin(bitstream) if isinstance(bitstream, (str, os.PathLike)) else bitstream
-        dev = self.device_name
-        m = self.model
-        med = m.entropy_bottleneck.quantiles[:, 0, 1].reshape(1, -1, 1, 1)
-        z_hat = stream["z"].to(dev).float() + med
-        y_hat = stream["y"].to(dev).float()
-        # h_s(z_hat) only conditions the entropy decoder of y (models/google.py:326-333); with the symbol container
-        # there is nothing to decode, so reconstruction needs y_hat alone.  z travels for format stability.
-        del z_hat
-        x_hat = m.synthesis(Fn.nhwc(y_hat, Fn.BF16), stream["level_hw"])
-        out = {"data": {k: t.float().contiguous() for k, t in zip(stream["keys"], x_hat)}}
+        self._ensure_tables()
+        rec = self.model.decompress([stream["y_strings"], stream["z_strings"]], stream["shape"], stream["y_hw"],
+                                    stream["mid_hw"], stream["level_hw"])
+        out = {"data": {k: rec["x_hat"][lv].float().contiguous() for k, lv in zip(stream["keys"], self.spec.levels)}}
         if stream.get("input_size") is not None:
             out["input_size"] = stream["input_size"]
         if org_img_size is not None or stream.get("org_input_size") is not None:
             out["org_input_size"] = org_img_size if org_img_size is not None else stream["org_input_size"]
         return out
 
-    # ------------------------------------------------------------------ container (raw symbols until rANS lands)
+    # ------------------------------------------------------------------ container: header + per-frame rANS strings
     @staticmethod
     def _write_bin(path, s):
         with open(path, "wb") as f:
-            y, z = s["y"].cpu().contiguous(), s["z"].cpu().contiguous()
-            f.write(MAGIC + struct.pack("<B", 1))
-            f.write(struct.pack("<4I", *y.shape) + struct.pack("<4I", *z.shape))
+            f.write(MAGIC + struct.pack("<B", 2))
+            f.write(struct.pack("<I", len(s["y_strings"])))
+            f.write(struct.pack("<6I", *s["shape"], *s["y_hw"], *s["mid_hw"]))
             f.write(struct.pack("<B", len(s["keys"])))
             for k, hw in zip(s["keys"], s["level_hw"]):
                 kb = str(k).encode()
                 f.write(struct.pack("<B", len(kb)) + kb + struct.pack("<2I", *hw))
-            f.write(struct.pack("<2I", *s["mid_hw"]))
-            f.write(y.numpy().tobytes() + z.numpy().tobytes())
+            for ys, zs in zip(s["y_strings"], s["z_strings"]):
+                f.write(struct.pack("<2I", len(ys), len(zs)) + ys + zs)
 
     @staticmethod
     def _read_bin(path):
-        import numpy as np
         with open(path, "rb") as f:
-            if f.read(4) != MAGIC or struct.unpack("<B", f.read(1))[0] != 1:
-                raise ValueError(f"{path}: not an lmsfc v1 bitstream")
-            ys, zs = struct.unpack("<4I", f.read(16)), struct.unpack("<4I", f.read(16))
+            if f.read(4) != MAGIC or struct.unpack("<B", f.read(1))[0] != 2:
+                raise ValueError(f"{path}: not an lmsfc v2 bitstream")
+            frames = struct.unpack("<I", f.read(4))[0]
+            dims = struct.unpack("<6I", f.read(24))
             keys, level_hw = [], []
             for _ in range(struct.unpack("<B", f.read(1))[0]):
                 n = struct.unpack("<B", f.read(1))[0]
                 keys.append(f.read(n).decode())
                 level_hw.append(struct.unpack("<2I", f.read(8)))
-            mid_hw = struct.unpack("<2I", f.read(8))
-            ny, nz = int(np.prod(ys)), int(np.prod(zs))
-            y = torch.from_numpy(np.frombuffer(f.read(2 * ny), dtype=np.int16).copy()).reshape(ys)
-            z = torch.from_numpy(np.frombuffer(f.read(2 * nz), dtype=np.int16).copy()).reshape(zs)
-        return {"y": y, "z": z, "keys": keys, "level_hw": level_hw, "mid_hw": mid_hw}
+            ys, zs = [], []
+            for _ in range(frames):
+                ly, lz = struct.unpack("<2I", f.read(8))
+                ys.append(f.read(ly))
+                zs.append(f.read(lz))
+        return {"y_strings": ys, "z_strings": zs, "shape": dims[0:2], "y_hw": dims[2:4], "mid_hw": dims[4:6],
+                "keys": keys, "level_hw": level_hw}

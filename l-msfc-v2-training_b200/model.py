@@ -179,6 +179,38 @@ class LMSFC(nn.Module):
             main.wait_stream(hs)
         return p2h, p3h, p4h, p5h
 
+    # ------------------------------------------------------------------ entropy-coded path (models/google.py:313-333)
+    @torch.no_grad()
+    def compress(self, feats):
+        """ScaleHyperprior.compress: -> {"strings": [y_strings, z_strings], "shape": z H x W, plus the sizes the
+        ragged pyramid needs to be rebuilt ("y_hw", "mid_hw", "level_hw")}.  The scales that index y's CDFs are
+        computed from the DECODED z_hat, by the same kernels the decoder runs, so both sides see identical bits."""
+        if self.entropy_bottleneck._offset.numel() == 0 or self.gaussian_conditional._offset.numel() == 0:
+            raise ValueError("Uninitialized CDFs. Run update() first")
+        lv = self.spec.levels
+        ps = tuple(Fn.nhwc(feats[k], Fn.BF16) for k in lv)
+        y, z, mid_hw = self.analysis(ps)
+        eb, gc = self.entropy_bottleneck, self.gaussian_conditional
+        z_strings = eb.compress(z)
+        z_hat = eb.decompress(z_strings, z.shape[-2:])
+        scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), mid_hw, y.shape[2:])
+        indexes = gc.build_indexes(scales)
+        y_strings = gc.compress(y, indexes)
+        return {"strings": [y_strings, z_strings], "shape": tuple(z.shape[-2:]), "y_hw": tuple(y.shape[2:]),
+                "mid_hw": tuple(mid_hw), "level_hw": [tuple(p.shape[2:]) for p in ps]}
+
+    @torch.no_grad()
+    def decompress(self, strings, shape, y_hw, mid_hw, level_hw):
+        """ScaleHyperprior.decompress: -> {"x_hat": {level: tensor}}."""
+        assert isinstance(strings, list) and len(strings) == 2
+        eb, gc = self.entropy_bottleneck, self.gaussian_conditional
+        z_hat = eb.decompress(strings[1], shape)
+        scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), tuple(mid_hw), tuple(y_hw))
+        indexes = gc.build_indexes(scales)
+        y_hat = gc.decompress(strings[0], indexes, z_hat.dtype)
+        x_hat = self.synthesis(Fn.nhwc(y_hat.contiguous(), Fn.BF16), [tuple(h) for h in level_hw])
+        return {"x_hat": dict(zip(self.spec.levels, x_hat))}
+
     # ------------------------------------------------------------------ CompressionModel contract
     def aux_loss(self):
         """models/base.py:115-144: sum of the EntropyBottleneck aux losses."""

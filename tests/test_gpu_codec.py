@@ -44,8 +44,26 @@ def test_encode_decode_round_trip(tmp_path, B, H2, W2, where):
     for k in vm.split_layer_list:
         assert dec["data"][k].shape == feats[k].shape
         assert torch.equal(dec["data"][k], out["x_hat"][k].float()), k
-    bits = -(torch.log2(out["likelihoods"]["y"]).flatten(1).sum(1) + torch.log2(out["likelihoods"]["z"]).flatten(1).sum(1))
-    assert [int(torch.ceil(b / 8)) for b in bits.cpu()] == res["bytes"]
+    # `bytes` are real string lengths; the strings decode, with the ORACLE's coder, to the symbols of the eval forward
+    import numpy as np
+    from oracle import rans as OR
+    m = codec.model
+    st = res["bitstream"]
+    assert res["bytes"] == [len(a) + len(b) for a, b in zip(st["y_strings"], st["z_strings"])]
+    eb, gc = m.entropy_bottleneck, m.gaussian_conditional
+    med = eb._get_medians().detach().reshape(1, -1, 1, 1)
+    z_sym = torch.round(out["latents"]["z_hat"] - med).int().cpu().numpy()
+    z_idx = np.broadcast_to(np.arange(z_sym.shape[1], dtype=np.int32).reshape(1, -1, 1, 1), z_sym.shape)
+    tabs = [t.cpu().numpy() for t in (eb._quantized_cdf, eb._cdf_length, eb._offset)]
+    assert np.array_equal(OR.decompress(st["z_strings"], z_idx, *tabs), z_sym)
+    y_sym = torch.round(out["latents"]["y_hat"]).int().cpu().numpy()
+    sc = torch.clamp(out["latents"]["scales"].float().cpu(), min=0.11)
+    y_idx = torch.full(sc.shape, len(gc.scale_table) - 1).int()
+    for t in gc.scale_table.cpu()[:-1]:
+        y_idx -= (sc <= t).int()
+    tabs = [t.cpu().numpy() for t in (gc._quantized_cdf, gc._cdf_length, gc._offset)]
+    assert st["y_strings"] == OR.compress(y_sym, y_idx.numpy(), *tabs)
+    assert np.array_equal(OR.decompress(st["y_strings"], y_idx.numpy(), *tabs), y_sym)
     # through the .bin a decode-only run would pick up ("{bitstream_name}-{file_prefix}*.bin")
     res2 = codec.encode(inp, str(tmp_path), "feat", "img0")
     assert os.path.basename(res2["bitstream"]) == "feat-img0.bin" and os.path.getsize(res2["bitstream"]) > 0
@@ -53,6 +71,22 @@ def test_encode_decode_round_trip(tmp_path, B, H2, W2, where):
     assert dec2["org_input_size"] == {"height": 1, "width": 2}
     for k in vm.split_layer_list:
         assert torch.equal(dec2["data"][k], dec["data"][k])
+
+
+def test_interleaved_lanes_round_trip(tmp_path):
+    codec_m = importlib.import_module(PKG + ".codec")
+    torch.manual_seed(0)
+    vm = _FakeVisionModel()
+    codec = codec_m.LMSFCCodec(eval_encode="bitrate", encoder_config={"qp": 1, "coder_lanes": 16}, device="cuda",
+                               vision_model=vm, dataset=None)
+    feats = _features(2, 20, 28, "cuda")
+    inp = {"data": dict(feats), "input_size": [(80, 112)], "org_input_size": {"height": 80, "width": 112}}
+    res = codec.encode(inp, str(tmp_path), "feat", "v")
+    dec = codec.decode(res["bitstream"], str(tmp_path), "v")
+    with torch.no_grad():
+        out = codec.model(feats)
+    for k in vm.split_layer_list:
+        assert torch.equal(dec["data"][k], out["x_hat"][k].float()), k
 
 
 def test_codec_refuses_cpu_device():
