@@ -4,13 +4,15 @@
 //   compressai/entropy_models/entropy_models.py:235-325,684-689 (compress / decompress / build_indexes)
 //
 // A string is inherently serial (every record depends on the coder state), so parallelism comes from strings:
-// one THREAD codes one lane, lane k of K of an item = symbols[k::K] of that item coded exactly like the reference
-// codes a whole item.  K = 1 reproduces the reference's bytes; K > 1 is this library's interleaved container
-// (K strings + a length table per item, see coder.py).  Consecutive lanes sit in consecutive threads, so the
-// strided symbol / index reads of a warp coalesce.  Per record the state-dependent chain is one 64-bit division
-// (encode) or one table search (decode); symbol, index and CDF loads do not depend on the state and are issued a
-// chunk ahead.  The division is done exactly with an fp64 reciprocal estimate and an integer fix-up
-// (the quotient is < 2^47, so the estimate is off by at most one).
+// lane k of K of an item = symbols[k::K] of that item, coded exactly like the reference codes a whole item.
+// K = 1 reproduces the reference's bytes; K > 1 is this library's interleaved container (K strings + a length
+// table per item, see coder.py).  One WARP owns one string: the state is replicated in its 32 threads and the
+// serial chain runs warp-uniform, while everything that does not depend on the state is done 32 symbols at a
+// time by the 32 threads -- symbol / index / CDF fetches (one memory round trip per 32 symbols, the next chunk in
+// flight while this one is coded), the reciprocal of each frequency, and, in the decoder, the table search itself
+// (32 probes per round trip, ballot).  Per record the state-dependent chain is one exact 64-bit division (encode:
+// fp64 reciprocal estimate + integer fix-up; the quotient is < 2^47, so the estimate is off by at most one) or one
+// warp-wide probe of the CDF row (decode).
 #include "../../include/b200lmsfc.h"
 #include "kernels.cuh"
 
@@ -18,7 +20,6 @@ namespace lmsfc {
 
 static constexpr uint32_t kPrecision = 16, kBypassBits = 4, kBypassMax = 15;
 static constexpr uint64_t kRansLow = 1ull << 31;
-static constexpr int kChunk = 4;
 
 struct RansTables {
   const int32_t* cdfs;     // [rows][cdf_stride]
@@ -27,91 +28,132 @@ struct RansTables {
   int rows, cdf_stride;
 };
 
-// x / freq for x < 2^47 * freq, freq < 2^17 (rans64.h:89), exact
-__device__ __forceinline__ void divmod(uint64_t x, uint32_t freq, double rcp, uint64_t& q, uint32_t& r) {
-  uint64_t qe = (uint64_t)__double2ull_rz(__ull2double_rz(x) * rcp);
-  int64_t rem = (int64_t)(x - qe * freq);
-  while (rem < 0) { --qe; rem += freq; }
-  while (rem >= (int64_t)freq) { ++qe; rem -= freq; }
-  q = qe;
-  r = (uint32_t)rem;
+// Division by an invariant integer (Alverson / Granlund-Montgomery): with sh = ceil(log2 freq) and
+// m = ceil(2^(63+sh) / freq), floor(x / freq) = mulhi64(x, m) >> (sh - 1) for every x < 2^63 -- the error term
+// x * (m * freq - 2^(63+sh)) / (freq * 2^(63+sh)) stays below 1 / freq because 2^sh >= freq.  The coder's state is
+// < 2^47 * freq <= 2^63 when the division happens (rans64.h:80-89), so the quotient is exact.  m needs 2^(63+sh)
+// / freq, an 80-bit dividend: two rounds of schoolbook division in 64 bits.  freq = 1: m = 2^64 - 1, sh = 0 gives
+// mulhi = x - 1, which the caller compensates in the additive term.
+__device__ __forceinline__ uint64_t magic_reciprocal(uint32_t freq, uint32_t& sh) {
+  if (freq < 2) { sh = 0; return ~0ull; }
+  uint32_t lg = 32 - __clz(freq - 1);                  // ceil(log2 freq), 1..16
+  const uint64_t top = 1ull << (lg + 31);              // 2^(63+lg) = top * 2^32
+  const uint64_t q1 = top / freq, r1 = top - q1 * freq;
+  const uint64_t q0 = ((r1 << 32) + (freq - 1)) / freq;   // ceil of the low round
+  sh = lg - 1;
+  return (q1 << 32) + q0;
 }
 
+// The coder state lives, replicated, in every thread of the warp that owns the string: the serial chain runs
+// warp-uniform, operands arrive by shuffle from the thread that fetched them, thread 0 does the stores.
 struct Enc {
   uint64_t x;
   uint32_t* p;
-  __device__ __forceinline__ void put(uint32_t start, uint32_t freq, double rcp) {      // rans64.h:75-90
-    const uint64_t lim = ((kRansLow >> kPrecision) << 32) * freq;
-    if (x >= lim) { *--p = (uint32_t)x; x >>= 32; }
-    uint64_t q; uint32_t r;
-    divmod(x, freq, rcp, q, r);
-    x = (q << kPrecision) + r + start;
+  bool writer;
+  __device__ __forceinline__ void emit() {
+    --p;
+    if (writer) *p = (uint32_t)x;
+    x >>= 32;
+  }
+  // rans64.h:75-90: x' = ((x / f) << 16) + x % f + start = x + start + (x / f) * (2^16 - f)
+  __device__ __forceinline__ void put(uint64_t magic, uint32_t sh, uint32_t add, uint32_t cmpl) {
+    const uint64_t lim = (uint64_t)(65536u - cmpl) << 47;
+    if (x >= lim) emit();
+    const uint64_t q = __umul64hi(x, magic) >> sh;
+    x = x + add + q * cmpl;
   }
   __device__ __forceinline__ void put_bits(uint32_t val) {                              // rans_interface.cpp:68-86
-    if (x >= (1ull << 59)) { *--p = (uint32_t)x; x >>= 32; }
+    if (x >= (1ull << 59)) emit();
     x = (x << kBypassBits) | val;
   }
 };
 
+// what one symbol contributes, fetched and prepared by one thread: the reciprocal of its frequency (0 marks a
+// record that must be skipped: bad index / row), additive term, 2^16 - freq and shift, escape payload (raw + 1)
+struct Rec { uint64_t magic; uint32_t add, cmpl_sh, esc; };
+
+__device__ __forceinline__ Rec fetch_record(const int32_t* __restrict__ sym, const int32_t* __restrict__ idx, int64_t i,
+                                            const RansTables& tb, int& bad) {
+  Rec r{0ull, 0u, 0u, 0u};
+  const int32_t row = __ldg(idx + i);
+  if (row < 0 || row >= tb.rows) { bad = 1; return r; }
+  const int32_t max_value = __ldg(tb.sizes + row) - 2;
+  int32_t v = __ldg(sym + i) - __ldg(tb.offsets + row);
+  if (max_value < 0 || max_value + 1 >= tb.cdf_stride) { bad = 1; return r; }
+  uint32_t raw = 0;
+  if (v < 0) { raw = (uint32_t)(-2 * v - 1); v = max_value; }                           // :136-142
+  else if (v >= max_value) { raw = (uint32_t)(2 * (v - max_value)); v = max_value; }
+  const int32_t* c = tb.cdfs + (int64_t)row * tb.cdf_stride + v;
+  const uint32_t c0 = (uint32_t)__ldg(c), freq = (uint32_t)__ldg(c + 1) - c0;
+  if (freq == 0 || freq > 65536u || c0 > 65535u) { bad = 1; return r; }
+  uint32_t sh;
+  r.magic = magic_reciprocal(freq, sh);
+  r.add = freq < 2 ? c0 + 65535u : c0;                 // mulhi(x, 2^64 - 1) = x - 1: (x - 1) * 65535 + x + 65535 + c0 = (x << 16) + c0
+  r.cmpl_sh = (65536u - freq) | (sh << 24);
+  r.esc = (v == max_value) ? raw + 1 : 0u;
+  return r;
+}
+
+// One WARP per string.  Chunks of 128 symbols: every thread fetches and prepares four records (four independent
+// load chains in flight) into the warp's slice of shared memory, then thread 0 codes the 128 records in order, last
+// symbol first (flush, :189-199) -- a loop without collectives or loads from global memory.
 // status: 0 ok, 1 index outside the table, 2 scratch exhausted
+static constexpr int kEncChunk = 128;
 __global__ void __launch_bounds__(128) rans_encode_kernel(const int32_t* __restrict__ symbols,
                                                           const int32_t* __restrict__ indexes, int64_t n, int items,
                                                           int lanes, RansTables tb, uint32_t* scratch, int64_t lane_cap,
                                                           uint32_t* lane_words, int* status) {
   pdl_sync();
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ Rec recs[4][kEncChunk];
+  const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int j = threadIdx.x & 31;
   if (t >= (int64_t)items * lanes) return;
+  Rec* const mine = recs[threadIdx.x >> 5];
   const int item = (int)(t / lanes), lane = (int)(t % lanes);
   const int64_t count = lane < n ? (n - lane + lanes - 1) / lanes : 0;
   const int32_t* sym = symbols + (int64_t)item * n;
   const int32_t* idx = indexes + (int64_t)item * n;
   uint32_t* const base = scratch + t * lane_cap;
-  Enc e{kRansLow, base + lane_cap};
+  Enc e{kRansLow, base + lane_cap, true};
   int bad = 0;
-  for (int64_t hi = count; hi > 0; hi -= kChunk) {        // records are coded last-to-first (flush, :189-199)
-    uint32_t start[kChunk], freq[kChunk], raw[kChunk];
-    double rcp[kChunk];
-    bool esc[kChunk];
+  for (int64_t hi = count; hi > 0; hi -= kEncChunk) {
+    const int m = hi < kEncChunk ? (int)hi : kEncChunk;
+    Rec r[kEncChunk / 32];
 #pragma unroll
-    for (int u = 0; u < kChunk; ++u) {                    // state-independent part, loads in flight together
-      const int64_t tt = hi - 1 - u;
-      start[u] = 0; freq[u] = 0; raw[u] = 0; esc[u] = false; rcp[u] = 0.0;
-      if (tt < 0) continue;
-      const int64_t i = lane + tt * lanes;
-      const int32_t row = __ldg(idx + i);
-      if (row < 0 || row >= tb.rows) { bad = 1; continue; }
-      const int32_t max_value = __ldg(tb.sizes + row) - 2;
-      int32_t v = __ldg(sym + i) - __ldg(tb.offsets + row);
-      if (max_value < 0 || max_value + 1 >= tb.cdf_stride) { bad = 1; continue; }
-      if (v < 0) { raw[u] = (uint32_t)(-2 * v - 1); v = max_value; }                    // :136-142
-      else if (v >= max_value) { raw[u] = (uint32_t)(2 * (v - max_value)); v = max_value; }
-      esc[u] = (v == max_value);
-      const int32_t* c = tb.cdfs + (int64_t)row * tb.cdf_stride + v;
-      const int32_t c0 = __ldg(c), c1 = __ldg(c + 1);
-      start[u] = (uint32_t)c0;
-      freq[u] = (uint32_t)(c1 - c0);
-      if (freq[u] == 0 || freq[u] > 65536u) { bad = 1; freq[u] = 0; continue; }
-      rcp[u] = 1.0 / (double)freq[u];
+    for (int k = 0; k < kEncChunk / 32; ++k) {            // slot u of the chunk = symbol hi-1-u
+      const int u = j + 32 * k;
+      r[k] = u < m ? fetch_record(sym, idx, lane + (hi - 1 - u) * lanes, tb, bad) : Rec{0ull, 0u, 0u, 0u};
     }
-    if (e.p - base < 3 * kChunk + 2) { bad = 2; break; }
+    __syncwarp();                                         // thread 0 is done with the previous chunk
 #pragma unroll
-    for (int u = 0; u < kChunk; ++u) {
-      if (freq[u] == 0) continue;
-      if (esc[u]) {                                       // bypass digits, :147-175 reversed
-        int nb = 0;
-        while (((uint64_t)raw[u] >> (nb * kBypassBits)) != 0) ++nb;
-        for (int j = nb - 1; j >= 0; --j) e.put_bits((raw[u] >> (j * kBypassBits)) & kBypassMax);
-        e.put_bits((uint32_t)nb % kBypassMax);
-        for (int q = nb / (int)kBypassMax; q > 0; --q) e.put_bits(kBypassMax);
+    for (int k = 0; k < kEncChunk / 32; ++k) mine[j + 32 * k] = r[k];
+    __syncwarp();
+    if (j == 0 && e.p - base < 2 * m + 2) bad = 2;         // cannot happen with lane_cap >= lmsfc_rans_lane_cap()
+    if (j == 0 && bad != 2) {
+      for (int u = 0; u < m; ++u) {
+        const Rec c = mine[u];
+        if (c.magic == 0) continue;
+        if (c.esc) {                                      // bypass digits, :147-175 reversed
+          const uint32_t raw = c.esc - 1u;
+          int nb = 0;
+          while (((uint64_t)raw >> (nb * kBypassBits)) != 0) ++nb;
+          for (int d = nb - 1; d >= 0; --d) e.put_bits((raw >> (d * kBypassBits)) & kBypassMax);
+          e.put_bits((uint32_t)nb % kBypassMax);
+          for (int q = nb / (int)kBypassMax; q > 0; --q) e.put_bits(kBypassMax);
+        }
+        e.put(c.magic, c.cmpl_sh >> 24, c.add, c.cmpl_sh & 0x1FFFFu);
       }
-      e.put(start[u], freq[u], rcp[u]);
     }
   }
-  e.p -= 2;                                               // rans64.h:93-100
-  e.p[0] = (uint32_t)e.x;
-  e.p[1] = (uint32_t)(e.x >> 32);
-  lane_words[t] = (uint32_t)(base + lane_cap - e.p);
-  if (bad) atomicMax(status, bad);
+  if (j == 0) {
+    e.p -= 2;                                             // rans64.h:93-100
+    e.p[0] = (uint32_t)e.x;
+    e.p[1] = (uint32_t)(e.x >> 32);
+    lane_words[t] = (uint32_t)(base + lane_cap - e.p);
+  }
+  __syncwarp();
+  bad = __reduce_max_sync(0xffffffffu, bad);
+  if (bad && j == 0) atomicMax(status, bad);
 }
 
 // One warp per lane: exclusive offset = sum of the lane lengths in front of it, then the lane's words move from
@@ -137,12 +179,18 @@ __global__ void __launch_bounds__(256) rans_pack_kernel(const uint32_t* __restri
   for (uint32_t j = l; j < w; j += 32) packed[acc + j] = src[j];
 }
 
+// Decoder state, replicated in the warp like the encoder's.  The next stream word is kept loaded one refill ahead.
 struct Dec {
   uint64_t x;
   const uint32_t* p;
   const uint32_t* end;
+  uint32_t ahead;                          // *p
   __device__ __forceinline__ void refill() {
-    if (x < kRansLow) { x = (x << 32) | (p < end ? __ldg(p) : 0u); ++p; }
+    if (x < kRansLow) {
+      x = (x << 32) | ahead;
+      ++p;
+      ahead = p < end ? __ldg(p) : 0u;
+    }
   }
   __device__ __forceinline__ uint32_t get_bits() {                                      // rans_interface.cpp:88-104
     const uint32_t v = (uint32_t)(x & kBypassMax);
@@ -152,31 +200,55 @@ struct Dec {
   }
 };
 
-// largest s in [0, size-2] with cdf[s] <= cf (std::find_if of :244-248).  Two probes around the centre of the
-// row (where a trained latent's mass sits) settle most symbols in one memory round trip; the rest bisect.
-__device__ __forceinline__ int cdf_search(const int32_t* __restrict__ cdf, int size, uint32_t cf) {
-  int lo = 0, hi = size - 1;                 // invariant: cdf[lo] <= cf < cdf[hi]  (cdf[size-1] = 2^16)
-  const int m = (size - 2) >> 1;
-  if (m > 0 && m + 1 < hi) {
-    const uint32_t a = (uint32_t)__ldg(cdf + m), b = (uint32_t)__ldg(cdf + m + 1);
-    if (b <= cf) lo = m + 1;
-    else if (a <= cf) { lo = m; hi = m + 1; }
-    else hi = m;
+// Largest s in [0, size-2] with cdf[s] <= cf (std::find_if of :244-248), found by the whole warp: thread j probes
+// one entry, a ballot counts the entries <= cf.  The first probe set is the 32 entries around the centre of the row,
+// where a latent's mass sits (rows of <= 32 entries are covered entirely): most symbols cost ONE memory round trip,
+// and start / next come out of the probed registers.  Otherwise 32-ary steps over what is left.
+// The first probe set does not depend on the coder state: the caller loads it one symbol ahead (probe_window).
+static constexpr uint32_t kAbove = 0x7fffffffu;
+__device__ __forceinline__ int window_base(int size) { return size > 32 ? ((size - 2) >> 1) - 15 : 0; }
+__device__ __forceinline__ uint32_t probe_window(const int32_t* __restrict__ cdf, int size, int j) {
+  const int w0 = window_base(size);
+  return (w0 + j < size) ? (uint32_t)__ldg(cdf + w0 + j) : kAbove;
+}
+__device__ __forceinline__ int cdf_search_warp(const int32_t* __restrict__ cdf, int size, uint32_t cf, int j,
+                                               uint32_t val, uint32_t& start, uint32_t& freq) {
+  const int w0 = window_base(size);
+  int cnt = __popc(__ballot_sync(0xffffffffu, val <= cf));
+  int lo, hi;
+  if (cnt > 0 && cnt < 32) {
+    start = __shfl_sync(0xffffffffu, val, cnt - 1);
+    freq = __shfl_sync(0xffffffffu, val, cnt) - start;
+    return w0 + cnt - 1;
   }
-  while (hi - lo > 1) {
-    const int mid = (lo + hi) >> 1;
-    if ((uint32_t)__ldg(cdf + mid) <= cf) lo = mid; else hi = mid;
+  if (cnt == 0) { lo = 0; hi = w0; } else { lo = w0 + 31; hi = size - 1; }
+  while (hi - lo > 1) {                    // invariant cdf[lo] <= cf < cdf[hi]
+    const int step = (hi - lo + 31) >> 5;
+    const int pidx = lo + (j + 1) * step;
+    val = pidx < hi ? (uint32_t)__ldg(cdf + pidx) : kAbove;
+    cnt = __popc(__ballot_sync(0xffffffffu, val <= cf));
+    lo += cnt * step;
+    hi = min(hi, lo + step);
   }
+  start = (uint32_t)__ldg(cdf + lo);
+  freq = (uint32_t)__ldg(cdf + lo + 1) - start;
   return lo;
 }
 
+// One WARP per string.  Chunks of 128 symbols: the threads fetch (row, size, offset) of four symbols each into the
+// warp's slice of shared memory, the warp decodes them in order (state replicated, search by ballot), and the
+// threads store four decoded values each.
+static constexpr int kDecChunk = 128;
 __global__ void __launch_bounds__(128) rans_decode_kernel(const uint32_t* __restrict__ packed, int64_t packed_words,
                                                           const uint32_t* __restrict__ lane_offsets,
                                                           const int32_t* __restrict__ indexes, int64_t n, int items,
                                                           int lanes, RansTables tb, int32_t* out, int* status) {
   pdl_sync();
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ int4 slots[4][kDecChunk];                    // row, size, offset, decoded value
+  const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int j = threadIdx.x & 31;
   if (t >= (int64_t)items * lanes) return;
+  int4* const mine = slots[threadIdx.x >> 5];
   const int item = (int)(t / lanes), lane = (int)(t % lanes);
   const int64_t count = lane < n ? (n - lane + lanes - 1) / lanes : 0;
   const int32_t* idx = indexes + (int64_t)item * n;
@@ -184,54 +256,71 @@ __global__ void __launch_bounds__(128) rans_decode_kernel(const uint32_t* __rest
   const uint32_t* w = packed + lane_offsets[t];
   Dec d;
   d.end = packed + packed_words;
-  if (w + 2 > d.end) { atomicMax(status, 2); return; }
+  if (w + 2 > d.end) { if (j == 0) atomicMax(status, 2); return; }
   d.x = (uint64_t)__ldg(w) | ((uint64_t)__ldg(w + 1) << 32);                            // rans64.h:104-112
   d.p = w + 2;
+  d.ahead = d.p < d.end ? __ldg(d.p) : 0u;
   int bad = 0;
-  for (int64_t lo = 0; lo < count; lo += kChunk) {
-    int32_t row[kChunk], size[kChunk], off[kChunk];
+  for (int64_t lo = 0; lo < count; lo += kDecChunk) {
+    const int m = count - lo < kDecChunk ? (int)(count - lo) : kDecChunk;
 #pragma unroll
-    for (int u = 0; u < kChunk; ++u) {
-      row[u] = -1; size[u] = 0; off[u] = 0;
-      if (lo + u >= count) continue;
-      const int32_t r = __ldg(idx + lane + (lo + u) * lanes);
-      if (r < 0 || r >= tb.rows) { bad = 1; continue; }
-      row[u] = r;
-      size[u] = __ldg(tb.sizes + r);
-      off[u] = __ldg(tb.offsets + r);
-      if (size[u] < 2 || size[u] > tb.cdf_stride) { bad = 1; row[u] = -1; }
-    }
-#pragma unroll
-    for (int u = 0; u < kChunk; ++u) {
-      if (lo + u >= count) break;
-      int32_t value = 0;
-      if (row[u] >= 0) {
-        const int32_t* cdf = tb.cdfs + (int64_t)row[u] * tb.cdf_stride;
-        const int32_t max_value = size[u] - 2;
-        const uint32_t cf = (uint32_t)(d.x & 0xFFFFu);
-        const int s = cdf_search(cdf, size[u], cf);
-        const uint32_t start = (uint32_t)__ldg(cdf + s), freq = (uint32_t)__ldg(cdf + s + 1) - start;
-        d.x = (uint64_t)freq * (d.x >> kPrecision) + cf - start;                        // rans64.h:120-137
-        d.refill();
-        value = s;
-        if (s == max_value) {                                                           // :254-275
-          uint32_t v = d.get_bits();
-          int nb = (int)v;
-          while (v == kBypassMax && nb < 64) { v = d.get_bits(); nb += (int)v; }
-          uint32_t raw = 0;
-          for (int j = 0; j < nb; ++j) {
-            const uint32_t dg = d.get_bits();
-            if (j < 8) raw |= dg << (j * kBypassBits);
-          }
-          value = (int32_t)(raw >> 1);
-          value = (raw & 1u) ? -value - 1 : value + max_value;
+    for (int k = 0; k < kDecChunk / 32; ++k) {
+      const int u = j + 32 * k;
+      int4 sl = make_int4(-1, 0, 0, 0);
+      if (u < m) {
+        const int32_t r = __ldg(idx + lane + (lo + u) * lanes);
+        if (r < 0 || r >= tb.rows) bad = 1;
+        else {
+          sl.y = __ldg(tb.sizes + r);
+          sl.z = __ldg(tb.offsets + r);
+          if (sl.y < 2 || sl.y > tb.cdf_stride) bad = 1; else sl.x = r;
         }
-        value += off[u];
       }
-      dst[lane + (lo + u) * lanes] = value;
+      mine[u] = sl;
     }
+    __syncwarp();
+    int4 nx = mine[0];
+    uint32_t win_n = nx.x >= 0 ? probe_window(tb.cdfs + (int64_t)nx.x * tb.cdf_stride, nx.y, j) : 0u;
+    for (int u = 0; u < m; ++u) {
+      const int4 sl = nx;
+      const uint32_t win = win_n;
+      if (u + 1 < m) {                                    // the next symbol's first probe set, off the serial chain
+        nx = mine[u + 1];
+        win_n = nx.x >= 0 ? probe_window(tb.cdfs + (int64_t)nx.x * tb.cdf_stride, nx.y, j) : 0u;
+      }
+      if (sl.x < 0) continue;
+      const int32_t* cdf = tb.cdfs + (int64_t)sl.x * tb.cdf_stride;
+      const int32_t max_value = sl.y - 2;
+      const uint32_t cf = (uint32_t)(d.x & 0xFFFFu);
+      uint32_t start, freq;
+      const int s = cdf_search_warp(cdf, sl.y, cf, j, win, start, freq);
+      d.x = (uint64_t)freq * (d.x >> kPrecision) + cf - start;                          // rans64.h:120-137
+      d.refill();
+      int32_t value = s;
+      if (s == max_value) {                                                             // :254-275
+        uint32_t v = d.get_bits();
+        int nb = (int)v;
+        while (v == kBypassMax && nb < 64) { v = d.get_bits(); nb += (int)v; }
+        uint32_t raw = 0;
+        for (int g = 0; g < nb; ++g) {
+          const uint32_t dg = d.get_bits();
+          if (g < 8) raw |= dg << (g * kBypassBits);
+        }
+        value = (int32_t)(raw >> 1);
+        value = (raw & 1u) ? -value - 1 : value + max_value;
+      }
+      if (j == 0) mine[u].w = value + sl.z;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < kDecChunk / 32; ++k) {
+      const int u = j + 32 * k;
+      if (u < m) dst[lane + (lo + u) * lanes] = mine[u].w;
+    }
+    __syncwarp();
   }
-  if (bad) atomicMax(status, bad);
+  bad = __reduce_max_sync(0xffffffffu, bad);
+  if (bad && j == 0) atomicMax(status, bad);
 }
 
 // GaussianConditional.build_indexes (entropy_models.py:684-689): T-1 minus the number of table entries (all
@@ -279,7 +368,7 @@ extern "C" int lmsfc_rans_encode(const int32_t* symbols, const int32_t* indexes,
   const int64_t T = (int64_t)items * lanes;
   LMSFC_CHECK_ARG(T * lane_cap < (1ll << 32), "rans_encode: more than 2^32 words");
   if (T == 0) return LMSFC_OK;
-  LMSFC_LAUNCH(rans_encode_kernel, dim3(ceil_div(T, 128)), dim3(128), 0, ST(stream), symbols, indexes, n, items, lanes,
+  LMSFC_LAUNCH(rans_encode_kernel, dim3(ceil_div(T * 32, 128)), dim3(128), 0, ST(stream), symbols, indexes, n, items, lanes,
                tb, scratch, lane_cap, lane_words, status);
   LMSFC_LAUNCH(rans_pack_kernel, dim3(ceil_div(T * 32, 256)), dim3(256), 0, ST(stream), (const uint32_t*)scratch,
                lane_cap, (const uint32_t*)lane_words, T, packed, packed_cap, lane_offsets, status);
@@ -297,7 +386,7 @@ extern "C" int lmsfc_rans_decode(const uint32_t* packed, int64_t packed_words, c
   if (T == 0) return LMSFC_OK;
   LMSFC_CHECK_ARG(packed && lane_offsets && status && packed_words >= 2 * T, "rans_decode: string shorter than its flush words");
   LMSFC_CHECK_ARG(n == 0 || (indexes && symbols_out), "rans_decode: null indexes / output");
-  LMSFC_LAUNCH(rans_decode_kernel, dim3(ceil_div(T, 128)), dim3(128), 0, ST(stream), packed, packed_words, lane_offsets,
+  LMSFC_LAUNCH(rans_decode_kernel, dim3(ceil_div(T * 32, 128)), dim3(128), 0, ST(stream), packed, packed_words, lane_offsets,
                indexes, n, items, lanes, tb, symbols_out, status);
   return LMSFC_OK;
 }

@@ -116,6 +116,26 @@ def main():
             rows.append({"case": name, "impl": "reference (oracle/_ref/ans, 1 host thread, incl. .tolist())",
                          "symbols": items * n, "encode_e2e_us": round(enc_ref, 1), "decode_e2e_us": round(dec_ref, 1)})
             print(rows[-1], flush=True)
+    # whole codec (SURVEY.md section 8 cfg 4: one OpenImages-seg frame, P2 = 200 x 304): encode = g_a, h_a, z coder, h_s,
+    # build_indexes, y coder; decode = z coder, h_s, build_indexes, y coder, g_s.  Random-init weights, CDFs from update().
+    codec_m = importlib.import_module(PKG + ".codec")
+    spec = importlib.import_module(PKG + ".spec").DEFAULT_SPEC
+    from oracle import lmsfc as OL
+    torch.manual_seed(0)
+    for frames, H2, W2 in ((1, 200, 304), (8, 200, 304)):
+        feats = {k: v.to(torch.bfloat16).float() for k, v in OL.synth_features(spec, frames, H2, W2, device=dev).items()}
+        inp = {"data": feats, "input_size": [(4 * H2, 4 * W2)], "org_input_size": {"height": 4 * H2, "width": 4 * W2}}
+        for K in (1, 64):
+            codec = codec_m.LMSFCCodec(eval_encode="bitrate", encoder_config={"qp": 3, "coder_lanes": K}, device=dev,
+                                       vision_model=None, dataset=None)
+            res = codec.encode(inp, "", "", "")
+            enc_us = wall(lambda: codec.encode(inp, "", "", ""), iters=5, warm=2)
+            dec_us = wall(lambda: codec.decode(res["bitstream"], "", ""), iters=5, warm=2)
+            rows.append({"case": f"lmsfc codec, {frames} frame(s) {4 * H2}x{4 * W2}", "lanes_per_item": K,
+                         "bytes_per_frame": int(np.mean(res["bytes"])), "encode_ms_per_frame": round(enc_us / 1e3 / frames, 3),
+                         "decode_ms_per_frame": round(dec_us / 1e3 / frames, 3)})
+            print(rows[-1], flush=True)
+            del codec
     if len(sys.argv) > 1:
         with open(sys.argv[1], "w") as f:
             json.dump(rows, f, indent=1)

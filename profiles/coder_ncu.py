@@ -1,0 +1,25 @@
+"""One encode + decode of a cfg-4 latent (1 x 256 x 13 x 19) per lane count, for `ncu -k regex:rans_` captures."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import cdf as OC      # noqa: E402  (tables for the synthetic latent only)
+from profiles.coder_bench import latent  # noqa: E402
+
+c = importlib.import_module("l-msfc-v2-training_b200.coder")
+table = OC.get_scale_table().numpy()
+cdfs, offsets, sizes = OC.gc_update(table)
+tc, ts, to = (torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (cdfs, sizes, offsets))
+sym, idx = latent(np.random.default_rng(5), table, (1, 256, 13, 19))
+ds, di = torch.from_numpy(sym).cuda(), torch.from_numpy(idx).cuda()
+for K in [int(a) for a in sys.argv[1:]] or [1, 64]:
+    for _ in range(2):
+        s = c.encode_batch(ds, di, tc, ts, to, lanes=K)
+        out = c.decode_batch(s, di, tc, ts, to, lanes=1 if K == 1 else None)
+    assert torch.equal(out, ds)
+print("ok")
