@@ -2,7 +2,7 @@
 
 Replaces `compressai.ans.RansEncoder().encode_with_indexes` / `RansDecoder().decode_with_indexes` and the
 per-item `.tolist()` loops around them (compressai/entropy_models/entropy_models.py:256-268, :309-323): the whole
-batch is coded by one launch (one thread per string), and only the finished bytes cross PCIe.
+batch is coded by one launch (one warp per string), and only the finished bytes cross PCIe.
 
 Strings
   lanes = 1   the item's string is byte-identical to the reference's (one rANS string over the flattened item).

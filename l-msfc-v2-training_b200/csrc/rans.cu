@@ -6,13 +6,10 @@
 // A string is inherently serial (every record depends on the coder state), so parallelism comes from strings:
 // lane k of K of an item = symbols[k::K] of that item, coded exactly like the reference codes a whole item.
 // K = 1 reproduces the reference's bytes; K > 1 is this library's interleaved container (K strings + a length
-// table per item, see coder.py).  One WARP owns one string: the state is replicated in its 32 threads and the
-// serial chain runs warp-uniform, while everything that does not depend on the state is done 32 symbols at a
-// time by the 32 threads -- symbol / index / CDF fetches (one memory round trip per 32 symbols, the next chunk in
-// flight while this one is coded), the reciprocal of each frequency, and, in the decoder, the table search itself
-// (32 probes per round trip, ballot).  Per record the state-dependent chain is one exact 64-bit division (encode:
-// fp64 reciprocal estimate + integer fix-up; the quotient is < 2^47, so the estimate is off by at most one) or one
-// warp-wide probe of the CDF row (decode).
+// table per item, see coder.py).  One WARP owns one string.  Everything that does not depend on the state is done
+// 128 symbols at a time by its 32 threads -- symbol / index / CDF fetches, the reciprocal of each frequency (so the
+// encoder's division is a multiply-high on the serial chain) and, in the decoder, the table search itself (32 probes
+// per round trip, ballot).  DESIGN.md section 3b has the measurements.
 #include "../../include/b200lmsfc.h"
 #include "kernels.cuh"
 
@@ -44,8 +41,7 @@ __device__ __forceinline__ uint64_t magic_reciprocal(uint32_t freq, uint32_t& sh
   return (q1 << 32) + q0;
 }
 
-// The coder state lives, replicated, in every thread of the warp that owns the string: the serial chain runs
-// warp-uniform, operands arrive by shuffle from the thread that fetched them, thread 0 does the stores.
+// Encoder state (held by thread 0 of the warp that owns the string).
 struct Enc {
   uint64_t x;
   uint32_t* p;
