@@ -52,9 +52,9 @@ struct Enc {
     x >>= 32;
   }
   // rans64.h:75-90: x' = ((x / f) << 16) + x % f + start = x + start + (x / f) * (2^16 - f)
-  __device__ __forceinline__ void put(uint64_t magic, uint32_t sh, uint32_t add, uint32_t cmpl) {
-    const uint64_t lim = (uint64_t)(65536u - cmpl) << 47;
-    if (x >= lim) emit();
+  // lim_hi = freq << 15: the renormalisation bound freq << 47 has a zero low word, so one 32-bit compare decides
+  __device__ __forceinline__ void put(uint64_t magic, uint32_t sh, uint32_t add, uint32_t cmpl, uint32_t lim_hi) {
+    if ((uint32_t)(x >> 32) >= lim_hi) emit();
     const uint64_t q = __umul64hi(x, magic) >> sh;
     x = x + add + q * cmpl;
   }
@@ -65,12 +65,13 @@ struct Enc {
 };
 
 // what one symbol contributes, fetched and prepared by one thread: the reciprocal of its frequency (0 marks a
-// record that must be skipped: bad index / row), additive term, 2^16 - freq and shift, escape payload (raw + 1)
-struct Rec { uint64_t magic; uint32_t add, cmpl_sh, esc; };
+// record that must be skipped: bad index / row), additive term, 2^16 - freq, shift, high word of the
+// renormalisation bound, escape payload (raw + 1)
+struct __align__(16) Rec { uint64_t magic; uint32_t add, cmpl; uint32_t lim_hi, sh, esc, pad; };
 
 __device__ __forceinline__ Rec fetch_record(const int32_t* __restrict__ sym, const int32_t* __restrict__ idx, int64_t i,
                                             const RansTables& tb, int& bad) {
-  Rec r{0ull, 0u, 0u, 0u};
+  Rec r{0ull, 0u, 0u, 0u, 0u, 0u, 0u};
   const int32_t row = __ldg(idx + i);
   if (row < 0 || row >= tb.rows) { bad = 1; return r; }
   const int32_t max_value = __ldg(tb.sizes + row) - 2;
@@ -85,7 +86,9 @@ __device__ __forceinline__ Rec fetch_record(const int32_t* __restrict__ sym, con
   uint32_t sh;
   r.magic = magic_reciprocal(freq, sh);
   r.add = freq < 2 ? c0 + 65535u : c0;                 // mulhi(x, 2^64 - 1) = x - 1: (x - 1) * 65535 + x + 65535 + c0 = (x << 16) + c0
-  r.cmpl_sh = (65536u - freq) | (sh << 24);
+  r.cmpl = 65536u - freq;
+  r.sh = sh;
+  r.lim_hi = freq << 15;
   r.esc = (v == max_value) ? raw + 1 : 0u;
   return r;
 }
@@ -118,7 +121,7 @@ __global__ void __launch_bounds__(128) rans_encode_kernel(const int32_t* __restr
 #pragma unroll
     for (int k = 0; k < kEncChunk / 32; ++k) {            // slot u of the chunk = symbol hi-1-u
       const int u = j + 32 * k;
-      r[k] = u < m ? fetch_record(sym, idx, lane + (hi - 1 - u) * lanes, tb, bad) : Rec{0ull, 0u, 0u, 0u};
+      r[k] = u < m ? fetch_record(sym, idx, lane + (hi - 1 - u) * lanes, tb, bad) : Rec{0ull, 0u, 0u, 0u, 0u, 0u, 0u};
     }
     __syncwarp();                                         // thread 0 is done with the previous chunk
 #pragma unroll
@@ -126,6 +129,7 @@ __global__ void __launch_bounds__(128) rans_encode_kernel(const int32_t* __restr
     __syncwarp();
     if (j == 0 && e.p - base < 2 * m + 2) bad = 2;         // cannot happen with lane_cap >= lmsfc_rans_lane_cap()
     if (j == 0 && bad != 2) {
+#pragma unroll 2
       for (int u = 0; u < m; ++u) {
         const Rec c = mine[u];
         if (c.magic == 0) continue;
@@ -137,7 +141,7 @@ __global__ void __launch_bounds__(128) rans_encode_kernel(const int32_t* __restr
           e.put_bits((uint32_t)nb % kBypassMax);
           for (int q = nb / (int)kBypassMax; q > 0; --q) e.put_bits(kBypassMax);
         }
-        e.put(c.magic, c.cmpl_sh >> 24, c.add, c.cmpl_sh & 0x1FFFFu);
+        e.put(c.magic, c.sh, c.add, c.cmpl, c.lim_hi);
       }
     }
   }
