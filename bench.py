@@ -200,7 +200,7 @@ def run_b200(args):
     sp = model_m.DEFAULT_SPEC
     torch.manual_seed(1234)
     net = model_m.LMSFC(sp).to(dev)
-    ts = train_m.TrainStep(net, lmbda=LMBDA, distributed=world > 1, bucket_mb=float(os.environ.get("LMSFC_BUCKET_MB", "32")))
+    ts = train_m.TrainStep(net, lmbda=LMBDA, distributed=world > 1, bucket_mb=float(os.environ.get("LMSFC_BUCKET_MB", "64")))
     nbuf = 4
     host = []
     for i in range(nbuf):                    # pinned bf16 NHWC feature shards, one per buffered step

@@ -12,7 +12,7 @@ import torch.distributed as dist
 
 
 class BucketedGradReducer:
-    def __init__(self, model, bucket_mb=32.0, process_group=None, tail_mb=8.0):
+    def __init__(self, model, bucket_mb=64.0, process_group=None, tail_mb=8.0):
         if model.arena is None:
             model.build_arena()
         self.model, self.arena = model, model.arena

@@ -30,7 +30,7 @@ from .parallel import BucketedGradReducer
 
 class TrainStep:
     def __init__(self, model: LMSFC, lmbda=0.0130, lr=1e-4, aux_lr=1e-3, clip_max_norm=1.0, distributed=False,
-                 bucket_mb=32.0, side_streams=True):
+                 bucket_mb=64.0, side_streams=True):
         self.model = model
         if model.arena is None:
             model.build_arena()
