@@ -196,7 +196,7 @@ def run_b200(args):
     model_m = importlib.import_module(PKG + ".model")
     train_m = importlib.import_module(PKG + ".train")
     layers = importlib.import_module(PKG + ".layers")
-    from oracle import lmsfc as OL          # synthetic feature generator + cpu_baseline only
+    data_m = importlib.import_module(PKG + ".data")
     sp = model_m.DEFAULT_SPEC
     torch.manual_seed(1234)
     net = model_m.LMSFC(sp).to(dev)
@@ -204,7 +204,7 @@ def run_b200(args):
     nbuf = 4
     host = []
     for i in range(nbuf):                    # pinned bf16 NHWC feature shards, one per buffered step
-        f = OL.synth_features(sp, BATCH, H2, W2, seed=1234 + rank * 100 + i)
+        f = data_m.synth_features(sp, BATCH, H2, W2, seed=1234 + rank * 100 + i)
         host.append({k: v.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).pin_memory() for k, v in f.items()})
     feats = {k: v.to(dev, non_blocking=True) for k, v in host[0].items()}
     h2d = sum(v.numel() * 2 for v in host[0].values())

@@ -21,6 +21,18 @@ import torch
 from .spec import DEFAULT_SPEC, LMSFCSpec
 
 
+def synth_features(spec: LMSFCSpec, B: int, H2: int, W2: int, seed: int = 1234, device="cpu", dtype=torch.float32):
+    """The synthetic benchmark input: FPN-like features relu(N(0,1)) * s_l + N(0, 0.1), clipped to the
+    dataset range [-26.43, 28.40] of compressai_vision/codecs/utils.py:30-39; seeded, identical on every rank count."""
+    g = torch.Generator().manual_seed(seed)
+    feats = {}
+    for i, (k, (h, w)) in enumerate(zip(spec.levels, spec.level_shapes(H2, W2))):
+        a = torch.relu(torch.randn(B, spec.F, h, w, generator=g)) * (1.0 + 0.5 * i)
+        a = a + 0.1 * torch.randn(B, spec.F, h, w, generator=g)
+        feats[k] = a.clamp_(-26.43, 28.40).to(device=device, dtype=dtype)
+    return feats
+
+
 class FeatureFolder:
     """Samples = (file, frame) pairs of the feature dumps under `root`.  `crop` is in INPUT pixels (256 -> a 64x64
     window of P2, 32x32 of P3, ...); it must be a multiple of 4 * 2^(levels-1) so the windows line up on every level."""

@@ -21,8 +21,15 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 PKG = "l-msfc-v2-training_b200"
-from oracle import cdf as OC      # noqa: E402  (bench's cpu_baseline leg: the checker / reference arm only)
-from oracle import rans as OR     # noqa: E402
+
+
+def product_tables(dev="cuda"):
+    """GaussianConditional CDF tables built by the product (entropy_models.update on the device CDF kernel)."""
+    em = importlib.import_module(PKG + ".entropy_models")
+    model_m = importlib.import_module(PKG + ".model")
+    gc = em.GaussianConditional(None).to(dev)
+    gc.update_scale_table(model_m.get_scale_table().tolist())
+    return gc.scale_table.cpu().numpy(), gc._quantized_cdf, gc._cdf_length, gc._offset
 
 
 def latent(rng, table, shape):
@@ -61,9 +68,12 @@ def main():
     L = importlib.import_module(PKG + "._lib")
     ptr, stream = L.ptr, L.stream
     dev = "cuda"
-    table = OC.get_scale_table().numpy()
-    cdfs, offsets, sizes = OC.gc_update(table)
-    tc, ts, to = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (cdfs, sizes, offsets))
+    table, tc, ts, to = product_tables(dev)
+    cdfs, sizes, offsets = (t.cpu().numpy() for t in (tc, ts, to))
+    try:        # the CPU arm only: the reference's own compiled coder (oracle/_ref), like bench.py's cpu_baseline leg
+        from oracle import rans as OR
+    except Exception:
+        OR = None
     rng = np.random.default_rng(5)
     rows = []
     for name, shape in (("cfg2 y 16x256x4x4", (16, 256, 4, 4)), ("cfg4 y 1x256x13x19", (1, 256, 13, 19)),
@@ -103,7 +113,7 @@ def main():
                          "encode_Msym_s": round(nsym / enc_us, 1), "decode_Msym_s": round(nsym / dec_us, 1),
                          "encode_GBps_algorithmic": round((16 * nsym + 4 * total_words) / enc_us / 1e3, 2)})
             print(rows[-1], flush=True)
-        if OR.ref_available():
+        if OR is not None and OR.ref_available():
             # the reference arm: compressai's own compiled coder driven as EntropyModel.compress does (1 thread)
             def ref_enc():
                 return [OR.ref_encode(sym[i], idx[i], cdfs, sizes, offsets) for i in range(items)]
@@ -120,10 +130,10 @@ def main():
     # build_indexes, y coder; decode = z coder, h_s, build_indexes, y coder, g_s.  Random-init weights, CDFs from update().
     codec_m = importlib.import_module(PKG + ".codec")
     spec = importlib.import_module(PKG + ".spec").DEFAULT_SPEC
-    from oracle import lmsfc as OL
     torch.manual_seed(0)
     for frames, H2, W2 in ((1, 200, 304), (8, 200, 304)):
-        feats = {k: v.to(torch.bfloat16).float() for k, v in OL.synth_features(spec, frames, H2, W2, device=dev).items()}
+        feats = {k: v.to(torch.bfloat16).float()
+                 for k, v in importlib.import_module(PKG + ".data").synth_features(spec, frames, H2, W2, device=dev).items()}
         inp = {"data": feats, "input_size": [(4 * H2, 4 * W2)], "org_input_size": {"height": 4 * H2, "width": 4 * W2}}
         for K in (1, 64):
             codec = codec_m.LMSFCCodec(eval_encode="bitrate", encoder_config={"qp": 3, "coder_lanes": K}, device=dev,

@@ -8,13 +8,10 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from oracle import cdf as OC      # noqa: E402  (tables for the synthetic latent only)
-from profiles.coder_bench import latent  # noqa: E402
+from profiles.coder_bench import latent, product_tables  # noqa: E402
 
 c = importlib.import_module("l-msfc-v2-training_b200.coder")
-table = OC.get_scale_table().numpy()
-cdfs, offsets, sizes = OC.gc_update(table)
-tc, ts, to = (torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (cdfs, sizes, offsets))
+table, tc, ts, to = product_tables()
 sym, idx = latent(np.random.default_rng(5), table, (1, 256, 13, 19))
 ds, di = torch.from_numpy(sym).cuda(), torch.from_numpy(idx).cuda()
 for K in [int(a) for a in sys.argv[1:]] or [1, 64]:

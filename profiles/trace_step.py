@@ -10,14 +10,13 @@ sys.path.insert(0, ROOT)
 PKG = "l-msfc-v2-training_b200"
 model_m = importlib.import_module(PKG + ".model")
 train_m = importlib.import_module(PKG + ".train")
-from oracle import lmsfc as OL        # synthetic feature generator only
 
 dev = torch.device("cuda", 0)
 sp = model_m.DEFAULT_SPEC
 torch.manual_seed(1234)
 net = model_m.LMSFC(sp).to(dev)
 ts = train_m.TrainStep(net, lmbda=0.013)
-f = OL.synth_features(sp, 16, 64, 64, seed=1234)
+f = importlib.import_module(PKG + '.data').synth_features(sp, 16, 64, 64, seed=1234)
 feats = {k: v.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).to(dev) for k, v in f.items()}
 ts.step(feats)
 ts.capture(feats, warmup=1, pipelined=os.environ.get("LMSFC_SEQUENTIAL", "0") != "1")

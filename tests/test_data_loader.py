@@ -106,3 +106,14 @@ def test_loader_feeds_the_captured_step(tmp_path):
             ld.close()
     a, b = run(True), run(False)
     assert torch.isfinite(a).all() and torch.allclose(a, b, rtol=1e-3, atol=1e-5), (a, b)
+
+
+def test_synthetic_features_equal_the_oracles():
+    """bench.py's product arm and the CPU arm must see the same synthetic inputs."""
+    from oracle import lmsfc as OL
+    data_m = importlib.import_module(PKG + ".data")
+    spec = importlib.import_module(PKG + ".spec").DEFAULT_SPEC
+    a = data_m.synth_features(spec, 2, 13, 19, seed=77)
+    b = OL.synth_features(spec, 2, 13, 19, seed=77)
+    assert list(a) == list(b) and all(torch.equal(a[k], b[k]) for k in a)
+    assert float(max(v.max() for v in a.values())) <= 28.40 and float(min(v.min() for v in a.values())) >= -26.43
