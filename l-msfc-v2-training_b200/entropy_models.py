@@ -36,6 +36,8 @@ class EntropyModel(nn.Module):
     def __init__(self, likelihood_bound: float = 1e-9, entropy_coder: Optional[str] = None,
                  entropy_coder_precision: int = 16):
         super().__init__()
+        if entropy_coder is not None and entropy_coder != "ans":      # entropy_models.py:44-56: available_entropy_coders()
+            raise ValueError(f'Invalid entropy coder "{entropy_coder}", choose from (ans)')
         self.entropy_coder_name = entropy_coder or "ans"
         self.entropy_coder_precision = int(entropy_coder_precision)
         self.likelihood_bound = float(likelihood_bound)
