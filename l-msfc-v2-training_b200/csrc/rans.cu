@@ -67,11 +67,11 @@ struct Enc {
 // what one symbol contributes, fetched and prepared by one thread: the reciprocal of its frequency (0 marks a
 // record that must be skipped: bad index / row), additive term, 2^16 - freq, shift, high word of the
 // renormalisation bound, escape payload (raw + 1)
-struct __align__(16) Rec { uint64_t magic; uint32_t add, cmpl; uint32_t lim_hi, sh, esc, pad; };
+struct __align__(16) Rec { uint64_t magic; uint32_t add, cmpl; uint32_t lim_hi, sh, esc, rare; };   // rare: 1 skip, 2 escape
 
 __device__ __forceinline__ Rec fetch_record(const int32_t* __restrict__ sym, const int32_t* __restrict__ idx, int64_t i,
                                             const RansTables& tb, int& bad) {
-  Rec r{0ull, 0u, 0u, 0u, 0u, 0u, 0u};
+  Rec r{0ull, 0u, 0u, 0u, 0u, 0u, 1u};
   const int32_t row = __ldg(idx + i);
   if (row < 0 || row >= tb.rows) { bad = 1; return r; }
   const int32_t max_value = __ldg(tb.sizes + row) - 2;
@@ -90,6 +90,7 @@ __device__ __forceinline__ Rec fetch_record(const int32_t* __restrict__ sym, con
   r.sh = sh;
   r.lim_hi = freq << 15;
   r.esc = (v == max_value) ? raw + 1 : 0u;
+  r.rare = r.esc ? 2u : 0u;
   return r;
 }
 
@@ -121,7 +122,7 @@ __global__ void __launch_bounds__(128) rans_encode_kernel(const int32_t* __restr
 #pragma unroll
     for (int k = 0; k < kEncChunk / 32; ++k) {            // slot u of the chunk = symbol hi-1-u
       const int u = j + 32 * k;
-      r[k] = u < m ? fetch_record(sym, idx, lane + (hi - 1 - u) * lanes, tb, bad) : Rec{0ull, 0u, 0u, 0u, 0u, 0u, 0u};
+      r[k] = u < m ? fetch_record(sym, idx, lane + (hi - 1 - u) * lanes, tb, bad) : Rec{0ull, 0u, 0u, 0u, 0u, 0u, 1u};
     }
     __syncwarp();                                         // thread 0 is done with the previous chunk
 #pragma unroll
@@ -132,8 +133,9 @@ __global__ void __launch_bounds__(128) rans_encode_kernel(const int32_t* __restr
 #pragma unroll 2
       for (int u = 0; u < m; ++u) {
         const Rec c = mine[u];
-        if (c.magic == 0) continue;
-        if (c.esc) {                                      // bypass digits, :147-175 reversed
+        if (c.rare) {                                     // one branch for both uncommon cases
+          if (c.rare & 1u) continue;
+          // bypass digits, :147-175 reversed
           const uint32_t raw = c.esc - 1u;
           int nb = 0;
           while (((uint64_t)raw >> (nb * kBypassBits)) != 0) ++nb;
@@ -204,29 +206,31 @@ struct Dec {
 // one entry, a ballot counts the entries <= cf.  The first probe set is the 32 entries around the centre of the row,
 // where a latent's mass sits (rows of <= 32 entries are covered entirely): most symbols cost ONE memory round trip,
 // and start / next come out of the probed registers.  Otherwise 32-ary steps over what is left.
-// The first probe set does not depend on the coder state: the caller loads it one symbol ahead (probe_window).
 static constexpr uint32_t kAbove = 0x7fffffffu;
 __device__ __forceinline__ int window_base(int size) { return size > 32 ? ((size - 2) >> 1) - 15 : 0; }
-__device__ __forceinline__ uint32_t probe_window(const int32_t* __restrict__ cdf, int size, int j) {
-  const int w0 = window_base(size);
-  return (w0 + j < size) ? (uint32_t)__ldg(cdf + w0 + j) : kAbove;
-}
 __device__ __forceinline__ int cdf_search_warp(const int32_t* __restrict__ cdf, int size, uint32_t cf, int j,
-                                               uint32_t val, uint32_t& start, uint32_t& freq) {
+                                               uint32_t& start, uint32_t& freq) {
   const int w0 = window_base(size);
+  // thread j probes entry w0+j and its successor: the thread that holds the answer hands over start and freq
+  // (freq - 1 fits 16 bits) in ONE shuffle
+  const uint32_t val = (w0 + j < size) ? (uint32_t)__ldg(cdf + w0 + j) : kAbove;
+  const uint32_t nxt = (w0 + j + 1 < size) ? (uint32_t)__ldg(cdf + w0 + j + 1) : kAbove;
+  const uint32_t pack = (val & 0xFFFFu) | ((nxt - val - 1u) << 16);
   int cnt = __popc(__ballot_sync(0xffffffffu, val <= cf));
   int lo, hi;
   if (cnt > 0 && cnt < 32) {
-    start = __shfl_sync(0xffffffffu, val, cnt - 1);
-    freq = __shfl_sync(0xffffffffu, val, cnt) - start;
+    const uint32_t got = __shfl_sync(0xffffffffu, pack, cnt - 1);
+    start = got & 0xFFFFu;
+    freq = (got >> 16) + 1u;
     return w0 + cnt - 1;
   }
+  uint32_t v2;
   if (cnt == 0) { lo = 0; hi = w0; } else { lo = w0 + 31; hi = size - 1; }
   while (hi - lo > 1) {                    // invariant cdf[lo] <= cf < cdf[hi]
     const int step = (hi - lo + 31) >> 5;
     const int pidx = lo + (j + 1) * step;
-    val = pidx < hi ? (uint32_t)__ldg(cdf + pidx) : kAbove;
-    cnt = __popc(__ballot_sync(0xffffffffu, val <= cf));
+    v2 = pidx < hi ? (uint32_t)__ldg(cdf + pidx) : kAbove;
+    cnt = __popc(__ballot_sync(0xffffffffu, v2 <= cf));
     lo += cnt * step;
     hi = min(hi, lo + step);
   }
@@ -279,21 +283,15 @@ __global__ void __launch_bounds__(128) rans_decode_kernel(const uint32_t* __rest
       mine[u] = sl;
     }
     __syncwarp();
-    int4 nx = mine[0];
-    uint32_t win_n = nx.x >= 0 ? probe_window(tb.cdfs + (int64_t)nx.x * tb.cdf_stride, nx.y, j) : 0u;
+#pragma unroll 2
     for (int u = 0; u < m; ++u) {
-      const int4 sl = nx;
-      const uint32_t win = win_n;
-      if (u + 1 < m) {                                    // the next symbol's first probe set, off the serial chain
-        nx = mine[u + 1];
-        win_n = nx.x >= 0 ? probe_window(tb.cdfs + (int64_t)nx.x * tb.cdf_stride, nx.y, j) : 0u;
-      }
+      const int4 sl = mine[u];
       if (sl.x < 0) continue;
       const int32_t* cdf = tb.cdfs + (int64_t)sl.x * tb.cdf_stride;
       const int32_t max_value = sl.y - 2;
       const uint32_t cf = (uint32_t)(d.x & 0xFFFFu);
       uint32_t start, freq;
-      const int s = cdf_search_warp(cdf, sl.y, cf, j, win, start, freq);
+      const int s = cdf_search_warp(cdf, sl.y, cf, j, start, freq);
       d.x = (uint64_t)freq * (d.x >> kPrecision) + cf - start;                          // rans64.h:120-137
       d.refill();
       int32_t value = s;
@@ -309,7 +307,7 @@ __global__ void __launch_bounds__(128) rans_decode_kernel(const uint32_t* __rest
         value = (int32_t)(raw >> 1);
         value = (raw & 1u) ? -value - 1 : value + max_value;
       }
-      if (j == 0) mine[u].w = value + sl.z;
+      mine[u].w = value + sl.z;                          // every thread holds the same value
     }
     __syncwarp();
 #pragma unroll
