@@ -30,6 +30,37 @@ def pmf_to_quantized_cdf(pmf, precision: int = 16):
     return torch.from_numpy(out.astype(np.int64)).int()
 
 
+class _EntropyCoder:
+    """entropy_models.py:47-80: the `entropy_model.entropy_coder` object, list-based like the pybind11 `ans` coder it
+    wraps there (`encode_with_indexes(symbols, indexes, cdfs, cdf_lengths, offsets) -> bytes` and back), here one
+    string on the device coder.  `device` is where the lists are staged."""
+
+    def __init__(self, method: str = "ans", device="cuda"):
+        if method != "ans":
+            raise ValueError(f'Unknown entropy coder "{method}" (available: ans)')
+        self.name = method
+        self.device = device
+
+    def _tabs(self, cdfs, cdf_lengths, offsets):
+        i32 = dict(dtype=torch.int32, device=self.device)
+        width = max(len(r) for r in cdfs)
+        cdf = torch.zeros((len(cdfs), width), **i32)
+        for r, row in enumerate(cdfs):
+            cdf[r, : len(row)] = torch.as_tensor(row, **i32)
+        return cdf, torch.as_tensor(cdf_lengths, **i32), torch.as_tensor(offsets, **i32)
+
+    def encode_with_indexes(self, symbols, indexes, cdfs, cdf_lengths, offsets) -> bytes:
+        from . import coder
+        i32 = dict(dtype=torch.int32, device=self.device)
+        return coder.encode_batch(torch.as_tensor(symbols, **i32).reshape(1, -1), torch.as_tensor(indexes, **i32).reshape(1, -1),
+                                  *self._tabs(cdfs, cdf_lengths, offsets))[0]
+
+    def decode_with_indexes(self, string, indexes, cdfs, cdf_lengths, offsets):
+        from . import coder
+        idx = torch.as_tensor(indexes, dtype=torch.int32, device=self.device).reshape(1, -1)
+        return coder.decode_batch([string], idx, *self._tabs(cdfs, cdf_lengths, offsets), lanes=1).reshape(-1).tolist()
+
+
 class EntropyModel(nn.Module):
     """entropy_models.py:99-325."""
 
@@ -39,6 +70,7 @@ class EntropyModel(nn.Module):
         if entropy_coder is not None and entropy_coder != "ans":      # entropy_models.py:44-56: available_entropy_coders()
             raise ValueError(f'Invalid entropy coder "{entropy_coder}", choose from (ans)')
         self.entropy_coder_name = entropy_coder or "ans"
+        self.entropy_coder = _EntropyCoder(self.entropy_coder_name)
         self.entropy_coder_precision = int(entropy_coder_precision)
         self.likelihood_bound = float(likelihood_bound)
         self.use_likelihood_bound = likelihood_bound > 0

@@ -93,3 +93,27 @@ def test_compress_needs_a_cuda_module(em):
     eb.update()
     with pytest.raises(RuntimeError, match="(?i)cuda|no CPU fallback"):
         eb.compress(torch.rand(1, 8, 4, 4))                      # host tensor: refused, never coded on the CPU
+
+
+def test_modules_pickle_and_deepcopy(em):
+    """entropy_models.py:131-138 (__getstate__ / __setstate__ exist there because the pybind11 coder cannot be pickled)."""
+    import copy
+    import pickle
+    eb = em.EntropyBottleneck(8)
+    eb2 = pickle.loads(pickle.dumps(eb))
+    assert eb2.entropy_coder.name == "ans" and torch.equal(eb2.quantiles, eb.quantiles)
+    gc = copy.deepcopy(em.GaussianConditional([0.11, 0.5, 1.0]))
+    assert gc.entropy_coder.name == "ans" and gc.scale_table.numel() == 3
+
+
+@pytest.mark.gpu
+def test_entropy_coder_object_speaks_the_list_api(em):
+    """entropy_model.entropy_coder.encode_with_indexes(list, list, cdfs, lengths, offsets) -> the reference's bytes."""
+    import os
+    import numpy as np
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "rans.npz"))
+    sym, idx, cdfs, sizes, offsets = (G[f"gc_outliers.{k}"] for k in ("sym", "idx", "cdfs", "sizes", "offsets"))
+    m = em.EntropyModel()
+    s = m.entropy_coder.encode_with_indexes(sym.tolist(), idx.tolist(), cdfs.tolist(), sizes.tolist(), offsets.tolist())
+    assert s == G["gc_outliers.string"].tobytes()
+    assert m.entropy_coder.decode_with_indexes(s, idx.tolist(), cdfs.tolist(), sizes.tolist(), offsets.tolist()) == sym.tolist()
