@@ -59,9 +59,11 @@ class LMSFCCodec(nn.Module):
         if ckpt:
             sd = torch.load(ckpt, map_location=self.device_name)
             self.model.load_state_dict(sd.get("state_dict", sd))
-        lanes = int(enc.get("coder_lanes", 1))
-        self.model.entropy_bottleneck.coder_lanes = lanes
-        self.model.gaussian_conditional.coder_lanes = lanes
+        lanes = enc.get("coder_lanes", 1)          # 1: the reference's bytes; K: K strings per item; "auto": by latent size
+        self.model.coder_lanes_auto = (lanes == "auto")
+        if lanes != "auto":
+            self.model.entropy_bottleneck.coder_lanes = int(lanes)
+            self.model.gaussian_conditional.coder_lanes = int(lanes)
         self._tables_ready = False      # CDF tables are built on first use (after any checkpoint load)
         vm = kwargs.get("vision_model")
         self.layer_keys = list(getattr(vm, "split_layer_list", self.spec.levels))

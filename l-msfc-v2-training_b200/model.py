@@ -191,6 +191,9 @@ class LMSFC(nn.Module):
         ps = tuple(Fn.nhwc(feats[k], Fn.BF16) for k in lv)
         y, z, mid_hw = self.analysis(ps)
         eb, gc = self.entropy_bottleneck, self.gaussian_conditional
+        if getattr(self, "coder_lanes_auto", False):     # ~1024 symbols per string: <= ~4 % container overhead
+            eb.coder_lanes = max(1, min(256, z[0].numel() // 1024))
+            gc.coder_lanes = max(1, min(256, y[0].numel() // 1024))
         z_strings = eb.compress(z)
         z_hat = eb.decompress(z_strings, z.shape[-2:])
         scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), mid_hw, y.shape[2:])
@@ -204,6 +207,8 @@ class LMSFC(nn.Module):
         """ScaleHyperprior.decompress: -> {"x_hat": {level: tensor}}."""
         assert isinstance(strings, list) and len(strings) == 2
         eb, gc = self.entropy_bottleneck, self.gaussian_conditional
+        if getattr(self, "coder_lanes_auto", False):     # lane counts are read from the strings
+            eb.coder_lanes = gc.coder_lanes = 0
         z_hat = eb.decompress(strings[1], shape)
         scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), tuple(mid_hw), tuple(y_hw))
         indexes = gc.build_indexes(scales)

@@ -73,14 +73,16 @@ def test_encode_decode_round_trip(tmp_path, B, H2, W2, where):
         assert torch.equal(dec2["data"][k], dec["data"][k])
 
 
-def test_interleaved_lanes_round_trip(tmp_path):
+@pytest.mark.parametrize("lanes", [16, "auto"])
+def test_interleaved_lanes_round_trip(tmp_path, lanes):
     codec_m = importlib.import_module(PKG + ".codec")
     torch.manual_seed(0)
     vm = _FakeVisionModel()
-    codec = codec_m.LMSFCCodec(eval_encode="bitrate", encoder_config={"qp": 1, "coder_lanes": 16}, device="cuda",
+    codec = codec_m.LMSFCCodec(eval_encode="bitrate", encoder_config={"qp": 1, "coder_lanes": lanes}, device="cuda",
                                vision_model=vm, dataset=None)
-    feats = _features(2, 20, 28, "cuda")
-    inp = {"data": dict(feats), "input_size": [(80, 112)], "org_input_size": {"height": 80, "width": 112}}
+    H2, W2 = (20, 28) if lanes == 16 else (72, 104)      # auto: y has 256 x 5 x 7 symbols -> 8 lanes, z 256 x 2 x 2 -> 1
+    feats = _features(2, H2, W2, "cuda")
+    inp = {"data": dict(feats), "input_size": [(4 * H2, 4 * W2)], "org_input_size": {"height": 4 * H2, "width": 4 * W2}}
     res = codec.encode(inp, str(tmp_path), "feat", "v")
     dec = codec.decode(res["bitstream"], str(tmp_path), "v")
     with torch.no_grad():
