@@ -128,6 +128,78 @@ class OracleLMSFC(nn.Module):
                 "likelihoods": {"y": y_lik, "z": z_lik},
                 "latents": {"y": y, "z": z, "y_hat": y_hat, "z_hat": z_hat, "scales": scales}}
 
+
+    # ------------------------------------------------------------------ entropy-coded path (models/google.py:313-333)
+    def update(self):
+        """models/base.py:90-113: integer CDF tables of both entropy models (entropy_models.py:389-429, 625-648)."""
+        from . import cdf as OC
+        m, b, f = self.entropy_bottleneck.mbf()
+        self._eb_tabs = OC.eb_update([t.detach() for t in m], [t.detach() for t in b], [t.detach() for t in f],
+                                     self.entropy_bottleneck.quantiles.detach())
+        self._scale_table = OC.get_scale_table()
+        self._gc_tabs = OC.gc_update(self._scale_table)
+
+    def build_indexes(self, scales):
+        """entropy_models.py:684-689."""
+        scales = torch.clamp(scales, min=self.spec.scale_bound)
+        indexes = scales.new_full(scales.size(), len(self._scale_table) - 1).int()
+        for s in self._scale_table[:-1]:
+            indexes -= (scales <= s).int()
+        return indexes
+
+    def _scales_from(self, z_hat, mid_hw, y_hw):
+        hs = self.h_s
+        t = hs[1](hs[0](z_hat)[..., : mid_hw[0], : mid_hw[1]])
+        t = hs[3](hs[2](t)[..., : y_hw[0], : y_hw[1]])
+        return hs[5](hs[4](t))
+
+    @torch.no_grad()
+    def compress(self, feats):
+        """ScaleHyperprior.compress (models/google.py:313-324) with the oracle's coder (oracle/rans.py)."""
+        from . import rans as OR
+        p2, p3, p4, p5 = (feats[k] for k in self.spec.levels)
+        a = self.g_a
+        e2 = a.gdn2(a.conv2(p2))
+        e3 = a.gdn3(a.conv3(torch.cat([e2, p3], 1)))
+        e4 = a.gdn4(a.conv4(torch.cat([e3, p4], 1)))
+        y = a.conv5(torch.cat([e4, p5], 1))
+        ha = self.h_a
+        z1 = ha[2](ha[1](ha[0](torch.abs(y))))
+        z = ha[4](ha[3](z1))
+        med = self.entropy_bottleneck.quantiles[:, 0, 1].reshape(1, -1, 1, 1)
+        cdf, off, ln = self._eb_tabs
+        z_sym = torch.round(z - med).int().numpy()
+        z_idx = np.broadcast_to(np.arange(z.shape[1], dtype=np.int32).reshape(1, -1, 1, 1), z_sym.shape)
+        z_strings = OR.compress(z_sym, z_idx, cdf, ln, off)
+        z_hat = torch.from_numpy(OR.decompress(z_strings, z_idx, cdf, ln, off)).float() + med
+        scales = self._scales_from(z_hat, z1.shape[-2:], y.shape[-2:])
+        indexes = self.build_indexes(scales)
+        cdf, off, ln = self._gc_tabs
+        y_strings = OR.compress(torch.round(y).int().numpy(), indexes.numpy(), cdf, ln, off)
+        return {"strings": [y_strings, z_strings], "shape": tuple(z.shape[-2:]), "y_hw": tuple(y.shape[-2:]),
+                "mid_hw": tuple(z1.shape[-2:]), "level_hw": [tuple(feats[k].shape[-2:]) for k in self.spec.levels]}
+
+    @torch.no_grad()
+    def decompress(self, strings, shape, y_hw, mid_hw, level_hw):
+        """ScaleHyperprior.decompress (models/google.py:326-333)."""
+        from . import rans as OR
+        B, N = len(strings[1]), self.entropy_bottleneck.channels
+        med = self.entropy_bottleneck.quantiles[:, 0, 1].reshape(1, -1, 1, 1)
+        cdf, off, ln = self._eb_tabs
+        z_idx = np.broadcast_to(np.arange(N, dtype=np.int32).reshape(1, -1, 1, 1), (B, N, *shape))
+        z_hat = torch.from_numpy(OR.decompress(strings[1], z_idx, cdf, ln, off)).float() + med
+        scales = self._scales_from(z_hat, mid_hw, y_hw)
+        indexes = self.build_indexes(scales)
+        cdf, off, ln = self._gc_tabs
+        y_hat = torch.from_numpy(OR.decompress(strings[0], indexes.numpy(), cdf, ln, off)).float()
+        s = self.g_s
+        crop = lambda t, hw: t[..., : hw[0], : hw[1]]
+        d5 = s.igdn5(crop(s.up5(y_hat), level_hw[3])); p5h = s.head5(d5)
+        d4 = s.igdn4(crop(s.up4(d5), level_hw[2])); p4h = s.head4(d4)
+        d3 = s.igdn3(crop(s.up3(d4), level_hw[1])); p3h = s.head3(d3)
+        p2h = crop(s.up2(d3), level_hw[0])
+        return {"x_hat": {"p2": p2h, "p3": p3h, "p4": p4h, "p5": p5h}}
+
     def aux_loss(self):
         """models/base.py:115-144."""
         return self.entropy_bottleneck.loss()

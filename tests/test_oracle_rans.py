@@ -73,3 +73,28 @@ def test_live_against_compiled_reference():
         assert OR.encode(sym, idx, cdfs, sizes, offsets) == s
         assert np.array_equal(OR.ref_decode(s, idx, cdfs, sizes, offsets), sym)
         assert np.array_equal(OR.decode(s, idx, cdfs, sizes, offsets), sym)
+
+
+def test_oracle_model_compress_decompress_round_trip():
+    """ScaleHyperprior.compress / decompress (models/google.py:313-333) restated on the oracle graph: the decoded
+    reconstruction equals the eval-mode forward, and `bytes` are close to the likelihood estimate of the rate."""
+    import importlib
+    import torch
+    from oracle import lmsfc as OL
+    spec = importlib.import_module("l-msfc-v2-training_b200.spec").DEFAULT_SPEC
+    torch.manual_seed(3)
+    net = OL.OracleLMSFC(spec).eval()
+    net.update()
+    feats = OL.synth_features(spec, 2, 26, 38, seed=5)              # ragged pyramid: 26x38 -> 13x19 -> 7x10 -> 4x5
+    out = net.compress(feats)
+    assert len(out["strings"][0]) == 2 and len(out["strings"][1]) == 2 and out["y_hw"] == (2, 3) and out["shape"] == (1, 1)
+    rec = net.decompress(out["strings"], out["shape"], out["y_hw"], out["mid_hw"], out["level_hw"])
+    with torch.no_grad():
+        fwd = net(feats, training=False)
+    for k in spec.levels:
+        assert rec["x_hat"][k].shape == feats[k].shape
+        assert torch.equal(rec["x_hat"][k], fwd["x_hat"][k]), k
+    # z strings decode to the forward's z_hat; rate: z is inside its tables at init, so bytes ~ -sum log2 L / 8 + flush
+    bits_z = float(-torch.log2(fwd["likelihoods"]["z"]).sum())
+    nbytes_z = sum(len(s) for s in out["strings"][1])
+    assert bits_z / 8 <= nbytes_z <= bits_z / 8 * 1.02 + 2 * 8 + 8
