@@ -1,13 +1,19 @@
-"""bench.py -- L-MSFC train-step throughput (feature-sets/s) on N B200s; see DESIGN.md §Measurement.
+"""bench.py -- L-MSFC train-step throughput (feature-sets/s) on N B200s; see DESIGN.md §6.
 
-  python bench.py --gpus N --steps K --warmup W            # this framework (CUDA kernels via C ABI)
-  python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (oracle port)
+  python bench.py --gpus N --steps K --warmup W            # this framework (CUDA kernels via the C ABI)
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (oracle port), same config
 
 Workload = BASELINE.json configs[1]: batch 16 synthetic P2-P5 feature crops (256x256 input ->
 P2 64x64 ... P5 8x8, 256 channels), bf16, one lambda, per GPU (weak scaling).
 A step = zero_grad -> forward -> RD loss -> backward -> [all-reduce] -> clip + Adam -> aux Adam.
+
+Besides the contract's keys the line carries: `kernels` (live-timed rooflines: the two dominant GEMMs against the
+measured tensor peak, the memory-bound kernels against the measured HBM copy bandwidth), `gpu_incumbent` (the oracle
+graph = the reference's modules, eager on the same B200: fp32 with TF32 and bf16 autocast), `cpu_baseline`, and
+`loss_check` (the first step's loss against the value pinned in tests/golden/bench_loss.json).
 """
 import argparse
+import ctypes
 import importlib
 import json
 import os
@@ -21,6 +27,7 @@ sys.path.insert(0, ROOT)
 PKG = "l-msfc-v2-training_b200"
 BATCH, H2, W2, LMBDA = 16, 64, 64, 0.0130
 METRIC, UNIT = "L-MSFC train feature-sets/sec", "feature-sets/s"
+WORKLOAD = "L-MSFC training, batch 16/GPU synthetic P2-P5 feature crops (256x256 input), one lambda"
 
 
 def peaks():
@@ -28,6 +35,13 @@ def peaks():
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
     except Exception:
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+def pinned_loss():
+    try:
+        return json.load(open(os.path.join(ROOT, "tests", "golden", "bench_loss.json")))
+    except Exception:
+        return None
 
 
 class ClockSampler(threading.Thread):
@@ -57,97 +71,153 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
 
 
-# ------------------------------------------------------------------------------- reference arm
-def run_reference(args):
-    """The reference's own CPU implementation of the step: its modules as restated in oracle/
-    (PyTorch fp32 eager, all host threads), bounded sample of the same workload."""
-    import torch
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    from oracle import lmsfc as OL
-    sp = _load_spec()
-    cores = len(os.sched_getaffinity(0))
-    torch.set_num_threads(cores)
-    torch.manual_seed(0)
-    bs = 2                                   # bounded sample: 2 of the 16 feature-sets per step
-    net = OL.OracleLMSFC(sp)
-    opt, aux = OL.configure_optimizers(net)
-    feats = OL.synth_features(sp, bs, H2, W2)
-    for _ in range(max(1, min(args.warmup, 1))):
-        OL.train_step(net, opt, aux, feats, LMBDA)
-    steps = max(1, min(args.steps, 3))
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        OL.train_step(net, opt, aux, feats, LMBDA)
-    dt = time.perf_counter() - t0
-    v = bs * steps / dt
-    sample = f"{steps} steps of batch {bs} (of {BATCH}) 256x256-crop feature-sets, fp32, torch {torch.__version__} CPU"
-    print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-        "warmup": 1, "ms_per_step": 1e3 * dt / steps * BATCH / bs, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "L-MSFC training, batch 16 synthetic P2-P5 crops (256x256 input), one lambda",
-                   "lambda": LMBDA, "note": "CPU path, rank 0 only"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
-
-
 def _load_spec():
     return importlib.import_module(PKG + ".spec").DEFAULT_SPEC
 
 
-def cpu_baseline(sp):
+# ------------------------------------------------------------------------------- reference arm / CPU baseline
+def _time_oracle_cpu(sp, batch, h2, w2, steps, warmup=1):
+    """The reference's own CPU implementation of the step: its modules as restated in oracle/ (PyTorch fp32 eager,
+    all host threads).  Returns (seconds per step, cores)."""
     import torch
     from oracle import lmsfc as OL
     cores = len(os.sched_getaffinity(0))
     torch.set_num_threads(cores)
-    bs = 2
+    torch.manual_seed(0)
     net = OL.OracleLMSFC(sp)
     opt, aux = OL.configure_optimizers(net)
-    feats = OL.synth_features(sp, bs, H2, W2)
-    OL.train_step(net, opt, aux, feats, LMBDA)
-    t0 = time.perf_counter()
-    n = 2
-    for _ in range(n):
+    feats = OL.synth_features(sp, batch, h2, w2)
+    for _ in range(warmup):
         OL.train_step(net, opt, aux, feats, LMBDA)
-    dt = time.perf_counter() - t0
-    return {"value": bs * n / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n} steps of batch {bs} (of {BATCH}) feature-sets, oracle port (torch {torch.__version__} fp32 CPU)"}
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        OL.train_step(net, opt, aux, feats, LMBDA)
+    return (time.perf_counter() - t0) / steps, cores
+
+
+def run_reference(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sp = _load_spec()
+    steps = max(1, min(args.steps, 3))
+    dt, cores = _time_oracle_cpu(sp, BATCH, H2, W2, steps)          # the SAME config as the B200 arm: batch 16
+    v = BATCH / dt
+    sample = f"{steps} steps of batch {BATCH} 256x256-crop feature-sets (the whole workload), fp32, torch {torch.__version__} CPU"
+    # BASELINE configs[0]: the reference's own CPU-runnable case (512x768 input, batch 1)
+    dt1, _ = _time_oracle_cpu(sp, 1, 128, 192, 2)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": 1, "ms_per_step": 1e3 * dt, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "lambda": LMBDA, "note": "CPU path (oracle port of the reference's modules), rank 0 only"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cfg1_cpu": {"workload": "BASELINE configs[0]: 512x768 input (P2 128x192), batch 1, fp32, one lambda",
+                     "ms_per_step": 1e3 * dt1, "value": 1.0 / dt1, "unit": UNIT, "cores": cores},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def cpu_baseline(sp):
+    import torch
+    n = 2
+    dt, cores = _time_oracle_cpu(sp, BATCH, H2, W2, n)
+    return {"value": BATCH / dt, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_step": 1e3 * dt,
+            "sample": f"{n} steps of batch {BATCH} (the whole workload), oracle port (torch {torch.__version__} fp32 CPU)"}
+
+
+def gpu_incumbent(sp, dev):
+    """SURVEY §8(d) / BASELINE.md §4: the reference's modules (oracle graph) eager on the same B200 -- what a user of
+    the reference gets today from cuDNN / cuBLAS.  fp32 with TF32 allowed, and bf16 autocast; channels-last; CUDA events."""
+    import torch
+    from oracle import lmsfc as OL
+    res = {}
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.benchmark)
+    try:
+        torch.backends.cudnn.allow_tf32 = True
+        torch.backends.cuda.matmul.allow_tf32 = True
+        torch.backends.cudnn.benchmark = True
+        for mode in ("tf32", "bf16_autocast"):
+            torch.manual_seed(0)
+            net = OL.OracleLMSFC(sp).to(dev).to(memory_format=torch.channels_last)
+            opt, aux = OL.configure_optimizers(net)
+            feats = {k: v.contiguous(memory_format=torch.channels_last)
+                     for k, v in OL.synth_features(sp, BATCH, H2, W2, device=dev).items()}
+
+            def step():
+                if mode == "tf32":
+                    return OL.train_step(net, opt, aux, feats, LMBDA)
+                opt.zero_grad()
+                aux.zero_grad()
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    out = net(feats, training=True)
+                out["x_hat"] = {k: v.float() for k, v in out["x_hat"].items()}
+                out["likelihoods"] = {k: v.float() for k, v in out["likelihoods"].items()}
+                crit = net.criterion(out, feats, LMBDA)
+                crit["loss"].backward()
+                torch.nn.utils.clip_grad_norm_(net.parameters(), 1.0)
+                opt.step()
+                a = net.aux_loss()
+                a.backward()
+                aux.step()
+                return crit
+            try:
+                for _ in range(4):
+                    step()
+            except Exception as e:
+                res[mode] = {"error": str(e)[:200]}
+                continue
+            torch.cuda.synchronize()
+            n = 10
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(n):
+                step()
+            b.record()
+            torch.cuda.synchronize()
+            ms = a.elapsed_time(b) / n
+            res[mode] = {"ms_per_step": ms, "value": BATCH / (ms * 1e-3), "unit": UNIT}
+            del net, opt, aux, feats
+            torch.cuda.empty_cache()
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.benchmark = old
+    res["what"] = f"oracle graph (the reference's modules) eager on the same GPU, batch {BATCH}, torch {torch.__version__}, cuDNN benchmark mode"
+    return res
 
 
 # ------------------------------------------------------------------------------- kernel rooflines
 def kernel_rooflines(torch, L, layers, dev):
-    """Dominant kernels timed live with CUDA events on the launching stream (each launch bracketed,
-    averaged): conv2-shaped forward implicit GEMM and its weight-gradient GEMM.
-    Algorithmic FLOPs per launch = 2 * M * N * K (SURVEY.md §8d / DESIGN.md)."""
+    """Kernels timed live with CUDA events on the launching stream.  GEMMs: the conv2-shaped forward implicit GEMM and its
+    weight-gradient GEMM, algorithmic FLOPs per launch = 2*M*N*K, against the measured bf16 burst peak.  Memory-bound
+    kernels: algorithmic bytes per launch (every operand read or written once) against the measured HBM
+    copy bandwidth; their operands rotate over several buffer sets so that a launch never finds its inputs in the
+    126 MB L2.  `traffic` = dram__bytes_read+write per launch from the committed ncu capture (profiles/r2_traffic.json)."""
     pk, which = peaks()
-    conv = layers.Conv(256, 256, 5, 2).to(dev)
-    x = torch.randn(BATCH, 256, H2, W2, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
-    x.requires_grad_()
-    res = {}
+    P = L.ptr
     stream = torch.cuda.current_stream()
-    y = conv(x)
-    g = torch.randn_like(y)
-    y.backward(g)                                   # warm-up of fwd, dgrad, wgrad
-    M, N, K = BATCH * (H2 // 2) * (W2 // 2), 256, 25 * 256
-    flops = 2.0 * M * N * K
+    res = {}
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
+    except Exception:
+        traffic = {}
 
-    def timeit(fn, n=10, reps=20):
-        """Average launch duration: n launches recorded into a CUDA graph (the host side of one eager call -- ctypes,
-        tensor-map encode -- is longer than the kernel), replayed `reps` times between CUDA events on the launching
-        stream; the median replay / n."""
+    def timeit(fns, n=10, reps=20):
+        """Average launch duration: n launches (cycling through `fns`) recorded into a CUDA graph (the host side of one
+        eager call -- ctypes, tensor-map encode -- is longer than the kernel), replayed `reps` times between CUDA
+        events on the launching stream; the median replay / n."""
+        if callable(fns):
+            fns = [fns]
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(stream)
         with torch.cuda.stream(side):
-            for _ in range(3):
-                fn()
+            for f in fns:
+                f()
         stream.wait_stream(side)
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
-            for _ in range(n):
-                fn()
+            for i in range(n):
+                fns[i % len(fns)]()
         ts = []
         for _ in range(reps):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -155,17 +225,21 @@ def kernel_rooflines(torch, L, layers, dev):
             torch.cuda.synchronize()
             ts.append(a.elapsed_time(b) / n)
         ts.sort()
+        del g
         return ts[len(ts) // 2]
 
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
-    except Exception:
-        traffic = {}
-
+    # ---- tensor-bound: g_a.conv2 at batch 16
+    conv = layers.Conv(256, 256, 5, 2).to(dev)
+    x = torch.randn(BATCH, 256, H2, W2, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    x.requires_grad_()
+    y = conv(x)
+    g = torch.randn_like(y)
+    y.backward(g)                                   # warm-up of fwd, dgrad, wgrad
+    M, N, K = BATCH * (H2 // 2) * (W2 // 2), 256, 25 * 256
+    flops = 2.0 * M * N * K
     st = conv._state
     d = st.desc(BATCH, H2, W2, H2 // 2, W2 // 2)
     yb = torch.empty_like(y)
-    P = L.ptr
     ms_f = timeit(lambda: L.conv_forward(d, P(x), None, P(st.w_direct), P(conv.bias), 0, P(yb), None, None, L.stream()))
     gw = torch.zeros((256, 25, 256), device=dev)
     gb = g.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
@@ -176,6 +250,76 @@ def kernel_rooflines(torch, L, layers, dev):
                      "frac": a / pk["bf16_tflops"], "traffic": (traffic.get(name) or {}).get("bytes"), "ms_per_launch": ms,
                      "flops_per_launch": flops, "peak_source": f"bf16_tflops (burst) of {which}",
                      "shape": f"M={M} N={N} K={K} (g_a.conv2 at batch 16)"}
+    del conv, x, y, g, gw, gb, yb
+
+    # ---- HBM-bound kernels
+    def hbm(name, ms, nbytes, what):
+        a = nbytes / (ms * 1e-3) / 1e9
+        res[name] = {"bound": "hbm", "achieved": a, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": a / pk["hbm_gbs"],
+                     "traffic": (traffic.get(name) or {}).get("bytes"), "ms_per_launch": ms, "bytes_per_launch": nbytes,
+                     "peak_source": f"hbm_gbs (copy) of {which}", "shape": what}
+
+    F32, BF16, I32 = torch.float32, torch.bfloat16, torch.int32
+    # Adam over an arena of the model's size (27.9 M parameters): p, m, v read + written, g read + cleared, bf16 shadow
+    n = 27_900_000 // 64 * 64
+    p_, m_, v_, g_ = (torch.zeros(n, dtype=F32, device=dev) for _ in range(4))
+    g_.normal_(0, 1e-3)
+    sh = torch.empty(n, dtype=BF16, device=dev)
+    scratch = torch.zeros(8, dtype=F32, device=dev)
+    step = torch.zeros(1, dtype=I32, device=dev)
+    L.adam_prep(1e-4, None, 0.9, 0.999, 0.0, None, P(step), P(scratch), None, 1, None, L.stream())
+    ms = timeit(lambda: L.adam_update(P(p_), P(m_), P(v_), P(g_), P(sh), n, 0.9, 0.999, 1e-8, P(scratch), 1, L.stream()), n=4)
+    hbm("adam_kernel", ms, n * 34, f"{n} parameters x 34 B (p,m,v read+written, g read+cleared, bf16 shadow written)")
+    ss = torch.zeros(1, dtype=F32, device=dev)
+    ms = timeit([lambda b=b: L.sumsq(P(b), n, P(ss), None, L.stream()) for b in (p_, m_, v_)], n=6)
+    hbm("sumsq_kernel", ms, n * 4, f"{n} gradients x 4 B (3 rotating buffers)")
+    del p_, m_, v_, g_, sh
+    # MSE + gradient over the four reconstructed pyramid levels of one batch-16 step: xhat, x read, grad written (bf16)
+    sp = _load_spec()
+    sets = []
+    for _ in range(3):
+        xs = [torch.randn(BATCH, 256, h, w, device=dev).to(BF16) for h, w in sp.level_shapes(H2, W2)]
+        sets.append((xs, [torch.randn_like(t) for t in xs], [torch.empty_like(t) for t in xs]))
+    nl = len(sets[0][0])
+    ns = [t.numel() for t in sets[0][0]]
+    VP, I64, F32A = ctypes.c_void_p * nl, ctypes.c_int64 * nl, ctypes.c_float * nl
+    acc = torch.zeros(nl, dtype=F32, device=dev)
+    fns = [lambda a=a, b=b, c=c: L.mse_forward_backward_multi(nl, VP(*[P(t) for t in a]), VP(*[P(t) for t in b]), I64(*ns),
+                                                              F32A(*[1e-3] * nl), P(acc), VP(*[P(t) for t in c]), L.stream())
+           for a, b, c in sets]
+    ms = timeit(fns, n=6)
+    hbm("mse_multi_kernel", ms, sum(ns) * 6, f"{sum(ns)} elements x 6 B (p2..p5 of a batch-16 step; 3 rotating sets)")
+    del sets, fns
+    # likelihood kernels at a large latent (8.4 M elements = 32768 pixels x 256 channels): forward + backward pair
+    Pn, C = 32768, 256
+    ne = Pn * C
+    sets = []
+    for _ in range(2):
+        sets.append(dict(y=torch.randn(ne, device=dev) * 3, s=torch.rand(ne, device=dev) * 2 + 0.05, yh=torch.empty(ne, device=dev),
+                         yb=torch.empty(ne, dtype=BF16, device=dev), lk=torch.empty(ne, device=dev),
+                         gb=torch.randn(ne, device=dev).to(BF16), gy=torch.empty(ne, device=dev), gs=torch.empty(ne, device=dev)))
+    sl = torch.zeros(1, dtype=F32, device=dev)
+    rng = torch.tensor([1234, 0], dtype=torch.int64, device=dev)
+    f_fwd = [lambda t=t: L.gc_forward(P(t["y"]), P(t["s"]), None, None, ne, 0, 0.11, 1e-9, 0, 1, P(rng), P(t["yh"]), P(t["yb"]),
+                                      P(t["lk"]), P(sl), L.stream()) for t in sets]
+    f_bwd = [lambda t=t: L.gc_backward(P(t["yh"]), P(t["s"]), None, None, None, P(t["gb"]), ne, 0, 0.11, 1e-9, 1e-6, P(t["gy"]),
+                                       P(t["gs"]), None, L.stream()) for t in sets]
+    ms = timeit(f_fwd, n=4)
+    hbm("gc_forward_kernel", ms, ne * 18, f"{ne} latent elements x 18 B (y, scales -> y_hat, likelihood, bf16 y_hat)")
+    ms = timeit(f_bwd, n=4)
+    hbm("gc_backward_kernel", ms, ne * 18, f"{ne} latent elements x 18 B (y_hat, scales, bf16 grad -> g_y, g_scales)")
+    eb = importlib.import_module(PKG + ".entropy_models").EntropyBottleneck(C).to(dev)
+    packed = eb.packed_parameters().detach().contiguous()
+    if True:
+        gp = torch.zeros_like(packed)
+        f_fwd = [lambda t=t: L.eb_forward(P(t["y"]), P(packed), None, None, Pn, C, 0, 1e-9, 0, 0, P(rng), P(t["yh"]), P(t["yb"]),
+                                          P(t["lk"]), P(sl), L.stream()) for t in sets]
+        f_bwd = [lambda t=t: L.eb_backward(P(t["yh"]), P(packed), None, None, P(t["gb"]), Pn, C, 0, 1e-9, 1e-6, P(t["gy"]), P(gp),
+                                           L.stream()) for t in sets]
+        ms = timeit(f_fwd, n=4)
+        hbm("eb_forward_kernel", ms, ne * 14, f"{ne} latent elements x 14 B (x -> y_hat, likelihood, bf16 y_hat)")
+        ms = timeit(f_bwd, n=4)
+        hbm("eb_backward_kernel", ms, ne * 10, f"{ne} latent elements x 10 B (y_hat, bf16 grad -> g_x; parameter gradients in L2)")
     return res
 
 
@@ -208,13 +352,25 @@ def run_b200(args):
         host.append({k: v.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).pin_memory() for k, v in f.items()})
     feats = {k: v.to(dev, non_blocking=True) for k, v in host[0].items()}
     h2d = sum(v.numel() * 2 for v in host[0].values())
+
     def note(msg):
         if args.verbose:
             print(f"[bench rank {rank}] {msg}", file=sys.stderr, flush=True)
 
     note("model built")
-    ts.step(feats)                           # eager once (lazy init), then capture the graph
+    first = ts.step(feats)                   # eager once (lazy init), then capture the graph
     torch.cuda.synchronize()
+    first_loss = float(first["loss"])
+    # parity gate on the benchmark configuration itself: seed-1234 weights and features, loss of the first step against
+    # the oracle's (tests/golden/bench_loss.json, written by tests/golden/make_bench_loss.py; north_star: rel <= 1e-2)
+    pin = pinned_loss()
+    loss_check = None
+    if pin is not None and rank == 0:
+        rel = abs(first_loss - pin["loss"]) / abs(pin["loss"])
+        loss_check = {"first_loss": first_loss, "pinned": pin["loss"], "rel": rel, "tolerance": 1e-2, "ok": rel <= 1e-2,
+                      "source": "tests/golden/bench_loss.json (oracle, fp32)"}
+        if not loss_check["ok"]:
+            raise SystemExit(f"bench.py: first-step loss {first_loss} differs from the oracle's {pin['loss']} (rel {rel:.3e})")
     note("eager step done")
     ts.capture(feats, warmup=1, pipelined=not args.sequential, n_buffers=2)
     launches_per_step = ts.launches_per_step               # launches of this library recorded into the graph
@@ -271,24 +427,39 @@ def run_b200(args):
     barrier()
     ms_e2e = f0.elapsed_time(f1)
     ts.flush()                               # pipelined order: apply the update of the last backward pass
+    torch.cuda.synchronize()
     if sampler:
         sampler.stop = True
         sampler.join()
     t = torch.tensor([ms, ms_e2e], device=dev)
+    replicas_equal = None
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        # replicas must still be bit-identical after the timed loops (deterministic gradient norm, same all-reduced
+        # gradients): compare every rank's weights with rank 0's
+        mine = net.arena.net_params
+        ref0 = mine.clone()
+        dist.broadcast(ref0, src=0)
+        same = torch.tensor([1 if torch.equal(mine, ref0) else 0], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        replicas_equal = bool(int(same))
+        if not replicas_equal:
+            raise SystemExit("bench.py: data-parallel replicas diverged (weights differ between ranks)")
     ms, ms_e2e = float(t[0]), float(t[1])
+    final_loss = float(loss_host[-1, 0])
+    if not (final_loss == final_loss and final_loss < 1.5 * first_loss):
+        raise SystemExit(f"bench.py: the timed steps diverged (first loss {first_loss}, final {final_loss})")
     if rank == 0:
         roof = kernel_rooflines(torch, L, layers, dev)
-        dom = max(roof, key=lambda k: roof[k]["ms_per_launch"])
+        gemms = {k: v for k, v in roof.items() if v["bound"] == "tensor"}
+        dom = max(gemms, key=lambda k: gemms[k]["ms_per_launch"])
         pk, which = peaks()
         flops_step = sp.flops_train(H2, W2) * BATCH
         line = {
             "metric": METRIC, "value": world * BATCH * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "L-MSFC training, batch 16/GPU synthetic P2-P5 feature crops (256x256 input), bf16, one lambda",
-                       "lambda": LMBDA, "spec": "N=M=F=256 (spec.py)", "cuda_graph": True,
+            "config": {"workload": WORKLOAD, "lambda": LMBDA, "spec": "N=M=F=256 (spec.py)", "cuda_graph": True,
                        "step_order": "sequential" if args.sequential else
                                      "pipelined: each step = [Adam of the previous backward || forward] -> backward (train.py)",
                        "l2": "per-step working set (weights+Adam state+activations ~0.9 GB) exceeds the 126 MB L2",
@@ -301,29 +472,33 @@ def run_b200(args):
             "step_tensor_frac_of_sustained": flops_step / (ms / args.steps * 1e-3) / 1e12 / pk["bf16_tflops_sustained"],
             "roofline": dict(roof[dom], kernel=dom), "kernels": roof,
             "clocks": sampler.summary() if sampler else None,
-            "final_loss": float(loss_host[-1, 0]),
+            "first_loss": first_loss, "final_loss": final_loss, "loss_check": loss_check,
+            "replicas_bit_identical": replicas_equal,
         }
-        if world == 1:                       # the CPU baseline is measured at N=1 only (rank 0, idle host cores)
-            try:
-                line["cpu_baseline"] = cpu_baseline(sp)
-            except Exception as e:  # the baseline is reported, never a dependency
-                line["cpu_baseline"] = {"value": None, "error": str(e)}
+        if world == 1:                       # the baselines are measured at N=1 only (rank 0, idle host cores)
+            if not args.no_baselines:
+                try:
+                    line["gpu_incumbent"] = gpu_incumbent(sp, dev)
+                    best = min(v["ms_per_step"] for v in line["gpu_incumbent"].values() if isinstance(v, dict) and "ms_per_step" in v)
+                    line["gpu_incumbent"]["speedup_vs_best"] = best / (ms / args.steps)
+                except Exception as e:
+                    line["gpu_incumbent"] = {"error": str(e)}
+                try:
+                    line["cpu_baseline"] = cpu_baseline(sp)
+                except Exception as e:  # the baseline is reported, never a dependency
+                    line["cpu_baseline"] = {"value": None, "error": str(e)}
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line), flush=True)
     if world > 1:
-        # Tear down in order: the captured graph holds NCCL kernels, and destroying the communicator under a live
-        # graph hung (measured, 2 GPUs).  Drop the graph first; exit hard if the teardown still does not return.
+        # Tear down in order: the captured graphs hold NCCL kernels, and destroying the communicator under a live graph
+        # hung (measured, 2 GPUs).  Drop the graphs first, then the communicator.
         dist.barrier()
         torch.cuda.synchronize()
         ts.release()
         del ts
         torch.cuda.synchronize()
-        killer = threading.Timer(20.0, lambda: os._exit(0))
-        killer.daemon = True
-        killer.start()
         dist.destroy_process_group()
-        killer.cancel()
 
 
 if __name__ == "__main__":
@@ -333,6 +508,7 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--verbose", action="store_true", help="progress notes on stderr")
+    ap.add_argument("--no-baselines", action="store_true", help="skip the GPU-incumbent and CPU-baseline legs (N=1)")
     ap.add_argument("--sequential", action="store_true",
                     help="capture the eager order (update at the end of the step) instead of the rotated, pipelined one")
     a = ap.parse_args()

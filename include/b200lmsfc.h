@@ -41,6 +41,11 @@ typedef struct {
   int Cout;
 } lmsfc_conv_desc;
 
+/* Thread-local switch for the entropy-coded path (models/google.py:313-333): with on != 0 every conv / deconv / GDN
+ * launch of the calling thread uses one fixed tiling (128-wide tiles, no split K), so a tensor's bits do not depend on
+ * the batch it was computed in or on the device's SM count -- h_s(z_hat) picks CDF rows through hard thresholds
+ * (entropy_models.py:684-689) and must be bit-identical in compress() and decompress(). */
+int lmsfc_set_batch_invariant(int on);
 /* out = act(conv(cat[src0,src1]) + bias).  Any of out_bf16 / out_f32 / out_abs (|.| as bf16, the
  * abs(y) fed to h_a, models/google.py:294) may be null. */
 int lmsfc_conv_forward(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* w,
@@ -131,21 +136,26 @@ int lmsfc_cast_bf16_f32(const void* in, float* out, int64_t n, void* stream);
 int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C, int HW, void* stream);
 
 /* ------------------------------------------------------------------ optimiser (examples/train.py:100-107) */
-int lmsfc_sumsq(const float* g, int64_t n, float* accum, void* stream);
+/* accum += sum(g^2), deterministic (fixed-order two-stage reduction); set_flag (nullable device int) = 1 afterwards */
+int lmsfc_sumsq(const float* g, int64_t n, float* accum, int* set_flag, void* stream);
 /* clip_grad_norm_(max_norm) + torch.optim.Adam step over a flat fp32 arena; p_bf16 (nullable) gets
- * the bf16 shadow; step (device int) is incremented; scratch (>=4 floats) receives
- * {clip_coef, bias_corr1, bias_corr2, grad_norm}.  sumsq null or max_norm<=0 -> no clipping. */
+ * the bf16 shadow; step (device int) is incremented; scratch (>=8 floats) receives
+ * {clip_coef, bias_corr1, bias_corr2, grad_norm, lr, active, -, -}.  sumsq null or max_norm<=0 -> no clipping. */
 int lmsfc_adam_step(float* p, float* m, float* v, const float* g, void* p_bf16, int64_t n, float lr, float beta1,
                     float beta2, float eps, float max_norm, const float* sumsq, int* step, float* scratch,
                     void* stream);
 
 /* The same step in two parts, so that the element-wise pass can run slice by slice (in the order the next forward
  * pass needs the weights) on a stream of its own: adam_prep bumps `step` and fills scratch from sumsq; adam_update
- * applies it to one 16-byte aligned slice and, with zero_g, clears the slice's gradient in the same pass. */
-int lmsfc_adam_prep(float beta1, float beta2, float max_norm, const float* sumsq, int* step, float* scratch,
-                    void* stream);
-int lmsfc_adam_update(float* p, float* m, float* v, float* g, void* p_bf16, int64_t n, float lr, float beta1,
-                      float beta2, float eps, const float* scratch, int zero_g, void* stream);
+ * applies it to one 16-byte aligned slice and, with zero_g, clears the slice's gradient in the same pass.
+ * lr_dev (nullable device float) overrides lr: a captured CUDA graph then follows torch.optim.lr_scheduler
+ * (examples/train.py:279).  pending (nullable device int): the update is applied only when *pending != 0, and the flag is
+ * cleared (set again by lmsfc_sumsq at the end of the next backward pass); force != 0: apply regardless and clear the
+ * flag (an eager step); gate (nullable): take the decision from another optimiser's scratch[5] instead. */
+int lmsfc_adam_prep(float lr, const float* lr_dev, float beta1, float beta2, float max_norm, const float* sumsq, int* step,
+                    float* scratch, int* pending, int force, const float* gate, void* stream);
+int lmsfc_adam_update(float* p, float* m, float* v, float* g, void* p_bf16, int64_t n, float beta1, float beta2, float eps,
+                      const float* scratch, int zero_g, void* stream);
 
 /* ------------------------------------------------------------------ CDF tables (cpp_exts/ops/ops.cpp:40-109) */
 /* host pointers; cdf must hold n+1 entries.  Errors mirror the reference's ValueError cases. */

@@ -52,14 +52,15 @@ _SIGS = {
     "lmsfc_cast_f32_bf16": [P, P, c_int64, P],
     "lmsfc_cast_bf16_f32": [P, P, c_int64, P],
     "lmsfc_nchw_to_nhwc_bf16": [P, P, c_int, c_int, c_int, P],
-    "lmsfc_sumsq": [P, c_int64, P, P],
+    "lmsfc_sumsq": [P, c_int64, P, P, P],
     "lmsfc_adam_step": [P, P, P, P, P, c_int64, c_float, c_float, c_float, c_float, c_float, P, P, P, P],
-    "lmsfc_adam_prep": [c_float, c_float, c_float, P, P, P, P],
-    "lmsfc_adam_update": [P, P, P, P, P, c_int64, c_float, c_float, c_float, c_float, P, c_int, P],
+    "lmsfc_adam_prep": [c_float, P, c_float, c_float, c_float, P, P, P, P, c_int, P, P],
+    "lmsfc_adam_update": [P, P, P, P, P, c_int64, c_float, c_float, c_float, P, c_int, P],
     "lmsfc_pmf_to_quantized_cdf": [P, c_int, c_int, P],
     "lmsfc_pmf_rows_to_cdf": [P, c_int, P, P, c_int, c_int, P, c_int, P, P],
     "lmsfc_rans_encode": [P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, c_int64, P, P, P, c_int64, P, P],
     "lmsfc_rans_decode": [P, c_int64, P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, P, P],
+    "lmsfc_set_batch_invariant": [c_int],
     "lmsfc_gc_build_indexes": [P, c_int64, P, c_int, c_float, P, P],
 }
 EXPORTS = ["lmsfc_last_error", "lmsfc_version", "lmsfc_launch_count", "lmsfc_rans_lane_cap"] + list(_SIGS)
@@ -96,6 +97,18 @@ def _wrap(name, argtypes):
 
 for _n, _a in _SIGS.items():
     globals()[_n[len("lmsfc_"):]] = _wrap(_n, _a)
+
+
+class batch_invariant:
+    """Context manager around lmsfc_set_batch_invariant (the entropy-coded path's h_s)."""
+
+    def __enter__(self):
+        set_batch_invariant(1)
+        return self
+
+    def __exit__(self, *a):
+        set_batch_invariant(0)
+        return False
 
 
 def ptr(t):

@@ -18,6 +18,11 @@ extern "C" const char* lmsfc_last_error(void) { return lmsfc::get_error(); }
 extern "C" int lmsfc_version(void) { return 100; }
 extern "C" uint64_t lmsfc_launch_count(void) { return lmsfc::g_launch_count; }
 
+extern "C" int lmsfc_set_batch_invariant(int on) {
+  lmsfc::set_batch_invariant(on != 0);
+  return LMSFC_OK;
+}
+
 // ---------------------------------------------------------------- tap tables
 static void taps_regular(int k, int pad, int* ntaps, int8_t* dy, int8_t* dx, int16_t* widx) {
   int n = 0;
@@ -331,24 +336,29 @@ extern "C" int lmsfc_cast_bf16_f32(const void* in, float* out, int64_t n, void* 
 extern "C" int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C, int HW, void* stream) {
   return nchw_to_nhwc_bf16(in, (bf16*)out, B, C, HW, ST(stream));
 }
-extern "C" int lmsfc_sumsq(const float* g, int64_t n, float* accum, void* stream) { return sumsq_f32(g, n, accum, ST(stream)); }
+extern "C" int lmsfc_sumsq(const float* g, int64_t n, float* accum, int* set_flag, void* stream) {
+  return sumsq_f32(g, n, accum, set_flag, ST(stream));
+}
 extern "C" int lmsfc_adam_step(float* p, float* m, float* v, const float* g, void* p_bf16, int64_t n, float lr, float beta1,
                                float beta2, float eps, float max_norm, const float* sumsq, int* step, float* scratch,
                                void* stream) {
   LMSFC_CHECK_ARG(n == 0 || (p && m && v && g && step && scratch), "adam_step: null operand");
-  AdamArgs a{p, m, v, const_cast<float*>(g), (bf16*)p_bf16, n, lr, beta1, beta2, eps, max_norm, sumsq, step, scratch, 0};
+  AdamArgs a{p, m, v, const_cast<float*>(g), (bf16*)p_bf16, n, lr, beta1, beta2, eps, max_norm, sumsq, step, scratch, 0,
+             nullptr, nullptr, 0, nullptr};
   return adam_step(a, ST(stream));
 }
-extern "C" int lmsfc_adam_prep(float beta1, float beta2, float max_norm, const float* sumsq, int* step, float* scratch,
-                               void* stream) {
+extern "C" int lmsfc_adam_prep(float lr, const float* lr_dev, float beta1, float beta2, float max_norm, const float* sumsq,
+                               int* step, float* scratch, int* pending, int force, const float* gate, void* stream) {
   LMSFC_CHECK_ARG(step && scratch, "adam_prep: null operand");
-  AdamArgs a{nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0.f, beta1, beta2, 0.f, max_norm, sumsq, step, scratch, 0};
+  AdamArgs a{nullptr, nullptr, nullptr, nullptr, nullptr, 0, lr, beta1, beta2, 0.f, max_norm, sumsq, step, scratch, 0,
+             lr_dev, pending, force, gate};
   return adam_prep(a, ST(stream));
 }
-extern "C" int lmsfc_adam_update(float* p, float* m, float* v, float* g, void* p_bf16, int64_t n, float lr, float beta1,
-                                 float beta2, float eps, const float* scratch, int zero_g, void* stream) {
+extern "C" int lmsfc_adam_update(float* p, float* m, float* v, float* g, void* p_bf16, int64_t n, float beta1, float beta2,
+                                 float eps, const float* scratch, int zero_g, void* stream) {
   LMSFC_CHECK_ARG(n == 0 || (p && m && v && g && scratch), "adam_update: null operand");
-  AdamArgs a{p, m, v, g, (bf16*)p_bf16, n, lr, beta1, beta2, eps, 0.f, nullptr, nullptr, const_cast<float*>(scratch), zero_g};
+  AdamArgs a{p, m, v, g, (bf16*)p_bf16, n, 0.f, beta1, beta2, eps, 0.f, nullptr, nullptr, const_cast<float*>(scratch), zero_g,
+             nullptr, nullptr, 0, nullptr};
   return adam_update(a, ST(stream));
 }
 extern "C" int lmsfc_pmf_to_quantized_cdf(const float* pmf_host, int n, int precision, uint32_t* cdf_host) {

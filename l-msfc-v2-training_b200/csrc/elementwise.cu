@@ -5,6 +5,8 @@
 //   GDN helper passes (x^2, t, beta gradient)  compressai/layers/gdn.py:77-92
 //   NonNegativeParametrizer fwd/bwd            compressai/ops/parametrizers.py:38-64
 //   clip_grad_norm_ + Adam                     compressai/examples/train.py:100-103
+#include <mutex>
+
 #include "kernels.cuh"
 
 namespace lmsfc {
@@ -191,28 +193,46 @@ __device__ __forceinline__ void colsum_finish(const float (&acc)[8], int c8, int
 }
 
 // One scratch slot per CUDA stream: kernels of one stream serialise, kernels of different streams (the
-// weight-gradient side stream, the hyperprior side stream) may overlap and must not share partial sums.
-constexpr int kRedBlocksY = 296, kRedMaxC = 2048, kRedSlots = 16;
+// weight-gradient side streams, the hyperprior side stream) may overlap and must not share partial sums.
+// The table is guarded by a mutex (the autograd worker thread and the main thread both launch); when every slot
+// is taken, the least recently used one is handed over -- its counters reset themselves after every launch, so a
+// slot whose stream is idle is reusable, and 64 slots cover torch's whole stream pool (32 handles per priority).
+// All slots are allocated up front: cudaMalloc is not allowed while a stream is being captured.
+constexpr int kRedBlocksY = 296, kRedMaxC = 1024, kRedSlots = 64;
 float* g_red_scratch = nullptr;
 unsigned int* g_red_count = nullptr;
 cudaStream_t g_red_streams[kRedSlots];
+unsigned long long g_red_stamp[kRedSlots];
+unsigned long long g_red_clock = 0;
 int g_red_nstreams = 0;
+std::mutex g_red_mutex;
 int ensure_reduce_scratch() {
+  std::lock_guard<std::mutex> lock(g_red_mutex);
   if (g_red_scratch) return LMSFC_OK;
-  LMSFC_CUDA(cudaMalloc(&g_red_scratch, sizeof(float) * kRedSlots * kRedBlocksY * kRedMaxC));
+  float* scratch = nullptr;
+  LMSFC_CUDA(cudaMalloc(&scratch, sizeof(float) * kRedSlots * kRedBlocksY * kRedMaxC));
   LMSFC_CUDA(cudaMalloc(&g_red_count, sizeof(unsigned int) * kRedSlots * 64));
   LMSFC_CUDA(cudaMemset(g_red_count, 0, sizeof(unsigned int) * kRedSlots * 64));
   LMSFC_CUDA(cudaDeviceSynchronize());
+  g_red_scratch = scratch;
   return LMSFC_OK;
 }
 int red_slot(cudaStream_t s) {
+  std::lock_guard<std::mutex> lock(g_red_mutex);
+  ++g_red_clock;
   for (int i = 0; i < g_red_nstreams; ++i)
-    if (g_red_streams[i] == s) return i;
+    if (g_red_streams[i] == s) { g_red_stamp[i] = g_red_clock; return i; }
+  int slot = g_red_nstreams;
   if (g_red_nstreams < kRedSlots) {
-    g_red_streams[g_red_nstreams] = s;
-    return g_red_nstreams++;
+    ++g_red_nstreams;
+  } else {
+    slot = 0;
+    for (int i = 1; i < kRedSlots; ++i)
+      if (g_red_stamp[i] < g_red_stamp[slot]) slot = i;
   }
-  return (int)(((uintptr_t)s >> 4) % kRedSlots);
+  g_red_streams[slot] = s;
+  g_red_stamp[slot] = g_red_clock;
+  return slot;
 }
 float* red_scratch(cudaStream_t s) { return g_red_scratch + (size_t)red_slot(s) * kRedBlocksY * kRedMaxC; }
 unsigned int* red_count(cudaStream_t s) { return g_red_count + red_slot(s) * 64; }

@@ -668,6 +668,12 @@ static int launch_fwd_t(const IgemmParams& p, dim3 grid, cudaStream_t stream) {
   return LMSFC_OK;
 }
 
+// Entropy-coded path: h_s(z_hat) indexes the Gaussian CDF tables through hard thresholds, so encoder and decoder must
+// compute it with the SAME fp32 summation order whatever the batch size or the GPU's occupancy.  In this mode every
+// output element is one CTA's sequential K loop (128-wide tiles, no split K): independent of M, B and the device.
+static thread_local int g_batch_invariant = 0;
+void set_batch_invariant(int on) { g_batch_invariant = on; }
+
 int launch_igemm(IgemmParams& p, cudaStream_t stream) {
   LMSFC_CHECK_ARG(p.N > 0 && p.N % 128 == 0, "igemm: N=%d must be a multiple of 128", p.N);
   LMSFC_CHECK_ARG(p.c0 % 64 == 0 && p.c1 % 64 == 0 && p.c0 > 0, "igemm: channels (%d,%d) must be multiples of 64",
@@ -697,9 +703,10 @@ int launch_igemm(IgemmParams& p, cudaStream_t stream) {
   double best = 1e30;
   static const int ks_opts[] = {1, 2, 4, 8};
   for (int cand_bn = 128; cand_bn <= 256; cand_bn += 128) {
-    if (p.N % cand_bn != 0) continue;
+    if (p.N % cand_bn != 0 || (g_batch_invariant && cand_bn != 128)) continue;
     const int64_t tiles = tiles128 * (p.N / cand_bn);
     for (int ks : ks_opts) {
+      if (ks > 1 && g_batch_invariant) continue;
       if (ks > 1) {
         if (cand_bn / ks < 16) continue;
         const int kb_per = ceil_div(min_taps * kc, ks);

@@ -99,6 +99,7 @@ inline void fast_div_magic(int d, uint32_t* mul, uint32_t* shr) {
 }
 
 int launch_igemm(IgemmParams& p, cudaStream_t stream);
+void set_batch_invariant(int on);   // thread-local: fixed tile width, no split K (see igemm.cu)
 int launch_wgrad(WgradParams& p, cudaStream_t stream);
 
 }  // namespace lmsfc

@@ -76,7 +76,7 @@ int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, i
 int cast_f32_bf16(const float* in, __nv_bfloat16* out, int64_t n, cudaStream_t s);
 int cast_bf16_f32(const __nv_bfloat16* in, float* out, int64_t n, cudaStream_t s);
 int nchw_to_nhwc_bf16(const float* in, __nv_bfloat16* out, int B, int C, int HW, cudaStream_t s);
-int sumsq_f32(const float* g, int64_t n, float* accum, cudaStream_t s);
+int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, cudaStream_t s);
 struct AdamArgs {
   float *p, *m, *v;
   float* g;                  // read; zeroed in the same pass when zero_g
@@ -85,8 +85,12 @@ struct AdamArgs {
   float lr, beta1, beta2, eps, max_norm;   // max_norm <= 0: no clipping
   const float* sumsq;        // device scalar with sum(g^2) (clip_grad_norm_); nullable
   int* step;                 // device step counter, incremented by the prep kernel
-  float* scratch;            // >= 4 floats: {clip_coef, bias_corr1, bias_corr2, grad_norm}
+  float* scratch;            // >= 8 floats: {clip_coef, bias_corr1, bias_corr2, grad_norm, lr, active, -, -}
   int zero_g;
+  const float* lr_dev;       // prep only, nullable: learning rate in device memory (overrides lr)
+  int* pending;              // prep only, nullable: "update pending" flag, consumed
+  int force;                 // prep only: apply regardless of the flag (and clear it)
+  const float* gate;         // prep only, nullable: another optimiser's scratch[5]
 };
 // reduction scratch shared by the two-stage reductions (elementwise.cu): one slot per stream, 296 x 2048 floats and 64
 // self-resetting counters each

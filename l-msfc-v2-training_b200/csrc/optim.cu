@@ -20,7 +20,7 @@ inline int grid1d(int64_t work_items) {
 // ranks holding the same (all-reduced) gradient compute bit-identical norms -> identical clip coefficients -> replicas
 // never drift apart (float atomics made the norm differ in the last bits from run to run and rank to rank).
 __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g, int64_t n4, const float* tail, int ntail,
-                                                    float* accum, float* partial, unsigned int* counter) {
+                                                    float* accum, float* partial, unsigned int* counter, int* set_flag) {
   pdl_sync();
   float local = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n4; i += (int64_t)gridDim.x * TPB) {
@@ -44,23 +44,41 @@ __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g
     float v = 0.f;
     for (int i = threadIdx.x; i < (int)gridDim.x; i += TPB) v += __ldcg(partial + i);   // fixed order per thread
     v = block_sum(v, red);                                                               // fixed tree
-    if (threadIdx.x == 0) *accum += v;
+    if (threadIdx.x == 0) {
+      *accum += v;
+      if (set_flag) *set_flag = 1;      // "an update is pending" (pipelined train step), consumed by adam_prep
+    }
   }
 }
-int sumsq_f32(const float* g, int64_t n, float* accum, cudaStream_t s) {
+int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
   LMSFC_CHECK_ARG(((uintptr_t)g & 15) == 0, "sumsq: pointer must be 16-byte aligned");
   if (int rc = ensure_reduce_scratch()) return rc;
   const int64_t n4 = n / 4;
   LMSFC_LAUNCH(sumsq_kernel, dim3(grid1d(n4 > 0 ? n4 : 1)), dim3(TPB), 0, s, (const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum,
-               red_scratch(s), red_count(s) + 63);
+               red_scratch(s), red_count(s) + 63, set_flag);
   return LMSFC_OK;
 }
 
 // ---------------------------------------------------------------- Adam
-// prep: one thread bumps the step counter and derives {clip_coef, bias_corr1, bias_corr2, norm}
+// prep: one thread bumps the step counter and derives {clip_coef, bias_corr1, bias_corr2, norm, lr, active}.
+// The learning rate is read from device memory when lr_dev is given, so a captured graph follows an LR schedule
+// (torch.optim.lr_scheduler writes param_groups[..]["lr"]; the host mirrors it into lr_dev between replays).
+// `pending` (nullable): consume the "an update is pending" flag -- when it is 0 nothing is applied (no step bump, the
+// element-wise pass returns at once): the replay that follows a flush() of the pipelined train step.  `gate`
+// (nullable): take "active" from another optimiser's scratch[5] instead (the aux optimiser follows the net one).
 __global__ void adam_prep_kernel(AdamArgs a) {
   pdl_sync();
+  float active = 1.f;
+  if (a.pending) {
+    active = (a.force || *a.pending != 0) ? 1.f : 0.f;     // force: an eager step applies its own backward pass
+    *a.pending = 0;
+  } else if (a.gate) {
+    active = *a.gate;
+  }
+  a.scratch[4] = a.lr_dev ? *a.lr_dev : a.lr;
+  a.scratch[5] = active;
+  if (active == 0.f) return;
   const int step = *a.step + 1;
   *a.step = step;
   float clip = 1.f, norm = 0.f;
@@ -92,8 +110,9 @@ __device__ __forceinline__ void adam_quad(const float4& g, float4& m, float4& v,
 }
 __global__ void __launch_bounds__(TPB, 4) adam_kernel(AdamArgs a) {
   pdl_sync();
+  if (a.scratch[5] == 0.f) return;        // no update pending (see adam_prep_kernel)
   const float clip = a.scratch[0], bc1 = a.scratch[1], bc2 = a.scratch[2];
-  const float step_size = a.lr / bc1, rs_bc2 = rsqrtf(bc2);
+  const float step_size = a.scratch[4] / bc1, rs_bc2 = rsqrtf(bc2);
   const int64_t n4 = a.n >> 2, stride = (int64_t)gridDim.x * TPB;
   float4* __restrict__ p4 = reinterpret_cast<float4*>(a.p);
   float4* __restrict__ m4 = reinterpret_cast<float4*>(a.m);

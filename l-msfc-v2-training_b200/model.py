@@ -72,7 +72,11 @@ class LMSFC(nn.Module):
         if hs is None:
             y, z, z2_hw = self.analysis(ps)
             z_hat, z_lik = self.entropy_bottleneck(z, noise=noise_z)
-            scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
+            if self.training:
+                scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
+            else:                  # eval: the bits compress() / decompress() compute (batch-invariant tiling)
+                with L.batch_invariant():
+                    scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
             y_hat, y_lik = self.gaussian_conditional(y, scales, noise=noise_y)
             x_hat = self.synthesis(getattr(y_hat, Fn._BF16_ATTR), level_hw)
         else:
@@ -196,7 +200,8 @@ class LMSFC(nn.Module):
             gc.coder_lanes = max(1, min(256, y[0].numel() // 1024))
         z_strings = eb.compress(z)
         z_hat = eb.decompress(z_strings, z.shape[-2:])
-        scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), mid_hw, y.shape[2:])
+        with L.batch_invariant():     # same bits whatever the batch: the decoder may see the frames one at a time
+            scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), mid_hw, y.shape[2:])
         indexes = gc.build_indexes(scales)
         y_strings = gc.compress(y, indexes)
         return {"strings": [y_strings, z_strings], "shape": tuple(z.shape[-2:]), "y_hw": tuple(y.shape[2:]),
@@ -210,7 +215,8 @@ class LMSFC(nn.Module):
         if getattr(self, "coder_lanes_auto", False):     # lane counts are read from the strings
             eb.coder_lanes = gc.coder_lanes = 0
         z_hat = eb.decompress(strings[1], shape)
-        scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), tuple(mid_hw), tuple(y_hw))
+        with L.batch_invariant():
+            scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), tuple(mid_hw), tuple(y_hw))
         indexes = gc.build_indexes(scales)
         y_hat = gc.decompress(strings[0], indexes, z_hat.dtype)
         x_hat = self.synthesis(Fn.nhwc(y_hat.contiguous(), Fn.BF16), [tuple(h) for h in level_hw])

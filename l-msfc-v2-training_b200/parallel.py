@@ -63,6 +63,29 @@ class BucketedGradReducer:
             if st is not None and hasattr(st, "grad_ready"):
                 st.grad_ready = self._on_ready
         self.eb_names = [n for n in names if ".entropy_bottleneck." in n or n.startswith("entropy_bottleneck.")]
+        self.sync_replicas()
+
+    def sync_replicas(self, optimizers=None):
+        """What DistributedDataParallel does at construction: every rank starts from rank 0's parameters (and, on
+        resume, optimiser state), whatever seed it built its model with.  The quantisation noise must NOT be shared:
+        nn.DataParallel (examples/train.py:275-276) draws independent U(-.5,.5) per sample, so the rank is folded into
+        the Philox key -- identical weights, distinct noise streams."""
+        if self.world == 1 or not dist.is_initialized():
+            return
+        rank = dist.get_rank(self.pg)
+        bufs = [b for b in (getattr(self.arena, "net_params", None), getattr(self.arena, "aux_params", None)) if b is not None]
+        for opt in (optimizers or {}).values():
+            bufs += [opt.m, opt.v, opt.step_count]
+        for b in bufs:
+            dist.broadcast(b, src=dist.get_global_rank(self.pg, 0) if self.pg is not None else 0, group=self.pg)
+        if self.grads.is_cuda:
+            self.arena.refresh_shadows(cast=True)
+            rng = self.model.entropy_bottleneck._rng(self.grads.device)
+            if not getattr(rng, "_rank_folded", False):
+                seed = (rng.seed + rank * 0x9E3779B97F4A7C15) & 0x7FFFFFFFFFFFFFFF
+                rng.state[0] = seed
+                rng.seed = seed
+                rng._rank_folded = True
 
     # called at the start of every step (before backward)
     def begin(self):

@@ -38,7 +38,15 @@ class TrainStep:
         self.criterion = RateDistortionLoss(lmbda=lmbda, spec=model.spec)
         self.opt = net_aux_optimizer(model, {"net": {"type": "Adam", "lr": lr}, "aux": {"type": "Adam", "lr": aux_lr}},
                                      clip_max_norm=clip_max_norm)
+        # pipelined order: "the gradients of the last backward pass still await their update", kept on the device
+        # (raised by the gradient-norm kernel, consumed by the update's prep kernel) so that a captured replay after
+        # flush() applies nothing; the aux optimiser follows the net optimiser's decision
+        self.pending_flag = torch.zeros(1, dtype=torch.int32, device=self.arena.device)
+        self.opt["net"].pending_flag = self.pending_flag
+        self.opt["aux"].gate = self.opt["net"]
         self.reducer = BucketedGradReducer(model, bucket_mb=bucket_mb) if distributed else None
+        if self.reducer is not None:
+            self.reducer.sync_replicas(self.opt)     # replicas start from rank 0's weights, with distinct noise streams
         if side_streams:
             Fn.SideStreams.enable(self.arena.device)
         self.graph = None
@@ -97,7 +105,7 @@ class TrainStep:
             os_.wait_stream(main)
         arena.gates = {}
         with ctx:
-            net.prep()
+            net.prep(use_pending=True)
             for i, (lo, hi, gate) in enumerate(self._slices()):
                 net.update(lo, hi, zero_grad=True)
                 if i == 0:
@@ -110,7 +118,8 @@ class TrainStep:
             aux_opt.zero_grad()
             aux = model.aux_loss()
             aux.backward()
-            aux_opt.step()
+            aux_opt.prep(use_pending=True)
+            aux_opt.update(0, aux_opt.flat_params.numel())
         if os_ is not None:
             main.wait_event(arena.gates.pop("start"))          # the later gates are waited on inside model.forward
         self.pending = False
@@ -149,13 +158,25 @@ class TrainStep:
             self.arena.gates = {}
 
     # ------------------------------------------------------------------ CUDA graph
-    def capture(self, feats, warmup=2, pipelined=False, n_buffers=1):
+    def capture(self, feats, warmup=2, pipelined=False, n_buffers=1, resume=False):
         """Record one iteration.  `feats` fixes the shapes; its values are copied into static
         input buffers on every replay.  pipelined: see the module docstring (call flush() at the end).
         n_buffers > 1 records the same iteration once per input buffer (`input_buffers(k)`, `replay(buffer=k)`):
-        a loader copies host features straight into buffer k+1 while the step on buffer k runs -- no staging copy."""
+        a loader copies host features straight into buffer k+1 while the step on buffer k runs -- no staging copy.
+        The eager warm-up iterations before the capture TRAIN (they are real steps); resume=True (after
+        load_state_dict) restores weights, optimiser state and the noise counter afterwards, so the first replay
+        continues the saved run exactly."""
         lv = self.model.spec.levels
         dev = self.arena.device
+        snap = None
+        if resume:
+            self.flush()
+            rng = self.model.entropy_bottleneck._rng(dev)
+            keep = [self.arena.net_params, self.arena.aux_params, rng.state]
+            for o in self.opt.values():
+                keep += [o.m, o.v, o.step_count]
+            snap = [(t, t.clone()) for t in keep]
+            warmup = max(1, int(warmup))         # at least one eager pass: lazy one-time initialisation cannot be captured
         self.static_ins = [{k: Fn.nhwc(feats[k], Fn.BF16).clone(memory_format=torch.channels_last) for k in lv}
                            for _ in range(max(1, int(n_buffers)))]
         self.static_in = self.static_ins[0]
@@ -169,6 +190,15 @@ class TrainStep:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.pipelined = bool(pipelined)
+        if snap is not None:                     # undo the warm-up's training; nothing is pending
+            with torch.no_grad():
+                for t, saved in snap:
+                    t.copy_(saved)
+            self.arena.zero_grad()
+            self.pending_flag.zero_()
+            self.pending = False
+            self.arena.refresh_shadows(cast=True)
+            torch.cuda.synchronize()
         # the critical path (forward / data-gradient chain) is captured on a high-priority stream: its CTAs are
         # dispatched before those of the weight-gradient / optimiser / hyper / head streams whenever SMs free up
         cap = torch.cuda.Stream(device=dev, priority=-1)
@@ -184,6 +214,8 @@ class TrainStep:
             self.graphs.append(g)
             self.static_outs.append(out)
         self.graph, self.static_out = self.graphs[0], self.static_outs[0]
+        if snap is not None:
+            self.pending = False                 # the capture recorded, not ran, a backward pass
         return self
 
     def release(self):
@@ -207,8 +239,32 @@ class TrainStep:
                 src = feats[k]
                 if src.data_ptr() != buf.data_ptr():
                     buf.copy_(src, non_blocking=True)
+        for o in self.opt.values():
+            o.sync_lr()                          # an LR scheduler may have written param_groups[..]["lr"]
         self.graphs[buffer].replay()
+        if self.pipelined:
+            self.pending = True                  # the replay's backward pass awaits its update (flush())
         return self.static_outs[buffer]
+
+    # ------------------------------------------------------------------ checkpoint / resume (examples/train.py:283-321)
+    def state_dict(self):
+        """Everything the step keeps besides the model's own state_dict: both optimisers (Adam moments, step counters,
+        learning rates) and the device-side noise counter.  A pending pipelined update is applied first."""
+        self.flush()
+        rng = self.model.entropy_bottleneck._rng(self.arena.device)
+        return {"optimizer": self.opt["net"].state_dict(), "aux_optimizer": self.opt["aux"].state_dict(),
+                "rng_state": rng.state.clone(), "lmbda": self.criterion.lmbda}
+
+    def load_state_dict(self, sd):
+        """Restore after `model.load_state_dict(...)`; the next step continues the saved run."""
+        self.flush()
+        self.opt["net"].load_state_dict(sd["optimizer"])
+        self.opt["aux"].load_state_dict(sd["aux_optimizer"])
+        rng = self.model.entropy_bottleneck._rng(self.arena.device)
+        rng.state.copy_(sd["rng_state"])
+        self.pending_flag.zero_()
+        self.pending = False
+        self.model.refresh_shadows()
 
 
 class _Null:

@@ -71,8 +71,13 @@ def _worker(rank, world, port, q):
         par = importlib.import_module(PKG + ".parallel")
         net = _Net()
         net.arena = _FakeArena(net)
+        # replicas built from different seeds: construction must leave every rank with rank 0's parameters
+        # (what DistributedDataParallel does; the reference's nn.DataParallel replicates from GPU 0 every step)
+        net.arena.net_params = torch.full((64,), float(rank + 1))
+        net.arena.aux_params = torch.full((12,), float(10 * rank + 5))
         red = par.BucketedGradReducer(net, bucket_mb=2048 * 4 / (1 << 20))      # 2048-float buckets
         ar = net.arena
+        assert torch.all(ar.net_params == 1.0) and torch.all(ar.aux_params == 5.0)
         # buckets tile the arena, back to front, without gaps
         spans = sorted((b["lo"], b["hi"]) for b in red.buckets)
         assert spans[0][0] == 0 and spans[-1][1] == ar.net_grads.numel()

@@ -91,6 +91,25 @@ def test_interleaved_lanes_round_trip(tmp_path, lanes):
         assert torch.equal(dec["data"][k], out["x_hat"][k].float()), k
 
 
+def test_frames_encoded_together_decode_one_at_a_time():
+    """h_s(z_hat) picks the CDF rows through hard thresholds; its bits must not depend on the batch it was
+    computed in (tile width / split-K choices follow the tile count).  Encode 4 frames in one call, decode each alone."""
+    model_m = importlib.import_module(PKG + ".model")
+    torch.manual_seed(0)
+    net = model_m.LMSFC().cuda().eval()
+    net.update(force=True)
+    feats = _features(4, 40, 56, "cuda")
+    with torch.no_grad():
+        enc = net.compress(feats)
+        whole = net.decompress(enc["strings"], enc["shape"], enc["y_hw"], enc["mid_hw"], enc["level_hw"])
+        for i in range(4):
+            one = net.decompress([[enc["strings"][0][i]], [enc["strings"][1][i]]], enc["shape"], enc["y_hw"], enc["mid_hw"],
+                                 enc["level_hw"])
+            for k in net.spec.levels:
+                a, b = one["x_hat"][k].float(), whole["x_hat"][k][i:i + 1].float()
+                assert float((a - b).abs().max()) <= 2e-2 * float(b.abs().max()), k      # g_s itself may tile differently
+
+
 def test_codec_refuses_cpu_device():
     codec_m = importlib.import_module(PKG + ".codec")
     with pytest.raises(RuntimeError, match="no CPU fallback"):

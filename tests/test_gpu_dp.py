@@ -42,10 +42,15 @@ def _worker(rank, world, port, out):
     sl = slice(rank * B, (rank + 1) * B)
     feats = {k: v[sl].to(dev) for k, v in feats_all.items()}
 
-    # ---- eager DP, injected noise
-    torch.manual_seed(21)
+    # ---- eager DP, injected noise.  The ranks build their replicas from DIFFERENT seeds: construction must leave every
+    # rank with rank 0's weights (the reducer used to rely on identical seeding)
+    torch.manual_seed(21 + 5 * rank)
     net = model_m.LMSFC(spec).to(dev)
     ts = train_m.TrainStep(net, lmbda=0.013, distributed=True)
+    start = net.arena.net_params.clone()
+    dist.broadcast(start, src=0)
+    out[f"start_equal_{rank}"] = bool(torch.equal(start, net.arena.net_params))
+    out[f"noise_seed_{rank}"] = int(net.entropy_bottleneck._rng(dev).state[0])
     for _ in range(2):
         ts.step(feats, nz_all[sl].to(dev), ny_all[sl].to(dev))
     torch.cuda.synchronize()
@@ -107,6 +112,8 @@ def test_dp_two_gpus_matches_single_process_and_ranks_agree():
     # where the gradient is ~0)
     assert res["eager_step_rel"] < 0.1, res
     assert res["graph_equal_0"] and res["graph_equal_1"], res
+    assert res["start_equal_0"] and res["start_equal_1"], res
+    assert res["noise_seed_0"] != res["noise_seed_1"], res      # independent quantisation noise per replica
     l0, l1 = res["losses_0"], res["losses_1"]
     assert all(l == l and l < 1e6 for l in l0 + l1)
     assert l0[-1] < l0[0] * 1.5 and len(set(l0)) > 3
