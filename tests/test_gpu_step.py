@@ -24,7 +24,11 @@ def _oracle_in_true_fp32():
     torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
 
 
-COS_MIN, RELL2_MAX = 0.98, 0.2       # per parameter tensor: cosine with / relative L2 distance from the fp32 gradient
+# per parameter tensor: cosine with / relative L2 distance from the fp32 gradient.  Measured on a B200 (profiles/
+# r2_parity_bench_configs.txt): the worst tensors are always the hyper-analysis ones (|g| ~1e-4 of the total norm; the
+# ReLU / |y| kinks flip between bf16 and fp32 activations) at relL2 0.06-0.10; everything outside h_a / h_s stays
+# below 0.02
+COS_MIN, RELL2_MAX, RELL2_MAX_MAIN = 0.99, 0.15, 0.06
 
 
 def _mods():
@@ -106,6 +110,10 @@ def test_forward_loss_and_gradients(B, H2, W2):
     assert cos > 0.9999 and abs(na ** 0.5 / nb ** 0.5 - 1) < 1e-2
     assert rows[0][0] > COS_MIN, rows[0]
     assert worst[0][2] < RELL2_MAX, worst[0]
+    main = [r for r in sorted(rows, key=lambda r: -r[2]) if not r[1].startswith(("h_a.", "h_s."))]
+    for r in main[:3]:
+        print("  largest relL2 outside the hyper nets  %.3e  %-34s cosine %.5f  |g| %.3e" % (r[2], r[1], r[0], r[3]))
+    assert main[0][2] < RELL2_MAX_MAIN, main[0]
 
 
 def test_train_steps_track_the_oracle():
