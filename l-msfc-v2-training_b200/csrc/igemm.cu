@@ -36,6 +36,9 @@ struct FwdCfg {
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int STAGES = (BLOCK_N == 256) ? 4 : 6;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  // fused GDN: one 32 rows x (64 + 16) B staging block per warp behind the barriers (x leaves through it in phase 1)
+  static constexpr int XS_ROW = 80, XS_WARP = 32 * XS_ROW;
+  static constexpr int SMEM_BYTES_FUSED = SMEM_BYTES + 8 * XS_WARP;
 };
 
 __device__ __forceinline__ int fast_div(int n, uint32_t mul, uint32_t shr) {   // n / d, d's magic from fast_div_magic
@@ -76,13 +79,14 @@ __device__ __forceinline__ float pick(const uint32_t (&r)[H], int j) {
 
 // GDN forward / backward maths on W channels of one pixel; xr / gr / rr = x, grad_out, rsqrt(norm) as packed bf16
 template <int W>
-__device__ __forceinline__ void gdn_math(const IgemmParams& p, float (&v)[W], const uint32_t (&xr)[W / 2],
-                                         const uint32_t (&gr)[W / 2], const uint32_t (&rr)[W / 2], float (&rn)[W], int nb) {
+__device__ __forceinline__ void gdn_math(const IgemmParams& p, int epi, const float* __restrict__ beta_ptr, float (&v)[W],
+                                         const uint32_t (&xr)[W / 2], const uint32_t (&gr)[W / 2],
+                                         const uint32_t (&rr)[W / 2], float (&rn)[W], int nb) {
   // norm >= beta_min > 0 and rn is a bf16 value: the approximate rsqrt / reciprocal (2 ulp) lose nothing here,
   // while the IEEE division of the inverse backward was a call per element
-  if (p.epi == EPI_GDN) {
+  if (epi == EPI_GDN) {
     float beta[W];
-    load_f32<W>(p.bias + nb, beta);
+    load_f32<W>(beta_ptr + nb, beta);
 #pragma unroll
     for (int j = 0; j < W; ++j) {
       const float nrm = v[j] + beta[j];
@@ -166,7 +170,7 @@ __device__ __forceinline__ void epilogue_chunk(const IgemmParams& p, float (&v)[
       load_bf16<W>(p.aux_rn + o, rr);
     }
     float rn[W];
-    gdn_math<W>(p, v, xr, gr, rr, rn, nb);
+    gdn_math<W>(p, p.epi, p.bias, v, xr, gr, rr, rn, nb);
     if (p.epi == EPI_GDN && p.out_rn) store_bf16<W>(p.out_rn + o, rn);
   }
   if (p.out_bf16) store_bf16<W>(p.out_bf16 + o, v);
@@ -210,16 +214,20 @@ __device__ __forceinline__ unsigned long long gtimer() {
 
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-template <int BLOCK_N, bool B_MN>
+template <int BLOCK_N, bool B_MN, bool FUSE>
 __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_constant__ IgemmParams p) {
+  static_assert(!FUSE || BLOCK_N == 256, "the fused GDN needs all 256 channels of a pixel in one CTA");
   using Cfg = FwdCfg<BLOCK_N>;
   constexpr int STAGES = Cfg::STAGES;
+  constexpr int TMEM_COLS = FUSE ? 512 : BLOCK_N;      // fused: accumulator 0 (conv / dgrad) and 1 (GDN contraction)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = (uint64_t*)(smem + STAGES * Cfg::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;
-  uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+  uint64_t* tmem_full2_bar = tmem_full_bar + 1;        // FUSE: the GDN contraction has retired
+  uint64_t* stage_free_bar = tmem_full_bar + 2;        // FUSE (backward): phase-1 staging inside the B slots is released
+  uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 3);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) TL(0);
@@ -270,14 +278,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
 
   if (warp == 4 && lane == 0) {
     tma_prefetch_desc(&p.tmapB);
+    if (FUSE && p.fuse) tma_prefetch_desc(&p.tmapG);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], NUM_GATHER_THREADS + 1);
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(tmem_full_bar, 1);
+    if (FUSE) {
+      mbar_init(tmem_full2_bar, 1);
+      mbar_init(stage_free_bar, NUM_THREADS);
+    }
     fence_barrier_init();
   }
-  if (warp == 5) tmem_alloc<BLOCK_N>(tmem_slot);
+  if (warp == 5) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -291,6 +304,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   if (tid == 0) TL(1);
 
   const uint32_t trow = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+  const bool fused = FUSE && p.fuse != 0;
+  int ring_stage = 0, ring_phase = 0;    // FUSE: where the TMA / MMA thread's ring stands after the main loop
 
   if (warp < 4) {
     // ================= activation gather (producer) =================
@@ -390,6 +405,25 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
         if (++kc == kc_per_tap) { kc = 0; ++tap; }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
+      if (fused) {
+        // gamma_eff follows the weights through the same ring: 4 K blocks of 64 channels into the B slots.  Backward
+        // (fuse 2) defers blocks 2 and 3: their B slots stage the aux tiles of phase 1 first.
+        const int early = p.fuse == 1 ? 4 : 2;
+        for (int i = 0; i < early; ++i) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::B_STAGE_BYTES);
+          const uint32_t sb = smem_base + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES;
+          if (p.fuse == 1) {
+            tma_load_2d(&p.tmapG, &full_bar[stage], sb, i * BLOCK_K, 0);
+          } else {
+#pragma unroll
+            for (int seg = 0; seg < BLOCK_N / 64; ++seg)
+              tma_load_2d(&p.tmapG, &full_bar[stage], sb + seg * (BLOCK_K * 128), 64 * seg, i * BLOCK_K);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        ring_stage = stage; ring_phase = phase;
+      }
     }
   } else if (warp == 5) {
     // ================= MMA issuer (one thread) =================
@@ -415,6 +449,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
       if (nkb > 0) umma_commit(tmem_full_bar);
+      ring_stage = stage; ring_phase = phase;
       TL(10);
     }
   }
@@ -437,13 +472,193 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
     constexpr int SLOT_B = BLOCK_M * ROWB, SLOT_F = BLOCK_M * ROWF, GROUP = 3 * SLOT_B + SLOT_F;
     static_assert(2 * GROUP <= Cfg::STAGES * Cfg::STAGE_BYTES, "staging slots");
     const int half = warp >> 2, wrow0 = (warp & 3) * 32;
-    const bool gdn_f = p.epi == EPI_GDN, gdn_b = p.epi == EPI_GDN_BWD;
+    const long long orow = ok ? (long long)obase : -1ll;      // element offset of this row (column n0), -1: not stored
+
+    if constexpr (FUSE) {
+      if (fused) {
+        // ================= fused GDN, phase 1: accumulator 0 -> second operand (x^2 | t) in the A slots =================
+        // Thread = one pixel row x the 128 channels of its warp's column half, in four 32-channel chunks.  Channels
+        // [64 i, 64 i + 64) are K block i of the contraction: its A tile is written by the four warps of column half
+        // i / 2 (128 threads = the gather threads' arrival count of full_bar), its B tile (gamma) arrives by TMA.
+        constexpr int XS_ROW = Cfg::XS_ROW, XS_WARP = Cfg::XS_WARP;
+        const bool fwd = p.fuse == 1;
+        // phase-1 staging: forward -- x on its way out, one 32 x 80 B block per warp behind the barriers;
+        // backward -- the aux tiles x, rn, addend (3 blocks per warp) inside the B slots of K blocks 2 / 3
+        const uint32_t xs_warp = fwd ? smem_base + STAGES * Cfg::STAGE_BYTES + 256 + (uint32_t)warp * XS_WARP
+                                     : smem_base + (uint32_t)((nkb + 2 + half) % STAGES) * Cfg::STAGE_BYTES + A_STAGE_BYTES +
+                                           (uint32_t)(warp & 3) * (3 * XS_WARP);
+        const uint32_t xs_row = xs_warp + (uint32_t)lane * XS_ROW;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          const int col = half * 128 + c * 32;
+          if (!fwd) {                    // aux rows of the warp's 32 pixels, 64 B each: 4 lanes per row, coalesced
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int rr = 8 * i + (lane >> 2);
+              const long long o = __shfl_sync(0xffffffffu, orow, rr);
+              if (o >= 0) {
+                const uint32_t d = xs_warp + (uint32_t)rr * XS_ROW + (lane & 3) * 16;
+                const long long g = o + col + (lane & 3) * 8;
+                cp_async16(d, p.aux_x + g, 16u);
+                cp_async16(d + XS_WARP, p.aux_rn + g, 16u);
+                if (p.aux_add) cp_async16(d + 2 * XS_WARP, p.aux_add + g, 16u);
+              }
+            }
+          }
+          uint32_t r[32];
+          tmem_ld32(trow + col, r);
+          tmem_ld_wait();
+          uint32_t a2[16];                // the second GEMM's operand for this row: x^2 (forward) | t (backward), bf16
+          if (fwd) {
+            float bv[32];
+            if (p.bias) {
+              load_f32<32>(p.bias + col, bv);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) bv[j] = 0.f;
+            }
+            uint32_t xb[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              xb[j] = pack_bf16(__uint_as_float(r[2 * j]) + bv[2 * j], __uint_as_float(r[2 * j + 1]) + bv[2 * j + 1]);
+              const float x0 = bf16_lo(xb[j]), x1 = bf16_hi(xb[j]);      // x^2 of the bf16 value every later reader sees
+              a2[j] = pack_bf16(x0 * x0, x1 * x1);
+            }
+            if (p.out_x) {               // x leaves as 64-byte row pieces through the warp's staging block
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(xs_row + 16 * j), "r"(xb[4 * j]),
+                             "r"(xb[4 * j + 1]), "r"(xb[4 * j + 2]), "r"(xb[4 * j + 3])
+                             : "memory");
+              __syncwarp();
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int rr = 8 * i + (lane >> 2);
+                const long long o = __shfl_sync(0xffffffffu, orow, rr);
+                if (o >= 0) {
+                  uint32_t q0, q1, q2, q3;
+                  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                               : "=r"(q0), "=r"(q1), "=r"(q2), "=r"(q3)
+                               : "r"(xs_warp + (uint32_t)rr * XS_ROW + (lane & 3) * 16));
+                  *reinterpret_cast<uint4*>(p.out_x + o + col + (lane & 3) * 8) = make_uint4(q0, q1, q2, q3);
+                }
+              }
+              __syncwarp();
+            }
+          } else {
+            cp_async_wait_all();
+            __syncwarp();
+            if (ok) {
+              uint32_t xr[16], rr16[16], ar[16];
+              load_bf16_smem32(xs_row, xr);
+              load_bf16_smem32(xs_row + XS_WARP, rr16);
+              if (p.aux_add) {
+                load_bf16_smem32(xs_row + 2 * XS_WARP, ar);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) ar[j] = 0u;
+              }
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                // gy = data gradient (+ the other consumer's), rounded to the bf16 value phase 2 recomputes
+                const uint32_t gb = pack_bf16(__uint_as_float(r[2 * j]) + bf16_lo(ar[j]), __uint_as_float(r[2 * j + 1]) + bf16_hi(ar[j]));
+                const float r0 = bf16_lo(rr16[j]), r1 = bf16_hi(rr16[j]);
+                const float f0 = p.inverse ? 0.5f * r0 : -0.5f * r0 * r0 * r0;
+                const float f1 = p.inverse ? 0.5f * r1 : -0.5f * r1 * r1 * r1;
+                a2[j] = pack_bf16(bf16_lo(gb) * bf16_lo(xr[j]) * f0, bf16_hi(gb) * bf16_hi(xr[j]) * f1);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) a2[j] = 0u;
+            }
+            __syncwarp();                // the staging blocks are refilled by the next chunk's loads
+          }
+          // this row's 64 bytes of K block kbg, SWIZZLE_128B K-major: 16-byte chunk q of row r sits at r*128 + ((q ^ (r & 7)) << 4)
+          const int kbg = col >> 6;
+          const uint32_t sA = smem_base + (uint32_t)((nkb + kbg) % STAGES) * Cfg::STAGE_BYTES;
+          {
+            const uint32_t arow = sA + (uint32_t)row * 128;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int q = (c & 1) * 4 + j;
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(arow + (uint32_t)((q ^ (row & 7)) << 4)),
+                           "r"(a2[4 * j]), "r"(a2[4 * j + 1]), "r"(a2[4 * j + 2]), "r"(a2[4 * j + 3])
+                           : "memory");
+            }
+          }
+          if (c & 1) {
+            fence_proxy_async_smem();    // generic-proxy stores -> visible to the tensor core's async proxy
+            mbar_arrive(&full_bar[(nkb + kbg) % STAGES]);
+            if (p.out_t) {               // x^2 / t also leave for HBM (gamma's gradient reads them): straight from the A slot
+              __syncwarp();              // the warp's own 32 rows of this K block are complete
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const int rr = 4 * i + (lane >> 3), q = lane & 7, R = wrow0 + rr;
+                const long long o = __shfl_sync(0xffffffffu, orow, rr);
+                if (o >= 0) {
+                  uint32_t q0, q1, q2, q3;
+                  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                               : "=r"(q0), "=r"(q1), "=r"(q2), "=r"(q3)
+                               : "r"(sA + (uint32_t)R * 128 + (uint32_t)((q ^ (R & 7)) << 4)));
+                  *reinterpret_cast<uint4*>(p.out_t + o + kbg * 64 + q * 8) = make_uint4(q0, q1, q2, q3);
+                }
+              }
+            }
+          }
+        }
+        if (!fwd) {
+          fence_proxy_async_smem();      // staging reads (generic proxy) before the TMA writes of gamma blocks 2, 3
+          mbar_arrive(stage_free_bar);
+          if (warp == 4 && lane == 0) {
+            mbar_wait(stage_free_bar, 0);
+            int stage = ring_stage, phase = ring_phase;
+            for (int i = 2; i < 4; ++i) {
+              mbar_wait(&empty_bar[stage], phase ^ 1);
+              mbar_arrive_expect_tx(&full_bar[stage], Cfg::B_STAGE_BYTES);
+              const uint32_t sb = smem_base + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES;
+#pragma unroll
+              for (int seg = 0; seg < BLOCK_N / 64; ++seg)
+                tma_load_2d(&p.tmapG, &full_bar[stage], sb + seg * (BLOCK_K * 128), 64 * seg, i * BLOCK_K);
+              if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+        if (warp == 5 && lane == 0) {
+          // ---- the contraction: 4 K blocks x 4 MMAs into TMEM columns [256, 512)
+          const uint32_t idesc2 = make_idesc_bf16(BLOCK_M, BLOCK_N, 0, fwd ? 0 : 1);
+          int stage = ring_stage, phase = ring_phase;
+          for (int i = 0; i < 4; ++i) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+            const uint32_t sb = sa + A_STAGE_BYTES;
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k) {
+              const uint64_t ad = make_sdesc_sw128(sa + k * 32, 16, 1024);
+              const uint64_t bd = fwd ? make_sdesc_sw128(sb + k * 32, 16, 1024)
+                                      : make_sdesc_sw128(sb + k * 2048, BLOCK_K * 128, 1024);
+              umma_bf16(tmem_base + BLOCK_N, ad, bd, idesc2, (i | k) != 0);
+            }
+            umma_commit(&empty_bar[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+          umma_commit(tmem_full2_bar);
+        }
+        __syncwarp();
+        mbar_wait(tmem_full2_bar, 0);
+        tc_fence_after();
+        __syncthreads();                 // every warp's x^2 / t copy-out has left the A slots: phase 2 stages over them
+      }
+    }
+    // fused phase 2 == the GDN epilogues below with the GEMM result in accumulator 1 and x (forward) resp. grad_out
+    // (backward) recomputed from accumulator 0 instead of loaded
+    const bool gdn_f = fused ? p.fuse == 1 : p.epi == EPI_GDN, gdn_b = fused ? p.fuse == 2 : p.epi == EPI_GDN_BWD;
+    const uint32_t tacc = fused ? trow + BLOCK_N : trow;
     // per column half: bf16 slots 0..2 and one fp32 slot.  GDN forward {x -> y in place, rn}; GDN backward
     // {x -> grad_in in place, grad_out, rn}; conv {y, |y|, -, fp32}
     const uint32_t sgroup = smem_base + (uint32_t)half * GROUP;
     const uint32_t srow_b = sgroup + (uint32_t)row * ROWB, swarp_b = sgroup + (uint32_t)wrow0 * ROWB;
     const uint32_t srow_f = sgroup + 3 * SLOT_B + (uint32_t)row * ROWF, swarp_f = sgroup + 3 * SLOT_B + (uint32_t)wrow0 * ROWF;
-    const long long orow = ok ? (long long)obase : -1ll;      // element offset of this row (column n0), -1: not stored
     auto issue = [&](const __nv_bfloat16* src, int col, int slot) {   // 4 rows x 128 B per instruction
       const uint32_t sdst = swarp_b + (uint32_t)slot * SLOT_B + (lane & 7) * 16;
 #pragma unroll
@@ -468,10 +683,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
 #pragma unroll 1
     for (int ps = 0; ps < PASSES; ++ps) {
       const int col = half * HALF + ps * PW;                // first column of this pass inside the tile
-      if (gdn_f || gdn_b) {
+      if ((gdn_f && !fused) || gdn_b) {
         issue(p.aux_x, col, 0);
         if (gdn_b) {
-          issue(p.aux_gy, col, 1);
+          if (!fused) issue(p.aux_gy, col, 1);
+          else if (p.aux_add) issue(p.aux_add, col, 1);
           issue(p.aux_rn, col, 2);
         }
         cp_async_wait_all();
@@ -482,11 +698,18 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
       for (int cb = 0; cb < PW; cb += 32) {
         uint32_t r[32];
         if (nkb > 0) {                   // warp-uniform: tcgen05.ld is .sync.aligned
-          tmem_ld32(trow + col + cb, r);
+          tmem_ld32(tacc + col + cb, r);
           tmem_ld_wait();
         } else {
 #pragma unroll
           for (int j = 0; j < 32; ++j) r[j] = 0u;
+        }
+        uint32_t r0[FUSE ? 32 : 1];      // fused: accumulator 0 (x resp. grad_out before rounding)
+        if constexpr (FUSE) {
+          if (fused) {
+            tmem_ld32(trow + col + cb, r0);
+            tmem_ld_wait();
+          }
         }
         if (!ok) continue;               // rows past M / cropped outputs are never stored
         float v[32];
@@ -496,12 +719,43 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
         if (gdn_f || gdn_b) {
           uint32_t xr[16], gr[16], rr[16];
           float rn[32];
-          load_bf16_smem32(srow_b + coff, xr);
-          if (gdn_b) {
-            load_bf16_smem32(srow_b + SLOT_B + coff, gr);
-            load_bf16_smem32(srow_b + 2 * SLOT_B + coff, rr);
+          bool from_acc = false;
+          if constexpr (FUSE) {
+            if (fused && gdn_f) {        // x = bf16(acc0 + bias), exactly the value phase 1 stored and squared
+              float bv[32];
+              if (p.bias) {
+                load_f32<32>(p.bias + col + cb, bv);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) bv[j] = 0.f;
+              }
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                xr[j] = pack_bf16(__uint_as_float(r0[2 * j]) + bv[2 * j], __uint_as_float(r0[2 * j + 1]) + bv[2 * j + 1]);
+              from_acc = true;
+            }
           }
-          gdn_math<32>(p, v, xr, gr, rr, rn, n0 + col + cb);
+          if (!from_acc) load_bf16_smem32(srow_b + coff, xr);
+          if (gdn_b) {
+            load_bf16_smem32(srow_b + 2 * SLOT_B + coff, rr);
+            bool gy_from_acc = false;
+            if constexpr (FUSE) {
+              if (fused) {               // grad_out = bf16(acc0 + addend), as in phase 1
+                if (p.aux_add) {
+                  load_bf16_smem32(srow_b + SLOT_B + coff, gr);
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 16; ++j) gr[j] = 0u;
+                }
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                  gr[j] = pack_bf16(__uint_as_float(r0[2 * j]) + bf16_lo(gr[j]), __uint_as_float(r0[2 * j + 1]) + bf16_hi(gr[j]));
+                gy_from_acc = true;
+              }
+            }
+            if (!gy_from_acc) load_bf16_smem32(srow_b + SLOT_B + coff, gr);
+          }
+          gdn_math<32>(p, gdn_f ? EPI_GDN : EPI_GDN_BWD, fused ? p.beta : p.bias, v, xr, gr, rr, rn, n0 + col + cb);
           if (gdn_f && p.out_rn) stage_bf16_32(srow_b + SLOT_B + coff, rn);
           if (p.out_bf16) stage_bf16_32(srow_b + coff, v);
         } else {
@@ -612,7 +866,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
   __syncthreads();
   if (warp == 5) {
     tc_fence_after();
-    tmem_dealloc<BLOCK_N>(tmem_base);
+    tmem_dealloc<TMEM_COLS>(tmem_base);
   }
   if (tid == 0) TL(8);
 }

@@ -56,6 +56,23 @@ struct IgemmParams {
   const __nv_bfloat16* aux_x;   // EPI_GDN / EPI_GDN_BWD
   const __nv_bfloat16* aux_gy;  // EPI_GDN_BWD
   const __nv_bfloat16* aux_rn;  // EPI_GDN_BWD
+  // ---- GDN fused behind the GEMM that produces its input (FUSE kernels: BLOCK_N == N == 256, ksplit == 1).  The CTA
+  // owns all 256 channels of its 128 pixels, so after the main loop it forms the second operand (x^2 resp. t) from the
+  // accumulator in shared memory and runs the channel contraction as a second tcgen05 GEMM into the other 256 TMEM
+  // columns -- no x^2 / t round trip through HBM, no separate launch (layers/gdn.py:77-92 and its backward).
+  //   fuse 1 (behind conv/deconv forward):  x = acc0 + bias ; A2 = x^2 ; acc1 = A2 . gamma^T ; nrm = acc1 + beta ;
+  //                                         y = x * rsqrt(nrm) | x * sqrt(nrm) ; stores x, x^2, y, rn
+  //   fuse 2 (behind a data gradient):      gy = acc0 (+ aux_add) ; A2 = t = gy * x * (-rn^3/2 | rn/2) ; acc1 = A2 . gamma ;
+  //                                         gx = gy * (rn | 1/rn) + 2 x acc1 ; stores t, gx
+  int fuse;
+  int dry_run;                  // host only: launch_igemm just reports the tiling it would use (ksplit, dry_bn)
+  int dry_bn;
+  CUtensorMap tmapG;            // filled by launch_igemm: gamma_eff bf16 [C][C]; fuse 1 box {64 k, 256 n}, fuse 2 {64 n, 64 k}
+  const __nv_bfloat16* gamma;   // gamma_eff (host side: tensor-map source)
+  const float* beta;            // fuse 1: beta_eff [C]
+  __nv_bfloat16* out_x;         // fuse 1: the convolution's own output x (nullable)
+  __nv_bfloat16* out_t;         // fuse 1: x^2 (nullable, kept for gamma's gradient); fuse 2: t = dL/dnorm
+  const __nv_bfloat16* aux_add; // fuse 2: gradient w.r.t. y from its other consumer (nullable)
 };
 
 // Weight-gradient GEMM (K = pixels):
