@@ -57,6 +57,26 @@ int lmsfc_conv_dgrad(const lmsfc_conv_desc* d, const void* gout, const void* w, 
 int lmsfc_conv_wgrad(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* gout, float* gw,
                      float* gbias, void* stream);
 
+/* conv / deconv with the GDN / IGDN that follows it fused into the same kernel (models/utils.py:128-146 followed by
+ * layers/gdn.py:77-92): the CTA that owns all 256 channels of 128 pixels squares its own accumulator tile in shared
+ * memory and runs the channel contraction as a second tcgen05 GEMM -- x^2 never makes a round trip through HBM.
+ * Cout must be 256.  x_out (conv output, read by the backward pass), x2_out (x^2, read by gamma's gradient) and rn_out
+ * (rsqrt(norm)) are nullable (inference); y_out = x * rsqrt(beta' + gamma' . x^2) (inverse: * sqrt).
+ * lmsfc_conv_gdn_fusable: *fusable = 1 when the launch (forward, or with dgrad != 0 the data gradient w.r.t. the first
+ * n_in input channels) would use whole-K 256-wide tiles anyway, i.e. fusing costs no occupancy; callers fall back to
+ * the separate calls otherwise. */
+int lmsfc_conv_gdn_fusable(const lmsfc_conv_desc* d, int dgrad, int n_in, int* fusable);
+int lmsfc_conv_gdn_forward(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* w,
+                           const float* bias, const void* gamma_eff, const float* beta_eff, int inverse, void* x_out,
+                           void* x2_out, void* y_out, void* rn_out, void* stream);
+/* The backward counterpart: the data gradient of conv `d` w.r.t. its first n_in (= 256) input channels IS the gradient
+ * w.r.t. the output y of the GDN that produced them; the same kernel adds `addend` (the gradient from y's other
+ * consumer, nullable), forms t = dL/dnorm (stored to t_out for gamma's / beta's gradient, lmsfc_gdn_wgrad), contracts
+ * it with gamma and writes gx_out = the gradient w.r.t. the GDN's INPUT x.  x, rn: saved by the forward pass. */
+int lmsfc_conv_dgrad_gdn_backward(const lmsfc_conv_desc* d, const void* gout, const void* w, int n_in, const void* addend,
+                                  const void* x, const void* rn, const void* gamma_eff, int inverse, void* t_out,
+                                  void* gx_out, void* stream);
+
 /* ------------------------------------------------------------------ GDN / IGDN   (layers/gdn.py:77-92)
  * y = x * rsqrt(beta' + gamma' . x^2)  (inverse: * sqrt).  gamma_eff bf16 [C][C] ([out][in]) and
  * beta_eff fp32 [C] are the reparametrised values (lmsfc_reparam_forward).  rn = rsqrt(norm) is

@@ -30,6 +30,9 @@ _SIGS = {
     "lmsfc_conv_forward": [POINTER(ConvDesc), P, P, P, P, c_int, P, P, P, P],
     "lmsfc_conv_dgrad": [POINTER(ConvDesc), P, P, c_int, P, P],
     "lmsfc_conv_wgrad": [POINTER(ConvDesc), P, P, P, P, P, P],
+    "lmsfc_conv_gdn_fusable": [POINTER(ConvDesc), c_int, c_int, POINTER(c_int)],
+    "lmsfc_conv_gdn_forward": [POINTER(ConvDesc), P, P, P, P, P, P, c_int, P, P, P, P, P],
+    "lmsfc_conv_dgrad_gdn_backward": [POINTER(ConvDesc), P, P, c_int, P, P, P, P, c_int, P, P, P],
     "lmsfc_gdn_forward": [P, P, P, c_int, c_int64, c_int, P, P, P, P],
     "lmsfc_gdn_backward": [P, P, P, P, c_int, c_int64, c_int, P, c_int, P, P, P, P, P],
     "lmsfc_gdn_wgrad": [P, P, c_int64, c_int, P, P, P],
@@ -97,6 +100,20 @@ def _wrap(name, argtypes):
 
 for _n, _a in _SIGS.items():
     globals()[_n[len("lmsfc_"):]] = _wrap(_n, _a)
+
+
+_FUSABLE = {}
+
+
+def gdn_fusable(desc, dgrad=False, n_in=0):
+    """True when conv `desc` (forward, or its data gradient w.r.t. the first n_in channels) can carry a fused GDN."""
+    key = (tuple(getattr(desc, f) for f, _ in ConvDesc._fields_), bool(dgrad), int(n_in))
+    r = _FUSABLE.get(key)
+    if r is None:
+        out = c_int(0)
+        conv_gdn_fusable(desc, int(dgrad), int(n_in), ctypes.byref(out))
+        r = _FUSABLE[key] = bool(out.value)
+    return r
 
 
 class batch_invariant:

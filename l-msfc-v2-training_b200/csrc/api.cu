@@ -137,6 +137,74 @@ extern "C" int lmsfc_conv_dgrad(const lmsfc_conv_desc* d, const void* gout, cons
                      (const bf16*)w, cin, n_in, p, ST(stream));
 }
 
+// ---------------------------------------------------------------- conv / data gradient with the GDN fused behind it
+static int conv_fwd_params(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* w, IgemmParams& p,
+                           cudaStream_t st) {
+  if (d->kind == 0)
+    return run_regular((const bf16*)src0, (const bf16*)src1, d->c0, d->c1, d->B, d->Hin, d->Win, d->Hout, d->Wout, d->k,
+                       d->stride, (const bf16*)w, d->Cout, d->Cout, p, st);
+  LMSFC_CHECK_ARG(d->stride != 1, "deconv with stride 1 is not part of the L-MSFC path");
+  return run_transposed((const bf16*)src0, d->c0, d->B, d->Hin, d->Win, d->Hout, d->Wout, d->k, d->stride, (const bf16*)w,
+                        d->Cout, d->Cout, p, st);
+}
+static int conv_dgrad_params(const lmsfc_conv_desc* d, const void* gout, const void* w, int n_in, IgemmParams& p,
+                             cudaStream_t st) {
+  const int cin = d->c0 + d->c1;
+  if (d->kind == 0)
+    return run_transposed((const bf16*)gout, d->Cout, d->B, d->Hout, d->Wout, d->Hin, d->Win, d->k, d->stride,
+                          (const bf16*)w, cin, n_in, p, st);
+  return run_regular((const bf16*)gout, nullptr, d->Cout, 0, d->B, d->Hout, d->Wout, d->Hin, d->Win, d->k, d->stride,
+                     (const bf16*)w, cin, n_in, p, st);
+}
+
+extern "C" int lmsfc_conv_gdn_fusable(const lmsfc_conv_desc* d, int dgrad, int n_in, int* fusable) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  LMSFC_CHECK_ARG(fusable != nullptr, "conv_gdn_fusable: null result");
+  *fusable = 0;
+  const int N = dgrad ? n_in : d->Cout;
+  if (N != 256) return LMSFC_OK;
+  IgemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.dry_run = 1;
+  static bf16* dummy = nullptr;      // the dry run never dereferences its operands
+  rc = dgrad ? conv_dgrad_params(d, dummy, dummy, n_in, p, nullptr) : conv_fwd_params(d, dummy, dummy, dummy, p, nullptr);
+  if (rc) return rc;
+  *fusable = (p.dry_bn == 256 && p.ksplit == 1) ? 1 : 0;
+  return LMSFC_OK;
+}
+
+extern "C" int lmsfc_conv_gdn_forward(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* w,
+                                      const float* bias, const void* gamma_eff, const float* beta_eff, int inverse,
+                                      void* x_out, void* x2_out, void* y_out, void* rn_out, void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  LMSFC_CHECK_ARG(src0 && w && (d->c1 == 0 || src1) && gamma_eff && beta_eff && y_out, "conv_gdn_forward: null operand");
+  LMSFC_CHECK_ARG(d->Cout == 256, "conv_gdn_forward: the fused GDN needs 256 output channels, got %d", d->Cout);
+  IgemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.epi = EPI_BIAS; p.bias = bias; p.inverse = inverse;
+  p.fuse = 1; p.gamma = (const bf16*)gamma_eff; p.beta = beta_eff;
+  p.out_x = (bf16*)x_out; p.out_t = (bf16*)x2_out; p.out_bf16 = (bf16*)y_out; p.out_rn = (bf16*)rn_out;
+  return conv_fwd_params(d, src0, src1, w, p, ST(stream));
+}
+
+extern "C" int lmsfc_conv_dgrad_gdn_backward(const lmsfc_conv_desc* d, const void* gout, const void* w, int n_in,
+                                             const void* addend, const void* x, const void* rn, const void* gamma_eff,
+                                             int inverse, void* t_out, void* gx_out, void* stream) {
+  int rc = check_desc(d);
+  if (rc) return rc;
+  LMSFC_CHECK_ARG(gout && w && x && rn && gamma_eff && t_out && gx_out, "conv_dgrad_gdn_backward: null operand");
+  LMSFC_CHECK_ARG(n_in == 256 && n_in <= d->c0 + d->c1, "conv_dgrad_gdn_backward: the fused GDN needs n_in == 256, got %d", n_in);
+  IgemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.epi = EPI_BIAS; p.inverse = inverse;
+  p.fuse = 2; p.gamma = (const bf16*)gamma_eff;
+  p.aux_add = (const bf16*)addend; p.aux_x = (const bf16*)x; p.aux_rn = (const bf16*)rn;
+  p.out_t = (bf16*)t_out; p.out_bf16 = (bf16*)gx_out;
+  return conv_dgrad_params(d, gout, w, n_in, p, ST(stream));
+}
+
 extern "C" int lmsfc_conv_wgrad(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* gout, float* gw,
                                 float* gbias, void* stream) {
   int rc = check_desc(d);

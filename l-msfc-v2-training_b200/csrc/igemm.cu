@@ -885,7 +885,7 @@ static int max_active_clusters_t(int ks) {
   static int cache[9] = {0};
   if (cache[ks]) return cache[ks];
   using Cfg = FwdCfg<BLOCK_N>;
-  cudaFuncSetAttribute(igemm_fwd_kernel<BLOCK_N, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+  cudaFuncSetAttribute(igemm_fwd_kernel<BLOCK_N, B_MN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(1, 1, ks * 64);
   cfg.blockDim = dim3(NUM_THREADS);
@@ -895,7 +895,7 @@ static int max_active_clusters_t(int ks) {
   attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = (unsigned)ks;
   cfg.attrs = attr; cfg.numAttrs = 1;
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, igemm_fwd_kernel<BLOCK_N, B_MN>, &cfg) != cudaSuccess || n <= 0) {
+  if (cudaOccupancyMaxActiveClusters(&n, igemm_fwd_kernel<BLOCK_N, B_MN, false>, &cfg) != cudaSuccess || n <= 0) {
     cudaGetLastError();
     n = 148 / ks / 2;                      // conservative guess
   }
@@ -906,17 +906,17 @@ static int max_active_clusters(int bn, bool mn, int ks) {
   return mn ? max_active_clusters_t<128, true>(ks) : max_active_clusters_t<128, false>(ks);
 }
 
-template <int BLOCK_N, bool B_MN>
+template <int BLOCK_N, bool B_MN, bool FUSE>
 static int launch_fwd_t(const IgemmParams& p, dim3 grid, cudaStream_t stream) {
   using Cfg = FwdCfg<BLOCK_N>;
+  constexpr int SMEM = FUSE ? Cfg::SMEM_BYTES_FUSED : Cfg::SMEM_BYTES;
   static bool attr_done = false;
   if (!attr_done) {
-    LMSFC_CUDA(cudaFuncSetAttribute(igemm_fwd_kernel<BLOCK_N, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    Cfg::SMEM_BYTES));
+    LMSFC_CUDA(cudaFuncSetAttribute(igemm_fwd_kernel<BLOCK_N, B_MN, FUSE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     attr_done = true;
   }
   // the K slices of one output tile form a cluster along z
-  LMSFC_CUDA(launch_pdl(igemm_fwd_kernel<BLOCK_N, B_MN>, grid, dim3(NUM_THREADS), (size_t)Cfg::SMEM_BYTES, stream,
+  LMSFC_CUDA(launch_pdl(igemm_fwd_kernel<BLOCK_N, B_MN, FUSE>, grid, dim3(NUM_THREADS), (size_t)SMEM, stream,
                         (unsigned)p.ksplit, p));
   ++g_launch_count;
   return LMSFC_OK;
@@ -975,6 +975,21 @@ int launch_igemm(IgemmParams& p, cudaStream_t stream) {
       if (t < best) { best = t; bn = cand_bn; ksplit = ks; }
     }
   }
+  if (p.dry_run) {                       // the caller only asks which tiling the cost model picks (fusion decision)
+    p.ksplit = ksplit;
+    p.dry_bn = bn;
+    return LMSFC_OK;
+  }
+  if (p.fuse) {
+    // the fused GDN needs a CTA to own all 256 channels of its pixels and the whole K loop
+    LMSFC_CHECK_ARG(p.N == 256 && p.gamma && (p.fuse == 1 ? p.beta != nullptr : (p.aux_x && p.aux_rn && p.out_t)) && p.out_bf16,
+                    "igemm: fused GDN needs N == 256 (got %d) and its operands", p.N);
+    bn = 256;
+    ksplit = 1;
+    int rcg = p.fuse == 1 ? make_tmap_2d_bf16(&p.tmapG, p.gamma, 256, 256, 256, 256, 64)
+                          : make_tmap_2d_bf16(&p.tmapG, p.gamma, 256, 256, 256, 64, 64);
+    if (rcg) return rcg;
+  }
   dim3 grid(grid_x, p.N / bn, p.nphase * ksplit);
   p.ksplit = ksplit;
 #ifdef LMSFC_TIMELINE
@@ -983,8 +998,9 @@ int launch_igemm(IgemmParams& p, cudaStream_t stream) {
   int rc = make_tmap_2d_bf16(&p.tmapB, p.w, (uint64_t)p.w_rows, (uint64_t)p.w_cols, (uint64_t)p.w_cols,
                              p.w_mn ? 64 : bn, 64);
   if (rc) return rc;
-  if (p.w_mn) return bn == 256 ? launch_fwd_t<256, true>(p, grid, stream) : launch_fwd_t<128, true>(p, grid, stream);
-  return bn == 256 ? launch_fwd_t<256, false>(p, grid, stream) : launch_fwd_t<128, false>(p, grid, stream);
+  if (p.fuse) return p.w_mn ? launch_fwd_t<256, true, true>(p, grid, stream) : launch_fwd_t<256, false, true>(p, grid, stream);
+  if (p.w_mn) return bn == 256 ? launch_fwd_t<256, true, false>(p, grid, stream) : launch_fwd_t<128, true, false>(p, grid, stream);
+  return bn == 256 ? launch_fwd_t<256, false, false>(p, grid, stream) : launch_fwd_t<128, false, false>(p, grid, stream);
 }
 
 }  // namespace lmsfc
