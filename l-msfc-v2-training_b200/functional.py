@@ -169,12 +169,116 @@ class ConvState:
         self._version = v
 
 
+class GDNLink:
+    """What a GDN layer shares with the consumers of its output y during one forward / backward pass, so that the
+    consumer's data-gradient kernel can run the GDN's backward contraction in its own epilogue
+    (lmsfc_conv_dgrad_gdn_backward): the GDN's saved x, rn, gamma, and -- in backward -- the gradient of a second
+    ("side") consumer of y, which the main consumer's kernel adds before the contraction.
+
+    Protocol (all decided while the forward pass is recorded, so a captured graph replays it):
+      * the MAIN consumer's forward sets `main_fuses` (its dgrad launch is fusable: csrc/igemm.cu cost model);
+      * a SIDE consumer that runs after it and sees main_fuses defers: in backward it parks its data gradient in `addend`
+        (returning None to autograd) instead of letting autograd add the two gradients with a separate kernel;
+        a side consumer that ran BEFORE the main one registers `side_plain`, and the main consumer then does not fuse;
+      * autograd runs the later-recorded node first, so the model records main before side (model.LMSFC.synthesis).
+    """
+    __slots__ = ("x", "rn", "gamma_bf", "inverse", "main_fuses", "side_plain", "n_side", "addend", "addend_ev", "t",
+                 "fused_done")
+
+    def __init__(self, x, rn, gamma_bf, inverse):
+        self.x, self.rn, self.gamma_bf, self.inverse = x, rn, gamma_bf, bool(inverse)
+        self.main_fuses = None
+        self.side_plain = False
+        self.n_side = 0
+        self.addend = self.addend_ev = self.t = None
+        self.fused_done = False
+
+    def register_consumer(self, state, d, side):
+        """Called from the consumer's forward; returns the consumer's role: "main", "side" or None (plain)."""
+        if side:
+            if self.main_fuses:
+                self.n_side += 1
+                if self.n_side > 1:
+                    raise RuntimeError("GDNLink: one deferred side consumer per GDN output")
+                return "side"
+            self.side_plain = True
+            return None
+        if self.main_fuses is not None:
+            raise RuntimeError("GDNLink: a GDN output has one main consumer")
+        self.main_fuses = (not self.side_plain and state.c0 == self.x.shape[1] == 256
+                           and L.gdn_fusable(d, dgrad=True, n_in=state.c0))
+        return "main" if self.main_fuses else None
+
+
+def _conv_backward(state, shape, x0, x1, g, weight, bias, need_dx, link, role):
+    """Data gradient (critical path) then weight / bias gradients (side stream) of one conv / deconv.
+    With a GDNLink the data gradient either carries the producing GDN's backward (role "main": returns the gradient
+    w.r.t. the GDN's INPUT) or is parked for the main consumer (role "side": returns None)."""
+    B, H, W, Ho, Wo = shape
+    st = stream()
+    d = state.desc(B, H, W, Ho, Wo)
+    gx = None
+    if need_dx:
+        gx = empty_nhwc(B, state.c0, H, W, BF16, g.device)
+        if role == "main":
+            if link.n_side and link.addend is None:
+                raise RuntimeError("GDNLink: the side consumer's backward has not run yet (autograd order changed?)")
+            if link.addend_ev is not None:
+                torch.cuda.current_stream().wait_event(link.addend_ev)
+                link.addend.record_stream(torch.cuda.current_stream())
+            t = torch.empty_like(link.x)
+            L.conv_dgrad_gdn_backward(d, ptr(g), ptr(state.w_direct), state.c0, ptr(link.addend), ptr(link.x), ptr(link.rn),
+                                      ptr(link.gamma_bf), int(link.inverse), ptr(t), ptr(gx), st)
+            link.t, link.fused_done = t, True
+        else:
+            L.conv_dgrad(d, ptr(g), ptr(state.w_direct), state.c0, ptr(gx), st)
+            if role == "side":
+                ev = torch.cuda.Event()
+                ev.record()
+                link.addend, link.addend_ev = gx, ev
+                gx = None
+    if weight.requires_grad:
+        ws = SideStreams.next_wgrad()
+        if ws is not None:
+            ev = torch.cuda.Event()
+            ev.record()                      # g is complete on the current stream
+            for t_ in (g, x0, x1):
+                if t_ is not None:
+                    t_.record_stream(ws)
+            with torch.cuda.stream(ws):
+                ws.wait_event(ev)
+                _conv_wgrad(state, d, x0, x1, g, weight, bias)
+            SideStreams.queue_join()
+        else:
+            _conv_wgrad(state, d, x0, x1, g, weight, bias)
+    return gx
+
+
+def _conv_wgrad(state, d, x0, x1, g, weight, bias):
+    st = stream()
+    ready = []
+    gw = grad_view(weight, (0, 2, 3, 1))
+    gb = grad_view(bias) if (bias is not None and bias.requires_grad) else None
+    if gw is not None:
+        L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(gw), ptr(gb), st)
+    else:  # foreign (non GEMM-layout) parameter: stage and add
+        tmp = torch.zeros((state.D0, state.T, state.D1), dtype=F32, device=g.device)
+        L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(tmp), ptr(gb), st)
+        weight.grad.add_(tmp.view(state.D0, state.k, state.k, state.D1).permute(0, 3, 1, 2))
+    ready.append(weight)
+    if gb is not None:
+        ready.append(bias)
+    if state.grad_ready is not None:
+        state.grad_ready(ready)        # the DP reducer records its event on the stream the gradient was produced on
+
+
 class _ConvFn(torch.autograd.Function):
     """conv / deconv (+bias, +ReLU) -- compressai/models/utils.py:128-146.
-    mode 0: returns bf16 activation; mode 1 (latent head): returns (fp32 y, bf16 |y|)."""
+    mode 0: returns bf16 activation; mode 1 (latent head): returns (fp32 y, bf16 |y|).
+    `link` (GDNLink of the GDN that produced x0) / `side`: see GDNLink."""
 
     @staticmethod
-    def forward(ctx, x0, x1, weight, bias, state, relu, mode, out_hw):
+    def forward(ctx, x0, x1, weight, bias, state, relu, mode, out_hw, link, side):
         B, _, H, W = x0.shape
         Ho, Wo = state.out_hw(H, W, out_hw)
         state.refresh(weight)
@@ -191,6 +295,8 @@ class _ConvFn(torch.autograd.Function):
         ctx.state, ctx.relu, ctx.mode, ctx.shape = state, relu, mode, (B, H, W, Ho, Wo)
         ctx.weight, ctx.bias = weight, bias
         ctx.need_dx = ctx.needs_input_grad[0]
+        ctx.link = link
+        ctx.role = link.register_consumer(state, d, side) if (link is not None and ctx.need_dx) else None
         if mode == 0:
             ctx.save_for_backward(x0, x1, out_b if relu else None, None)
             return out_b
@@ -214,50 +320,12 @@ class _ConvFn(torch.autograd.Function):
             gd = None if g_direct is None else nhwc(g_direct, F32)
             ga = None if g_abs is None else nhwc(g_abs, BF16)
             L.abs_backward(ptr(gd), ptr(ga), ptr(y_f32), g.numel(), int(ctx.relu), ptr(g), st)
-        d = state.desc(B, H, W, Ho, Wo)
-        # ---- data gradient first: it is the critical path (only source 0 is differentiable: source 1 is input data)
-        gx = None
-        if ctx.need_dx:
-            gx = empty_nhwc(B, state.c0, H, W, BF16, g.device)
-            L.conv_dgrad(d, ptr(g), ptr(state.w_direct), state.c0, ptr(gx), st)
-        # ---- weight / bias gradients, straight into param.grad; on the side stream when one is enabled
-        weight, bias = ctx.weight, ctx.bias
-        if weight.requires_grad:
-            ws = SideStreams.next_wgrad()
-            if ws is not None:
-                ev = torch.cuda.Event()
-                ev.record()                      # g is complete on the current stream
-                for t in (g, x0, x1):
-                    if t is not None:
-                        t.record_stream(ws)
-                with torch.cuda.stream(ws):
-                    ws.wait_event(ev)
-                    _ConvFn._wgrad(ctx, state, d, x0, x1, g, weight, bias)
-                SideStreams.queue_join()
-            else:
-                _ConvFn._wgrad(ctx, state, d, x0, x1, g, weight, bias)
-        return gx, None, None, None, None, None, None, None
-
-    @staticmethod
-    def _wgrad(ctx, state, d, x0, x1, g, weight, bias):
-        st = stream()
-        ready = []
-        gw = grad_view(weight, (0, 2, 3, 1))
-        gb = grad_view(bias) if (bias is not None and bias.requires_grad) else None
-        if gw is not None:
-            L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(gw), ptr(gb), st)
-        else:  # foreign (non GEMM-layout) parameter: stage and add
-            tmp = torch.zeros((state.D0, state.T, state.D1), dtype=F32, device=g.device)
-            L.conv_wgrad(d, ptr(x0), ptr(x1), ptr(g), ptr(tmp), ptr(gb), st)
-            weight.grad.add_(tmp.view(state.D0, state.k, state.k, state.D1).permute(0, 3, 1, 2))
-        ready.append(weight)
-        if gb is not None:
-            ready.append(bias)
-        if state.grad_ready is not None:
-            state.grad_ready(ready)        # the DP reducer records its event on the stream the gradient was produced on
+        # only source 0 is differentiable: source 1 is input data
+        gx = _conv_backward(state, ctx.shape, x0, x1, g, ctx.weight, ctx.bias, ctx.need_dx, ctx.link, ctx.role)
+        return gx, None, None, None, None, None, None, None, None, None
 
 
-def conv_apply(state, x0, x1, weight, bias, relu=False, mode=0, out_hw=None):
+def conv_apply(state, x0, x1, weight, bias, relu=False, mode=0, out_hw=None, link=None, side=False):
     x0 = nhwc(x0, BF16)
     if x1 is not None:
         x1 = nhwc(x1, BF16)
@@ -265,7 +333,7 @@ def conv_apply(state, x0, x1, weight, bias, relu=False, mode=0, out_hw=None):
             raise ValueError(f"concat sources disagree: {tuple(x0.shape)} vs {tuple(x1.shape)}")
     if x0.shape[1] != state.c0 or (x1 is not None and x1.shape[1] != state.c1):
         raise ValueError(f"expected {state.c0}+{state.c1} input channels, got {x0.shape[1]}")
-    return _ConvFn.apply(x0, x1, weight, bias, state, relu, mode, out_hw)
+    return _ConvFn.apply(x0, x1, weight, bias, state, relu, mode, out_hw, link, side)
 
 
 # ====================================================================== GDN / IGDN
@@ -283,6 +351,7 @@ class GDNState:
         self.beta_bound, self.gamma_bound = float(beta_bound), float(gamma_bound)
         self.grad_ready = None
         self.arena = None
+        self.link = None           # GDNLink of the latest forward pass (conv_gdn_apply)
         self.beta_eff = self.gamma_bf = self.g_beta_eff = self.g_gamma_eff = None
 
 
@@ -355,6 +424,114 @@ class _GDNFn(torch.autograd.Function):
 
 def gdn_apply(state, x, beta, gamma):
     return _GDNFn.apply(nhwc(x, BF16), beta, gamma, state)
+
+
+class _ConvGDNFn(torch.autograd.Function):
+    """conv / deconv followed by GDN / IGDN as ONE node (models/utils.py:128-146 + layers/gdn.py:77-92).
+
+    Forward: when the conv's launch uses whole-K 256-wide tiles anyway (lmsfc_conv_gdn_fusable) the GDN's channel
+    contraction runs in the conv kernel's epilogue on the accumulator tile (lmsfc_conv_gdn_forward); otherwise the two
+    kernels run back to back.  Backward: the GDN part is skipped when the consumer of y already ran it inside its
+    data-gradient kernel (GDNLink.fused_done: the incoming gradient then IS the gradient w.r.t. the conv output); the
+    conv part hands ITS data gradient to the GDN of the layer before (`in_link`) the same way.
+    Returns y; the GDNLink for the consumers of y is left in `gdn_state.link`."""
+
+    @staticmethod
+    def forward(ctx, x0, x1, weight, bias, beta, gamma, cstate, gstate, out_hw, in_link):
+        B, _, H, W = x0.shape
+        Ho, Wo = cstate.out_hw(H, W, out_hw)
+        C = cstate.cout
+        cstate.refresh(weight)
+        d = cstate.desc(B, H, W, Ho, Wo)
+        dev, st = x0.device, stream()
+        arena = gstate.arena
+        if arena is not None:
+            arena.ensure_prepared(beta, gamma)
+            beta_eff, gamma_bf = gstate.beta_eff, gstate.gamma_bf
+        else:
+            beta_eff = torch.empty(C, dtype=F32, device=dev)
+            gamma_bf = torch.empty((C, C), dtype=BF16, device=dev)
+            L.reparam_forward(ptr(beta), C, gstate.beta_bound, PEDESTAL, ptr(beta_eff), None, st)
+            L.reparam_forward(ptr(gamma), C * C, gstate.gamma_bound, PEDESTAL, None, ptr(gamma_bf), st)
+        train = any(ctx.needs_input_grad[:6])
+        y = empty_nhwc(B, C, Ho, Wo, BF16, dev)
+        x = rn = x2 = None
+        if train:
+            x, rn, x2 = (empty_nhwc(B, C, Ho, Wo, BF16, dev) for _ in range(3))
+        if C == 256 and L.gdn_fusable(d):
+            L.conv_gdn_forward(d, ptr(x0), ptr(x1), ptr(cstate.w_direct), ptr(bias), ptr(gamma_bf), ptr(beta_eff),
+                               int(gstate.inverse), ptr(x), ptr(x2), ptr(y), ptr(rn), st)
+        else:
+            if x is None:
+                x = empty_nhwc(B, C, Ho, Wo, BF16, dev)
+            L.conv_forward(d, ptr(x0), ptr(x1), ptr(cstate.w_direct), ptr(bias), 0, ptr(x), None, None, st)
+            L.gdn_forward(ptr(x), ptr(gamma_bf), ptr(beta_eff), int(gstate.inverse), B * Ho * Wo, C, ptr(x2), ptr(y), ptr(rn), st)
+        ctx.cstate, ctx.gstate, ctx.shape = cstate, gstate, (B, H, W, Ho, Wo)
+        ctx.weight, ctx.bias, ctx.beta, ctx.gamma = weight, bias, beta, gamma
+        ctx.need_dx = ctx.needs_input_grad[0]
+        ctx.in_link = in_link
+        ctx.in_role = in_link.register_consumer(cstate, d, False) if (in_link is not None and ctx.need_dx) else None
+        link = GDNLink(x, rn, gamma_bf, gstate.inverse) if train else None
+        ctx.link = gstate.link = link
+        if train:
+            ctx.save_for_backward(x0, x1, x, rn, gamma_bf, x2)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        cstate, gstate, link = ctx.cstate, ctx.gstate, ctx.link
+        x0, x1, x, rn, gamma_bf, x2 = ctx.saved_tensors
+        B, H, W, Ho, Wo = ctx.shape
+        C, P = cstate.cout, B * Ho * Wo
+        dev, st = x.device, stream()
+        gy = nhwc(gy, BF16)
+        arena = gstate.arena
+        if arena is not None:
+            g_gamma_eff, g_beta_eff = gstate.g_gamma_eff, gstate.g_beta_eff
+        else:
+            g_gamma_eff = torch.zeros((C, C), dtype=F32, device=dev)
+            g_beta_eff = torch.zeros(C, dtype=F32, device=dev)
+        ws = SideStreams.next_wgrad() if arena is not None else None
+        if link.fused_done:                      # the consumer's dgrad kernel ran the contraction: gy is d loss / d x
+            gx, t = gy, link.t
+        else:
+            t = torch.empty_like(x)
+            gx = torch.empty_like(x)
+            L.gdn_backward(ptr(gy), ptr(x), ptr(rn), ptr(gamma_bf), int(gstate.inverse), P, C, ptr(x2), 1, ptr(t), ptr(gx),
+                           None, None, st)
+        if ws is not None:                       # gamma's / beta's gradient GEMM is off the critical path
+            ev = torch.cuda.Event()
+            ev.record()
+            t.record_stream(ws)
+            x2.record_stream(ws)
+            with torch.cuda.stream(ws):
+                ws.wait_event(ev)
+                L.gdn_wgrad(ptr(t), ptr(x2), P, C, ptr(g_gamma_eff), ptr(g_beta_eff), stream())
+        else:
+            L.gdn_wgrad(ptr(t), ptr(x2), P, C, ptr(g_gamma_eff), ptr(g_beta_eff), st)
+        beta, gamma = ctx.beta, ctx.gamma
+        if arena is not None:
+            arena.queue_finish_backward()        # one batched reparam-backward at the end of this backward pass
+        else:
+            gb, gg = grad_view(beta), grad_view(gamma)
+            L.reparam_backward(ptr(g_beta_eff), ptr(beta), C, gstate.beta_bound, ptr(gb), st)
+            L.reparam_backward(ptr(g_gamma_eff), ptr(gamma), C * C, gstate.gamma_bound, ptr(gg), st)
+            if gstate.grad_ready is not None:
+                gstate.grad_ready([beta, gamma])
+        link.t = link.addend = None              # drop the per-pass tensors
+        gin = _conv_backward(cstate, ctx.shape, x0, x1, gx, ctx.weight, ctx.bias, ctx.need_dx, ctx.in_link, ctx.in_role)
+        return gin, None, None, None, None, None, None, None, None, None
+
+
+def conv_gdn_apply(cstate, gstate, x0, x1, weight, bias, beta, gamma, out_hw=None, in_link=None):
+    """-> (y, GDNLink or None)."""
+    x0 = nhwc(x0, BF16)
+    if x1 is not None:
+        x1 = nhwc(x1, BF16)
+    if x0.shape[1] != cstate.c0 or (x1 is not None and x1.shape[1] != cstate.c1) or cstate.cout != gstate.C:
+        raise ValueError(f"conv_gdn: channels {x0.shape[1]} / {cstate.c0}+{cstate.c1} -> {cstate.cout} / GDN({gstate.C})")
+    y = _ConvGDNFn.apply(x0, x1, weight, bias, beta, gamma, cstate, gstate, out_hw, in_link)
+    return y, gstate.link
 
 
 # ====================================================================== entropy models

@@ -70,11 +70,21 @@ class _ConvBase(nn.Module):
         self._state._version = -1
         return out
 
-    def forward(self, x, x_cat=None, relu=False, out_hw=None, latent_head=False):
+    def forward(self, x, x_cat=None, relu=False, out_hw=None, latent_head=False, link=None, side=False):
+        """`link` / `side`: the GDNLink of the GDN that produced `x` (see functional.GDNLink) -- lets this layer's
+        data-gradient kernel run that GDN's backward contraction in its epilogue."""
         if (x_cat is None) != (self.concat_channels == 0):
             raise ValueError("concat source mismatch")
         return Fn.conv_apply(self._state, x, x_cat, self.weight, self.bias, relu=relu, mode=1 if latent_head else 0,
-                             out_hw=out_hw)
+                             out_hw=out_hw, link=link, side=side)
+
+    def forward_gdn(self, gdn, x, x_cat=None, out_hw=None, link=None):
+        """gdn(self(x)) as one autograd node, the GDN contraction fused into this layer's kernel where the tiling
+        allows it (functional._ConvGDNFn).  -> (y, GDNLink for y's consumers)."""
+        if (x_cat is None) != (self.concat_channels == 0):
+            raise ValueError("concat source mismatch")
+        return Fn.conv_gdn_apply(self._state, gdn._state, x, x_cat, self.weight, self.bias, gdn.beta, gdn.gamma,
+                                 out_hw=out_hw, in_link=link)
 
 
 class Conv(_ConvBase):

@@ -113,13 +113,14 @@ class LMSFC(nn.Module):
         """g_a: (p2..p5 bf16 NHWC) -> y fp32 and |y| bf16 (the input of h_a, models/google.py:294)."""
         p2, p3, p4, p5 = ps
         a = self.g_a
-        e2 = a.gdn2(a.conv2(p2))
+        # conv + GDN are one node each; the GDNLink lets the NEXT layer's data-gradient kernel run this GDN's backward
+        e2, l2 = a.conv2.forward_gdn(a.gdn2, p2)
         self._gate("g_a.conv3.weight")
-        e3 = a.gdn3(a.conv3(e2, p3))
+        e3, l3 = a.conv3.forward_gdn(a.gdn3, e2, p3, link=l2)
         self._gate("g_a.conv4.weight")
-        e4 = a.gdn4(a.conv4(e3, p4))
+        e4, l4 = a.conv4.forward_gdn(a.gdn4, e3, p4, link=l3)
         self._gate("g_a.conv5.weight")
-        return a.conv5(e4, p5, latent_head=True)
+        return a.conv5(e4, p5, latent_head=True, link=l4)
 
     # first parameter of every optimiser slice of the pipelined train step, in arena (= forward) order
     GATES = ("g_a.conv3.weight", "g_a.conv4.weight", "g_a.conv5.weight", "h_a.0.weight", "g_s.up5.weight")
@@ -160,25 +161,38 @@ class LMSFC(nn.Module):
         hs = Fn.SideStreams.heads if (self.training and torch.is_grad_enabled()) else None
         main = torch.cuda.current_stream()
 
-        def head(layer, d):
+        def produced():
+            """Event right behind the kernel that produced d_l: the head depends on d_l only, not on whatever the main
+            stream records between d_l and the head's own (later) recording."""
             if hs is None:
-                return layer(d)
+                return None
             ev = torch.cuda.Event()
             ev.record(main)
+            return ev
+
+        def head(layer, d, link, ev):
+            if hs is None:
+                return layer(d, link=link, side=True)
             d.record_stream(hs)
             with torch.cuda.stream(hs):
                 hs.wait_event(ev)
-                out = layer(d)
+                out = layer(d, link=link, side=True)
             out.record_stream(main)
             return out
 
-        d5 = s.igdn5(s.up5(y_hat_bf16, out_hw=hw5))
-        p5h = head(s.head5, d5)
-        d4 = s.igdn4(s.up4(d5, out_hw=hw4))
-        p4h = head(s.head4, d4)
-        d3 = s.igdn3(s.up3(d4, out_hw=hw3))
-        p3h = head(s.head3, d3)
-        p2h = s.up2(d3, out_hw=hw2)
+        # Each d_l feeds the next up-sampling stage (main consumer) and its 3x3 head (side consumer).  The main consumer is
+        # recorded FIRST: autograd then runs the head's backward first, which parks its data gradient in the GDNLink, and
+        # the up-sampling stage's data-gradient kernel adds it and runs the IGDN's backward in its epilogue.
+        d5, l5 = s.up5.forward_gdn(s.igdn5, y_hat_bf16, out_hw=hw5)
+        e5 = produced()
+        d4, l4 = s.up4.forward_gdn(s.igdn4, d5, out_hw=hw4, link=l5)
+        e4 = produced()
+        p5h = head(s.head5, d5, l5, e5)
+        d3, l3 = s.up3.forward_gdn(s.igdn3, d4, out_hw=hw3, link=l4)
+        e3 = produced()
+        p4h = head(s.head4, d4, l4, e4)
+        p2h = s.up2(d3, out_hw=hw2, link=l3)
+        p3h = head(s.head3, d3, l3, e3)
         if hs is not None:
             main.wait_stream(hs)
         return p2h, p3h, p4h, p5h
