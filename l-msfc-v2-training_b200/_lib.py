@@ -103,10 +103,22 @@ for _n, _a in _SIGS.items():
 
 
 _FUSABLE = {}
+# Where the GDN contraction is fused into the producing GEMM in TRAINING (bit mask; LMSFC_FUSE overrides, for A/B runs):
+# 1 conv/deconv forward + GDN; 2 data gradient + GDN backward; 4 also where the GDN output has a second consumer whose
+# gradient must be added first (the synthesis transform's heads: serialises head.dgrad -> up.dgrad).
+# Measured in the captured batch-16 step on a B200 (profiles/r2_fuse_ab.txt; ms/step, +-0.05 %): none 1.000, 1: 1.015,
+# 3: 1.007, 7: 1.014, 2: 0.966-0.990, 6: 0.999.  Solo, every fused kernel beats its separate launches (profiles/
+# r2_fused_bench.txt: conv2+gdn2 57.2 vs 60.5 us, conv3.dgrad+gdn2 32.1 vs 38.6 us) and halves the layer's HBM traffic;
+# inside the step the forward fusion loses: the separate square / GDN kernels overlapped the convolution's tail through
+# programmatic dependent launch, the fused CTA (512 TMEM columns, 213 KB) keeps its SM to itself until it exits.
+# Inference (no gradient) always takes the fused forward: y is the only tensor written.
+FUSE_MODE = int(os.environ.get("LMSFC_FUSE", "2"))
 
 
-def gdn_fusable(desc, dgrad=False, n_in=0):
+def gdn_fusable(desc, dgrad=False, n_in=0, inference=False):
     """True when conv `desc` (forward, or its data gradient w.r.t. the first n_in channels) can carry a fused GDN."""
+    if not inference and not (FUSE_MODE & (2 if dgrad else 1)):
+        return False
     key = (tuple(getattr(desc, f) for f, _ in ConvDesc._fields_), bool(dgrad), int(n_in))
     r = _FUSABLE.get(key)
     if r is None:

@@ -183,11 +183,12 @@ class GDNLink:
       * autograd runs the later-recorded node first, so the model records main before side (model.LMSFC.synthesis).
     """
     __slots__ = ("x", "rn", "gamma_bf", "inverse", "main_fuses", "side_plain", "n_side", "addend", "addend_ev", "t",
-                 "fused_done")
+                 "fused_done", "expect_side")
 
     def __init__(self, x, rn, gamma_bf, inverse):
         self.x, self.rn, self.gamma_bf, self.inverse = x, rn, gamma_bf, bool(inverse)
         self.main_fuses = None
+        self.expect_side = False       # set by the model when y has a second consumer (recorded after the main one)
         self.side_plain = False
         self.n_side = 0
         self.addend = self.addend_ev = self.t = None
@@ -205,8 +206,8 @@ class GDNLink:
             return None
         if self.main_fuses is not None:
             raise RuntimeError("GDNLink: a GDN output has one main consumer")
-        self.main_fuses = (not self.side_plain and state.c0 == self.x.shape[1] == 256
-                           and L.gdn_fusable(d, dgrad=True, n_in=state.c0))
+        self.main_fuses = (not self.side_plain and (not self.expect_side or (L.FUSE_MODE & 4) != 0)
+                           and state.c0 == self.x.shape[1] == 256 and L.gdn_fusable(d, dgrad=True, n_in=state.c0))
         return "main" if self.main_fuses else None
 
 
@@ -458,7 +459,7 @@ class _ConvGDNFn(torch.autograd.Function):
         x = rn = x2 = None
         if train:
             x, rn, x2 = (empty_nhwc(B, C, Ho, Wo, BF16, dev) for _ in range(3))
-        if C == 256 and L.gdn_fusable(d):
+        if C == 256 and L.gdn_fusable(d, inference=not train):
             L.conv_gdn_forward(d, ptr(x0), ptr(x1), ptr(cstate.w_direct), ptr(bias), ptr(gamma_bf), ptr(beta_eff),
                                int(gstate.inverse), ptr(x), ptr(x2), ptr(y), ptr(rn), st)
         else:

@@ -183,12 +183,20 @@ class LMSFC(nn.Module):
         # Each d_l feeds the next up-sampling stage (main consumer) and its 3x3 head (side consumer).  The main consumer is
         # recorded FIRST: autograd then runs the head's backward first, which parks its data gradient in the GDNLink, and
         # the up-sampling stage's data-gradient kernel adds it and runs the IGDN's backward in its epilogue.
+        def sided(link):
+            if link is not None:
+                link.expect_side = True
+            return link
+
         d5, l5 = s.up5.forward_gdn(s.igdn5, y_hat_bf16, out_hw=hw5)
+        sided(l5)
         e5 = produced()
         d4, l4 = s.up4.forward_gdn(s.igdn4, d5, out_hw=hw4, link=l5)
+        sided(l4)
         e4 = produced()
         p5h = head(s.head5, d5, l5, e5)
         d3, l3 = s.up3.forward_gdn(s.igdn3, d4, out_hw=hw3, link=l4)
+        sided(l3)
         e3 = produced()
         p4h = head(s.head4, d4, l4, e4)
         p2h = s.up2(d3, out_hw=hw2, link=l3)

@@ -45,7 +45,10 @@ busy = {s: 0.0 for s in streams}
 for e in ev:
     s = e["args"].get("stream", -1)
     busy[s] += e["dur"]
-    print(f"{e['ts'] - t0:9.2f} {e['dur']:8.2f}  s{streams[s]}  {e['name'][:90]}", file=out)
+    g = e["args"].get("grid")
+    gs = "x".join(str(v) for v in g) if g else "-"
+    nm = e["name"].replace("lmsfc::", "").replace("void ", "")
+    print(f"{e['ts'] - t0:9.2f} {e['dur']:8.2f}  s{streams[s]}  {gs:>10s}  {nm[:80]}", file=out)
 end = max(e["ts"] + e["dur"] for e in ev)
 # union of busy intervals
 iv = sorted((e["ts"], e["ts"] + e["dur"]) for e in ev)

@@ -88,7 +88,7 @@ def test_conv_gdn_forward_fused(L, case):
     xf, x2f, yf, rnf = (torch.full_like(xu, float("nan")) for _ in range(4))
     L.conv_gdn_forward(d, P(x0), P(x1), P(w), P(bias), P(gamma), P(beta), int(inverse), P(xf), P(x2f), P(yf), P(rnf), st)
     torch.cuda.synchronize()
-    if L.gdn_fusable(d):              # the separate conv uses the same whole-K 256-wide tiles: identical summation order
+    if L.gdn_fusable(d, inference=True):              # the separate conv uses the same whole-K 256-wide tiles: identical summation order
         assert torch.equal(xf, xu), nerr(xf, xu)
         assert torch.equal(x2f, x2u), nerr(x2f, x2u)
     else:                             # it splits K over a cluster: last-bit differences of the bf16 rounding
@@ -175,7 +175,7 @@ def test_conv_dgrad_gdn_backward_fused(L, case):
 def test_fusable_follows_the_tiling_cost_model(L):
     big = L.ConvDesc(0, 5, 2, 16, 64, 64, 32, 32, 256, 0, 256)
     small = L.ConvDesc(0, 5, 2, 16, 16, 16, 8, 8, 256, 256, 256)
-    assert L.gdn_fusable(big) and not L.gdn_fusable(small)
+    assert L.gdn_fusable(big, inference=True) and not L.gdn_fusable(small, inference=True)
     assert L.gdn_fusable(L.ConvDesc(0, 5, 2, 16, 32, 32, 16, 16, 256, 256, 256), dgrad=True, n_in=256)
     wide = L.ConvDesc(0, 3, 1, 16, 32, 32, 32, 32, 256, 0, 512)
-    assert not L.gdn_fusable(wide)
+    assert not L.gdn_fusable(wide, inference=True)
