@@ -177,6 +177,43 @@ int lmsfc_adam_prep(float lr, const float* lr_dev, float beta1, float beta2, flo
 int lmsfc_adam_update(float* p, float* m, float* v, float* g, void* p_bf16, int64_t n, float beta1, float beta2, float eps,
                       const float* scratch, int zero_g, void* stream);
 
+/* ------------------------------------------------------------------ data-parallel exchange over NVLink peer memory
+ * Replaces nn.DataParallel (examples/train.py:64-71, 275-276) + clip_grad_norm_ + Adam (:100-103) for N <= 8 ranks of one
+ * node, one process per GPU, with this library's own kernels on peer-mapped buffers (csrc/exchange.cu): each rank OWNS
+ * 1/N of every arena slice, pulls and averages that part of every rank's gradient (reduce-scatter by P2P loads in fixed
+ * rank order), the N partial squared norms visit every rank (identical clip coefficient everywhere), Adam runs on the
+ * owned part only and the new operands are stored into every rank's arena (all-gather by P2P stores): bf16 for the GEMM
+ * weights, fp32 as well for [0, fp32_end) (GDN, entropy bottleneck, biases).
+ * All pointer arrays hold the SAME buffer of every rank, peer-mapped into this process (e.g. torch symmetric memory):
+ * grads / params fp32 arenas, shadow bf16 arena, flags uint64 [LMSFC_XCHG_SLOTS][LMSFC_MAX_RANKS] (zero-initialised),
+ * norm_all float [LMSFC_MAX_RANKS]; tick: a local device uint64 (zero-initialised), the step epoch.
+ * Call order per step, identical on all ranks (flag slots are the caller's choice, distinct per call site):
+ *   xchg_reduce(slice) ... for every slice, after the rank's own gradients of the slice are complete on `stream`;
+ *   xchg_norm_publish(all the slices' norm parts); xchg_norm_wait -> sumsq; lmsfc_adam_prep(sumsq);
+ *   xchg_adam_push(slice) ... ; xchg_wait(slot of a push) before the first kernel that reads the slice's parameters. */
+#define LMSFC_MAX_RANKS 8
+#define LMSFC_XCHG_SLOTS 32
+typedef struct {
+  int world, rank;
+  float* grads[LMSFC_MAX_RANKS];
+  float* params[LMSFC_MAX_RANKS];
+  void* shadow[LMSFC_MAX_RANKS];
+  uint64_t* flags[LMSFC_MAX_RANKS];
+  float* norm_all[LMSFC_MAX_RANKS];
+  uint64_t* tick;
+} lmsfc_xchg_peers;
+/* grads[rank][lo:hi) = mean over ranks (the caller owns [lo, hi), multiples of 4); *norm_part = its squared norm */
+int lmsfc_xchg_reduce(const lmsfc_xchg_peers* peers, int slot, int64_t lo, int64_t hi, float* norm_part, int max_ctas,
+                      void* stream);
+int lmsfc_xchg_norm_publish(const lmsfc_xchg_peers* peers, const float* norm_parts, int nparts, int slot, void* stream);
+int lmsfc_xchg_norm_wait(const lmsfc_xchg_peers* peers, int slot, float* sumsq_out, void* stream);
+/* Adam (scratch from lmsfc_adam_prep) on [own_lo, own_hi) inside the slice [unit_lo, unit_hi); clears the whole slice's
+ * local gradient; signals `slot` on every rank when this rank's part has landed everywhere */
+int lmsfc_xchg_adam_push(const lmsfc_xchg_peers* peers, int slot, int64_t unit_lo, int64_t unit_hi, int64_t own_lo,
+                         int64_t own_hi, int64_t fp32_end, float* m, float* v, float beta1, float beta2, float eps,
+                         const float* scratch, int max_ctas, void* stream);
+int lmsfc_xchg_wait(const lmsfc_xchg_peers* peers, int slot, void* stream);
+
 /* ------------------------------------------------------------------ CDF tables (cpp_exts/ops/ops.cpp:40-109) */
 /* host pointers; cdf must hold n+1 entries.  Errors mirror the reference's ValueError cases. */
 int lmsfc_pmf_to_quantized_cdf(const float* pmf_host, int n, int precision, uint32_t* cdf_host);

@@ -25,6 +25,16 @@ class ConvDesc(Structure):
                 ("Hout", c_int), ("Wout", c_int), ("c0", c_int), ("c1", c_int), ("Cout", c_int)]
 
 
+MAX_RANKS, XCHG_SLOTS = 8, 32
+
+
+class XchgPeers(Structure):
+    """lmsfc_xchg_peers: the same buffer of every rank, peer-mapped (include/b200lmsfc.h)."""
+    _fields_ = [("world", c_int), ("rank", c_int), ("grads", c_void_p * MAX_RANKS), ("params", c_void_p * MAX_RANKS),
+                ("shadow", c_void_p * MAX_RANKS), ("flags", c_void_p * MAX_RANKS), ("norm_all", c_void_p * MAX_RANKS),
+                ("tick", c_void_p)]
+
+
 P = c_void_p
 _SIGS = {
     "lmsfc_conv_forward": [POINTER(ConvDesc), P, P, P, P, c_int, P, P, P, P],
@@ -64,6 +74,12 @@ _SIGS = {
     "lmsfc_rans_encode": [P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, c_int64, P, P, P, c_int64, P, P],
     "lmsfc_rans_decode": [P, c_int64, P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, P, P],
     "lmsfc_set_batch_invariant": [c_int],
+    "lmsfc_xchg_reduce": [POINTER(XchgPeers), c_int, c_int64, c_int64, P, c_int, P],
+    "lmsfc_xchg_norm_publish": [POINTER(XchgPeers), P, c_int, c_int, P],
+    "lmsfc_xchg_norm_wait": [POINTER(XchgPeers), c_int, P, P],
+    "lmsfc_xchg_adam_push": [POINTER(XchgPeers), c_int, c_int64, c_int64, c_int64, c_int64, c_int64, P, P, c_float, c_float,
+                             c_float, P, c_int, P],
+    "lmsfc_xchg_wait": [POINTER(XchgPeers), c_int, P],
     "lmsfc_gc_build_indexes": [P, c_int64, P, c_int, c_float, P, P],
 }
 EXPORTS = ["lmsfc_last_error", "lmsfc_version", "lmsfc_launch_count", "lmsfc_rans_lane_cap"] + list(_SIGS)

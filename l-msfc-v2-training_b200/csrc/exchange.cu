@@ -1,0 +1,302 @@
+// Data-parallel gradient exchange as this library's own kernels over NVLink / NVSwitch peer memory (no NCCL on the
+// data path).  Replaces nn.DataParallel's per-step replicate / gather (compressai/examples/train.py:64-71, 275-276) and
+// the clip + Adam that follows (examples/train.py:100-103) for N ranks:
+//
+//   every rank                       owner of a sub-slice (1/N of each arena slice)
+//   --------------------------------------------------------------------------------------------------------------
+//   backward -> local fp32 grads  -> xchg_reduce:  wait until all ranks finished the slice, g = mean_k grads_k (P2P loads,
+//                                     fixed rank order), kept in the owner's arena, sum(g^2) reduced deterministically
+//                                    xchg_norm_publish / xchg_norm_wait: the N per-rank sums visit every rank, summed in the
+//                                     same order everywhere -> one clip coefficient, bit-identical on all ranks
+//                                    xchg_adam_push: Adam on the OWNED sub-slice only (1/N of the optimiser's HBM traffic),
+//                                     the new bf16 GEMM operands (fp32 for the parameters kernels read in fp32: GDN, entropy
+//                                     bottleneck, biases) stored straight into every rank's arena (P2P stores)
+//   forward waits per slice       <- xchg_wait on the slice's flag
+//
+// Synchronisation is by flags in peer-mapped memory: flags[slot][sender] of the RECEIVING rank holds the epoch of the
+// sender's latest signal (st.release.sys after __threadfence_system; pollers ld.acquire.sys their own memory).  The epoch
+// (`tick`) is a device counter bumped once per step by xchg_norm_publish, so captured CUDA graphs replay the protocol
+// without host arguments.  Every spin is bounded (trap after ~4 s) so that a lost rank fails the step instead of hanging.
+#include "../../include/b200lmsfc.h"
+
+#include "kernels.cuh"
+
+namespace lmsfc {
+
+namespace {
+constexpr int TPB = 256;
+
+struct XP {                      // device-side copy of lmsfc_xchg_peers
+  int world, rank;
+  float* grads[LMSFC_MAX_RANKS];
+  float* params[LMSFC_MAX_RANKS];
+  __nv_bfloat16* shadow[LMSFC_MAX_RANKS];
+  unsigned long long* flags[LMSFC_MAX_RANKS];
+  float* norm_all[LMSFC_MAX_RANKS];
+  unsigned long long* tick;
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_tick(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+// thread k < world waits until rank k's signal in `slot` of this rank's flag block reaches `want`
+__device__ __forceinline__ void wait_all(const XP& P, int slot, unsigned long long want) {
+  if ((int)threadIdx.x < P.world) {
+    const unsigned long long* f = P.flags[P.rank] + slot * LMSFC_MAX_RANKS + threadIdx.x;
+    const long long t0 = clock64();
+    while (ld_acquire_sys(f) < want) {
+      if (clock64() - t0 > (8ll << 30)) {       // ~4 s at 2 GHz
+        printf("lmsfc exchange: rank %d timed out in slot %d waiting for rank %d (want %llu, have %llu)\n", P.rank, slot,
+               (int)threadIdx.x, want, ld_acquire_sys(f));
+        __trap();
+      }
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void signal_all(const XP& P, int slot, unsigned long long v) {   // threads k < world
+  if ((int)threadIdx.x < P.world) st_release_sys(P.flags[threadIdx.x] + slot * LMSFC_MAX_RANKS + P.rank, v);
+}
+
+// ---------------------------------------------------------------- reduce-scatter of one slice (owner side)
+__global__ void __launch_bounds__(TPB) xchg_reduce_kernel(XP P, int slot, long long lo4, long long n4, float inv_world,
+                                                          float* partial, unsigned int* counter, float* norm_part) {
+  pdl_sync();
+  const unsigned long long want = ld_tick(P.tick) + 1;
+  if (blockIdx.x == 0) {
+    __threadfence_system();                      // this rank's gradients of the slice are complete (stream order)
+    signal_all(P, slot, want);
+  }
+  wait_all(P, slot, want);                       // ... and so are every peer's
+  float local = 0.f;
+  float4* mine = reinterpret_cast<float4*>(P.grads[P.rank]) + lo4;
+  for (long long i = (long long)blockIdx.x * TPB + threadIdx.x; i < n4; i += (long long)gridDim.x * TPB) {
+    float4 v[LMSFC_MAX_RANKS];
+#pragma unroll
+    for (int k = 0; k < LMSFC_MAX_RANKS; ++k)
+      if (k < P.world) v[k] = __ldcg(reinterpret_cast<const float4*>(P.grads[k]) + lo4 + i);   // L1 is not coherent with peers
+    float4 a = v[0];
+#pragma unroll
+    for (int k = 1; k < LMSFC_MAX_RANKS; ++k)
+      if (k < P.world) { a.x += v[k].x; a.y += v[k].y; a.z += v[k].z; a.w += v[k].w; }        // fixed rank order
+    a.x *= inv_world; a.y *= inv_world; a.z *= inv_world; a.w *= inv_world;
+    mine[i] = a;
+    local += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+  }
+  // deterministic sum(g^2): block partials parked, the last block adds them in index order
+  __shared__ float red[32];
+  __shared__ unsigned int is_last;
+  local = block_sum(local, red);
+  if (threadIdx.x == 0) {
+    __stcg(partial + blockIdx.x, local);
+    __threadfence();
+    const unsigned int prev = atomicAdd(counter, 1u);
+    is_last = (prev == gridDim.x - 1) ? 1u : 0u;
+    if (is_last) *counter = 0;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    float v = 0.f;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += TPB) v += __ldcg(partial + i);
+    v = block_sum(v, red);
+    if (threadIdx.x == 0) *norm_part = v;
+  }
+}
+
+// ---------------------------------------------------------------- gradient norm: N numbers visit every rank
+__global__ void xchg_norm_publish_kernel(XP P, const float* parts, int nparts, int slot) {
+  pdl_sync();
+  const unsigned long long next = ld_tick(P.tick) + 1;
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int i = 0; i < nparts; ++i) s += parts[i];
+    for (int k = 0; k < P.world; ++k) __stcg(P.norm_all[k] + P.rank, s);
+    __threadfence_system();
+  }
+  __syncthreads();
+  signal_all(P, slot, next);
+  __syncthreads();
+  if (threadIdx.x == 0) *P.tick = next;          // the step's epoch: every later kernel of this step reads it
+}
+__global__ void xchg_norm_wait_kernel(XP P, int slot, float* sumsq_out) {
+  pdl_sync();
+  wait_all(P, slot, ld_tick(P.tick));
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int k = 0; k < P.world; ++k) s += __ldcg(P.norm_all[P.rank] + k);   // same order on every rank
+    *sumsq_out = s;
+  }
+}
+__global__ void xchg_wait_kernel(XP P, int slot) {
+  pdl_sync();
+  wait_all(P, slot, ld_tick(P.tick));
+}
+
+// ---------------------------------------------------------------- Adam on the owned sub-slice + all-gather by P2P stores
+__device__ __forceinline__ void adam1(float g, float& m, float& v, float& p, float clip, float b1, float b2, float step_size,
+                                      float rs_bc2, float eps) {
+  g *= clip;
+  m = b1 * m + (1.f - b1) * g;
+  v = b2 * v + (1.f - b2) * g * g;
+  p = p - step_size * m / (sqrtf(v) * rs_bc2 + eps);
+}
+struct PushArgs {
+  long long unit_lo4, unit_hi4, own_lo4, own_hi4, fp32_end4;   // in float4 units
+  float* m;
+  float* v;
+  float beta1, beta2, eps;
+  const float* scratch;            // {clip, bc1, bc2, norm, lr, active} from adam_prep
+  unsigned int* counter;
+  int slot;
+};
+__global__ void __launch_bounds__(TPB) xchg_adam_push_kernel(XP P, PushArgs a) {
+  pdl_sync();
+  const unsigned long long ep = ld_tick(P.tick);
+  const bool active = a.scratch[5] != 0.f;
+  if (active) {
+    const float clip = a.scratch[0], bc1 = a.scratch[1], bc2 = a.scratch[2];
+    const float step_size = a.scratch[4] / bc1, rs_bc2 = rsqrtf(bc2);
+    float4* p4 = reinterpret_cast<float4*>(P.params[P.rank]);
+    float4* g4 = reinterpret_cast<float4*>(P.grads[P.rank]);
+    float4* m4 = reinterpret_cast<float4*>(a.m);
+    float4* v4 = reinterpret_cast<float4*>(a.v);
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    const long long stride = (long long)gridDim.x * TPB, t0 = (long long)blockIdx.x * TPB + threadIdx.x;
+    for (long long i = a.own_lo4 + t0; i < a.own_hi4; i += stride) {
+      const float4 g = __ldcs(g4 + i);
+      float4 m = __ldcs(m4 + i), v = __ldcs(v4 + i), p = __ldcs(p4 + i);
+      adam1(g.x, m.x, v.x, p.x, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
+      adam1(g.y, m.y, v.y, p.y, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
+      adam1(g.z, m.z, v.z, p.z, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
+      adam1(g.w, m.w, v.w, p.w, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
+      __stcs(m4 + i, m); __stcs(v4 + i, v); __stcs(p4 + i, p);
+      g4[i] = zero;
+      const uint2 b = make_uint2(pack_bf16(p.x, p.y), pack_bf16(p.z, p.w));
+#pragma unroll
+      for (int k = 0; k < LMSFC_MAX_RANKS; ++k) {
+        if (k >= P.world) break;
+        reinterpret_cast<uint2*>(P.shadow[k])[i] = b;                                   // bf16 GEMM operands, every rank
+        if (i < a.fp32_end4 && k != P.rank) reinterpret_cast<float4*>(P.params[k])[i] = p;   // parameters read in fp32
+      }
+    }
+    // the rest of the slice belongs to other ranks: they have read this rank's gradients (norm wait), clear them
+    for (long long i = a.unit_lo4 + t0; i < a.own_lo4; i += stride) g4[i] = zero;
+    for (long long i = a.own_hi4 + t0; i < a.unit_hi4; i += stride) g4[i] = zero;
+  }
+  __threadfence_system();
+  __syncthreads();
+  __shared__ unsigned int is_last;
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(a.counter, 1u);
+    is_last = (prev == gridDim.x - 1) ? 1u : 0u;
+    if (is_last) *a.counter = 0;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence_system();
+    signal_all(P, a.slot, ep);                   // "my part of this slice has landed everywhere"
+  }
+}
+
+int to_xp(const lmsfc_xchg_peers* p, XP& x) {
+  LMSFC_CHECK_ARG(p && p->world >= 1 && p->world <= LMSFC_MAX_RANKS && p->rank >= 0 && p->rank < p->world && p->tick,
+                  "exchange: bad peer table");
+  x.world = p->world; x.rank = p->rank; x.tick = (unsigned long long*)p->tick;
+  for (int k = 0; k < LMSFC_MAX_RANKS; ++k) {
+    const bool in = k < p->world;
+    x.grads[k] = in ? p->grads[k] : nullptr;
+    x.params[k] = in ? p->params[k] : nullptr;
+    x.shadow[k] = in ? (__nv_bfloat16*)p->shadow[k] : nullptr;
+    x.flags[k] = in ? (unsigned long long*)p->flags[k] : nullptr;
+    x.norm_all[k] = in ? p->norm_all[k] : nullptr;
+    LMSFC_CHECK_ARG(!in || (x.grads[k] && x.params[k] && x.shadow[k] && x.flags[k] && x.norm_all[k]), "exchange: rank %d has a null buffer", k);
+  }
+  return LMSFC_OK;
+}
+
+// exchange kernels share their SMs with the GEMMs of the running backward / forward pass: ask for the shared-memory-heavy
+// carve-out so that a 200 KB GEMM CTA can join an SM one of these blocks occupies (see common.cuh)
+template <typename K>
+void prefer_shared(K kernel) {
+  static bool done = false;
+  if (!done) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    done = true;
+  }
+}
+}  // namespace
+}  // namespace lmsfc
+
+using namespace lmsfc;
+#define ST(s) ((cudaStream_t)(s))
+
+extern "C" int lmsfc_xchg_reduce(const lmsfc_xchg_peers* peers, int slot, int64_t lo, int64_t hi, float* norm_part,
+                                 int max_ctas, void* stream) {
+  XP P;
+  if (int rc = to_xp(peers, P)) return rc;
+  LMSFC_CHECK_ARG(slot >= 0 && slot < LMSFC_XCHG_SLOTS && lo % 4 == 0 && hi % 4 == 0 && hi >= lo && norm_part,
+                  "xchg_reduce: slot %d range [%lld, %lld)", slot, (long long)lo, (long long)hi);
+  if (int rc = ensure_reduce_scratch()) return rc;
+  const long long n4 = (hi - lo) / 4;
+  long long ctas = (n4 + 4 * TPB - 1) / (4 * TPB);
+  if (ctas < 1) ctas = 1;
+  if (max_ctas > 0 && ctas > max_ctas) ctas = max_ctas;
+  prefer_shared(xchg_reduce_kernel);
+  LMSFC_LAUNCH(xchg_reduce_kernel, dim3((unsigned)ctas), dim3(TPB), 0, ST(stream), P, slot, (long long)(lo / 4), n4,
+               1.0f / (float)P.world, red_scratch(ST(stream)), red_count(ST(stream)) + 62, norm_part);
+  return LMSFC_OK;
+}
+extern "C" int lmsfc_xchg_norm_publish(const lmsfc_xchg_peers* peers, const float* norm_parts, int nparts, int slot,
+                                       void* stream) {
+  XP P;
+  if (int rc = to_xp(peers, P)) return rc;
+  LMSFC_CHECK_ARG(norm_parts && nparts >= 1 && slot >= 0 && slot < LMSFC_XCHG_SLOTS, "xchg_norm_publish: bad argument");
+  LMSFC_LAUNCH(xchg_norm_publish_kernel, dim3(1), dim3(32), 0, ST(stream), P, norm_parts, nparts, slot);
+  return LMSFC_OK;
+}
+extern "C" int lmsfc_xchg_norm_wait(const lmsfc_xchg_peers* peers, int slot, float* sumsq_out, void* stream) {
+  XP P;
+  if (int rc = to_xp(peers, P)) return rc;
+  LMSFC_CHECK_ARG(sumsq_out && slot >= 0 && slot < LMSFC_XCHG_SLOTS, "xchg_norm_wait: bad argument");
+  LMSFC_LAUNCH(xchg_norm_wait_kernel, dim3(1), dim3(32), 0, ST(stream), P, slot, sumsq_out);
+  return LMSFC_OK;
+}
+extern "C" int lmsfc_xchg_wait(const lmsfc_xchg_peers* peers, int slot, void* stream) {
+  XP P;
+  if (int rc = to_xp(peers, P)) return rc;
+  LMSFC_CHECK_ARG(slot >= 0 && slot < LMSFC_XCHG_SLOTS, "xchg_wait: slot %d", slot);
+  LMSFC_LAUNCH(xchg_wait_kernel, dim3(1), dim3(32), 0, ST(stream), P, slot);
+  return LMSFC_OK;
+}
+extern "C" int lmsfc_xchg_adam_push(const lmsfc_xchg_peers* peers, int slot, int64_t unit_lo, int64_t unit_hi,
+                                    int64_t own_lo, int64_t own_hi, int64_t fp32_end, float* m, float* v, float beta1,
+                                    float beta2, float eps, const float* scratch, int max_ctas, void* stream) {
+  XP P;
+  if (int rc = to_xp(peers, P)) return rc;
+  LMSFC_CHECK_ARG(slot >= 0 && slot < LMSFC_XCHG_SLOTS && m && v && scratch && unit_lo <= own_lo && own_lo <= own_hi &&
+                      own_hi <= unit_hi && ((unit_lo | unit_hi | own_lo | own_hi | fp32_end) % 4) == 0,
+                  "xchg_adam_push: slot %d unit [%lld, %lld) own [%lld, %lld)", slot, (long long)unit_lo, (long long)unit_hi,
+                  (long long)own_lo, (long long)own_hi);
+  if (int rc = ensure_reduce_scratch()) return rc;
+  PushArgs a{unit_lo / 4, unit_hi / 4, own_lo / 4, own_hi / 4, fp32_end / 4, m, v, beta1, beta2, eps, scratch,
+             red_count(ST(stream)) + 61, slot};
+  const long long work4 = (unit_hi - unit_lo) / 4;
+  long long ctas = (work4 + 8 * TPB - 1) / (8 * TPB);
+  if (ctas < 1) ctas = 1;
+  if (max_ctas > 0 && ctas > max_ctas) ctas = max_ctas;
+  prefer_shared(xchg_adam_push_kernel);
+  LMSFC_LAUNCH(xchg_adam_push_kernel, dim3((unsigned)ctas), dim3(TPB), 0, ST(stream), P, a);
+  return LMSFC_OK;
+}
