@@ -202,6 +202,8 @@ typedef struct {
   float* norm_all[LMSFC_MAX_RANKS];
   uint64_t* tick;
 } lmsfc_xchg_peers;
+/* loads the exchange kernels and their scratch (call once before the first exchange; not capturable) */
+int lmsfc_xchg_init(void);
 /* grads[rank][lo:hi) = mean over ranks (the caller owns [lo, hi), multiples of 4); *norm_part = its squared norm */
 int lmsfc_xchg_reduce(const lmsfc_xchg_peers* peers, int slot, int64_t lo, int64_t hi, float* norm_part, int max_ctas,
                       void* stream);

@@ -74,6 +74,7 @@ _SIGS = {
     "lmsfc_rans_encode": [P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, c_int64, P, P, P, c_int64, P, P],
     "lmsfc_rans_decode": [P, c_int64, P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, P, P],
     "lmsfc_set_batch_invariant": [c_int],
+    "lmsfc_xchg_init": [],
     "lmsfc_xchg_reduce": [POINTER(XchgPeers), c_int, c_int64, c_int64, P, c_int, P],
     "lmsfc_xchg_norm_publish": [POINTER(XchgPeers), P, c_int, c_int, P],
     "lmsfc_xchg_norm_wait": [POINTER(XchgPeers), c_int, P, P],

@@ -242,6 +242,20 @@ void prefer_shared(K kernel) {
 using namespace lmsfc;
 #define ST(s) ((cudaStream_t)(s))
 
+// Load every exchange kernel now: with lazy module loading the first launch of a kernel can synchronise with kernels
+// already running on the device -- fatal when one of those is spinning on a flag that only a later launch can raise.
+extern "C" int lmsfc_xchg_init(void) {
+  cudaFuncAttributes a;
+  LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_reduce_kernel));
+  LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_norm_publish_kernel));
+  LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_norm_wait_kernel));
+  LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_wait_kernel));
+  LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_adam_push_kernel));
+  prefer_shared(xchg_reduce_kernel);
+  prefer_shared(xchg_adam_push_kernel);
+  return ensure_reduce_scratch();
+}
+
 extern "C" int lmsfc_xchg_reduce(const lmsfc_xchg_peers* peers, int slot, int64_t lo, int64_t hi, float* norm_part,
                                  int max_ctas, void* stream) {
   XP P;

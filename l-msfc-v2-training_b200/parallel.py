@@ -11,6 +11,15 @@ import torch
 import torch.distributed as dist
 
 
+def owned_range(lo, hi, rank, world, align=64):
+    """The part of arena slice [lo, hi) that `rank` owns (reduces, updates and publishes): `world` contiguous pieces,
+    boundaries on multiples of `align` floats (256 bytes: float4 / TMA alignment); identical on every rank."""
+    n = (hi - lo) // align                    # whole blocks; the tail block (if any) goes to the last rank
+    a = lo + (n * rank // world) * align
+    b = hi if rank == world - 1 else lo + (n * (rank + 1) // world) * align
+    return a, b
+
+
 class BucketedGradReducer:
     def __init__(self, model, bucket_mb=64.0, process_group=None, tail_mb=8.0):
         if model.arena is None:
