@@ -437,7 +437,7 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         # replicas must still be bit-identical after the timed loops (deterministic gradient norm, same all-reduced
         # gradients): compare every rank's weights with rank 0's
-        mine = net.arena.net_params
+        mine = net.arena.net_bf16                      # the operands every kernel reads (fp32 masters may be sharded)
         ref0 = mine.clone()
         dist.broadcast(ref0, src=0)
         same = torch.tensor([1 if torch.equal(mine, ref0) else 0], device=dev)
@@ -463,7 +463,9 @@ def run_b200(args):
                        "step_order": "sequential" if args.sequential else
                                      "pipelined: each step = [Adam of the previous backward || forward] -> backward (train.py)",
                        "l2": "per-step working set (weights+Adam state+activations ~0.9 GB) exceeds the 126 MB L2",
-                       "parallelism": f"dp{world}"},
+                       "parallelism": f"dp{world}",
+                       "exchange": (("p2p kernels: reduce-scatter + sharded Adam + all-gather over NVLink peer memory (csrc/exchange.cu)"
+                                     if ts.sharded else "NCCL bucketed all-reduce") if world > 1 else None)},
             "e2e": {"value": world * BATCH * args.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 16, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches_per_step * args.steps,

@@ -207,7 +207,9 @@ int lmsfc_xchg_init(void);
 /* grads[rank][lo:hi) = mean over ranks (the caller owns [lo, hi), multiples of 4); *norm_part = its squared norm */
 int lmsfc_xchg_reduce(const lmsfc_xchg_peers* peers, int slot, int64_t lo, int64_t hi, float* norm_part, int max_ctas,
                       void* stream);
-int lmsfc_xchg_norm_publish(const lmsfc_xchg_peers* peers, const float* norm_parts, int nparts, int slot, void* stream);
+/* set_flag (nullable device int) = 1 afterwards: the pending flag lmsfc_adam_prep consumes */
+int lmsfc_xchg_norm_publish(const lmsfc_xchg_peers* peers, const float* norm_parts, int nparts, int slot, int* set_flag,
+                            void* stream);
 int lmsfc_xchg_norm_wait(const lmsfc_xchg_peers* peers, int slot, float* sumsq_out, void* stream);
 /* Adam (scratch from lmsfc_adam_prep) on [own_lo, own_hi) inside the slice [unit_lo, unit_hi); clears the whole slice's
  * local gradient; signals `slot` on every rank when this rank's part has landed everywhere */

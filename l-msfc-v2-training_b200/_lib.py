@@ -76,7 +76,7 @@ _SIGS = {
     "lmsfc_set_batch_invariant": [c_int],
     "lmsfc_xchg_init": [],
     "lmsfc_xchg_reduce": [POINTER(XchgPeers), c_int, c_int64, c_int64, P, c_int, P],
-    "lmsfc_xchg_norm_publish": [POINTER(XchgPeers), P, c_int, c_int, P],
+    "lmsfc_xchg_norm_publish": [POINTER(XchgPeers), P, c_int, c_int, P, P],
     "lmsfc_xchg_norm_wait": [POINTER(XchgPeers), c_int, P, P],
     "lmsfc_xchg_adam_push": [POINTER(XchgPeers), c_int, c_int64, c_int64, c_int64, c_int64, c_int64, P, P, c_float, c_float,
                              c_float, P, c_int, P],

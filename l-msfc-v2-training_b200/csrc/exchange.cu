@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(TPB) xchg_reduce_kernel(XP P, int slot, long l
 }
 
 // ---------------------------------------------------------------- gradient norm: N numbers visit every rank
-__global__ void xchg_norm_publish_kernel(XP P, const float* parts, int nparts, int slot) {
+__global__ void xchg_norm_publish_kernel(XP P, const float* parts, int nparts, int slot, int* set_flag) {
   pdl_sync();
   const unsigned long long next = ld_tick(P.tick) + 1;
   if (threadIdx.x == 0) {
@@ -128,7 +128,10 @@ __global__ void xchg_norm_publish_kernel(XP P, const float* parts, int nparts, i
   __syncthreads();
   signal_all(P, slot, next);
   __syncthreads();
-  if (threadIdx.x == 0) *P.tick = next;          // the step's epoch: every later kernel of this step reads it
+  if (threadIdx.x == 0) {
+    *P.tick = next;                              // the step's epoch: every later kernel of this step reads it
+    if (set_flag) *set_flag = 1;                 // "an update is pending" (pipelined train step), consumed by adam_prep
+  }
 }
 __global__ void xchg_norm_wait_kernel(XP P, int slot, float* sumsq_out) {
   pdl_sync();
@@ -273,11 +276,11 @@ extern "C" int lmsfc_xchg_reduce(const lmsfc_xchg_peers* peers, int slot, int64_
   return LMSFC_OK;
 }
 extern "C" int lmsfc_xchg_norm_publish(const lmsfc_xchg_peers* peers, const float* norm_parts, int nparts, int slot,
-                                       void* stream) {
+                                       int* set_flag, void* stream) {
   XP P;
   if (int rc = to_xp(peers, P)) return rc;
   LMSFC_CHECK_ARG(norm_parts && nparts >= 1 && slot >= 0 && slot < LMSFC_XCHG_SLOTS, "xchg_norm_publish: bad argument");
-  LMSFC_LAUNCH(xchg_norm_publish_kernel, dim3(1), dim3(32), 0, ST(stream), P, norm_parts, nparts, slot);
+  LMSFC_LAUNCH(xchg_norm_publish_kernel, dim3(1), dim3(32), 0, ST(stream), P, norm_parts, nparts, slot, set_flag);
   return LMSFC_OK;
 }
 extern "C" int lmsfc_xchg_norm_wait(const lmsfc_xchg_peers* peers, int slot, float* sumsq_out, void* stream) {

@@ -282,9 +282,11 @@ class LMSFC(nn.Module):
     def conv_layers(self):
         return [m for m in self.modules() if isinstance(m, _ConvBase)]
 
-    def build_arena(self):
-        """Move all parameters (and .grad) into flat fp32 arenas; idempotent per device."""
-        self.arena = ParamArena(self)
+    def build_arena(self, alloc=None):
+        """Move all parameters (and .grad) into flat fp32 arenas.  `alloc(numel, dtype, device)` (optional) provides the
+        three big allocations -- parameters, gradients, bf16 operands -- e.g. from peer-mapped memory for the
+        data-parallel exchange (parallel.symmetric_alloc); calling it again re-homes the parameters."""
+        self.arena = ParamArena(self, alloc=alloc)
         return self.arena
 
     def refresh_shadows(self, cast=True):
@@ -319,7 +321,9 @@ class ParamArena:
 
     ALIGN = 64   # floats: 256-byte aligned slices (TMA bases, float4 kernels)
 
-    def __init__(self, model):
+    def __init__(self, model, alloc=None):
+        if alloc is None:
+            alloc = lambda numel, dtype, device: torch.zeros(numel, dtype=dtype, device=device)
         named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
         if not named or not named[0][1].is_cuda:
             raise RuntimeError("build_arena(): move the model to a CUDA device first (no CPU fallback)")
@@ -332,6 +336,9 @@ class ParamArena:
         gdn_ids = {id(p) for m in gdns for p in (m.beta, m.gamma)}
         eb_ids = {id(getattr(m, pn)) for m in ebs for pn, _, _ in m.PACK_COLUMNS}
         rest = [(n, p) for n, p in named if id(p) not in gdn_ids and id(p) not in eb_ids and not n.endswith(".quantiles")]
+        # the parameters kernels read in fp32 (biases ...) in front of the conv weights (read as bf16 operands only): the
+        # data-parallel exchange publishes [0, first weight) in fp32 and the rest as bf16 (csrc/exchange.cu)
+        rest = [(n, p) for n, p in rest if p.dim() != 4] + [(n, p) for n, p in rest if p.dim() == 4]
         self.aux = [(n, p) for n, p in named if n.endswith(".quantiles")]
         self.offsets = {}
         # ---- plan the net arena
@@ -369,8 +376,8 @@ class ParamArena:
                 o16 += _round_up(p.numel(), self.ALIGN)
             g_off += _round_up(p.numel(), self.ALIGN)
         with torch.no_grad():
-            self.net_params = torch.zeros(n_net, dtype=torch.float32, device=dev)
-            self._grads_all = torch.zeros(g_off, dtype=torch.float32, device=dev)
+            self.net_params = alloc(n_net, torch.float32, dev)
+            self._grads_all = alloc(g_off, torch.float32, dev)
             self.net_grads = self._grads_all[:n_net]
             self.net = []
             for n, p, o, shape, stride in plan:
@@ -417,7 +424,7 @@ class ParamArena:
         self.gates = {}            # parameter name -> event of the optimiser slice starting there (train.TrainStep)
         self.n_net = n_net
         # ---- bf16 GEMM operands of the conv weights: slices of one shadow of the whole arena
-        self.net_bf16 = torch.empty(self.net_params.numel(), dtype=torch.bfloat16, device=dev)
+        self.net_bf16 = alloc(self.net_params.numel(), torch.bfloat16, dev)
         for m in model.conv_layers():
             o = self.offsets[name_of[id(m.weight)]]
             st = m._state

@@ -21,7 +21,8 @@ def owned_range(lo, hi, rank, world, align=64):
 
 
 class BucketedGradReducer:
-    def __init__(self, model, bucket_mb=64.0, process_group=None, tail_mb=8.0):
+    def __init__(self, model, bucket_mb=64.0, process_group=None, tail_mb=8.0, edges=None):
+        """`edges` (optional, ascending arena offsets starting at 0): explicit bucket boundaries instead of size-based ones."""
         if model.arena is None:
             model.build_arena()
         self.model, self.arena = model, model.arena
@@ -29,6 +30,9 @@ class BucketedGradReducer:
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.grads = self.arena.net_grads
         self.comm_stream = torch.cuda.Stream(device=self.grads.device) if self.grads.is_cuda else None
+        if edges is not None:
+            self._init_from_edges(edges)
+            return
         # ---- buckets: walk parameters from the END of the arena, close a bucket every bucket_mb
         cap = int(bucket_mb * (1 << 20) / 4)
         names = self.arena.names("net")
@@ -58,6 +62,19 @@ class BucketedGradReducer:
                 head = {n for o, n in inside if o >= cut}
                 self.buckets[-1] = {"lo": cut, "hi": last["hi"], "names": head}
                 self.buckets.append({"lo": last["lo"], "hi": cut, "names": last["names"] - head})
+        self._finish_init()
+
+    def _init_from_edges(self, edges):
+        names = self.arena.names("net")
+        edges = list(edges) + [self.grads.numel()]
+        self.buckets = []
+        for lo, hi in zip(edges[:-1], edges[1:]):
+            inside = {n for n in names if lo <= self.arena.offsets[n] < hi}
+            self.buckets.append({"lo": lo, "hi": hi, "names": inside})
+        self._finish_init()
+
+    def _finish_init(self):
+        names = self.arena.names("net")
         self.bucket_of = {}
         for i, b in enumerate(self.buckets):
             for n in b["names"]:
@@ -67,7 +84,7 @@ class BucketedGradReducer:
         self._works = []
         self.launched = []
         # ---- hooks
-        for m in model.modules():
+        for m in self.model.modules():
             st = getattr(m, "_state", None)
             if st is not None and hasattr(st, "grad_ready"):
                 st.grad_ready = self._on_ready
@@ -124,6 +141,17 @@ class BucketedGradReducer:
             if not self._pending[i] and i not in self.launched:
                 self._launch(i)
 
+    def _producer_events(self):
+        """A bucket's gradients may come from any of the weight-gradient streams (round-robin) and from the current one:
+        the exchange waits for what has been enqueued on each of them so far."""
+        from .functional import SideStreams
+        evs = []
+        for s in {torch.cuda.current_stream()} | set(SideStreams._wgrad_pool):
+            ev = torch.cuda.Event()
+            ev.record(s)
+            evs.append(ev)
+        return evs
+
     def _launch(self, i):
         self.launched.append(i)
         if self.world == 1:
@@ -131,15 +159,7 @@ class BucketedGradReducer:
         b = self.buckets[i]
         view = self.grads[b["lo"]:b["hi"]]
         if self.comm_stream is not None:
-            # a bucket's gradients may come from any of the weight-gradient streams (round-robin) and from the
-            # current one: the exchange waits for what has been enqueued on each of them so far
-            from .functional import SideStreams
-            producers = {torch.cuda.current_stream()} | set(SideStreams._wgrad_pool)
-            evs = []
-            for s in producers:
-                ev = torch.cuda.Event()
-                ev.record(s)
-                evs.append(ev)
+            evs = self._producer_events()
             with torch.cuda.stream(self.comm_stream):
                 for ev in evs:
                     self.comm_stream.wait_event(ev)
@@ -160,3 +180,155 @@ class BucketedGradReducer:
         if self.comm_stream is not None and self.world > 1:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
         self._pending = None
+
+
+# ====================================================================== the exchange as this library's own kernels
+def symmetric_alloc(process_group=None):
+    """-> alloc(numel, dtype, device) handing out peer-mapped ("symmetric") tensors of torch.distributed, and the list
+    that collects (tensor, handle) pairs.  Plumbing only: the kernels get raw peer pointers (csrc/exchange.cu)."""
+    import torch.distributed._symmetric_memory as symm
+    group = process_group if process_group is not None else dist.group.WORLD
+    made = []
+    try:                                       # needed by older torch releases, a deprecated no-op in newer ones
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            symm.enable_symm_mem_for_group(group.group_name)
+    except Exception:
+        pass
+
+    def alloc(numel, dtype, device):
+        t = symm.empty(int(numel), dtype=dtype, device=device)
+        try:
+            hdl = symm.rendezvous(t, group.group_name)
+        except TypeError:
+            hdl = symm.rendezvous(t, group=group)
+        t.zero_()
+        made.append((t, hdl))
+        return t
+    alloc.made = made
+    return alloc
+
+
+class ShardedExchange(BucketedGradReducer):
+    """Data-parallel step over NVLink peer memory with this library's own kernels (csrc/exchange.cu; replaces
+    nn.DataParallel + clip_grad_norm_ + Adam of compressai/examples/train.py:64-71, 100-103, 275-276):
+
+      * units = the arena slices of the pipelined train step (forward order); every rank OWNS 1/N of each unit;
+      * backward: as soon as a unit's gradients are complete locally, `xchg_reduce` (exchange stream) waits for the
+        same on every peer, then averages the owned part over the ranks' arenas with P2P loads in fixed rank order and
+        reduces its squared norm deterministically -- overlapping the rest of backward;
+      * `publish()` sends the rank's squared norm to every peer; `update()` waits for all N, so every rank derives the
+        SAME clip coefficient, runs Adam on its owned parts only (1/N of the optimiser's HBM traffic per GPU) and stores
+        the new bf16 operands (fp32 for GDN / entropy-bottleneck / bias parameters) into every rank's arena;
+      * the forward pass waits per unit (`gate events`) for all ranks' stores.
+
+    Replicas are bit-identical by construction (every operand is computed once, by its owner).  The fp32 master weights
+    and Adam moments of a unit part live on its owner only: `consolidate()` gathers them (checkpoints)."""
+
+    R_SLOT, NORM_SLOT, PUSH_SLOT = 0, 8, 16
+
+    def __init__(self, model, edges, alloc, process_group=None):
+        from . import _lib as L
+        self.L = L
+        super().__init__(model, process_group=process_group, edges=edges)
+        arena = self.arena
+        dev = arena.device
+        self.rank = dist.get_rank(process_group)
+        if self.world > L.MAX_RANKS:
+            raise RuntimeError(f"the peer-memory exchange serves up to {L.MAX_RANKS} ranks of one node, got {self.world}")
+        handle = {t.data_ptr(): h for t, h in alloc.made}
+        try:
+            hg, hp, hs = (handle[t.data_ptr()] for t in (arena._grads_all, arena.net_params, arena.net_bf16))
+        except KeyError:
+            raise RuntimeError("ShardedExchange: the model's arena was not built from symmetric memory (build_arena(alloc=...))")
+        self.flags = alloc(L.XCHG_SLOTS * L.MAX_RANKS, torch.int64, dev)
+        self.norm_all = alloc(L.MAX_RANKS, torch.float32, dev)
+        hf, hn = handle_of(alloc, self.flags), handle_of(alloc, self.norm_all)
+        self.tick = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.norm_parts = torch.zeros(len(self.buckets), dtype=torch.float32, device=dev)
+        p = L.XchgPeers()
+        p.world, p.rank = self.world, self.rank
+        for k in range(self.world):
+            p.grads[k], p.params[k], p.shadow[k] = int(hg.buffer_ptrs[k]), int(hp.buffer_ptrs[k]), int(hs.buffer_ptrs[k])
+            p.flags[k], p.norm_all[k] = int(hf.buffer_ptrs[k]), int(hn.buffer_ptrs[k])
+        p.tick = self.tick.data_ptr()
+        self.peers = p
+        self._handles = (hg, hp, hs, hf, hn)
+        first_w = min(arena.offsets[n] for n, q in arena.net if q.dim() == 4)
+        self.fp32_end = first_w                      # [0, fp32_end): parameters the kernels read in fp32
+        self.units = [(b["lo"], b["hi"]) for b in self.buckets]
+        self.own = [owned_range(lo, hi, self.rank, self.world) for lo, hi in self.units]
+        import os
+        self.reduce_ctas = int(os.environ.get("LMSFC_XCHG_REDUCE_CTAS", "32"))
+        self.push_ctas = int(os.environ.get("LMSFC_XCHG_PUSH_CTAS", "32"))
+        L.xchg_init()
+        dist.barrier(group=process_group)            # every rank's buffers are mapped and zeroed before the first signal
+
+    # ---- backward side
+    def _launch(self, i):
+        self.launched.append(i)
+        evs = self._producer_events()
+        a, b = self.own[i]
+        with torch.cuda.stream(self.comm_stream):
+            for ev in evs:
+                self.comm_stream.wait_event(ev)
+            self.L.xchg_reduce(self.peers, self.R_SLOT + i, a, b, self.norm_parts[i:].data_ptr(), self.reduce_ctas,
+                               torch.cuda.current_stream().cuda_stream)
+
+    def finish(self, pending_flag=None):
+        """Flush units that never reported, then publish this rank's squared gradient norm (raises `pending_flag`)."""
+        if self._pending is not None:
+            for i in range(len(self.buckets)):
+                if i not in self.launched:
+                    self._launch(i)
+        with torch.cuda.stream(self.comm_stream):
+            self.L.xchg_norm_publish(self.peers, self.norm_parts.data_ptr(), len(self.buckets), self.NORM_SLOT,
+                                     None if pending_flag is None else pending_flag.data_ptr(),
+                                     torch.cuda.current_stream().cuda_stream)
+        torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self._pending = None
+
+    # ---- update side (current stream)
+    def norm_wait(self, sumsq):
+        self.L.xchg_norm_wait(self.peers, self.NORM_SLOT, sumsq.data_ptr(), torch.cuda.current_stream().cuda_stream)
+
+    def adam_push(self, i, opt):
+        lo, hi = self.units[i]
+        a, b = self.own[i]
+        b1, b2 = opt.betas
+        self.L.xchg_adam_push(self.peers, self.PUSH_SLOT + i, lo, hi, a, b, self.fp32_end, opt.m.data_ptr(), opt.v.data_ptr(),
+                              b1, b2, opt.eps, opt.scratch.data_ptr(), self.push_ctas, torch.cuda.current_stream().cuda_stream)
+
+    def wait_pushed(self, i):
+        self.L.xchg_wait(self.peers, self.PUSH_SLOT + i, torch.cuda.current_stream().cuda_stream)
+
+    def update(self, opt, after_first=None):
+        """The whole update in the eager order: norm -> clip / Adam on the owned parts -> wait for everybody's stores."""
+        self.norm_wait(opt.sumsq)
+        opt.prep()
+        for i in range(len(self.units)):
+            self.adam_push(i, opt)
+        for i in range(len(self.units)):
+            self.wait_pushed(i)
+            if i == 0 and after_first is not None:
+                after_first()
+
+    @torch.no_grad()
+    def consolidate(self, optimizers=()):
+        """Gather the owners' fp32 master weights (and Adam moments) so that every rank holds the full state."""
+        for i, (lo, hi) in enumerate(self.units):
+            for k in range(self.world):
+                a, b = owned_range(lo, hi, k, self.world)
+                if b <= a:
+                    continue
+                src = dist.get_global_rank(self.pg, k) if self.pg is not None else k
+                for buf in [self.arena.net_params] + [t for o in optimizers for t in (o.m, o.v)]:
+                    dist.broadcast(buf[a:b], src=src, group=self.pg)
+
+
+def handle_of(alloc, t):
+    for u, h in alloc.made:
+        if u.data_ptr() == t.data_ptr():
+            return h
+    raise KeyError("not a symmetric tensor")

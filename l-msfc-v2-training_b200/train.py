@@ -25,13 +25,27 @@ from . import functional as Fn
 from .losses import RateDistortionLoss
 from .model import LMSFC
 from .optim import net_aux_optimizer
-from .parallel import BucketedGradReducer
+from .parallel import BucketedGradReducer, ShardedExchange, symmetric_alloc
 
 
 class TrainStep:
     def __init__(self, model: LMSFC, lmbda=0.0130, lr=1e-4, aux_lr=1e-3, clip_max_norm=1.0, distributed=False,
-                 bucket_mb=64.0, side_streams=True):
+                 bucket_mb=64.0, side_streams=True, exchange=None):
+        """distributed: one process per GPU (torch.distributed initialised).  exchange: "p2p" (default; env LMSFC_DP) --
+        this library's own reduce-scatter / sharded Adam / all-gather kernels over peer-mapped memory
+        (parallel.ShardedExchange, csrc/exchange.cu) -- or "nccl": bucketed all-reduce + full Adam on every rank."""
+        import os
         self.model = model
+        self.sharded = False
+        alloc = None
+        if distributed:
+            exchange = exchange or os.environ.get("LMSFC_DP", "p2p")
+            if exchange not in ("p2p", "nccl"):
+                raise ValueError(f'exchange must be "p2p" or "nccl", got {exchange!r}')
+            if exchange == "p2p":
+                alloc = symmetric_alloc()
+                model.build_arena(alloc=alloc)       # (re)home parameters, gradients and bf16 operands in peer-mapped memory
+                self.sharded = True
         if model.arena is None:
             model.build_arena()
         self.arena = model.arena
@@ -44,7 +58,10 @@ class TrainStep:
         self.pending_flag = torch.zeros(1, dtype=torch.int32, device=self.arena.device)
         self.opt["net"].pending_flag = self.pending_flag
         self.opt["aux"].gate = self.opt["net"]
-        self.reducer = BucketedGradReducer(model, bucket_mb=bucket_mb) if distributed else None
+        if self.sharded:
+            self.reducer = ShardedExchange(model, [lo for lo, _, _ in self._slices()], alloc)
+        else:
+            self.reducer = BucketedGradReducer(model, bucket_mb=bucket_mb) if distributed else None
         if self.reducer is not None:
             self.reducer.sync_replicas(self.opt)     # replicas start from rank 0's weights, with distinct noise streams
         if side_streams:
@@ -69,7 +86,10 @@ class TrainStep:
         if self.reducer is not None:
             self.reducer.mark_ready(self.reducer.eb_names)
             self.reducer.finish()
-        opt["net"].step()                       # clip_grad_norm_ + Adam, bf16 shadow in the same pass
+        if self.sharded:                        # norm exchange -> clip + Adam on the owned parts -> operands to every rank
+            self.reducer.update(opt["net"], after_first=self.arena.prepare)
+        else:
+            opt["net"].step()                   # clip_grad_norm_ + Adam, bf16 shadow in the same pass
         aux = model.aux_loss()
         aux.backward()
         opt["aux"].step()
@@ -105,9 +125,15 @@ class TrainStep:
             os_.wait_stream(main)
         arena.gates = {}
         with ctx:
+            if self.sharded:
+                self.reducer.norm_wait(net.sumsq)
             net.prep(use_pending=True)
             for i, (lo, hi, gate) in enumerate(self._slices()):
-                net.update(lo, hi, zero_grad=True)
+                if self.sharded:               # Adam on the owned part, operands to every rank; then everybody's have landed
+                    self.reducer.adam_push(i, net)
+                    self.reducer.wait_pushed(i)
+                else:
+                    net.update(lo, hi, zero_grad=True)
                 if i == 0:
                     arena._grads_all[arena.n_net:].zero_()     # GDN effective-gradient scratch
                     arena.prepare()                            # GDN group (first in the arena) -> effective beta / gamma
@@ -138,8 +164,12 @@ class TrainStep:
         crit["loss"].backward()
         if self.reducer is not None:
             self.reducer.mark_ready(self.reducer.eb_names)
-            self.reducer.finish()
-        opt["net"].accumulate_norm()
+            if self.sharded:                     # publishes this rank's squared norm and raises the pending flag
+                self.reducer.finish(pending_flag=self.pending_flag)
+            else:
+                self.reducer.finish()
+        if not self.sharded:
+            opt["net"].accumulate_norm()
         self.pending = True
         return crit
 
@@ -250,10 +280,18 @@ class TrainStep:
     def state_dict(self):
         """Everything the step keeps besides the model's own state_dict: both optimisers (Adam moments, step counters,
         learning rates) and the device-side noise counter.  A pending pipelined update is applied first."""
-        self.flush()
+        self.consolidate()
         rng = self.model.entropy_bottleneck._rng(self.arena.device)
         return {"optimizer": self.opt["net"].state_dict(), "aux_optimizer": self.opt["aux"].state_dict(),
                 "rng_state": rng.state.clone(), "lmbda": self.criterion.lmbda}
+
+    def consolidate(self):
+        """Apply a pending update and, under the sharded exchange, gather the owners' fp32 master weights and Adam
+        moments, so that this rank's model / optimiser state is complete (collective: call on every rank)."""
+        self.flush()
+        if self.sharded:
+            self.reducer.consolidate([self.opt["net"]])
+            torch.cuda.synchronize()
 
     def load_state_dict(self, sd):
         """Restore after `model.load_state_dict(...)`; the next step continues the saved run."""

@@ -53,6 +53,7 @@ def _worker(rank, world, port, out):
     out[f"noise_seed_{rank}"] = int(net.entropy_bottleneck._rng(dev).state[0])
     for _ in range(2):
         ts.step(feats, nz_all[sl].to(dev), ny_all[sl].to(dev))
+    ts.consolidate()                                    # sharded exchange: gather the owners' fp32 masters
     torch.cuda.synchronize()
     dp_params = net.arena.net_params.clone()
     # ---- the same two steps in one process on the concatenated batch (rank 0 only)
@@ -70,8 +71,9 @@ def _worker(rank, world, port, out):
     # ---- captured, pipelined DP step
     ts.capture(feats, warmup=1, pipelined=True)
     losses = [float(ts.replay()["loss"]) for _ in range(6)]
-    ts.flush()
+    ts.consolidate()
     torch.cuda.synchronize()
+    out[f"shadow_equal_{rank}"] = bool(torch.equal(net.arena.net_bf16, _bcast0(dist, net.arena.net_bf16)))
     mine = net.arena.net_params.clone()
     other = mine.clone()
     dist.broadcast(other, src=0)
@@ -83,6 +85,12 @@ def _worker(rank, world, port, out):
     del ts
     torch.cuda.synchronize()
     dist.destroy_process_group()
+
+
+def _bcast0(dist, t):
+    o = t.clone()
+    dist.broadcast(o, src=0)
+    return o
 
 
 def _init_params(model_m, spec, dev):
@@ -112,6 +120,7 @@ def test_dp_two_gpus_matches_single_process_and_ranks_agree():
     # where the gradient is ~0)
     assert res["eager_step_rel"] < 0.1, res
     assert res["graph_equal_0"] and res["graph_equal_1"], res
+    assert res["shadow_equal_0"] and res["shadow_equal_1"], res
     assert res["start_equal_0"] and res["start_equal_1"], res
     assert res["noise_seed_0"] != res["noise_seed_1"], res      # independent quantisation noise per replica
     l0, l1 = res["losses_0"], res["losses_1"]

@@ -66,7 +66,7 @@ def test_exchange_on_simulated_ranks(world):
                 for u, (lo, hi) in enumerate(units):
                     a, b = parallel.owned_range(lo, hi, r, world)
                     L.xchg_reduce(peers, u, a, b, o["parts"][u:].data_ptr(), 4, st)
-                L.xchg_norm_publish(peers, o["parts"].data_ptr(), len(units), 8, st)
+                L.xchg_norm_publish(peers, o["parts"].data_ptr(), len(units), 8, None, st)
                 L.xchg_norm_wait(peers, 8, o["sumsq"].data_ptr(), st)
                 L.adam_prep(1e-2, None, 0.9, 0.999, 1.0, o["sumsq"].data_ptr(), o["step"].data_ptr(), o["scratch"].data_ptr(),
                             None, 1, None, st)
