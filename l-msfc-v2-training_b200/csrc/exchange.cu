@@ -81,18 +81,31 @@ __global__ void __launch_bounds__(TPB) xchg_reduce_kernel(XP P, int slot, long l
   wait_all(P, slot, want);                       // ... and so are every peer's
   float local = 0.f;
   float4* mine = reinterpret_cast<float4*>(P.grads[P.rank]) + lo4;
-  for (long long i = (long long)blockIdx.x * TPB + threadIdx.x; i < n4; i += (long long)gridDim.x * TPB) {
-    float4 v[LMSFC_MAX_RANKS];
+  // NVLink / HBM latency is hidden by loads in flight: U quads per thread and iteration, world loads each, all issued
+  // before the first use (world = 8: 32 independent 16-byte loads per thread)
+  constexpr int U = 4;
+  const long long stride = (long long)gridDim.x * TPB;
+  for (long long i0 = (long long)blockIdx.x * TPB + threadIdx.x; i0 < n4; i0 += U * stride) {
+    float4 v[U][LMSFC_MAX_RANKS];
 #pragma unroll
-    for (int k = 0; k < LMSFC_MAX_RANKS; ++k)
-      if (k < P.world) v[k] = __ldcg(reinterpret_cast<const float4*>(P.grads[k]) + lo4 + i);   // L1 is not coherent with peers
-    float4 a = v[0];
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
 #pragma unroll
-    for (int k = 1; k < LMSFC_MAX_RANKS; ++k)
-      if (k < P.world) { a.x += v[k].x; a.y += v[k].y; a.z += v[k].z; a.w += v[k].w; }        // fixed rank order
-    a.x *= inv_world; a.y *= inv_world; a.z *= inv_world; a.w *= inv_world;
-    mine[i] = a;
-    local += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+      for (int k = 0; k < LMSFC_MAX_RANKS; ++k)
+        if (k < P.world && i < n4) v[u][k] = __ldcg(reinterpret_cast<const float4*>(P.grads[k]) + lo4 + i);   // L1 is not coherent with peers
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= n4) break;
+      float4 a = v[u][0];
+#pragma unroll
+      for (int k = 1; k < LMSFC_MAX_RANKS; ++k)
+        if (k < P.world) { a.x += v[u][k].x; a.y += v[u][k].y; a.z += v[u][k].z; a.w += v[u][k].w; }   // fixed rank order
+      a.x *= inv_world; a.y *= inv_world; a.z *= inv_world; a.w *= inv_world;
+      mine[i] = a;
+      local += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+    }
   }
   // deterministic sum(g^2): block partials parked, the last block adds them in index order
   __shared__ float red[32];
@@ -177,9 +190,7 @@ __global__ void __launch_bounds__(TPB) xchg_adam_push_kernel(XP P, PushArgs a) {
     float4* v4 = reinterpret_cast<float4*>(a.v);
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
     const long long stride = (long long)gridDim.x * TPB, t0 = (long long)blockIdx.x * TPB + threadIdx.x;
-    for (long long i = a.own_lo4 + t0; i < a.own_hi4; i += stride) {
-      const float4 g = __ldcs(g4 + i);
-      float4 m = __ldcs(m4 + i), v = __ldcs(v4 + i), p = __ldcs(p4 + i);
+    auto one = [&](long long i, const float4& g, float4 m, float4 v, float4 p) {
       adam1(g.x, m.x, v.x, p.x, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
       adam1(g.y, m.y, v.y, p.y, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
       adam1(g.z, m.z, v.z, p.z, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
@@ -193,7 +204,18 @@ __global__ void __launch_bounds__(TPB) xchg_adam_push_kernel(XP P, PushArgs a) {
         reinterpret_cast<uint2*>(P.shadow[k])[i] = b;                                   // bf16 GEMM operands, every rank
         if (i < a.fp32_end4 && k != P.rank) reinterpret_cast<float4*>(P.params[k])[i] = p;   // parameters read in fp32
       }
+    };
+    long long i = a.own_lo4 + t0;
+    for (; i + stride < a.own_hi4; i += 2 * stride) {          // 2 x 4 independent 16-byte loads in flight per thread
+      const long long j = i + stride;
+      const float4 g0 = __ldcs(g4 + i), g1 = __ldcs(g4 + j);
+      const float4 m0 = __ldcs(m4 + i), m1 = __ldcs(m4 + j);
+      const float4 v0 = __ldcs(v4 + i), v1 = __ldcs(v4 + j);
+      const float4 q0 = __ldcs(p4 + i), q1 = __ldcs(p4 + j);
+      one(i, g0, m0, v0, q0);
+      one(j, g1, m1, v1, q1);
     }
+    if (i < a.own_hi4) one(i, __ldcs(g4 + i), __ldcs(m4 + i), __ldcs(v4 + i), __ldcs(p4 + i));
     // the rest of the slice belongs to other ranks: they have read this rank's gradients (norm wait), clear them
     for (long long i = a.unit_lo4 + t0; i < a.own_lo4; i += stride) g4[i] = zero;
     for (long long i = a.own_hi4 + t0; i < a.unit_hi4; i += stride) g4[i] = zero;
@@ -269,7 +291,8 @@ extern "C" int lmsfc_xchg_reduce(const lmsfc_xchg_peers* peers, int slot, int64_
   const long long n4 = (hi - lo) / 4;
   long long ctas = (n4 + 4 * TPB - 1) / (4 * TPB);
   if (ctas < 1) ctas = 1;
-  if (max_ctas > 0 && ctas > max_ctas) ctas = max_ctas;
+  if (max_ctas <= 0) max_ctas = 2 * 148;         // two blocks per SM keep ~1.2 MB of 16-byte loads in flight
+  if (ctas > max_ctas) ctas = max_ctas;
   prefer_shared(xchg_reduce_kernel);
   LMSFC_LAUNCH(xchg_reduce_kernel, dim3((unsigned)ctas), dim3(TPB), 0, ST(stream), P, slot, (long long)(lo / 4), n4,
                1.0f / (float)P.world, red_scratch(ST(stream)), red_count(ST(stream)) + 62, norm_part);
@@ -312,7 +335,8 @@ extern "C" int lmsfc_xchg_adam_push(const lmsfc_xchg_peers* peers, int slot, int
   const long long work4 = (unit_hi - unit_lo) / 4;
   long long ctas = (work4 + 8 * TPB - 1) / (8 * TPB);
   if (ctas < 1) ctas = 1;
-  if (max_ctas > 0 && ctas > max_ctas) ctas = max_ctas;
+  if (max_ctas <= 0) max_ctas = 4 * 148;
+  if (ctas > max_ctas) ctas = max_ctas;
   prefer_shared(xchg_adam_push_kernel);
   LMSFC_LAUNCH(xchg_adam_push_kernel, dim3((unsigned)ctas), dim3(TPB), 0, ST(stream), P, a);
   return LMSFC_OK;

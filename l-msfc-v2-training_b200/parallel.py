@@ -260,8 +260,12 @@ class ShardedExchange(BucketedGradReducer):
         self.units = [(b["lo"], b["hi"]) for b in self.buckets]
         self.own = [owned_range(lo, hi, self.rank, self.world) for lo, hi in self.units]
         import os
-        self.reduce_ctas = int(os.environ.get("LMSFC_XCHG_REDUCE_CTAS", "32"))
-        self.push_ctas = int(os.environ.get("LMSFC_XCHG_PUSH_CTAS", "32"))
+        self.reduce_ctas = int(os.environ.get("LMSFC_XCHG_REDUCE_CTAS", "0"))
+        self.push_ctas = int(os.environ.get("LMSFC_XCHG_PUSH_CTAS", "0"))
+        self.multicast = int(getattr(hg, "multicast_ptr", 0) or 0)
+        if os.environ.get("LMSFC_VERBOSE") and self.rank == 0:
+            print(f"[lmsfc exchange] world {self.world}, units {self.units}, fp32_end {self.fp32_end}, "
+                  f"multicast_ptr {self.multicast:#x}", flush=True)
         L.xchg_init()
         dist.barrier(group=process_group)            # every rank's buffers are mapped and zeroed before the first signal
 

@@ -66,6 +66,7 @@ class TrainStep:
             self.reducer.sync_replicas(self.opt)     # replicas start from rank 0's weights, with distinct noise streams
         if side_streams:
             Fn.SideStreams.enable(self.arena.device)
+        self.gate_stream = torch.cuda.Stream(device=self.arena.device, priority=-1) if self.sharded else None
         self.graph = None
         self.static_in = None
         self.static_out = None
@@ -128,19 +129,28 @@ class TrainStep:
             if self.sharded:
                 self.reducer.norm_wait(net.sumsq)
             net.prep(use_pending=True)
+            gs = self.gate_stream if (self.sharded and os_ is not None) else None
             for i, (lo, hi, gate) in enumerate(self._slices()):
-                if self.sharded:               # Adam on the owned part, operands to every rank; then everybody's have landed
+                if self.sharded:               # Adam on the owned part, its operands stored into every rank's arena
                     self.reducer.adam_push(i, net)
-                    self.reducer.wait_pushed(i)
                 else:
                     net.update(lo, hi, zero_grad=True)
-                if i == 0:
-                    arena._grads_all[arena.n_net:].zero_()     # GDN effective-gradient scratch
-                    arena.prepare()                            # GDN group (first in the arena) -> effective beta / gamma
-                if os_ is not None:
-                    ev = torch.cuda.Event()
-                    ev.record()
-                    arena.gates[gate] = ev
+                if gs is not None:             # "every rank's part of the slice has landed" is waited for on a stream of
+                    pushed = torch.cuda.Event()   # its own: this rank's next slice does not wait for the slowest peer
+                    pushed.record()
+                    gs.wait_event(pushed)
+                with (torch.cuda.stream(gs) if gs is not None else _Null()):
+                    if self.sharded:
+                        self.reducer.wait_pushed(i)
+                    if i == 0:
+                        arena._grads_all[arena.n_net:].zero_()     # GDN effective-gradient scratch
+                        arena.prepare()                            # GDN group (first in the arena) -> effective beta / gamma
+                    if os_ is not None:
+                        ev = torch.cuda.Event()
+                        ev.record()
+                        arena.gates[gate] = ev
+            if gs is not None:
+                os_.wait_stream(gs)
             aux_opt.zero_grad()
             aux = model.aux_loss()
             aux.backward()

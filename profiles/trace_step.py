@@ -11,11 +11,16 @@ PKG = "l-msfc-v2-training_b200"
 model_m = importlib.import_module(PKG + ".model")
 train_m = importlib.import_module(PKG + ".train")
 
-dev = torch.device("cuda", 0)
+world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+torch.cuda.set_device(dev)
+if world > 1:                          # torchrun: every rank runs the step, rank 0 writes its own timeline
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=dev)
 sp = model_m.DEFAULT_SPEC
 torch.manual_seed(1234)
 net = model_m.LMSFC(sp).to(dev)
-ts = train_m.TrainStep(net, lmbda=0.013)
+ts = train_m.TrainStep(net, lmbda=0.013, distributed=world > 1)
 f = importlib.import_module(PKG + '.data').synth_features(sp, 16, 64, 64, seed=1234)
 feats = {k: v.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).to(dev) for k, v in f.items()}
 ts.step(feats)
@@ -28,14 +33,14 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(3):
         ts.replay()
     torch.cuda.synchronize()
-path = os.path.join(tempfile.gettempdir(), "lmsfc_trace.json")
+path = os.path.join(tempfile.gettempdir(), f"lmsfc_trace_{rank}.json")
 prof.export_chrome_trace(path)
 ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset")]
 ev.sort(key=lambda e: e["ts"])
 n = len(ev) // 3
 ev = ev[2 * n:]                        # the last replay
 t0 = ev[0]["ts"]
-out = open(sys.argv[1], "w") if len(sys.argv) > 1 else sys.stdout
+out = open(sys.argv[1] if rank == 0 else os.devnull, "w") if len(sys.argv) > 1 else sys.stdout
 streams = {}
 for e in ev:
     s = e["args"].get("stream", -1)
@@ -63,3 +68,7 @@ cov += cur_e - cur_s
 print(f"# span {end - t0:.1f} us; any-kernel-running {cov:.1f} us; idle {end - t0 - cov:.1f} us", file=out)
 for s, i in streams.items():
     print(f"# stream s{i}: busy {busy[s]:.1f} us", file=out)
+
+out.flush()
+if world > 1:
+    dist.barrier(); torch.cuda.synchronize(); ts.release(); del ts; dist.destroy_process_group()
