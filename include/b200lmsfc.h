@@ -201,6 +201,12 @@ typedef struct {
   uint64_t* flags[LMSFC_MAX_RANKS];
   float* norm_all[LMSFC_MAX_RANKS];
   uint64_t* tick;
+  /* optional NVSwitch multicast addresses of the same three arenas (NULL: plain peer loads / stores): the reduction
+   * then happens inside the switch (multimem.ld_reduce: 1/N of the inbound traffic) and one store reaches every rank
+   * (multimem.st) */
+  float* mc_grads;
+  float* mc_params;
+  void* mc_shadow;
 } lmsfc_xchg_peers;
 /* loads the exchange kernels and their scratch (call once before the first exchange; not capturable) */
 int lmsfc_xchg_init(void);

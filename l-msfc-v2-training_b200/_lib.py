@@ -32,7 +32,7 @@ class XchgPeers(Structure):
     """lmsfc_xchg_peers: the same buffer of every rank, peer-mapped (include/b200lmsfc.h)."""
     _fields_ = [("world", c_int), ("rank", c_int), ("grads", c_void_p * MAX_RANKS), ("params", c_void_p * MAX_RANKS),
                 ("shadow", c_void_p * MAX_RANKS), ("flags", c_void_p * MAX_RANKS), ("norm_all", c_void_p * MAX_RANKS),
-                ("tick", c_void_p)]
+                ("tick", c_void_p), ("mc_grads", c_void_p), ("mc_params", c_void_p), ("mc_shadow", c_void_p)]
 
 
 P = c_void_p

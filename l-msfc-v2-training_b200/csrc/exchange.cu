@@ -34,6 +34,9 @@ struct XP {                      // device-side copy of lmsfc_xchg_peers
   unsigned long long* flags[LMSFC_MAX_RANKS];
   float* norm_all[LMSFC_MAX_RANKS];
   unsigned long long* tick;
+  float* mc_grads;               // NVSwitch multicast views (nullable)
+  float* mc_params;
+  __nv_bfloat16* mc_shadow;
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
@@ -49,6 +52,24 @@ __device__ __forceinline__ unsigned long long ld_tick(const unsigned long long* 
   asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
+// sum over all ranks of one float4, formed inside the NVSwitch (NVLS): one 16-byte response instead of N
+__device__ __forceinline__ float4 mc_ld_reduce(const float4* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st_b64(void* mc, uint2 v) {          // one store, delivered to every rank
+  const unsigned long long b = ((unsigned long long)v.y << 32) | v.x;
+  asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(mc), "l"(b) : "memory");
+}
+__device__ __forceinline__ void mc_st_f4(void* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
 // thread k < world waits until rank k's signal in `slot` of this rank's flag block reaches `want`
 __device__ __forceinline__ void wait_all(const XP& P, int slot, unsigned long long want) {
   if ((int)threadIdx.x < P.world) {
@@ -85,6 +106,28 @@ __global__ void __launch_bounds__(TPB) xchg_reduce_kernel(XP P, int slot, long l
   // before the first use (world = 8: 32 independent 16-byte loads per thread)
   constexpr int U = 4;
   const long long stride = (long long)gridDim.x * TPB;
+  if (P.mc_grads) {
+    // NVLS: the switch adds the N ranks' values; this rank receives only the sums of its own part
+    const float4* mc = reinterpret_cast<const float4*>(P.mc_grads) + lo4;
+    constexpr int UM = 8;
+    for (long long i0 = (long long)blockIdx.x * TPB + threadIdx.x; i0 < n4; i0 += UM * stride) {
+      float4 v[UM];
+#pragma unroll
+      for (int u = 0; u < UM; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < n4) v[u] = mc_ld_reduce(mc + i);
+      }
+#pragma unroll
+      for (int u = 0; u < UM; ++u) {
+        const long long i = i0 + u * stride;
+        if (i >= n4) break;
+        float4 a = v[u];
+        a.x *= inv_world; a.y *= inv_world; a.z *= inv_world; a.w *= inv_world;
+        mine[i] = a;
+        local += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+      }
+    }
+  } else
   for (long long i0 = (long long)blockIdx.x * TPB + threadIdx.x; i0 < n4; i0 += U * stride) {
     float4 v[U][LMSFC_MAX_RANKS];
 #pragma unroll
@@ -198,6 +241,11 @@ __global__ void __launch_bounds__(TPB) xchg_adam_push_kernel(XP P, PushArgs a) {
       __stcs(m4 + i, m); __stcs(v4 + i, v); __stcs(p4 + i, p);
       g4[i] = zero;
       const uint2 b = make_uint2(pack_bf16(p.x, p.y), pack_bf16(p.z, p.w));
+      if (P.mc_shadow) {                         // one multicast store reaches every rank's arena
+        mc_st_b64(reinterpret_cast<uint2*>(P.mc_shadow) + i, b);
+        if (i < a.fp32_end4) mc_st_f4(reinterpret_cast<float4*>(P.mc_params) + i, p);
+        return;
+      }
 #pragma unroll
       for (int k = 0; k < LMSFC_MAX_RANKS; ++k) {
         if (k >= P.world) break;
@@ -248,6 +296,10 @@ int to_xp(const lmsfc_xchg_peers* p, XP& x) {
     x.norm_all[k] = in ? p->norm_all[k] : nullptr;
     LMSFC_CHECK_ARG(!in || (x.grads[k] && x.params[k] && x.shadow[k] && x.flags[k] && x.norm_all[k]), "exchange: rank %d has a null buffer", k);
   }
+  x.mc_grads = p->mc_grads;
+  x.mc_params = p->mc_params;
+  x.mc_shadow = (__nv_bfloat16*)p->mc_shadow;
+  LMSFC_CHECK_ARG(!x.mc_shadow == !x.mc_params, "exchange: the multicast views of params and shadow come together");
   return LMSFC_OK;
 }
 

@@ -229,6 +229,7 @@ class ShardedExchange(BucketedGradReducer):
     R_SLOT, NORM_SLOT, PUSH_SLOT = 0, 8, 16
 
     def __init__(self, model, edges, alloc, process_group=None):
+        import os
         from . import _lib as L
         self.L = L
         super().__init__(model, process_group=process_group, edges=edges)
@@ -249,23 +250,34 @@ class ShardedExchange(BucketedGradReducer):
         self.norm_parts = torch.zeros(len(self.buckets), dtype=torch.float32, device=dev)
         p = L.XchgPeers()
         p.world, p.rank = self.world, self.rank
+
+        def peer_ptrs(h, t):
+            """Rank k's address of tensor `t`: the handle lists allocation bases, `t` may sit at an offset inside."""
+            delta = t.data_ptr() - int(h.buffer_ptrs[self.rank])
+            mc = int(getattr(h, "multicast_ptr", 0) or 0)
+            return [int(h.buffer_ptrs[k]) + delta for k in range(self.world)], (mc + delta if mc else 0)
+
+        (pg_, mg), (pp_, mp), (ps_, ms) = peer_ptrs(hg, arena._grads_all), peer_ptrs(hp, arena.net_params), peer_ptrs(hs, arena.net_bf16)
+        pf_, pn_ = peer_ptrs(hf, self.flags)[0], peer_ptrs(hn, self.norm_all)[0]
         for k in range(self.world):
-            p.grads[k], p.params[k], p.shadow[k] = int(hg.buffer_ptrs[k]), int(hp.buffer_ptrs[k]), int(hs.buffer_ptrs[k])
-            p.flags[k], p.norm_all[k] = int(hf.buffer_ptrs[k]), int(hn.buffer_ptrs[k])
+            p.grads[k], p.params[k], p.shadow[k], p.flags[k], p.norm_all[k] = pg_[k], pp_[k], ps_[k], pf_[k], pn_[k]
         p.tick = self.tick.data_ptr()
+        # NVSwitch multicast (NVLS) when the allocator provides it: in-switch reduction, one-store all-gather
+        use_mc = os.environ.get("LMSFC_XCHG_MULTICAST", "1") == "1" and mg and mp and ms
+        self.multicast = bool(use_mc)
+        if use_mc:
+            p.mc_grads, p.mc_params, p.mc_shadow = mg, mp, ms
         self.peers = p
         self._handles = (hg, hp, hs, hf, hn)
         first_w = min(arena.offsets[n] for n, q in arena.net if q.dim() == 4)
         self.fp32_end = first_w                      # [0, fp32_end): parameters the kernels read in fp32
         self.units = [(b["lo"], b["hi"]) for b in self.buckets]
         self.own = [owned_range(lo, hi, self.rank, self.world) for lo, hi in self.units]
-        import os
         self.reduce_ctas = int(os.environ.get("LMSFC_XCHG_REDUCE_CTAS", "0"))
         self.push_ctas = int(os.environ.get("LMSFC_XCHG_PUSH_CTAS", "0"))
-        self.multicast = int(getattr(hg, "multicast_ptr", 0) or 0)
         if os.environ.get("LMSFC_VERBOSE") and self.rank == 0:
             print(f"[lmsfc exchange] world {self.world}, units {self.units}, fp32_end {self.fp32_end}, "
-                  f"multicast_ptr {self.multicast:#x}", flush=True)
+                  f"multicast {self.multicast}", flush=True)
         L.xchg_init()
         dist.barrier(group=process_group)            # every rank's buffers are mapped and zeroed before the first signal
 
