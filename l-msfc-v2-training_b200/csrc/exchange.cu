@@ -81,7 +81,7 @@ __device__ __forceinline__ void wait_all(const XP& P, int slot, unsigned long lo
                (int)threadIdx.x, want, ld_acquire_sys(f));
         __trap();
       }
-      __nanosleep(64);
+      __nanosleep(200);
     }
   }
   __syncthreads();
@@ -91,15 +91,20 @@ __device__ __forceinline__ void signal_all(const XP& P, int slot, unsigned long 
 }
 
 // ---------------------------------------------------------------- reduce-scatter of one slice (owner side)
-__global__ void __launch_bounds__(TPB) xchg_reduce_kernel(XP P, int slot, long long lo4, long long n4, float inv_world,
-                                                          float* partial, unsigned int* counter, float* norm_part) {
+// "my gradients of this slice are complete" to every peer, then wait for theirs.  ONE block polls (a handful of
+// system-scope loads every 200 ns): the reduction grid behind it never spins -- hundreds of polling blocks were measured
+// to slow the concurrent host-to-device feature copies by 0.5 ms per step.
+__global__ void xchg_ready_kernel(XP P, int slot) {
   pdl_sync();
   const unsigned long long want = ld_tick(P.tick) + 1;
-  if (blockIdx.x == 0) {
-    __threadfence_system();                      // this rank's gradients of the slice are complete (stream order)
-    signal_all(P, slot, want);
-  }
-  wait_all(P, slot, want);                       // ... and so are every peer's
+  if ((int)threadIdx.x < P.world) __threadfence_system();   // this rank's gradients of the slice are complete (stream order)
+  signal_all(P, slot, want);
+  wait_all(P, slot, want);
+}
+
+__global__ void __launch_bounds__(TPB) xchg_reduce_kernel(XP P, int slot, long long lo4, long long n4, float inv_world,
+                                                          float* partial, unsigned int* counter, float* norm_part) {
+  pdl_sync();                                    // behind xchg_ready_kernel: every rank's gradients of the slice are complete
   float local = 0.f;
   float4* mine = reinterpret_cast<float4*>(P.grads[P.rank]) + lo4;
   // NVLink / HBM latency is hidden by loads in flight: U quads per thread and iteration, world loads each, all issued
@@ -268,10 +273,14 @@ __global__ void __launch_bounds__(TPB) xchg_adam_push_kernel(XP P, PushArgs a) {
     for (long long i = a.unit_lo4 + t0; i < a.own_lo4; i += stride) g4[i] = zero;
     for (long long i = a.own_hi4 + t0; i < a.unit_hi4; i += stride) g4[i] = zero;
   }
-  __threadfence_system();
+  // ONE system-scope fence per kernel: blocks publish their stores at GPU scope (barrier + fence + counter), the last
+  // block to arrive -- which thereby observes all of them -- issues the cumulative fence.sys in front of the flag stores.
+  // A fence.sys per block (let alone per thread) stalls for tens of microseconds while the copy engines keep PCIe busy:
+  // measured +0.54 ms per step in the end-to-end loop (profiles/tools/e2e_probe.py).
   __syncthreads();
   __shared__ unsigned int is_last;
   if (threadIdx.x == 0) {
+    __threadfence();
     const unsigned int prev = atomicAdd(a.counter, 1u);
     is_last = (prev == gridDim.x - 1) ? 1u : 0u;
     if (is_last) *a.counter = 0;
@@ -324,6 +333,7 @@ using namespace lmsfc;
 extern "C" int lmsfc_xchg_init(void) {
   cudaFuncAttributes a;
   LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_reduce_kernel));
+  LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_ready_kernel));
   LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_norm_publish_kernel));
   LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_norm_wait_kernel));
   LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_wait_kernel));
@@ -346,6 +356,7 @@ extern "C" int lmsfc_xchg_reduce(const lmsfc_xchg_peers* peers, int slot, int64_
   if (max_ctas <= 0) max_ctas = 2 * 148;         // two blocks per SM keep ~1.2 MB of 16-byte loads in flight
   if (ctas > max_ctas) ctas = max_ctas;
   prefer_shared(xchg_reduce_kernel);
+  LMSFC_LAUNCH(xchg_ready_kernel, dim3(1), dim3(32), 0, ST(stream), P, slot);
   LMSFC_LAUNCH(xchg_reduce_kernel, dim3((unsigned)ctas), dim3(TPB), 0, ST(stream), P, slot, (long long)(lo / 4), n4,
                1.0f / (float)P.world, red_scratch(ST(stream)), red_count(ST(stream)) + 62, norm_part);
   return LMSFC_OK;
