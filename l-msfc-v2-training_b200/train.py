@@ -43,9 +43,15 @@ class TrainStep:
             if exchange not in ("p2p", "nccl"):
                 raise ValueError(f'exchange must be "p2p" or "nccl", got {exchange!r}')
             if exchange == "p2p":
-                alloc = symmetric_alloc()
-                model.build_arena(alloc=alloc)       # (re)home parameters, gradients and bf16 operands in peer-mapped memory
-                self.sharded = True
+                try:
+                    alloc = symmetric_alloc()
+                    model.build_arena(alloc=alloc)   # (re)home parameters, gradients and bf16 operands in peer-mapped memory
+                    self.sharded = True
+                except Exception as e:               # no peer-mappable memory (e.g. GPUs without P2P): NCCL all-reduce
+                    import warnings
+                    warnings.warn(f"peer-memory exchange unavailable ({e}); falling back to the NCCL all-reduce")
+                    alloc = None
+                    model.arena = None
         if model.arena is None:
             model.build_arena()
         self.arena = model.arena

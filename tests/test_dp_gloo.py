@@ -142,3 +142,18 @@ def test_reducer_single_process_is_a_noop():
     red.finish()
     assert torch.all(net.arena.net_grads == 3.0)
     assert sorted(red.launched) == list(range(len(red.buckets)))
+
+
+def test_owned_ranges_partition_every_unit():
+    """parallel.owned_range: the N owners' parts tile a unit exactly, on 64-float boundaries, identically on every rank
+    (the reduce-scatter / sharded Adam / all-gather kernels of csrc/exchange.cu rely on it)."""
+    par = importlib.import_module(PKG + ".parallel")
+    for lo, hi in [(0, 2052352), (2052352, 5329152), (19616000, 27939072), (64, 64 * 3), (0, 64), (128, 128)]:
+        for world in (1, 2, 3, 4, 8):
+            parts = [par.owned_range(lo, hi, r, world) for r in range(world)]
+            assert parts[0][0] == lo and parts[-1][1] == hi
+            assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
+            assert all(a % 64 == 0 and b % 4 == 0 and b >= a for a, b in parts)
+            if hi - lo >= 64 * world * 8:
+                sizes = [b - a for a, b in parts]
+                assert max(sizes) - min(sizes) <= 64 + (hi - lo) % 64
