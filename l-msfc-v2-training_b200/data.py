@@ -27,8 +27,9 @@ def synth_features(spec: LMSFCSpec, B: int, H2: int, W2: int, seed: int = 1234, 
     g = torch.Generator().manual_seed(seed)
     feats = {}
     for i, (k, (h, w)) in enumerate(zip(spec.levels, spec.level_shapes(H2, W2))):
-        a = torch.relu(torch.randn(B, spec.F, h, w, generator=g)) * (1.0 + 0.5 * i)
-        a = a + 0.1 * torch.randn(B, spec.F, h, w, generator=g)
+        C = spec.channels[i]
+        a = torch.relu(torch.randn(B, C, h, w, generator=g)) * (1.0 + 0.5 * i)
+        a = a + 0.1 * torch.randn(B, C, h, w, generator=g)
         feats[k] = a.clamp_(-26.43, 28.40).to(device=device, dtype=dtype)
     return feats
 
@@ -40,7 +41,7 @@ class FeatureFolder:
     def __init__(self, root: str, crop: Tuple[int, int] = (256, 256), spec: LMSFCSpec = DEFAULT_SPEC,
                  pattern: str = "*.h5", rank: int = 0, world: int = 1, seed: int = 1234, cache_files: int = 4):
         self.spec, self.crop = spec, (int(crop[0]), int(crop[1]))
-        unit = 4 * 2 ** (len(spec.levels) - 1)
+        unit = spec.base_stride * 2 ** (len(spec.levels) - 1)
         if self.crop[0] % unit or self.crop[1] % unit:
             raise ValueError(f"crop {self.crop} must be a multiple of {unit} input pixels")
         self.files = sorted(glob.glob(os.path.join(root, pattern)))
@@ -79,7 +80,7 @@ class FeatureFolder:
         return len(self.samples)
 
     def level_crop_shapes(self):
-        h, w = self.crop[0] // 4, self.crop[1] // 4
+        h, w = self.crop[0] // self.spec.base_stride, self.crop[1] // self.spec.base_stride
         return self.spec.level_shapes(h, w)
 
     def crop_into(self, index: int, out: Dict[str, torch.Tensor], slot: int):
@@ -112,11 +113,11 @@ class ShardLoader:
         self.ds, self.batch = dataset, int(batch)
         pin = torch.cuda.is_available() if pin is None else pin
         shapes = dataset.level_crop_shapes()
-        C = dataset.spec.F
+        chans = dataset.spec.channels
 
         def staging():
-            b = {k: torch.empty((self.batch, C, h, w), dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
-                 for k, (h, w) in zip(dataset.spec.levels, shapes)}
+            b = {k: torch.empty((self.batch, c, h, w), dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+                 for k, c, (h, w) in zip(dataset.spec.levels, chans, shapes)}
             return {k: v.pin_memory() for k, v in b.items()} if pin else b
         self.ring = [staging() for _ in range(max(3, ring))]   # run_steps holds two while it waits for a third
         self.free: "queue.Queue[int]" = queue.Queue()

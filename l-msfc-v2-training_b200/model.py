@@ -33,12 +33,19 @@ class LMSFC(nn.Module):
     def __init__(self, spec: LMSFCSpec = DEFAULT_SPEC):
         super().__init__()
         self.spec = spec
-        Fc, N, M = spec.F, spec.N, spec.M
+        N, M, ch = spec.N, spec.M, spec.channels
+        if N % 256 or M % 256 or any(c % 256 for c in ch):
+            # csrc: the weight-gradient tiles are 256 x 256 channels (wgrad.cu), GDN's contraction needs C % 256 == 0
+            raise ValueError(f"LMSFC on the B200 kernels: N, M and the level channels must be multiples of 256, got {N}, {M}, {ch}")
+        n = len(spec.levels)
+        self._tags = [spec.tag(i) for i in range(n)]
         g_a = nn.Module()
-        g_a.conv2, g_a.gdn2 = Conv(Fc, N), GDN(N)
-        g_a.conv3, g_a.gdn3 = Conv(N + Fc, N, concat_channels=Fc), GDN(N)
-        g_a.conv4, g_a.gdn4 = Conv(N + Fc, N, concat_channels=Fc), GDN(N)
-        g_a.conv5 = Conv(N + Fc, M, concat_channels=Fc)
+        for i, t in enumerate(self._tags):        # conv<t> (+ gdn<t>) per level; the last one produces y
+            last = i == n - 1
+            cin = ch[i] + (N if i else 0)
+            setattr(g_a, f"conv{t}", Conv(cin, M if last else N, concat_channels=ch[i] if i else 0))
+            if not last:
+                setattr(g_a, f"gdn{t}", GDN(N))
         self.g_a = g_a
         # keys "0","2","4" mirror the nn.Sequential(conv, ReLU, conv, ReLU, conv) of google.py:267-282
         self.h_a = nn.ModuleDict({"0": Conv(M, N, 3, 1), "2": Conv(N, N), "4": Conv(N, N)})
@@ -47,14 +54,17 @@ class LMSFC(nn.Module):
         self.gaussian_conditional = GaussianConditional(None, scale_bound=spec.scale_bound,
                                                         likelihood_bound=spec.likelihood_bound)
         g_s = nn.Module()
-        g_s.up5, g_s.igdn5, g_s.head5 = Deconv(M, N), GDN(N, inverse=True), Conv(N, Fc, 3, 1)
-        g_s.up4, g_s.igdn4, g_s.head4 = Deconv(N, N), GDN(N, inverse=True), Conv(N, Fc, 3, 1)
-        g_s.up3, g_s.igdn3, g_s.head3 = Deconv(N, N), GDN(N, inverse=True), Conv(N, Fc, 3, 1)
-        g_s.up2 = Deconv(N, Fc)
+        for i in range(n - 1, 0, -1):             # up<t> + igdn<t> + head<t> from the coarsest level down; up<t0> ends
+            t = self._tags[i]
+            setattr(g_s, f"up{t}", Deconv(M if i == n - 1 else N, N))
+            setattr(g_s, f"igdn{t}", GDN(N, inverse=True))
+            setattr(g_s, f"head{t}", Conv(N, ch[i], 3, 1))
+        setattr(g_s, f"up{self._tags[0]}", Deconv(N, ch[0]))
         self.g_s = g_s
         self.arena = None
         self.entropy_bottleneck.rng_auto_advance = False
         self.gaussian_conditional.rng_auto_advance = False
+        self.GATES = spec.gate_names()            # first parameter of every optimiser slice, in arena (= forward) order
 
     def _share_rng(self, device):
         eb, gc = self.entropy_bottleneck, self.gaussian_conditional
@@ -110,20 +120,15 @@ class LMSFC(nn.Module):
                 "inputs_nhwc": dict(zip(lv, ps))}
 
     def encode_y(self, ps):
-        """g_a: (p2..p5 bf16 NHWC) -> y fp32 and |y| bf16 (the input of h_a, models/google.py:294)."""
-        p2, p3, p4, p5 = ps
-        a = self.g_a
+        """g_a: (pyramid levels, bf16 NHWC) -> y fp32 and |y| bf16 (the input of h_a, models/google.py:294)."""
+        a, tags = self.g_a, self._tags
         # conv + GDN are one node each; the GDNLink lets the NEXT layer's data-gradient kernel run this GDN's backward
-        e2, l2 = a.conv2.forward_gdn(a.gdn2, p2)
-        self._gate("g_a.conv3.weight")
-        e3, l3 = a.conv3.forward_gdn(a.gdn3, e2, p3, link=l2)
-        self._gate("g_a.conv4.weight")
-        e4, l4 = a.conv4.forward_gdn(a.gdn4, e3, p4, link=l3)
-        self._gate("g_a.conv5.weight")
-        return a.conv5(e4, p5, latent_head=True, link=l4)
-
-    # first parameter of every optimiser slice of the pipelined train step, in arena (= forward) order
-    GATES = ("g_a.conv3.weight", "g_a.conv4.weight", "g_a.conv5.weight", "h_a.0.weight", "g_s.up5.weight")
+        e, link = getattr(a, f"conv{tags[0]}").forward_gdn(getattr(a, f"gdn{tags[0]}"), ps[0])
+        for i in range(1, len(tags) - 1):
+            self._gate(f"g_a.conv{tags[i]}.weight")
+            e, link = getattr(a, f"conv{tags[i]}").forward_gdn(getattr(a, f"gdn{tags[i]}"), e, ps[i], link=link)
+        self._gate(f"g_a.conv{tags[-1]}.weight")
+        return getattr(a, f"conv{tags[-1]}")(e, ps[-1], latent_head=True, link=link)
 
     def _gate(self, name):
         """Pipelined train step: wait (on the current stream) for the optimiser slice that starts at this parameter."""
@@ -154,10 +159,10 @@ class LMSFC(nn.Module):
         return scales
 
     def synthesis(self, y_hat_bf16, level_hw):
-        """g_s: y_hat -> (p2_hat, p3_hat, p4_hat, p5_hat), each cropped to its level's H x W."""
-        s = self.g_s
-        hw2, hw3, hw4, hw5 = level_hw
-        self._gate("g_s.up5.weight")
+        """g_s: y_hat -> the reconstructed levels (level 0 first), each cropped to its level's H x W."""
+        s, tags = self.g_s, self._tags
+        n = len(tags)
+        self._gate(f"g_s.up{tags[-1]}.weight")
         hs = Fn.SideStreams.heads if (self.training and torch.is_grad_enabled()) else None
         main = torch.cuda.current_stream()
 
@@ -183,27 +188,23 @@ class LMSFC(nn.Module):
         # Each d_l feeds the next up-sampling stage (main consumer) and its 3x3 head (side consumer).  The main consumer is
         # recorded FIRST: autograd then runs the head's backward first, which parks its data gradient in the GDNLink, and
         # the up-sampling stage's data-gradient kernel adds it and runs the IGDN's backward in its epilogue.
-        def sided(link):
-            if link is not None:
-                link.expect_side = True
-            return link
-
-        d5, l5 = s.up5.forward_gdn(s.igdn5, y_hat_bf16, out_hw=hw5)
-        sided(l5)
-        e5 = produced()
-        d4, l4 = s.up4.forward_gdn(s.igdn4, d5, out_hw=hw4, link=l5)
-        sided(l4)
-        e4 = produced()
-        p5h = head(s.head5, d5, l5, e5)
-        d3, l3 = s.up3.forward_gdn(s.igdn3, d4, out_hw=hw3, link=l4)
-        sided(l3)
-        e3 = produced()
-        p4h = head(s.head4, d4, l4, e4)
-        p2h = s.up2(d3, out_hw=hw2, link=l3)
-        p3h = head(s.head3, d3, l3, e3)
+        outs = [None] * n
+        d, link, pending = y_hat_bf16, None, None
+        for i in range(n - 1, 0, -1):
+            t = tags[i]
+            d, lk = getattr(s, f"up{t}").forward_gdn(getattr(s, f"igdn{t}"), d, out_hw=level_hw[i], link=link)
+            if lk is not None:
+                lk.expect_side = True
+            ev = produced()
+            if pending is not None:               # the previous level's head, recorded after this level's main consumer
+                outs[pending[0]] = head(*pending[1:])
+            pending = (i, getattr(s, f"head{t}"), d, lk, ev)
+            link = lk
+        outs[0] = getattr(s, f"up{tags[0]}")(d, out_hw=level_hw[0], link=link)
+        outs[pending[0]] = head(*pending[1:])
         if hs is not None:
             main.wait_stream(hs)
-        return p2h, p3h, p4h, p5h
+        return tuple(outs)
 
     # ------------------------------------------------------------------ entropy-coded path (models/google.py:313-333)
     @torch.no_grad()

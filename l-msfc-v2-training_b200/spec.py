@@ -31,7 +31,15 @@ from typing import Tuple
 
 @dataclass(frozen=True)
 class LMSFCSpec:
-    F: int = 256            # FPN feature channels (P2..P5)
+    """One frozen topology.  The default is the 4-level, 256-channel Faster / Mask R-CNN FPN pyramid (P2..P5); any number
+    of levels >= 2 with per-level channel counts builds the same pattern (JDE_SPEC: the 3-scale, 256/512/1024-channel
+    split of the JDE tracker, cfgs/vision_model/default.yaml:33, compressai_vision/model_wrappers/jde.py:62-180):
+
+        enc:  e_0 = GDN(conv5s2(F_0 -> N)(x_0)) ; e_l = GDN(conv5s2(N+F_l -> N)(cat[e_{l-1}, x_l])) ;
+              y = conv5s2(N+F_last -> M)(cat[e_{last-1}, x_last])
+        dec:  d_l = IGDN(deconv5s2(. -> N)(.)) for l = last .. 1 with head conv3(N -> F_l) ; x_0_hat = deconv5s2(N -> F_0)(d_1)
+    """
+    F: int = 256            # feature channels of level 0 (all levels unless level_channels says otherwise)
     N: int = 256            # hidden / hyper-latent channels
     M: int = 256            # latent channels
     levels: Tuple[str, ...] = ("p2", "p3", "p4", "p5")
@@ -39,9 +47,31 @@ class LMSFCSpec:
     distortion_scale: float = 255.0 ** 2
     scale_bound: float = 0.11
     likelihood_bound: float = 1e-9
+    level_channels: Tuple[int, ...] = ()     # () -> F for every level
+    base_stride: int = 4                     # input pixels per level-0 feature pixel (P2: 4; JDE's first split: 8)
+
+    def __post_init__(self):
+        if len(self.levels) < 2 or len(self.level_weights) != len(self.levels):
+            raise ValueError("LMSFCSpec: at least two levels, one weight per level")
+        if self.level_channels and len(self.level_channels) != len(self.levels):
+            raise ValueError("LMSFCSpec: one channel count per level")
+
+    @property
+    def channels(self):
+        return tuple(self.level_channels) if self.level_channels else (self.F,) * len(self.levels)
+
+    def tag(self, i):
+        """Module-name suffix of level i: the digits of its key ("p3" -> "3", "l61" -> "61")."""
+        d = "".join(ch for ch in self.levels[i] if ch.isdigit())
+        return d or str(i)
+
+    def gate_names(self):
+        """First parameter of every optimiser slice of the pipelined train step, in arena (= forward) order."""
+        n = len(self.levels)
+        return tuple(f"g_a.conv{self.tag(i)}.weight" for i in range(1, n)) + ("h_a.0.weight", f"g_s.up{self.tag(n - 1)}.weight")
 
     def level_shapes(self, H2: int, W2: int):
-        """(H, W) of P2..P5 given P2's size: each level halves, rounding up
+        """(H, W) of every level given level 0's size: each level halves, rounding up
         (detectron2 pads inputs to a multiple of 32, so bench shapes are exact)."""
         out, h, w = [], H2, W2
         for _ in self.levels:
@@ -50,35 +80,35 @@ class LMSFCSpec:
         return out
 
     def num_pixels(self, B: int, H2: int, W2: int) -> int:
-        return B * (4 * H2) * (4 * W2)
+        return B * (self.base_stride * H2) * (self.base_stride * W2)
 
     def conv_layers(self, H2: int, W2: int):
         """[(name, kind, k, Cin, Cout, Hin, Win, Hout, Wout)] for the FLOP counter.
         kind: 'conv' (stride 2 for k=5, 1 for k=3), 'deconv' (k5 s2), 'gdn'."""
-        F, N, M = self.F, self.N, self.M
-        (h2, w2), (h3, w3), (h4, w4), (h5, w5) = self.level_shapes(H2, W2)
+        N, M, ch = self.N, self.M, self.channels
+        shp = self.level_shapes(H2, W2)
         c = lambda v: (v + 1) // 2
-        e2 = (c(h2), c(w2)); e3 = (c(h3), c(w3)); e4 = (c(h4), c(w4)); yy = (c(h5), c(w5))
+        n = len(self.levels)
+        L = []
+        for i in range(n):
+            h, w = shp[i]
+            cin = ch[i] + (N if i else 0)
+            last = i == n - 1
+            L.append((f"g_a.conv{self.tag(i)}", "conv", 5, cin, M if last else N, h, w, c(h), c(w)))
+            if not last:
+                L.append((f"g_a.gdn{self.tag(i)}", "gdn", 1, N, N, c(h), c(w), c(h), c(w)))
+        yy = (c(shp[-1][0]), c(shp[-1][1]))
         z1 = (c(yy[0]), c(yy[1])); z2 = (c(z1[0]), c(z1[1]))
-        L = [
-            ("g_a.conv2", "conv", 5, F, N, h2, w2, *e2), ("g_a.gdn2", "gdn", 1, N, N, *e2, *e2),
-            ("g_a.conv3", "conv", 5, N + F, N, h3, w3, *e3), ("g_a.gdn3", "gdn", 1, N, N, *e3, *e3),
-            ("g_a.conv4", "conv", 5, N + F, N, h4, w4, *e4), ("g_a.gdn4", "gdn", 1, N, N, *e4, *e4),
-            ("g_a.conv5", "conv", 5, N + F, M, h5, w5, *yy),
-            ("h_a.0", "conv", 3, M, N, *yy, *yy),
-            ("h_a.2", "conv", 5, N, N, *yy, *z1),
-            ("h_a.4", "conv", 5, N, N, *z1, *z2),
-            ("h_s.0", "deconv", 5, N, N, *z2, *z1),
-            ("h_s.2", "deconv", 5, N, N, *z1, *yy),
-            ("h_s.4", "conv", 3, N, M, *yy, *yy),
-            ("g_s.up5", "deconv", 5, M, N, *yy, h5, w5), ("g_s.igdn5", "gdn", 1, N, N, h5, w5, h5, w5),
-            ("g_s.head5", "conv", 3, N, F, h5, w5, h5, w5),
-            ("g_s.up4", "deconv", 5, N, N, h5, w5, h4, w4), ("g_s.igdn4", "gdn", 1, N, N, h4, w4, h4, w4),
-            ("g_s.head4", "conv", 3, N, F, h4, w4, h4, w4),
-            ("g_s.up3", "deconv", 5, N, N, h4, w4, h3, w3), ("g_s.igdn3", "gdn", 1, N, N, h3, w3, h3, w3),
-            ("g_s.head3", "conv", 3, N, F, h3, w3, h3, w3),
-            ("g_s.up2", "deconv", 5, N, F, h3, w3, h2, w2),
-        ]
+        L += [("h_a.0", "conv", 3, M, N, *yy, *yy), ("h_a.2", "conv", 5, N, N, *yy, *z1), ("h_a.4", "conv", 5, N, N, *z1, *z2),
+              ("h_s.0", "deconv", 5, N, N, *z2, *z1), ("h_s.2", "deconv", 5, N, N, *z1, *yy), ("h_s.4", "conv", 3, N, M, *yy, *yy)]
+        src = yy
+        for i in range(n - 1, 0, -1):
+            h, w = shp[i]
+            L.append((f"g_s.up{self.tag(i)}", "deconv", 5, M if i == n - 1 else N, N, *src, h, w))
+            L.append((f"g_s.igdn{self.tag(i)}", "gdn", 1, N, N, h, w, h, w))
+            L.append((f"g_s.head{self.tag(i)}", "conv", 3, N, ch[i], h, w, h, w))
+            src = (h, w)
+        L.append((f"g_s.up{self.tag(0)}", "deconv", 5, N, ch[0], *src, *shp[0]))
         return L
 
     def flops_fwd(self, H2: int, W2: int) -> int:
@@ -97,6 +127,9 @@ class LMSFCSpec:
 
 
 DEFAULT_SPEC = LMSFCSpec()
+# BASELINE configs[4]: JDE-1088x608, the three Darknet-53 split tensors (layers 36 / 61 / 74: 256 x 76 x 136,
+# 512 x 38 x 68, 1024 x 19 x 34; cfgs/vision_model/default.yaml:33, data/mpeg-fcm/MPEGTVDTRACKING/fpn-sizes)
+JDE_SPEC = LMSFCSpec(levels=("l36", "l61", "l74"), level_weights=(1.0, 1.0, 1.0), level_channels=(256, 512, 1024), base_stride=8)
 
 # first six reference MSE lambdas, compressai/docs/source/zoo.rst:68
 LAMBDAS = (0.0018, 0.0035, 0.0067, 0.0130, 0.0250, 0.0483)

@@ -72,39 +72,63 @@ class EBParams(nn.Module):
 
 
 class OracleLMSFC(nn.Module):
+    """The graph spec.py freezes (any number of levels / per-level channels), from the restated reference modules."""
+
     def __init__(self, spec):
         super().__init__()
         self.spec = spec
-        Fc, N, M = spec.F, spec.N, spec.M
+        N, M, ch = spec.N, spec.M, spec.channels
+        n = len(spec.levels)
+        self._tags = [spec.tag(i) for i in range(n)]
         g_a = nn.Module()
-        g_a.conv2, g_a.gdn2 = conv(Fc, N), GDNParams(N)
-        g_a.conv3, g_a.gdn3 = conv(N + Fc, N), GDNParams(N)
-        g_a.conv4, g_a.gdn4 = conv(N + Fc, N), GDNParams(N)
-        g_a.conv5 = conv(N + Fc, M)
+        for i, t in enumerate(self._tags):
+            last = i == n - 1
+            setattr(g_a, f"conv{t}", conv(ch[i] + (N if i else 0), M if last else N))
+            if not last:
+                setattr(g_a, f"gdn{t}", GDNParams(N))
         self.g_a = g_a
         self.h_a = nn.Sequential(conv(M, N, 3, 1), nn.ReLU(), conv(N, N), nn.ReLU(), conv(N, N))
         self.h_s = nn.Sequential(deconv(N, N), nn.ReLU(), deconv(N, N), nn.ReLU(), conv(N, M, 3, 1), nn.ReLU())
         self.entropy_bottleneck = EBParams(N)
         g_s = nn.Module()
-        g_s.up5, g_s.igdn5, g_s.head5 = deconv(M, N), GDNParams(N, True), conv(N, Fc, 3, 1)
-        g_s.up4, g_s.igdn4, g_s.head4 = deconv(N, N), GDNParams(N, True), conv(N, Fc, 3, 1)
-        g_s.up3, g_s.igdn3, g_s.head3 = deconv(N, N), GDNParams(N, True), conv(N, Fc, 3, 1)
-        g_s.up2 = deconv(N, Fc)
+        for i in range(n - 1, 0, -1):
+            t = self._tags[i]
+            setattr(g_s, f"up{t}", deconv(M if i == n - 1 else N, N))
+            setattr(g_s, f"igdn{t}", GDNParams(N, True))
+            setattr(g_s, f"head{t}", conv(N, ch[i], 3, 1))
+        setattr(g_s, f"up{self._tags[0]}", deconv(N, ch[0]))
         self.g_s = g_s
 
     @staticmethod
     def _crop(t, ref):
         return t[..., : ref.shape[-2], : ref.shape[-1]]
 
+    def _analysis(self, xs):
+        a, tags = self.g_a, self._tags
+        e = getattr(a, f"gdn{tags[0]}")(getattr(a, f"conv{tags[0]}")(xs[0]))
+        for i in range(1, len(tags) - 1):
+            e = getattr(a, f"gdn{tags[i]}")(getattr(a, f"conv{tags[i]}")(torch.cat([e, xs[i]], 1)))
+        return getattr(a, f"conv{tags[-1]}")(torch.cat([e, xs[-1]], 1))
+
+    def _synthesis(self, y_hat, level_hw):
+        s, tags = self.g_s, self._tags
+        n = len(tags)
+        crop = lambda t, hw: t[..., : hw[0], : hw[1]]
+        outs = [None] * n
+        d = y_hat
+        for i in range(n - 1, 0, -1):
+            t = tags[i]
+            d = getattr(s, f"igdn{t}")(crop(getattr(s, f"up{t}")(d), level_hw[i]))
+            outs[i] = getattr(s, f"head{t}")(d)
+        outs[0] = crop(getattr(s, f"up{tags[0]}")(d), level_hw[0])
+        return outs
+
     def forward(self, feats, noise_z=None, noise_y=None, training=True):
-        """feats: dict p2..p5 of [B,F,H,W] fp32.  noise_z in EB's [C,1,B*h*w]
+        """feats: dict of the pyramid levels, [B,F_l,H,W] fp32.  noise_z in EB's [C,1,B*h*w]
         layout, noise_y in [B,M,h,w]; drawn here (EB first) when None."""
-        p2, p3, p4, p5 = (feats[k] for k in self.spec.levels)
-        a = self.g_a
-        e2 = a.gdn2(a.conv2(p2))
-        e3 = a.gdn3(a.conv3(torch.cat([e2, p3], 1)))
-        e4 = a.gdn4(a.conv4(torch.cat([e3, p4], 1)))
-        y = a.conv5(torch.cat([e4, p5], 1))
+        lv = self.spec.levels
+        xs = [feats[k] for k in lv]
+        y = self._analysis(xs)
         ha = self.h_a
         z1 = ha[2](ha[1](ha[0](torch.abs(y))))
         z = ha[4](ha[3](z1))
@@ -119,12 +143,8 @@ class OracleLMSFC(nn.Module):
             noise_y = torch.empty_like(y).uniform_(-0.5, 0.5)
         y_hat, y_lik = O.gc_forward(y, scales, None, training, noise_y,
                                     self.spec.scale_bound, self.spec.likelihood_bound)
-        s = self.g_s
-        d5 = s.igdn5(self._crop(s.up5(y_hat), p5)); p5h = s.head5(d5)
-        d4 = s.igdn4(self._crop(s.up4(d5), p4)); p4h = s.head4(d4)
-        d3 = s.igdn3(self._crop(s.up3(d4), p3)); p3h = s.head3(d3)
-        p2h = self._crop(s.up2(d3), p2)
-        return {"x_hat": {"p2": p2h, "p3": p3h, "p4": p4h, "p5": p5h},
+        outs = self._synthesis(y_hat, [x.shape[-2:] for x in xs])
+        return {"x_hat": dict(zip(lv, outs)),
                 "likelihoods": {"y": y_lik, "z": z_lik},
                 "latents": {"y": y, "z": z, "y_hat": y_hat, "z_hat": z_hat, "scales": scales}}
 
@@ -157,12 +177,7 @@ class OracleLMSFC(nn.Module):
     def compress(self, feats):
         """ScaleHyperprior.compress (models/google.py:313-324) with the oracle's coder (oracle/rans.py)."""
         from . import rans as OR
-        p2, p3, p4, p5 = (feats[k] for k in self.spec.levels)
-        a = self.g_a
-        e2 = a.gdn2(a.conv2(p2))
-        e3 = a.gdn3(a.conv3(torch.cat([e2, p3], 1)))
-        e4 = a.gdn4(a.conv4(torch.cat([e3, p4], 1)))
-        y = a.conv5(torch.cat([e4, p5], 1))
+        y = self._analysis([feats[k] for k in self.spec.levels])
         ha = self.h_a
         z1 = ha[2](ha[1](ha[0](torch.abs(y))))
         z = ha[4](ha[3](z1))
@@ -192,13 +207,7 @@ class OracleLMSFC(nn.Module):
         indexes = self.build_indexes(scales)
         cdf, off, ln = self._gc_tabs
         y_hat = torch.from_numpy(OR.decompress(strings[0], indexes.numpy(), cdf, ln, off)).float()
-        s = self.g_s
-        crop = lambda t, hw: t[..., : hw[0], : hw[1]]
-        d5 = s.igdn5(crop(s.up5(y_hat), level_hw[3])); p5h = s.head5(d5)
-        d4 = s.igdn4(crop(s.up4(d5), level_hw[2])); p4h = s.head4(d4)
-        d3 = s.igdn3(crop(s.up3(d4), level_hw[1])); p3h = s.head3(d3)
-        p2h = crop(s.up2(d3), level_hw[0])
-        return {"x_hat": {"p2": p2h, "p3": p3h, "p4": p4h, "p5": p5h}}
+        return {"x_hat": dict(zip(self.spec.levels, self._synthesis(y_hat, level_hw)))}
 
     def aux_loss(self):
         """models/base.py:115-144."""
@@ -244,7 +253,8 @@ def synth_features(spec, B, H2, W2, seed=1234, device="cpu", dtype=torch.float32
     g = torch.Generator().manual_seed(seed)
     feats = {}
     for i, (k, (h, w)) in enumerate(zip(spec.levels, spec.level_shapes(H2, W2))):
-        a = torch.relu(torch.randn(B, spec.F, h, w, generator=g)) * (1.0 + 0.5 * i)
-        a = a + 0.1 * torch.randn(B, spec.F, h, w, generator=g)
+        C = spec.channels[i]
+        a = torch.relu(torch.randn(B, C, h, w, generator=g)) * (1.0 + 0.5 * i)
+        a = a + 0.1 * torch.randn(B, C, h, w, generator=g)
         feats[k] = a.clamp_(-26.43, 28.40).to(device=device, dtype=dtype)
     return feats
