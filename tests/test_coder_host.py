@@ -1,4 +1,4 @@
-"""Host-side logic of the coder containers (no GPU): the per-item lane container of coder.py and the codec's .bin v2."""
+"""Host-side logic of the coder containers (no GPU): the per-item lane container of coder.py and the codec's .bin v3 (v2 still read)."""
 import importlib
 import struct
 
@@ -48,18 +48,31 @@ def test_host_tensors_are_refused_not_coded_on_the_cpu():
         c.gc_build_indexes(torch.ones(1, 4), torch.ones(3), 0.11)
 
 
-def test_bin_v2_round_trip_and_bad_magic(tmp_path):
+def test_bin_v3_round_trip_v2_still_read_and_bad_magic(tmp_path):
+    import struct
     codec = importlib.import_module(PKG + ".codec").LMSFCCodec
     s = {"y_strings": [b"\x01" * 12, b"\x02" * 20], "z_strings": [b"\x03" * 8, b"\x04" * 8], "shape": (2, 3), "y_hw": (7, 10),
-         "mid_hw": (4, 5), "keys": ["p2", "p3", "p4", "p5"], "level_hw": [(50, 75), (25, 38), (13, 19), (7, 10)]}
+         "mid_hw": (4, 5), "keys": ["p2", "p3", "p4", "p5"], "level_hw": [(50, 75), (25, 38), (13, 19), (7, 10)],
+         "input_size": [(200, 300)], "org_input_size": {"height": 199, "width": 298}}
     path = tmp_path / "feat-img0.bin"
     codec._write_bin(str(path), s)
     r = codec._read_bin(str(path))
     assert r["y_strings"] == s["y_strings"] and r["z_strings"] == s["z_strings"] and r["keys"] == s["keys"]
     assert tuple(r["shape"]) == (2, 3) and tuple(r["y_hw"]) == (7, 10) and tuple(r["mid_hw"]) == (4, 5)
     assert [tuple(h) for h in r["level_hw"]] == s["level_hw"]
-    assert path.stat().st_size == 5 + 4 + 24 + 1 + 4 * (1 + 2 + 8) + 2 * 8 + 12 + 20 + 8 + 8
+    # v3 carries what a decode-only run needs (image_split_inference.py:140-145 otherwise back-fills with a warning)
+    assert r["input_size"] == [(200, 300)] and r["org_input_size"] == {"height": 199, "width": 298}
+    # a v2 file (round 1) is still readable
+    v2 = tmp_path / "old.bin"
+    with open(v2, "wb") as f:
+        f.write(b"LMSF" + struct.pack("<B", 2) + struct.pack("<I", 2) + struct.pack("<6I", 2, 3, 7, 10, 4, 5) + struct.pack("<B", 4))
+        for k, hw in zip(s["keys"], s["level_hw"]):
+            f.write(struct.pack("<B", len(k)) + k.encode() + struct.pack("<2I", *hw))
+        for ys, zs in zip(s["y_strings"], s["z_strings"]):
+            f.write(struct.pack("<2I", len(ys), len(zs)) + ys + zs)
+    r2 = codec._read_bin(str(v2))
+    assert r2["y_strings"] == s["y_strings"] and [tuple(h) for h in r2["level_hw"]] == s["level_hw"]
     bad = tmp_path / "bad.bin"
-    bad.write_bytes(b"LMSF\x01" + b"\0" * 64)                          # the v1 (raw symbol) container is not read as v2
+    bad.write_bytes(b"LMSF\x01" + b"\0" * 64)                          # the v1 (raw symbol) container is not read
     with pytest.raises(ValueError):
         codec._read_bin(str(bad))

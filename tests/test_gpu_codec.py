@@ -110,6 +110,41 @@ def test_frames_encoded_together_decode_one_at_a_time():
                 assert float((a - b).abs().max()) <= 2e-2 * float(b.abs().max()), k      # g_s itself may tile differently
 
 
+class _FakeJDE:
+    split_layer_list = [36, 61, 74]          # cfgs/vision_model/default.yaml:33
+    device = "cuda"
+
+
+def test_jde_three_scale_video_encode_in_frame_chunks(tmp_path):
+    """BASELINE configs[4]: the JDE split hands three tensors of 256 / 512 / 1024 channels, and the video pipeline gives
+    ONE encode call all frames of the sequence concatenated on N, on the CPU (video_split_inference.py:150-159,251-263).
+    One .bin, per-frame byte counts, reconstruction == the model's eval forward frame by frame."""
+    codec_m = importlib.import_module(PKG + ".codec")
+    spec_m = importlib.import_module(PKG + ".spec")
+    from oracle import lmsfc as OL
+    torch.manual_seed(0)
+    codec = codec_m.LMSFCCodec(eval_encode="bitrate", encoder_config={"qp": 2, "frame_chunk": 2, "coder_lanes": "auto"},
+                               device="cuda", vision_model=_FakeJDE(), dataset=None)
+    assert codec.spec == spec_m.JDE_SPEC
+    T, H, W = 5, 20, 28
+    f = OL.synth_features(spec_m.JDE_SPEC, T, H, W)
+    feats = {k: v.to(torch.bfloat16).float() for k, v in f.items()}            # CPU tensors
+    assert [tuple(v.shape[1:]) for v in feats.values()] == [(256, 20, 28), (512, 10, 14), (1024, 5, 7)]
+    inp = {"data": dict(zip(_FakeJDE.split_layer_list, feats.values())), "input_size": [(8 * H, 8 * W)],
+           "org_input_size": {"height": 8 * H, "width": 8 * W}}
+    res = codec.encode(inp, str(tmp_path), "seq", "TVD-01")
+    assert len(res["bytes"]) == T and all(b > 0 for b in res["bytes"])
+    dec = codec.decode(res["bitstream"], str(tmp_path), "TVD-01")
+    assert list(dec["data"].keys()) == ["36", "61", "74"] and dec["input_size"] == [(8 * H, 8 * W)]
+    assert dec["org_input_size"] == {"height": 8 * H, "width": 8 * W}
+    with torch.no_grad():
+        out = codec.model({k: v.cuda() for k, v in feats.items()})
+    for key, lv in zip(["36", "61", "74"], spec_m.JDE_SPEC.levels):
+        a, b = dec["data"][key], out["x_hat"][lv].float()
+        assert a.shape == feats[lv].shape
+        assert float((a - b).abs().max()) <= 2e-2 * float(b.abs().max()), lv      # g_s may tile chunks of 2 differently from 5
+
+
 def test_codec_refuses_cpu_device():
     codec_m = importlib.import_module(PKG + ".codec")
     with pytest.raises(RuntimeError, match="no CPU fallback"):

@@ -35,11 +35,11 @@ def _mods():
     return [importlib.import_module(f"{PKG}.{m}") for m in ("spec", "model", "train")]
 
 
-def _pair(B, H2, W2, seed=0):
+def _pair(B, H2, W2, seed=0, spec=None):
     from oracle import lmsfc as OL
     spec_m, model_m, _ = _mods()
     torch.manual_seed(seed)
-    spec = spec_m.DEFAULT_SPEC
+    spec = spec or spec_m.DEFAULT_SPEC
     net = model_m.LMSFC(spec).to(DEV)
     ref = OL.OracleLMSFC(spec).to(DEV)
     sd = net.state_dict()
@@ -59,10 +59,15 @@ def _pair(B, H2, W2, seed=0):
 # (16, 64, 64) = BASELINE configs[1], the configuration bench.py is quoted on (every tile / split-K choice of the cost
 # model, the full-wave weight-gradient kernels); (1, 128, 192) = configs[0]; (1, 200, 304) = configs[3] (y 13 x 19,
 # ragged tiles at every level)
-@pytest.mark.parametrize("B,H2,W2", [(2, 32, 32), (1, 26, 38), (16, 64, 64), (1, 128, 192), (1, 200, 304)])
+# ("jde", 1, 76, 136) = configs[4]: the 3-scale 256 / 512 / 1024-channel JDE split (spec.JDE_SPEC), one 1088x608 frame
+@pytest.mark.parametrize("B,H2,W2", [(2, 32, 32), (1, 26, 38), (16, 64, 64), (1, 128, 192), (1, 200, 304), ("jde", 76, 136),
+                                     ("jde2", 20, 28)])
 def test_forward_loss_and_gradients(B, H2, W2):
     from oracle import lmsfc as OL
-    spec, net, ref, feats, nz, ny = _pair(B, H2, W2)
+    jde = isinstance(B, str)
+    if jde:
+        B = 2 if B == "jde2" else 1
+    spec, net, ref, feats, nz, ny = _pair(B, H2, W2, spec=_mods()[0].JDE_SPEC if jde else None)
     _, _, train_m = _mods()
     lmbda = 0.013
     net.build_arena()
