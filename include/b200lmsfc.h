@@ -232,6 +232,16 @@ int lmsfc_pmf_to_quantized_cdf(const float* pmf_host, int n, int precision, uint
 int lmsfc_pmf_rows_to_cdf(const float* pmf, int pmf_stride, const float* tail, const int* pmf_length, int rows,
                           int precision, int32_t* cdf, int cdf_stride, int* status, void* stream);
 
+/* The float pmf grids in front of the integer stage, on the device (per-frame table refresh):
+ * EntropyBottleneck.update's (entropy_models.py:412-424): pmf[c][j] for sample j + pmf_start[c], j < max_length, from
+ * the packed parameters; tail[c] as :423.  GaussianConditional.update's (:632-642): pmf[s][j] for |j - pmf_center[s]|
+ * under scale_table[s]; tail[s] = 2 * lower[0].  fp32 with precise libdevice functions: within a few ulp of the
+ * reference's CPU evaluation, i.e. tables equal up to single counts (the reference tolerates +-2 on rebuilt tables). */
+int lmsfc_eb_pmf(const float* params, const float* pmf_start, int C, int max_length, float* pmf, int pmf_stride,
+                 float* tail, void* stream);
+int lmsfc_gc_pmf(const float* scale_table, const int32_t* pmf_center, int S, int max_length, float* pmf, int pmf_stride,
+                 float* tail, void* stream);
+
 /* ------------------------------------------------------------------ range-ANS entropy coding
  * Replaces the pybind11 module `compressai.ans` (cpp_exts/rans/rans_interface.cpp:108-288, ryg rans64.h) behind
  * EntropyModel.compress / decompress (entropy_models/entropy_models.py:235-325).  symbols / indexes are int32

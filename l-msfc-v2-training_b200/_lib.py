@@ -56,6 +56,8 @@ _SIGS = {
     "lmsfc_eb_backward": [P, P, P, P, P, c_int64, c_int, c_int, c_float, c_float, P, P, P],
     "lmsfc_eb_aux_loss": [P, P, P, c_int, P, P, P],
     "lmsfc_rng_advance": [P, P],
+    "lmsfc_eb_pmf": [P, P, c_int, c_int, P, c_int, P, P],
+    "lmsfc_gc_pmf": [P, P, c_int, c_int, P, c_int, P, P],
     "lmsfc_mse_forward_backward": [P, P, c_int64, c_float, P, P, P],
     "lmsfc_mse_forward_backward_multi": [c_int, P, P, P, P, P, P, P],
     "lmsfc_loss_finalize": [P, P, c_int, c_int, c_float, P, P],

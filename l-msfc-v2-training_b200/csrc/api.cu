@@ -368,6 +368,16 @@ extern "C" int lmsfc_eb_aux_loss(const float* params, const float* quantiles, co
   LMSFC_CHECK_ARG(params && quantiles && target && loss && g_quantiles && C > 0, "eb_aux_loss: null operand");
   return eb_aux(params, quantiles, target, C, loss, g_quantiles, ST(stream));
 }
+extern "C" int lmsfc_eb_pmf(const float* params, const float* pmf_start, int C, int max_length, float* pmf, int pmf_stride,
+                            float* tail, void* stream) {
+  LMSFC_CHECK_ARG(params && pmf_start && pmf && tail && pmf_stride >= max_length, "eb_pmf: null operand / stride");
+  return eb_pmf(params, pmf_start, C, max_length, pmf, pmf_stride, tail, ST(stream));
+}
+extern "C" int lmsfc_gc_pmf(const float* scale_table, const int32_t* pmf_center, int S, int max_length, float* pmf,
+                            int pmf_stride, float* tail, void* stream) {
+  LMSFC_CHECK_ARG(scale_table && pmf_center && pmf && tail && pmf_stride >= max_length, "gc_pmf: null operand / stride");
+  return gc_pmf(scale_table, pmf_center, S, max_length, pmf, pmf_stride, tail, ST(stream));
+}
 extern "C" int lmsfc_rng_advance(uint64_t* rng_state, void* stream) { return rng_advance(rng_state, ST(stream)); }
 
 // ---------------------------------------------------------------- loss / small ops / optimiser / cdf

@@ -333,6 +333,77 @@ __global__ void __launch_bounds__(128) eb_aux_kernel(const float* params, const 
   if (threadIdx.x == 0) atomicAdd(loss, local);
 }
 
+// ---------------------------------------------------------------- float pmf grids for the CDF tables (update())
+// EntropyBottleneck.update (entropy_models.py:389-429, pmf at :412-424) and GaussianConditional.update (:625-648, pmf at
+// :632-642) evaluate the likelihood on an integer grid per channel / scale before the integer stage (cdf.cu).  Here the
+// grid is evaluated on the device in fp32 with the PRECISE libdevice functions (expf, log1pf, tanhf, erfcf: no fast
+// intrinsics).  The reference's CPU float ops differ from these by a few ulp, so the 16-bit tables can differ by one
+// count where pmf * 2^16 lands next to .5 -- inside the reference's own tolerance for rebuilt tables (+-2 counts,
+// tests/test_entropy_models.py:393-398); the default update() keeps the host evaluation that is bit-identical.
+__device__ __forceinline__ float softplus_p(float x) { return x > 20.f ? x : log1pf(expf(x)); }
+__device__ __forceinline__ float sigmoid_p(float x) { return 1.f / (1.f + expf(-x)); }
+__device__ float eb_logits_precise(const float* __restrict__ q, float v) {
+  float h[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const float a = softplus_p(q[j]) * v + q[3 + j];
+    h[j] = a + tanhf(q[6 + j]) * tanhf(a);
+  }
+#pragma unroll
+  for (int l = 0; l < 3; ++l) {
+    const float* r = q + 9 + 15 * l;
+    float n[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const float a = softplus_p(r[3 * i]) * h[0] + softplus_p(r[3 * i + 1]) * h[1] + softplus_p(r[3 * i + 2]) * h[2] + r[9 + i];
+      n[i] = a + tanhf(r[12 + i]) * tanhf(a);
+    }
+    h[0] = n[0]; h[1] = n[1]; h[2] = n[2];
+  }
+  return softplus_p(q[54]) * h[0] + softplus_p(q[55]) * h[1] + softplus_p(q[56]) * h[2] + q[57];
+}
+__global__ void __launch_bounds__(128) eb_pmf_kernel(const float* __restrict__ params, const float* __restrict__ pmf_start,
+                                                     int max_length, float* __restrict__ pmf, int stride,
+                                                     float* __restrict__ tail) {
+  pdl_sync();
+  const int c = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= max_length) return;
+  const float* q = params + (size_t)c * EB_NP;
+  const float sample = (float)j + pmf_start[c];                      // arange(max_length) + pmf_start, :408-409
+  const float lower = eb_logits_precise(q, sample - 0.5f), upper = eb_logits_precise(q, sample + 0.5f);
+  const float t = lower + upper;
+  const float sg = (t > 0.f) ? -1.f : ((t < 0.f) ? 1.f : 0.f);
+  pmf[(size_t)c * stride + j] = fabsf(sigmoid_p(sg * upper) - sigmoid_p(sg * lower));
+  if (j == 0) {                                                      // tail mass: first lower + last upper of the grid, :423
+    const float last = (float)(max_length - 1) + pmf_start[c];
+    tail[c] = sigmoid_p(lower) + sigmoid_p(-eb_logits_precise(q, last + 0.5f));
+  }
+}
+__global__ void __launch_bounds__(128) gc_pmf_kernel(const float* __restrict__ table, const int* __restrict__ center,
+                                                     int max_length, float* __restrict__ pmf, int stride,
+                                                     float* __restrict__ tail) {
+  pdl_sync();
+  const int s = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= max_length) return;
+  const float scale = table[s];
+  const float v = fabsf((float)(j - center[s]));                     // |arange(max_length) - pmf_center|, :632-634
+  const float c = -0.70710678118654752440f;                          // -(2 ** -0.5), :636
+  const float upper = 0.5f * erfcf(c * ((0.5f - v) / scale)), lower = 0.5f * erfcf(c * ((-0.5f - v) / scale));
+  pmf[(size_t)s * stride + j] = upper - lower;
+  if (j == 0) tail[s] = 2.f * lower;                                 // :642
+}
+int eb_pmf(const float* params, const float* pmf_start, int C, int max_length, float* pmf, int stride, float* tail,
+           cudaStream_t s) {
+  if (C <= 0 || max_length <= 0) return LMSFC_OK;
+  LMSFC_LAUNCH(eb_pmf_kernel, dim3((max_length + 127) / 128, C), dim3(128), 0, s, params, pmf_start, max_length, pmf, stride, tail);
+  return LMSFC_OK;
+}
+int gc_pmf(const float* table, const int* center, int S, int max_length, float* pmf, int stride, float* tail, cudaStream_t s) {
+  if (S <= 0 || max_length <= 0) return LMSFC_OK;
+  LMSFC_LAUNCH(gc_pmf_kernel, dim3((max_length + 127) / 128, S), dim3(128), 0, s, table, center, max_length, pmf, stride, tail);
+  return LMSFC_OK;
+}
+
 static dim3 eb_grid(int C, int64_t P) {
   const int bx = (C + 127) / 128;
   int64_t by = (148 * 4 + bx - 1) / bx;

@@ -50,6 +50,9 @@ int eb_backward(const EbBwdArgs& a, cudaStream_t s);
 int eb_aux(const float* params, const float* quantiles, const float* target, int C, float* loss, float* g_quantiles,
            cudaStream_t s);
 int rng_advance(uint64_t* state, cudaStream_t s);
+int eb_pmf(const float* params, const float* pmf_start, int C, int max_length, float* pmf, int stride, float* tail,
+           cudaStream_t s);
+int gc_pmf(const float* table, const int* center, int S, int max_length, float* pmf, int stride, float* tail, cudaStream_t s);
 
 // ---- elementwise.cu
 int mse_fwd_bwd(const __nv_bfloat16* xhat, const __nv_bfloat16* x, int64_t n, float grad_coef, float* sse,

@@ -12,6 +12,8 @@ from typing import Any, List, Optional, Tuple, Union
 
 import numpy as np
 import scipy.stats
+import os
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -82,6 +84,10 @@ class EntropyModel(nn.Module):
         self.rng = None          # Fn.RNG, created lazily on the module's device (a model may share one)
         self.rng_offset = 0      # distinguishes the draws of different modules within one step
         self.rng_auto_advance = True   # False when the owning model advances a shared RNG once per step
+        # float pmf of update() on the device (kernels eb_pmf / gc_pmf) instead of the host: for per-frame table refresh.
+        # Off by default: the host evaluation reproduces the reference's CPU float ops bit for bit, the device one only
+        # up to single counts of the 16-bit tables (inside the reference's +-2 tolerance for rebuilt tables).
+        self.device_pmf = os.environ.get("LMSFC_DEVICE_PMF", "0") == "1"
         self.coder_lanes = 1     # strings per item (coder.py): 1 = the reference's bytes, K > 1 = interleaved container
 
     @property
@@ -303,6 +309,17 @@ class EntropyBottleneck(EntropyModel):
         pmf_start = medians - minima
         pmf_length = maxima + minima + 1
         max_length = int(pmf_length.max().item())
+        if self.device_pmf:                      # the pmf grid by one kernel on the packed parameters
+            C = self.channels
+            packed = self.packed_parameters().detach().float().contiguous()
+            pmf = torch.empty((C, max_length), dtype=torch.float32, device=dev)
+            tail_mass = torch.empty(C, dtype=torch.float32, device=dev)
+            start_d = pmf_start.float().to(dev)
+            L.eb_pmf(ptr(packed), ptr(start_d), C, max_length, ptr(pmf), max_length, ptr(tail_mass), stream())
+            self._offset = (-minima).to(dev)
+            self._quantized_cdf = self._pmf_to_cdf(pmf, tail_mass, pmf_length, max_length).to(dev)
+            self._cdf_length = (pmf_length + 2).to(dev)
+            return True
         samples = torch.arange(max_length)[None, :] + pmf_start[:, None, None]
 
         def logits(v):
@@ -428,6 +445,16 @@ class GaussianConditional(EntropyModel):
         pmf_center = torch.ceil(table * multiplier).int()
         pmf_length = 2 * pmf_center + 1
         max_length = int(torch.max(pmf_length).item())
+        if self.device_pmf:                      # the erfc grid by one kernel
+            S = table.numel()
+            pmf = torch.empty((S, max_length), dtype=torch.float32, device=dev)
+            tail_mass = torch.empty(S, dtype=torch.float32, device=dev)
+            table_d, center_d = self.scale_table.detach().float().contiguous().to(dev), pmf_center.to(dev)
+            L.gc_pmf(ptr(table_d), ptr(center_d), S, max_length, ptr(pmf), max_length, ptr(tail_mass), stream())
+            self._quantized_cdf = self._pmf_to_cdf(pmf, tail_mass, pmf_length, max_length).to(dev)
+            self._offset = (-pmf_center).to(dev)
+            self._cdf_length = (pmf_length + 2).to(dev)
+            return
         samples = torch.abs(torch.arange(max_length).int() - pmf_center[:, None]).float()
         samples_scale = table.unsqueeze(1).float()
         const = float(-(2 ** -0.5))

@@ -336,3 +336,64 @@ def test_update_tables_match_oracle(P):
     cdf, off, ln = OC.gc_update(table)
     assert np.array_equal(gc._quantized_cdf.cpu().numpy(), cdf)
     assert np.array_equal(gc._offset.cpu().numpy(), off) and np.array_equal(gc._cdf_length.cpu().numpy(), ln)
+
+
+def test_device_pmf_tables_within_reference_tolerance(P):
+    """update() with the float pmf evaluated on the device (eb_pmf / gc_pmf kernels) against the default
+    host evaluation (bit-identical to the reference).  Lengths and offsets must be equal; the 16-bit CDF entries may
+    differ by single counts where pmf * 2^16 sits next to .5 (fp32 ulp differences of erfc / tanh / exp between the CPU
+    and libdevice) -- the reference accepts +-2 counts for rebuilt tables (tests/test_entropy_models.py:393-398)."""
+    import time
+    torch.manual_seed(3)
+    eb_h = P.entropy_models.EntropyBottleneck(256).to(DEV)
+    with torch.no_grad():                       # "trained" parameters: move everything off its init
+        for n, p in eb_h.named_parameters():
+            if n == "quantiles":
+                p.copy_(torch.tensor([-12.0, 0.3, 9.0]).repeat(256, 1, 1).to(DEV) + torch.randn(256, 1, 3, device=DEV) * 2)
+                p[:, 0, 0].clamp_(max=-1.0); p[:, 0, 2].clamp_(min=1.5); p[:, 0, 1].clamp_(-0.9, 1.4)
+            else:
+                p.add_(0.3 * torch.randn_like(p))
+    eb_d = P.entropy_models.EntropyBottleneck(256).to(DEV)
+    eb_d.load_state_dict(eb_h.state_dict())
+    eb_d.device_pmf = True
+    res = {}
+    for name, m in (("host", eb_h), ("device", eb_d)):
+        m.update(force=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            m.update(force=True)
+        torch.cuda.synchronize()
+        res["eb_" + name] = (time.perf_counter() - t0) / 5 * 1e3
+    assert torch.equal(eb_h._offset, eb_d._offset) and torch.equal(eb_h._cdf_length, eb_d._cdf_length)
+    d = (eb_h._quantized_cdf - eb_d._quantized_cdf).abs()
+    res["eb_differing"] = (int((d > 0).sum()), int(d.numel()), int(d.max()))
+    assert int(d.max()) <= 2
+    gc_h = P.entropy_models.GaussianConditional(None).to(DEV)
+    gc_d = P.entropy_models.GaussianConditional(None).to(DEV)
+    gc_d.device_pmf = True
+    table = P.model.get_scale_table()
+    for name, m in (("host", gc_h), ("device", gc_d)):
+        m.update_scale_table(table, force=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            m.update_scale_table(table, force=True)
+        torch.cuda.synchronize()
+        res["gc_" + name] = (time.perf_counter() - t0) / 5 * 1e3
+    assert torch.equal(gc_h._offset, gc_d._offset) and torch.equal(gc_h._cdf_length, gc_d._cdf_length)
+    d = (gc_h._quantized_cdf - gc_d._quantized_cdf).abs()
+    res["gc_differing"] = (int((d > 0).sum()), int(d.numel()), int(d.max()))
+    assert int(d.max()) <= 2
+    print("update() ms and differing CDF entries (count, of, max):", res)
+    # a table is valid whichever way it was built: strictly increasing rows ending at 2^16, and the coder round-trips on it
+    for m in (eb_d, gc_d):
+        cdf, ln = m._quantized_cdf, m._cdf_length
+        for r in range(0, cdf.shape[0], 17):
+            row = cdf[r, : int(ln[r])]
+            assert int(row[0]) == 0 and int(row[-1]) == 1 << 16 and bool((row[1:] > row[:-1]).all())
+    x = torch.round(torch.randn(2, 256, 4, 4, device=DEV) * 3)
+    strings = eb_d.compress(x)
+    back = eb_d.decompress(strings, x.shape[-2:])
+    med = eb_d._get_medians().detach().reshape(1, -1, 1, 1)
+    assert torch.equal(back, torch.round(x - med) + med)
