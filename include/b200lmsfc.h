@@ -158,6 +158,11 @@ int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C, int HW, vo
 /* ------------------------------------------------------------------ optimiser (examples/train.py:100-107) */
 /* accum += sum(g^2), deterministic (fixed-order two-stage reduction); set_flag (nullable device int) = 1 afterwards */
 int lmsfc_sumsq(const float* g, int64_t n, float* accum, int* set_flag, void* stream);
+/* The same in slices, so that the norm overlaps the backward pass instead of trailing it: *out = sum(g[0:n]^2) of one
+ * arena slice (overwritten), launched as soon as the slice's gradients are complete; then out = sum of the parts in index
+ * order (set_flag as above). */
+int lmsfc_sumsq_part(const float* g, int64_t n, float* out, void* stream);
+int lmsfc_sum_parts(const float* parts, int n, float* out, int* set_flag, void* stream);
 /* clip_grad_norm_(max_norm) + torch.optim.Adam step over a flat fp32 arena; p_bf16 (nullable) gets
  * the bf16 shadow; step (device int) is incremented; scratch (>=8 floats) receives
  * {clip_coef, bias_corr1, bias_corr2, grad_norm, lr, active, -, -}.  sumsq null or max_norm<=0 -> no clipping. */

@@ -415,7 +415,16 @@ extern "C" int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C,
   return nchw_to_nhwc_bf16(in, (bf16*)out, B, C, HW, ST(stream));
 }
 extern "C" int lmsfc_sumsq(const float* g, int64_t n, float* accum, int* set_flag, void* stream) {
-  return sumsq_f32(g, n, accum, set_flag, ST(stream));
+  return sumsq_f32(g, n, accum, set_flag, 0, ST(stream));
+}
+extern "C" int lmsfc_sumsq_part(const float* g, int64_t n, float* out, void* stream) {
+  LMSFC_CHECK_ARG(out != nullptr, "sumsq_part: null result");
+  if (n == 0) return sum_parts(nullptr, 0, out, nullptr, ST(stream));
+  return sumsq_f32(g, n, out, nullptr, 1, ST(stream));
+}
+extern "C" int lmsfc_sum_parts(const float* parts, int n, float* out, int* set_flag, void* stream) {
+  LMSFC_CHECK_ARG(parts && out && n >= 0, "sum_parts: null operand");
+  return sum_parts(parts, n, out, set_flag, ST(stream));
 }
 extern "C" int lmsfc_adam_step(float* p, float* m, float* v, const float* g, void* p_bf16, int64_t n, float lr, float beta1,
                                float beta2, float eps, float max_norm, const float* sumsq, int* step, float* scratch,

@@ -20,7 +20,8 @@ inline int grid1d(int64_t work_items) {
 // ranks holding the same (all-reduced) gradient compute bit-identical norms -> identical clip coefficients -> replicas
 // never drift apart (float atomics made the norm differ in the last bits from run to run and rank to rank).
 __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g, int64_t n4, const float* tail, int ntail,
-                                                    float* accum, float* partial, unsigned int* counter, int* set_flag) {
+                                                    float* accum, float* partial, unsigned int* counter, int* set_flag,
+                                                    int overwrite) {
   pdl_sync();
   float local = 0.f;
   for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n4; i += (int64_t)gridDim.x * TPB) {
@@ -45,18 +46,30 @@ __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g
     for (int i = threadIdx.x; i < (int)gridDim.x; i += TPB) v += __ldcg(partial + i);   // fixed order per thread
     v = block_sum(v, red);                                                               // fixed tree
     if (threadIdx.x == 0) {
-      *accum += v;
+      if (overwrite) *accum = v; else *accum += v;
       if (set_flag) *set_flag = 1;      // "an update is pending" (pipelined train step), consumed by adam_prep
     }
   }
 }
-int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, cudaStream_t s) {
+// out = parts[0] + parts[1] + ... in index order (the slices' squared norms -> the whole gradient's)
+__global__ void sum_parts_kernel(const float* parts, int n, float* out, int* set_flag) {
+  pdl_sync();
+  float s = 0.f;
+  for (int i = 0; i < n; ++i) s += parts[i];
+  *out = s;
+  if (set_flag) *set_flag = 1;
+}
+int sum_parts(const float* parts, int n, float* out, int* set_flag, cudaStream_t s) {
+  LMSFC_LAUNCH(sum_parts_kernel, dim3(1), dim3(1), 0, s, parts, n, out, set_flag);
+  return LMSFC_OK;
+}
+int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, int overwrite, cudaStream_t s) {
   if (n == 0) return LMSFC_OK;
   LMSFC_CHECK_ARG(((uintptr_t)g & 15) == 0, "sumsq: pointer must be 16-byte aligned");
   if (int rc = ensure_reduce_scratch()) return rc;
   const int64_t n4 = n / 4;
   LMSFC_LAUNCH(sumsq_kernel, dim3(grid1d(n4 > 0 ? n4 : 1)), dim3(TPB), 0, s, (const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum,
-               red_scratch(s), red_count(s) + 63, set_flag);
+               red_scratch(s), red_count(s) + 63, set_flag, overwrite);
   return LMSFC_OK;
 }
 

@@ -182,6 +182,42 @@ class BucketedGradReducer:
         self._pending = None
 
 
+class SlicedNorm(BucketedGradReducer):
+    """Single GPU: clip_grad_norm_'s squared norm (examples/train.py:100-101) slice by slice on a side stream, each part as
+    soon as the slice's gradients are complete, instead of one 112 MB pass behind the last weight gradient (23 us of
+    the 1 ms step with nothing to overlap).  Same readiness tracking as the multi-GPU reducers; fixed summation order."""
+
+    def __init__(self, model, edges):
+        from . import _lib as L
+        self.L = L
+        super().__init__(model, edges=edges)
+        self.parts = torch.zeros(len(self.buckets), dtype=torch.float32, device=self.grads.device)
+
+    def sync_replicas(self, optimizers=None):
+        pass
+
+    def _launch(self, i):
+        self.launched.append(i)
+        b = self.buckets[i]
+        evs = self._producer_events()
+        with torch.cuda.stream(self.comm_stream):
+            for ev in evs:
+                self.comm_stream.wait_event(ev)
+            self.L.sumsq_part(self.grads[b["lo"]:].data_ptr(), b["hi"] - b["lo"], self.parts[i:].data_ptr(),
+                              torch.cuda.current_stream().cuda_stream)
+
+    def finish(self, sumsq, pending_flag=None):
+        if self._pending is not None:
+            for i in range(len(self.buckets)):
+                if i not in self.launched:
+                    self._launch(i)
+        with torch.cuda.stream(self.comm_stream):
+            self.L.sum_parts(self.parts.data_ptr(), len(self.buckets), sumsq.data_ptr(),
+                             None if pending_flag is None else pending_flag.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self._pending = None
+
+
 # ====================================================================== the exchange as this library's own kernels
 def symmetric_alloc(process_group=None):
     """-> alloc(numel, dtype, device) handing out peer-mapped ("symmetric") tensors of torch.distributed, and the list

@@ -25,7 +25,7 @@ from . import functional as Fn
 from .losses import RateDistortionLoss
 from .model import LMSFC
 from .optim import net_aux_optimizer
-from .parallel import BucketedGradReducer, ShardedExchange, symmetric_alloc
+from .parallel import BucketedGradReducer, ShardedExchange, SlicedNorm, symmetric_alloc
 
 
 class TrainStep:
@@ -70,6 +70,9 @@ class TrainStep:
             self.reducer = BucketedGradReducer(model, bucket_mb=bucket_mb) if distributed else None
         if self.reducer is not None:
             self.reducer.sync_replicas(self.opt)     # replicas start from rank 0's weights, with distinct noise streams
+        # single GPU, pipelined order: the gradient norm slice by slice beside the backward pass
+        self.norms = (SlicedNorm(model, [lo for lo, _, _ in self._slices()])
+                      if (self.reducer is None and clip_max_norm > 0 and os.environ.get("LMSFC_SLICED_NORM", "1") == "1") else None)
         if side_streams:
             Fn.SideStreams.enable(self.arena.device)
         self.gate_stream = torch.cuda.Stream(device=self.arena.device, priority=-1) if self.sharded else None
@@ -167,16 +170,22 @@ class TrainStep:
         self.pending = False
         return aux.detach()
 
-    def _grad_pass(self, feats):
-        """forward -> RD loss -> backward -> [DP all-reduce] -> squared gradient norm; leaves the update pending."""
+    def _grad_pass(self, feats, aux=None):
+        """forward -> RD loss -> backward -> [DP all-reduce] -> squared gradient norm; leaves the update pending.
+        aux (the aux loss of this replay's update): the four loss scalars are packed right behind the loss kernels, not
+        behind the backward pass (where the tiny copy kernel would sit on the step's critical tail)."""
         model, opt = self.model, self.opt
         if self.reducer is not None:
             self.reducer.begin()
+        if self.norms is not None:
+            self.norms.begin()
         out = model(feats)
         if Fn.SideStreams.opt is not None:       # gradient buffers are cleared by the update pass: join before backward
             torch.cuda.current_stream().wait_stream(Fn.SideStreams.opt)
         self.arena.gates = {}
         crit = self.criterion(out, feats)
+        if aux is not None:
+            crit["scalars"] = torch.stack([crit["loss"].detach(), crit["bpp_loss"].detach(), crit["mse_loss"].detach(), aux])
         crit["loss"].backward()
         if self.reducer is not None:
             self.reducer.mark_ready(self.reducer.eb_names)
@@ -184,16 +193,19 @@ class TrainStep:
                 self.reducer.finish(pending_flag=self.pending_flag)
             else:
                 self.reducer.finish()
-        if not self.sharded:
+        if self.norms is not None:
+            self.norms.mark_ready(self.norms.eb_names)
+            self.norms.finish(opt["net"].sumsq, self.pending_flag)
+        elif not self.sharded:
             opt["net"].accumulate_norm()
         self.pending = True
         return crit
 
     def _iteration_pipelined(self, feats):
         aux = self._apply_pending()
-        crit = self._grad_pass(feats)
+        crit = self._grad_pass(feats, aux)
         return {"loss": crit["loss"].detach(), "mse_loss": crit["mse_loss"].detach(),
-                "bpp_loss": crit["bpp_loss"].detach(), "aux_loss": aux}
+                "bpp_loss": crit["bpp_loss"].detach(), "aux_loss": aux, "scalars": crit["scalars"]}
 
     def flush(self):
         """Apply the update left pending by the last pipelined replay."""
@@ -255,7 +267,8 @@ class TrainStep:
             with torch.cuda.graph(g, stream=cap):
                 out = (self._iteration_pipelined if pipelined else self._iteration)(buf)
                 # the four loss scalars packed for one device-to-host read per step
-                out["scalars"] = torch.stack([out["loss"], out["bpp_loss"], out["mse_loss"], out["aux_loss"]])
+                if "scalars" not in out:
+                    out["scalars"] = torch.stack([out["loss"], out["bpp_loss"], out["mse_loss"], out["aux_loss"]])
             self.launches_per_step = L.launch_count() - c0
             self.graphs.append(g)
             self.static_outs.append(out)
