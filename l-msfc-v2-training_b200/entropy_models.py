@@ -226,7 +226,9 @@ class EntropyBottleneck(EntropyModel):
         self.init_scale = float(init_scale)
         self.tail_mass = float(tail_mass)
         if self.filters != (3, 3, 3, 3):
-            raise ValueError("the fused kernel implements the reference's default filters=(3, 3, 3, 3)")
+            raise ValueError("EntropyBottleneck on the B200 kernels implements the reference's default filters=(3, 3, 3, 3) "
+                             "(the per-channel 1-3-3-3-3-1 network is unrolled in registers, csrc/entropy.cu); every model "
+                             "of the reference's zoo and of this path uses that default -- see INTEGRATION.md")
         filters = (1,) + self.filters + (1,)
         scale = self.init_scale ** (1 / (len(self.filters) + 1))
         channels = self.channels
