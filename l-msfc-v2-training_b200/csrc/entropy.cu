@@ -44,33 +44,71 @@ __device__ __forceinline__ float std_cumulative(float x) {  // entropy_models.py
 }
 __device__ __forceinline__ float normal_pdf(float t) { return 0.3989422804014327f * __expf(-0.5f * t * t); }
 
+// all four uniforms of one Philox block (elements 4q .. 4q+3 of draw `offset`): the same values philox_uniform returns
+__device__ __forceinline__ void philox_uniform4(uint64_t seed, uint64_t offset, uint64_t q, float (&u)[4]) {
+  uint32_t c[4] = {(uint32_t)q, (uint32_t)(q >> 32), (uint32_t)offset, (uint32_t)(offset >> 32)};
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    philox_round(c, k0, k1);
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) u[j] = (float)(c[j] >> 8) * (1.0f / 16777216.0f) - 0.5f;
+}
+
+__device__ __forceinline__ float gc_one(const GcArgs& a, float y, float mu, float u, float scale, bool has_scale, float& yh) {
+  if (a.mode == QUANT_NOISE) yh = y + u;                       // entropy_models.py:161-165
+  else if (a.mode == QUANT_DEQUANTIZE) yh = rintf(y - mu) + mu;   // :167-176 (torch.round = half to even)
+  else yh = y;                                                 // QUANT_GIVEN: the caller quantised already
+  if (!has_scale) return 1.f;
+  const float v = fabsf(yh - mu);
+  const float s = fmaxf(scale, a.scale_bound);
+  const float L = std_cumulative((0.5f - v) / s) - std_cumulative((-0.5f - v) / s);
+  return fmaxf(L, a.lik_bound);
+}
+
+// Four consecutive elements per thread: one Philox block serves all four (each thread used to recompute the block for
+// one value), 16-byte loads and stores.  Instruction-bound (two erfc per element), not HBM-bound.
 __global__ void __launch_bounds__(256) gc_forward_kernel(GcArgs a) {
   pdl_sync();
   float local = 0.f;
   // key = seed perturbed per module (`offset`), counter = device step count
   const uint64_t seed = (a.rng_state ? a.rng_state[0] : a.seed) + a.offset * 0x9E3779B97F4A7C15ull;
   const uint64_t off = a.rng_state ? a.rng_state[1] : 0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * blockDim.x) {
-    const float y = a.y[i], mu = a.means ? a.means[i] : 0.f;
-    float yh;
-    if (a.mode == QUANT_NOISE) {
-      const float u = a.noise ? a.noise[i] : philox_uniform(seed, off, (uint64_t)i);
-      yh = y + u;                                  // entropy_models.py:161-165
-    } else if (a.mode == QUANT_DEQUANTIZE) {
-      yh = rintf(y - mu) + mu;                     // :167-176 (torch.round = half to even)
-    } else {
-      yh = y;                                      // QUANT_GIVEN: the caller quantised already
+  const int64_t n4 = a.n >> 2;
+  const bool draw = a.mode == QUANT_NOISE && !a.noise;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
+    const float4 y4 = reinterpret_cast<const float4*>(a.y)[q];
+    const float4 m4 = a.means ? reinterpret_cast<const float4*>(a.means)[q] : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 s4 = a.scales ? reinterpret_cast<const float4*>(a.scales)[q] : make_float4(1.f, 1.f, 1.f, 1.f);
+    float u[4] = {0.f, 0.f, 0.f, 0.f};
+    if (draw) {
+      philox_uniform4(seed, off, (uint64_t)q, u);
+    } else if (a.noise) {
+      const float4 t = reinterpret_cast<const float4*>(a.noise)[q];
+      u[0] = t.x; u[1] = t.y; u[2] = t.z; u[3] = t.w;
     }
+    const float yy[4] = {y4.x, y4.y, y4.z, y4.w}, mm[4] = {m4.x, m4.y, m4.z, m4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+    float yh[4], lk[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) lk[j] = gc_one(a, yy[j], mm[j], u[j], ss[j], a.scales != nullptr, yh[j]);
+    if (a.y_hat) reinterpret_cast<float4*>(a.y_hat)[q] = make_float4(yh[0], yh[1], yh[2], yh[3]);
+    if (a.y_hat_bf16) reinterpret_cast<uint2*>(a.y_hat_bf16)[q] = make_uint2(pack_bf16(yh[0], yh[1]), pack_bf16(yh[2], yh[3]));
+    if (a.scales) {
+      reinterpret_cast<float4*>(a.lik)[q] = make_float4(lk[0], lk[1], lk[2], lk[3]);
+      local += __logf(lk[0]) + __logf(lk[1]) + __logf(lk[2]) + __logf(lk[3]);
+    }
+  }
+  if (blockIdx.x == 0 && (int64_t)threadIdx.x < a.n - n4 * 4) {          // scalar tail (n not a multiple of 4)
+    const int64_t i = n4 * 4 + threadIdx.x;
+    const float mu = a.means ? a.means[i] : 0.f;
+    const float u = a.mode == QUANT_NOISE ? (a.noise ? a.noise[i] : philox_uniform(seed, off, (uint64_t)i)) : 0.f;
+    float yh;
+    const float lk = gc_one(a, a.y[i], mu, u, a.scales ? a.scales[i] : 1.f, a.scales != nullptr, yh);
     if (a.y_hat) a.y_hat[i] = yh;
     if (a.y_hat_bf16) a.y_hat_bf16[i] = __float2bfloat16(yh);
-    if (a.scales) {                                // null: quantise only (the likelihood runs elsewhere)
-      const float v = fabsf(yh - mu);
-      const float s = fmaxf(a.scales[i], a.scale_bound);
-      const float L = std_cumulative((0.5f - v) / s) - std_cumulative((-0.5f - v) / s);
-      const float lik = fmaxf(L, a.lik_bound);
-      a.lik[i] = lik;
-      local += __logf(lik);
-    }
+    if (a.scales) { a.lik[i] = lk; local += __logf(lk); }
   }
   if (a.sum_ln) {
     __shared__ float red[32];
@@ -115,7 +153,9 @@ static int grid_for(int64_t n, int threads) {
 
 int gc_forward(const GcArgs& a, cudaStream_t s) {
   if (a.n <= 0) return LMSFC_OK;
-  LMSFC_LAUNCH(gc_forward_kernel, dim3(grid_for(a.n, 256)), dim3(256), 0, s, a);
+  LMSFC_CHECK_ARG((((uintptr_t)a.y | (uintptr_t)a.scales | (uintptr_t)a.means | (uintptr_t)a.noise | (uintptr_t)a.y_hat |
+                    (uintptr_t)a.lik) & 15) == 0 && ((uintptr_t)a.y_hat_bf16 & 7) == 0, "gc_forward: operands must be 16-byte aligned");
+  LMSFC_LAUNCH(gc_forward_kernel, dim3(grid_for((a.n + 3) / 4, 256)), dim3(256), 0, s, a);
   return LMSFC_OK;
 }
 int gc_backward(const GcBwdArgs& a, cudaStream_t s) {
@@ -131,6 +171,11 @@ constexpr int EB_NP = 58;
 
 __device__ __forceinline__ float softplus_t(float x) { return x > 20.f ? x : log1pf(__expf(x)); }  // torch threshold 20
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + __expf(-x)); }
+
+// tanh of a pre-activation: 1 - 2 / (e^{2a} + 1) with ex2.approx / rcp.approx (absolute error ~1e-7, saturates to +-1).
+// The precise tanhf is ~25 instructions with branches and there are 24 of them per element: the likelihood kernels
+// were bound by them (0.08 of the HBM roofline at 8 M elements).  Per-channel constants (tanh(factor)) stay precise.
+__device__ __forceinline__ float tanh_fast(float x) { return 1.f - __fdividef(2.f, __expf(2.f * x) + 1.f); }
 
 struct EbChan {
   float sp0[3], b0[3], tf0[3];
@@ -163,7 +208,7 @@ __device__ __forceinline__ float eb_logits(const EbChan& c, float v, EbTape* tp)
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
     const float a = c.sp0[j] * v + c.b0[j];
-    const float t = tanhf(a);
+    const float t = tanh_fast(a);
     h[j] = a + c.tf0[j] * t;
     if (TAPE) { tp->ta[0][j] = t; tp->h[0][j] = h[j]; }
   }
@@ -173,7 +218,7 @@ __device__ __forceinline__ float eb_logits(const EbChan& c, float v, EbTape* tp)
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       const float a = c.sp[l][3 * i] * h[0] + c.sp[l][3 * i + 1] * h[1] + c.sp[l][3 * i + 2] * h[2] + c.b[l][i];
-      const float t = tanhf(a);
+      const float t = tanh_fast(a);
       n[i] = a + c.tf[l][i] * t;
       if (TAPE) { tp->ta[l + 1][i] = t; tp->h[l + 1][i] = n[i]; }
     }

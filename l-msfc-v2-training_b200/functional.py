@@ -627,13 +627,18 @@ class _GCFn(torch.autograd.Function):
         return g_y, g_s, g_m, None, None, None, None, None, None
 
 
+def _al16(t):
+    """The vectorised entropy kernels use 16-byte accesses: re-home a view that starts at an odd offset."""
+    return t if (t is None or t.data_ptr() % 16 == 0) else t.clone(memory_format=CL)
+
+
 def gc_apply(y, scales, means, noise, mode, scale_bound, lik_bound, rng=None, offset=1):
-    y = nhwc(y, F32)
-    scales = nhwc(scales, F32)
+    y = _al16(nhwc(y, F32))
+    scales = _al16(nhwc(scales, F32))
     if means is not None:
-        means = nhwc(means, F32)
+        means = _al16(nhwc(means, F32))
     if noise is not None:
-        noise = nhwc(noise, F32)
+        noise = _al16(nhwc(noise, F32))
     out, lik, out_b = _GCFn.apply(y, scales, means, noise, _mode_id(mode), float(scale_bound), float(lik_bound), rng, offset)
     setattr(out, _BF16_ATTR, out_b)
     return out, lik
@@ -663,15 +668,15 @@ class _QuantNoiseFn(torch.autograd.Function):
 
 
 def quant_noise_apply(y, noise=None, rng=None, offset=1):
-    y = nhwc(y, F32)
+    y = _al16(nhwc(y, F32))
     if noise is not None:
-        noise = nhwc(noise, F32)
+        noise = _al16(nhwc(noise, F32))
     return _QuantNoiseFn.apply(y, noise, rng, offset)
 
 
 def gc_likelihood_apply(y_hat, scales, scale_bound, lik_bound):
     """Gaussian likelihood of an already quantised latent (mode "given"); same node type as gc_apply."""
-    _, lik, _ = _GCFn.apply(nhwc(y_hat, F32), nhwc(scales, F32), None, None, 2, float(scale_bound), float(lik_bound), None, 0)
+    _, lik, _ = _GCFn.apply(_al16(nhwc(y_hat, F32)), _al16(nhwc(scales, F32)), None, None, 2, float(scale_bound), float(lik_bound), None, 0)
     return lik
 
 
