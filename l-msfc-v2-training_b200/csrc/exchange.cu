@@ -102,8 +102,11 @@ __global__ void xchg_ready_kernel(XP P, int slot) {
   wait_all(P, slot, want);
 }
 
-__global__ void __launch_bounds__(TPB) xchg_reduce_kernel(XP P, int slot, long long lo4, long long n4, float inv_world,
-                                                          float* partial, unsigned int* counter, float* norm_part) {
+// MC (NVLS) variant: <= 64 registers, so that its blocks fit beside a 256-thread, ~190-register GEMM CTA on the same SM
+// (the peer-load variant keeps world x 4 float4 in flight per thread and does not).
+template <bool MC>
+__global__ void __launch_bounds__(TPB, MC ? 4 : 1) xchg_reduce_kernel(XP P, int slot, long long lo4, long long n4, float inv_world,
+                                                                      float* partial, unsigned int* counter, float* norm_part) {
   pdl_sync();                                    // behind xchg_ready_kernel: every rank's gradients of the slice are complete
   float local = 0.f;
   float4* mine = reinterpret_cast<float4*>(P.grads[P.rank]) + lo4;
@@ -111,7 +114,7 @@ __global__ void __launch_bounds__(TPB) xchg_reduce_kernel(XP P, int slot, long l
   // before the first use (world = 8: 32 independent 16-byte loads per thread)
   constexpr int U = 4;
   const long long stride = (long long)gridDim.x * TPB;
-  if (P.mc_grads) {
+  if (MC) {
     // NVLS: the switch adds the N ranks' values; this rank receives only the sums of its own part
     const float4* mc = reinterpret_cast<const float4*>(P.mc_grads) + lo4;
     constexpr int UM = 8;
@@ -225,7 +228,7 @@ struct PushArgs {
   unsigned int* counter;
   int slot;
 };
-__global__ void __launch_bounds__(TPB) xchg_adam_push_kernel(XP P, PushArgs a) {
+__global__ void __launch_bounds__(TPB, 4) xchg_adam_push_kernel(XP P, PushArgs a) {   // <= 64 registers: fits beside a GEMM CTA
   pdl_sync();
   const unsigned long long ep = ld_tick(P.tick);
   const bool active = a.scratch[5] != 0.f;
@@ -332,13 +335,15 @@ using namespace lmsfc;
 // already running on the device -- fatal when one of those is spinning on a flag that only a later launch can raise.
 extern "C" int lmsfc_xchg_init(void) {
   cudaFuncAttributes a;
-  LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_reduce_kernel));
+  LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_reduce_kernel<false>));
+  LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_reduce_kernel<true>));
   LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_ready_kernel));
   LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_norm_publish_kernel));
   LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_norm_wait_kernel));
   LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_wait_kernel));
   LMSFC_CUDA(cudaFuncGetAttributes(&a, xchg_adam_push_kernel));
-  prefer_shared(xchg_reduce_kernel);
+  prefer_shared(xchg_reduce_kernel<false>);
+  prefer_shared(xchg_reduce_kernel<true>);
   prefer_shared(xchg_adam_push_kernel);
   return ensure_reduce_scratch();
 }
@@ -355,10 +360,14 @@ extern "C" int lmsfc_xchg_reduce(const lmsfc_xchg_peers* peers, int slot, int64_
   if (ctas < 1) ctas = 1;
   if (max_ctas <= 0) max_ctas = 2 * 148;         // two blocks per SM keep ~1.2 MB of 16-byte loads in flight
   if (ctas > max_ctas) ctas = max_ctas;
-  prefer_shared(xchg_reduce_kernel);
   LMSFC_LAUNCH(xchg_ready_kernel, dim3(1), dim3(32), 0, ST(stream), P, slot);
-  LMSFC_LAUNCH(xchg_reduce_kernel, dim3((unsigned)ctas), dim3(TPB), 0, ST(stream), P, slot, (long long)(lo / 4), n4,
-               1.0f / (float)P.world, red_scratch(ST(stream)), red_count(ST(stream)) + 62, norm_part);
+  if (P.mc_grads) {
+    LMSFC_LAUNCH(xchg_reduce_kernel<true>, dim3((unsigned)ctas), dim3(TPB), 0, ST(stream), P, slot, (long long)(lo / 4), n4,
+                 1.0f / (float)P.world, red_scratch(ST(stream)), red_count(ST(stream)) + 62, norm_part);
+  } else {
+    LMSFC_LAUNCH(xchg_reduce_kernel<false>, dim3((unsigned)ctas), dim3(TPB), 0, ST(stream), P, slot, (long long)(lo / 4), n4,
+                 1.0f / (float)P.world, red_scratch(ST(stream)), red_count(ST(stream)) + 62, norm_part);
+  }
   return LMSFC_OK;
 }
 extern "C" int lmsfc_xchg_norm_publish(const lmsfc_xchg_peers* peers, const float* norm_parts, int nparts, int slot,
