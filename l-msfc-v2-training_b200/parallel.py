@@ -299,7 +299,10 @@ class ShardedExchange(BucketedGradReducer):
             p.grads[k], p.params[k], p.shadow[k], p.flags[k], p.norm_all[k] = pg_[k], pp_[k], ps_[k], pf_[k], pn_[k]
         p.tick = self.tick.data_ptr()
         # NVSwitch multicast (NVLS) when the allocator provides it: in-switch reduction, one-store all-gather
-        use_mc = os.environ.get("LMSFC_XCHG_MULTICAST", "1") == "1" and mg and mp and ms
+        # measured (profiles/r2_scaling.txt): 2 ranks 1.096 ms/step with peer loads vs 1.105 with multicast, 4 ranks
+        # 1.098 vs 1.056, 8 ranks 1.153 vs 1.040 -- the switch's reduction pays from 4 ranks on
+        want_mc = os.environ.get("LMSFC_XCHG_MULTICAST", "1" if self.world > 2 else "0") == "1"
+        use_mc = want_mc and mg and mp and ms
         self.multicast = bool(use_mc)
         if use_mc:
             p.mc_grads, p.mc_params, p.mc_shadow = mg, mp, ms
