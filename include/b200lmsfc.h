@@ -151,6 +151,17 @@ int lmsfc_relu_backward(void* g_bf16_inplace, const void* out_bf16, int64_t n, v
 int lmsfc_abs_backward(const float* g_direct, const void* g_abs_bf16, const float* y, int64_t n, int relu,
                        void* g_out_bf16, void* stream);
 int lmsfc_colsum(const void* g_bf16, int64_t P, int C, float* out, void* stream);
+/* lmsfc_colsum with NO allocation inside.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments and result as lmsfc_colsum (out[c] += sum_p g[p][c], g bf16 [P][C],
+ * C a multiple of 8, out 16-byte aligned); the partial sums and arrival counters live in a file-scope device array of
+ * 296 x LMSFC_COLSUM_STATIC_MAX_C floats (1.16 MiB) + 256 B, held by every GPU that loads the library until exit.
+ * C > LMSFC_COLSUM_STATIC_MAX_C is rejected (return 1, message in lmsfc_last_error()); P is unlimited.  The call makes
+ * no cudaMalloc / cudaFree / allocating library call: one cudaMemsetAsync of the counters and one kernel on `stream`.
+ * All calls on a device share the one array: calls that overlap on the GPU (different streams without ordering) race;
+ * calls ordered by a stream or events do not. */
+#define LMSFC_COLSUM_STATIC_MAX_C 1024
+int lmsfc_colsum_static(const void* g_bf16, int64_t P, int C, float* out, void* stream);
 int lmsfc_cast_f32_bf16(const float* in, void* out, int64_t n, void* stream);
 int lmsfc_cast_bf16_f32(const void* in, float* out, int64_t n, void* stream);
 int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C, int HW, void* stream);

@@ -64,6 +64,7 @@ _SIGS = {
     "lmsfc_relu_backward": [P, P, c_int64, P],
     "lmsfc_abs_backward": [P, P, P, c_int64, c_int, P, P],
     "lmsfc_colsum": [P, c_int64, c_int, P, P],
+    "lmsfc_colsum_static": [P, c_int64, c_int, P, P],
     "lmsfc_cast_f32_bf16": [P, P, c_int64, P],
     "lmsfc_cast_bf16_f32": [P, P, c_int64, P],
     "lmsfc_nchw_to_nhwc_bf16": [P, P, c_int, c_int, c_int, P],

@@ -405,6 +405,9 @@ extern "C" int lmsfc_abs_backward(const float* g_direct, const void* g_abs, cons
 extern "C" int lmsfc_colsum(const void* g, int64_t P, int C, float* out, void* stream) {
   return colsum_bf16((const bf16*)g, P, C, out, ST(stream));
 }
+extern "C" int lmsfc_colsum_static(const void* g, int64_t P, int C, float* out, void* stream) {
+  return colsum_bf16_static((const bf16*)g, P, C, out, ST(stream));
+}
 extern "C" int lmsfc_cast_f32_bf16(const float* in, void* out, int64_t n, void* stream) {
   return cast_f32_bf16(in, (bf16*)out, n, ST(stream));
 }

@@ -337,6 +337,55 @@ int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream
   return LMSFC_OK;
 }
 
+// ---------------------------------------------------------------- column sums without any allocation
+// lmsfc_colsum_static (include/b200lmsfc.h): the colsum_kernel above with its partial-sum scratch and arrival counters
+// in file-scope device arrays instead of the cudaMalloc'ed per-stream slots, for callers that may not allocate (stream
+// capture, serving loops).  Every GPU that loads the library holds the 1.16 MiB + 256 B until exit.  In host code the
+// array names are host-side stand-ins, not device addresses: the addresses the kernel gets come from
+// cudaGetSymbolAddress, looked up once per device with that device current.  All calls share the arrays.
+constexpr int kStaticBlocksY = kRedBlocksY, kStaticMaxC = kRedMaxC, kStaticMaxDevices = 64;
+static __device__ __align__(256) float g_static_colsum_scratch[kStaticBlocksY * kStaticMaxC];
+static __device__ __align__(256) unsigned int g_static_colsum_count[64];
+namespace {
+struct StaticColsumAddr { float* scratch; unsigned int* count; };
+StaticColsumAddr g_static_addr[kStaticMaxDevices] = {};
+std::mutex g_static_mutex;
+}  // namespace
+int colsum_bf16_static(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream_t s) {
+  LMSFC_CHECK_ARG(g != nullptr && out != nullptr, "colsum_static: null pointer");
+  LMSFC_CHECK_ARG(P >= 0, "colsum_static: P=%lld is negative", (long long)P);
+  LMSFC_CHECK_ARG(C > 0 && C % 8 == 0, "colsum_static: C=%d must be a positive multiple of 8", C);
+  LMSFC_CHECK_ARG(C <= kStaticMaxC, "colsum_static: C=%d exceeds the static scratch (at most %d columns)", C, kStaticMaxC);
+  LMSFC_CHECK_ARG(((uintptr_t)out & 15) == 0, "colsum_static: out must be 16-byte aligned");
+  if (P == 0) return LMSFC_OK;
+  int dev = -1;
+  LMSFC_CUDA(cudaGetDevice(&dev));
+  LMSFC_CHECK_ARG(dev >= 0 && dev < kStaticMaxDevices, "colsum_static: device ordinal %d not supported", dev);
+  StaticColsumAddr a;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_addr[dev].scratch) {            // set-up, once per device, with that device current
+      float* sp = nullptr;
+      unsigned int* cp = nullptr;
+      LMSFC_CUDA(cudaGetSymbolAddress((void**)&sp, g_static_colsum_scratch));
+      LMSFC_CUDA(cudaGetSymbolAddress((void**)&cp, g_static_colsum_count));
+      g_static_addr[dev].count = cp;
+      g_static_addr[dev].scratch = sp;
+    }
+    a = g_static_addr[dev];
+  }
+  const int C8 = C / 8, bx = (C8 + 31) / 32;
+  int64_t by = (148 * 2 + bx - 1) / bx;
+  const int64_t maxy = (P + 7) / 8;
+  if (by > maxy) by = maxy;
+  // the counters must start at zero whatever an earlier (possibly failed) call left behind; the partial sums need no
+  // clearing, every row the last block reads is written by this launch first
+  LMSFC_CUDA(cudaMemsetAsync(a.count, 0, sizeof(unsigned int) * 64, s));
+  LMSFC_LAUNCH(colsum_kernel, dim3(dim3(bx, (unsigned)by)), dim3(dim3(32, 8)), 0, s, (const uint4*)g, P, C8, out, a.scratch,
+               a.count);
+  return LMSFC_OK;
+}
+
 // ---------------------------------------------------------------- NonNegativeParametrizer
 __global__ void reparam_fwd_kernel(const float* p, int64_t n, float bound, float ped, float* o32, __nv_bfloat16* o16) {
   pdl_sync();
