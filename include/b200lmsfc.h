@@ -193,6 +193,22 @@ int lmsfc_adam_prep(float lr, const float* lr_dev, float beta1, float beta2, flo
 int lmsfc_adam_update(float* p, float* m, float* v, float* g, void* p_bf16, int64_t n, float beta1, float beta2, float eps,
                       const float* scratch, int zero_g, void* stream);
 
+/* ------------------------------------------------------------------ the whole step as one replayable launch
+ * Replaces the per-operation eager dispatch of one training iteration (examples/train.py:85-118: every module call is
+ * a separate host-side launch) by ONE launch: every lmsfc_* call made between capture_begin and capture_end on `stream`
+ * (and on streams forked from / joined to it through events) is recorded instead of executed -- all entry points above are
+ * capturable: no allocation, no host synchronisation (lmsfc_xchg_init and the first call of the cudaMalloc'ing reductions
+ * must have happened before) -- and lmsfc_step_launch replays the recorded step on the same buffers; the host only
+ * rewrites the input buffers' contents between replays.  The graph keeps no reference to host memory; the caller keeps
+ * every device buffer alive until lmsfc_step_destroy.  (train.TrainStep captures the same calls with torch.cuda.CUDAGraph
+ * because torch's caching allocator has to follow the capture; a host without torch uses these.) */
+typedef struct lmsfc_step_graph lmsfc_step_graph;
+int lmsfc_step_capture_begin(void* stream);
+/* ends the capture and instantiates it; *kernels (nullable) = number of kernel nodes recorded */
+int lmsfc_step_capture_end(void* stream, lmsfc_step_graph** out, int* kernels);
+int lmsfc_step_launch(lmsfc_step_graph* g, void* stream);
+int lmsfc_step_destroy(lmsfc_step_graph* g);
+
 /* ------------------------------------------------------------------ data-parallel exchange over NVLink peer memory
  * Replaces nn.DataParallel (examples/train.py:64-71, 275-276) + clip_grad_norm_ + Adam (:100-103) for N <= 8 ranks of one
  * node, one process per GPU, with this library's own kernels on peer-mapped buffers (csrc/exchange.cu): each rank OWNS

@@ -87,6 +87,10 @@ _SIGS = {
                              c_float, P, c_int, P],
     "lmsfc_xchg_wait": [POINTER(XchgPeers), c_int, P],
     "lmsfc_gc_build_indexes": [P, c_int64, P, c_int, c_float, P, P],
+    "lmsfc_step_capture_begin": [P],
+    "lmsfc_step_capture_end": [P, POINTER(c_void_p), POINTER(c_int)],
+    "lmsfc_step_launch": [P, P],
+    "lmsfc_step_destroy": [P],
 }
 EXPORTS = ["lmsfc_last_error", "lmsfc_version", "lmsfc_launch_count", "lmsfc_rans_lane_cap"] + list(_SIGS)
 

@@ -459,3 +459,67 @@ extern "C" int lmsfc_pmf_rows_to_cdf(const float* pmf, int pmf_stride, const flo
                                      int precision, int32_t* cdf, int cdf_stride, int* status, void* stream) {
   return pmf_rows_to_cdf_device(pmf, pmf_stride, tail, pmf_length, rows, precision, cdf, cdf_stride, status, ST(stream));
 }
+
+// ---------------------------------------------------------------- whole-step capture / launch
+struct lmsfc_step_graph {
+  cudaGraph_t graph;
+  cudaGraphExec_t exec;
+  int kernels;
+};
+extern "C" int lmsfc_step_capture_begin(void* stream) {
+  LMSFC_CHECK_ARG(stream != nullptr, "step_capture_begin: the legacy default stream cannot be captured");
+  // thread-local mode: other host threads (a loader, an autograd worker launching on forked streams) stay legal
+  LMSFC_CUDA(cudaStreamBeginCapture(ST(stream), cudaStreamCaptureModeThreadLocal));
+  return LMSFC_OK;
+}
+extern "C" int lmsfc_step_capture_end(void* stream, lmsfc_step_graph** out, int* kernels) {
+  LMSFC_CHECK_ARG(out != nullptr, "step_capture_end: null out");
+  *out = nullptr;
+  cudaGraph_t graph = nullptr;
+  {
+    cudaError_t e = cudaStreamEndCapture(ST(stream), &graph);
+    if (e != cudaSuccess) {
+      cudaGetLastError();          // not sticky: leave no stale error behind for the caller's next launch check
+      lmsfc::set_error("step_capture_end: cudaStreamEndCapture -> %s", cudaGetErrorString(e));
+      return LMSFC_ERR_CUDA;
+    }
+  }
+  LMSFC_CHECK_ARG(graph != nullptr, "step_capture_end: the capture was invalidated (a call inside it is not capturable)");
+  size_t n = 0;
+  int nk = 0;
+  if (cudaGraphGetNodes(graph, nullptr, &n) == cudaSuccess && n > 0) {
+    cudaGraphNode_t* nodes = new cudaGraphNode_t[n];
+    if (cudaGraphGetNodes(graph, nodes, &n) == cudaSuccess)
+      for (size_t i = 0; i < n; ++i) {
+        cudaGraphNodeType t;
+        if (cudaGraphNodeGetType(nodes[i], &t) == cudaSuccess && t == cudaGraphNodeTypeKernel) ++nk;
+      }
+    delete[] nodes;
+  }
+  cudaGraphExec_t exec = nullptr;
+  cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
+  if (e != cudaSuccess) {
+    cudaGraphDestroy(graph);
+    lmsfc::set_error("step_capture_end: cudaGraphInstantiate -> %s", cudaGetErrorString(e));
+    return LMSFC_ERR_CUDA;
+  }
+  lmsfc_step_graph* g = new lmsfc_step_graph{graph, exec, nk};
+  if (kernels) *kernels = nk;
+  *out = g;
+  return LMSFC_OK;
+}
+extern "C" int lmsfc_step_launch(lmsfc_step_graph* g, void* stream) {
+  LMSFC_CHECK_ARG(g != nullptr && g->exec != nullptr, "step_launch: null graph");
+  LMSFC_CUDA(cudaGraphLaunch(g->exec, ST(stream)));
+  lmsfc::g_launch_count += (unsigned long long)g->kernels;
+  return LMSFC_OK;
+}
+extern "C" int lmsfc_step_destroy(lmsfc_step_graph* g) {
+  if (!g) return LMSFC_OK;
+  cudaError_t e1 = g->exec ? cudaGraphExecDestroy(g->exec) : cudaSuccess;
+  cudaError_t e2 = g->graph ? cudaGraphDestroy(g->graph) : cudaSuccess;
+  delete g;
+  LMSFC_CUDA(e1);
+  LMSFC_CUDA(e2);
+  return LMSFC_OK;
+}
