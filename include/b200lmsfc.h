@@ -294,6 +294,27 @@ int lmsfc_rans_decode(const uint32_t* packed, int64_t packed_words, const uint32
                       const int32_t* indexes, int items, int64_t n, int lanes, const int32_t* cdfs, int rows,
                       int cdf_stride, const int32_t* sizes, const int32_t* offsets, int32_t* symbols_out, int* status,
                       void* stream);
+/* The same coder with DECODER CHECKPOINTS, so that ONE reference-format string decodes in parallel (a string is a serial
+ * chain on the coder state: rans_interface.cpp:215-288 decodes it symbol by symbol).  While coding, the encoder notes, at
+ * every `ckpt_interval`-th symbol of a lane (a power of two >= 128), the coder state and the number of words written so
+ * far: ckpt[string][c - 1] = {state low, state high, words written} for symbol c * ckpt_interval, c = 1 .. ncp, ncp =
+ * lmsfc_rans_checkpoints(n, lanes, ckpt_interval).  That state is exactly the decoder's state in front of that symbol,
+ * so lmsfc_rans_decode_indexed starts one warp per (string, segment).  The strings themselves do not change -- they stay
+ * the reference's bytes, decodable by the stock decoder; the table travels beside them (coder.py appends it behind the
+ * string, where the stock decoder never looks).  For decode the caller rewrites the third word of every entry to the
+ * absolute word position in `packed` where the segment starts: lane_offsets[string] + words of the string - words
+ * written.  status 3: a segment did not end in the next checkpoint's state (corrupt table or string).
+ * ckpt_interval = 0: no checkpoints, identical to lmsfc_rans_encode / lmsfc_rans_decode. */
+int lmsfc_rans_checkpoints(int64_t n, int lanes, int ckpt_interval);
+int lmsfc_rans_encode_indexed(const int32_t* symbols, const int32_t* indexes, int items, int64_t n, int lanes,
+                              const int32_t* cdfs, int rows, int cdf_stride, const int32_t* sizes, const int32_t* offsets,
+                              uint32_t* scratch, int64_t lane_cap, uint32_t* lane_words, uint32_t* lane_offsets,
+                              uint32_t* packed, int64_t packed_cap, int* status, int ckpt_interval, int ncp, uint32_t* ckpt,
+                              void* stream);
+int lmsfc_rans_decode_indexed(const uint32_t* packed, int64_t packed_words, const uint32_t* lane_offsets,
+                              const int32_t* indexes, int items, int64_t n, int lanes, const int32_t* cdfs, int rows,
+                              int cdf_stride, const int32_t* sizes, const int32_t* offsets, int32_t* symbols_out, int* status,
+                              int ckpt_interval, int ncp, const uint32_t* ckpt, void* stream);
 /* GaussianConditional.build_indexes (entropy_models.py:684-689) */
 int lmsfc_gc_build_indexes(const float* scales, int64_t n, const float* scale_table, int table_len, float scale_bound,
                            int32_t* indexes, void* stream);

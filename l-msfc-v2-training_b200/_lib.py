@@ -78,6 +78,9 @@ _SIGS = {
     "lmsfc_pmf_rows_to_cdf": [P, c_int, P, P, c_int, c_int, P, c_int, P, P],
     "lmsfc_rans_encode": [P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, c_int64, P, P, P, c_int64, P, P],
     "lmsfc_rans_decode": [P, c_int64, P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, P, P],
+    "lmsfc_rans_encode_indexed": [P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, c_int64, P, P, P, c_int64, P,
+                                  c_int, c_int, P, P],
+    "lmsfc_rans_decode_indexed": [P, c_int64, P, P, c_int, c_int64, c_int, P, c_int, c_int, P, P, P, P, c_int, c_int, P, P],
     "lmsfc_set_batch_invariant": [c_int],
     "lmsfc_xchg_init": [],
     "lmsfc_xchg_reduce": [POINTER(XchgPeers), c_int, c_int64, c_int64, P, c_int, P],
@@ -92,7 +95,8 @@ _SIGS = {
     "lmsfc_step_launch": [P, P],
     "lmsfc_step_destroy": [P],
 }
-EXPORTS = ["lmsfc_last_error", "lmsfc_version", "lmsfc_launch_count", "lmsfc_rans_lane_cap"] + list(_SIGS)
+EXPORTS = ["lmsfc_last_error", "lmsfc_version", "lmsfc_launch_count", "lmsfc_rans_lane_cap",
+           "lmsfc_rans_checkpoints"] + list(_SIGS)
 
 lib.lmsfc_last_error.restype = c_char_p
 lib.lmsfc_last_error.argtypes = []
@@ -102,6 +106,8 @@ lib.lmsfc_launch_count.restype = c_uint64
 lib.lmsfc_launch_count.argtypes = []
 lib.lmsfc_rans_lane_cap.restype = c_int64
 lib.lmsfc_rans_lane_cap.argtypes = [c_int64, c_int]
+lib.lmsfc_rans_checkpoints.restype = c_int
+lib.lmsfc_rans_checkpoints.argtypes = [c_int64, c_int, c_int]
 
 
 def launch_count():

@@ -76,6 +76,9 @@ class LMSFCCodec(nn.Module):
         if lanes != "auto":
             self.model.entropy_bottleneck.coder_lanes = int(lanes)
             self.model.gaussian_conditional.coder_lanes = int(lanes)
+        index = int(enc.get("coder_index", 0))     # S > 0: decoder index every S symbols behind each reference string
+        self.model.entropy_bottleneck.coder_index = index
+        self.model.gaussian_conditional.coder_index = index
         self._tables_ready = False      # CDF tables are built on first use (after any checkpoint load)
         self.layer_keys = split or list(self.spec.levels)
 

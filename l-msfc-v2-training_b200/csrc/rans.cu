@@ -102,7 +102,8 @@ static constexpr int kEncChunk = 128;
 __global__ void __launch_bounds__(128) rans_encode_kernel(const int32_t* __restrict__ symbols,
                                                           const int32_t* __restrict__ indexes, int64_t n, int items,
                                                           int lanes, RansTables tb, uint32_t* scratch, int64_t lane_cap,
-                                                          uint32_t* lane_words, int* status) {
+                                                          uint32_t* lane_words, int* status, int ck_log2, int ncp,
+                                                          uint32_t* ckpt) {
   pdl_sync();
   __shared__ Rec recs[4][kEncChunk];
   const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -130,11 +131,26 @@ __global__ void __launch_bounds__(128) rans_encode_kernel(const int32_t* __restr
     __syncwarp();
     if (j == 0 && e.p - base < 2 * m + 2) bad = 2;         // cannot happen with lane_cap >= lmsfc_rans_lane_cap()
     if (j == 0 && bad != 2) {
+      // decoder checkpoints (lmsfc_rans_encode_indexed): the coder state right after symbol i = c * 2^ck_log2 has been
+      // coded IS the decoder's state right before it decodes symbol i, and the words emitted so far are the ones the
+      // decoder has not read yet.  Chunks hold 128 symbols and the interval is a multiple of 128: at most one per chunk.
+      int ck_u = -1;
+      if (ckpt) {
+        const int64_t i_lo = hi - m;                      // symbol of slot u: hi - 1 - u, slots cover [i_lo, hi)
+        const int64_t i_ck = ((hi - 1) >> ck_log2) << ck_log2;
+        if (i_ck >= i_lo && i_ck > 0) ck_u = (int)(hi - 1 - i_ck);
+      }
 #pragma unroll 2
       for (int u = 0; u < m; ++u) {
         const Rec c = mine[u];
         if (c.rare) {                                     // one branch for both uncommon cases
-          if (c.rare & 1u) continue;
+          if (c.rare & 1u) {
+            if (u == ck_u) {
+              uint32_t* ck = ckpt + ((size_t)t * ncp + (size_t)(((hi - 1 - u) >> ck_log2) - 1)) * 3;
+              ck[0] = (uint32_t)e.x; ck[1] = (uint32_t)(e.x >> 32); ck[2] = (uint32_t)(base + lane_cap - e.p);
+            }
+            continue;
+          }
           // bypass digits, :147-175 reversed
           const uint32_t raw = c.esc - 1u;
           int nb = 0;
@@ -144,6 +160,10 @@ __global__ void __launch_bounds__(128) rans_encode_kernel(const int32_t* __restr
           for (int q = nb / (int)kBypassMax; q > 0; --q) e.put_bits(kBypassMax);
         }
         e.put(c.magic, c.sh, c.add, c.cmpl, c.lim_hi);
+        if (u == ck_u) {
+          uint32_t* ck = ckpt + ((size_t)t * ncp + (size_t)(((hi - 1 - u) >> ck_log2) - 1)) * 3;
+          ck[0] = (uint32_t)e.x; ck[1] = (uint32_t)(e.x >> 32); ck[2] = (uint32_t)(base + lane_cap - e.p);
+        }
       }
     }
   }
@@ -246,26 +266,44 @@ static constexpr int kDecChunk = 128;
 __global__ void __launch_bounds__(128) rans_decode_kernel(const uint32_t* __restrict__ packed, int64_t packed_words,
                                                           const uint32_t* __restrict__ lane_offsets,
                                                           const int32_t* __restrict__ indexes, int64_t n, int items,
-                                                          int lanes, RansTables tb, int32_t* out, int* status) {
+                                                          int lanes, RansTables tb, int32_t* out, int* status,
+                                                          int ck_log2, int ncp, const uint32_t* __restrict__ ckpt) {
   pdl_sync();
   __shared__ int4 slots[4][kDecChunk];                    // row, size, offset, decoded value
-  const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  // one warp per (string, segment): segment c of a string starts at symbol c * 2^ck_log2 from checkpoint c - 1
+  // ({state low, state high, word position in `packed`}, lmsfc_rans_decode_indexed); without checkpoints nseg = 1
+  const int nseg = ncp + 1;
+  const int64_t wg = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t t = wg / nseg;
+  const int seg = (int)(wg - t * nseg);
   const int j = threadIdx.x & 31;
   if (t >= (int64_t)items * lanes) return;
   int4* const mine = slots[threadIdx.x >> 5];
   const int item = (int)(t / lanes), lane = (int)(t % lanes);
-  const int64_t count = lane < n ? (n - lane + lanes - 1) / lanes : 0;
+  const int64_t count_all = lane < n ? (n - lane + lanes - 1) / lanes : 0;
+  const int64_t first = (int64_t)seg << ck_log2;
+  if (seg > 0 && first >= count_all) return;
+  const int64_t count = (ckpt && first + (1ll << ck_log2) < count_all) ? first + (1ll << ck_log2) : count_all;
+  const bool has_next = count < count_all;                // the state this segment ends in is the next checkpoint
   const int32_t* idx = indexes + (int64_t)item * n;
   int32_t* dst = out + (int64_t)item * n;
   const uint32_t* w = packed + lane_offsets[t];
   Dec d;
   d.end = packed + packed_words;
-  if (w + 2 > d.end) { if (j == 0) atomicMax(status, 2); return; }
-  d.x = (uint64_t)__ldg(w) | ((uint64_t)__ldg(w + 1) << 32);                            // rans64.h:104-112
-  d.p = w + 2;
+  if (seg == 0) {
+    if (w + 2 > d.end) { if (j == 0) atomicMax(status, 2); return; }
+    d.x = (uint64_t)__ldg(w) | ((uint64_t)__ldg(w + 1) << 32);                          // rans64.h:104-112
+    d.p = w + 2;
+  } else {
+    const uint32_t* ck = ckpt + ((size_t)t * ncp + (size_t)(seg - 1)) * 3;
+    d.x = (uint64_t)__ldg(ck) | ((uint64_t)__ldg(ck + 1) << 32);
+    const uint32_t pos = __ldg(ck + 2);
+    if ((int64_t)pos > packed_words || d.x < kRansLow) { if (j == 0) atomicMax(status, 3); return; }
+    d.p = packed + pos;
+  }
   d.ahead = d.p < d.end ? __ldg(d.p) : 0u;
   int bad = 0;
-  for (int64_t lo = 0; lo < count; lo += kDecChunk) {
+  for (int64_t lo = first; lo < count; lo += kDecChunk) {
     const int m = count - lo < kDecChunk ? (int)(count - lo) : kDecChunk;
 #pragma unroll
     for (int k = 0; k < kDecChunk / 32; ++k) {
@@ -317,6 +355,11 @@ __global__ void __launch_bounds__(128) rans_decode_kernel(const uint32_t* __rest
     }
     __syncwarp();
   }
+  if (has_next) {                                         // integrity: a wrong side table cannot pass silently
+    const uint32_t* ck = ckpt + ((size_t)t * ncp + (size_t)seg) * 3;
+    const uint64_t want = (uint64_t)__ldg(ck) | ((uint64_t)__ldg(ck + 1) << 32);
+    if (d.x != want || (uint32_t)(d.p - packed) != __ldg(ck + 2)) bad = bad > 3 ? bad : 3;
+  }
   bad = __reduce_max_sync(0xffffffffu, bad);
   if (bad && j == 0) atomicMax(status, bad);
 }
@@ -352,6 +395,75 @@ extern "C" int64_t lmsfc_rans_lane_cap(int64_t n, int lanes) {
   return 2 * ((n + lanes - 1) / lanes) + 16;      // <= 52 bits per symbol (16 + 9 bypass digits) + flush + slack
 }
 
+static int check_ckpt(int interval, int64_t n, int lanes, int ncp, const char* who) {
+  LMSFC_CHECK_ARG(interval >= 128 && (interval & (interval - 1)) == 0, "%s: checkpoint interval %d is not a power of two >= 128",
+                  who, interval);
+  LMSFC_CHECK_ARG(ncp == lmsfc_rans_checkpoints(n, lanes < 1 ? 1 : lanes, interval), "%s: ncp=%d, lmsfc_rans_checkpoints() says %d", who, ncp,
+                  lmsfc_rans_checkpoints(n, lanes < 1 ? 1 : lanes, interval));
+  return LMSFC_OK;
+}
+static int ilog2(int v) { int l = 0; while ((1 << l) < v) ++l; return l; }
+
+extern "C" int lmsfc_rans_checkpoints(int64_t n, int lanes, int interval) {
+  if (lanes < 1 || interval < 1 || n <= 0) return 0;
+  const int64_t count = (n + lanes - 1) / lanes;          // the longest lane
+  return (int)((count + interval - 1) / interval - 1);
+}
+
+extern "C" int lmsfc_rans_encode_indexed(const int32_t* symbols, const int32_t* indexes, int items, int64_t n, int lanes,
+                                         const int32_t* cdfs, int rows, int cdf_stride, const int32_t* sizes,
+                                         const int32_t* offsets, uint32_t* scratch, int64_t lane_cap, uint32_t* lane_words,
+                                         uint32_t* lane_offsets, uint32_t* packed, int64_t packed_cap, int* status,
+                                         int ckpt_interval, int ncp, uint32_t* ckpt, void* stream) {
+  RansTables tb{cdfs, sizes, offsets, rows, cdf_stride};
+  if (int rc = check_tables(tb, "rans_encode")) return rc;
+  LMSFC_CHECK_ARG(items >= 0 && n >= 0 && lanes >= 1, "rans_encode: bad sizes");
+  LMSFC_CHECK_ARG(scratch && lane_words && lane_offsets && packed && status, "rans_encode: null buffer");
+  LMSFC_CHECK_ARG(n == 0 || (symbols && indexes), "rans_encode: null symbols / indexes");
+  LMSFC_CHECK_ARG(lane_cap >= lmsfc_rans_lane_cap(n, lanes), "rans_encode: lane_cap below lmsfc_rans_lane_cap()");
+  int lg = 0;
+  if (ckpt_interval) {
+    if (int rc = check_ckpt(ckpt_interval, n, lanes, ncp, "rans_encode_indexed")) return rc;
+    LMSFC_CHECK_ARG(ncp == 0 || ckpt, "rans_encode_indexed: null checkpoint table");
+    lg = ilog2(ckpt_interval);
+  } else {
+    ncp = 0; ckpt = nullptr;
+  }
+  const int64_t T = (int64_t)items * lanes;
+  LMSFC_CHECK_ARG(T * lane_cap < (1ll << 32), "rans_encode: more than 2^32 words");
+  if (T == 0) return LMSFC_OK;
+  LMSFC_LAUNCH(rans_encode_kernel, dim3(ceil_div(T * 32, 128)), dim3(128), 0, ST(stream), symbols, indexes, n, items, lanes,
+               tb, scratch, lane_cap, lane_words, status, lg, ncp, ncp ? ckpt : (uint32_t*)nullptr);
+  LMSFC_LAUNCH(rans_pack_kernel, dim3(ceil_div(T * 32, 256)), dim3(256), 0, ST(stream), (const uint32_t*)scratch,
+               lane_cap, (const uint32_t*)lane_words, T, packed, packed_cap, lane_offsets, status);
+  return LMSFC_OK;
+}
+
+extern "C" int lmsfc_rans_decode_indexed(const uint32_t* packed, int64_t packed_words, const uint32_t* lane_offsets,
+                                         const int32_t* indexes, int items, int64_t n, int lanes, const int32_t* cdfs,
+                                         int rows, int cdf_stride, const int32_t* sizes, const int32_t* offsets,
+                                         int32_t* symbols_out, int* status, int ckpt_interval, int ncp,
+                                         const uint32_t* ckpt, void* stream) {
+  RansTables tb{cdfs, sizes, offsets, rows, cdf_stride};
+  if (int rc = check_tables(tb, "rans_decode")) return rc;
+  LMSFC_CHECK_ARG(items >= 0 && n >= 0 && lanes >= 1, "rans_decode: bad sizes");
+  int lg = 0;
+  if (ckpt_interval) {
+    if (int rc = check_ckpt(ckpt_interval, n, lanes, ncp, "rans_decode_indexed")) return rc;
+    LMSFC_CHECK_ARG(ncp == 0 || ckpt, "rans_decode_indexed: null checkpoint table");
+    lg = ilog2(ckpt_interval);
+  } else {
+    ncp = 0; ckpt = nullptr;
+  }
+  const int64_t T = (int64_t)items * lanes;
+  if (T == 0) return LMSFC_OK;
+  LMSFC_CHECK_ARG(packed && lane_offsets && status && packed_words >= 2 * T, "rans_decode: string shorter than its flush words");
+  LMSFC_CHECK_ARG(n == 0 || (indexes && symbols_out), "rans_decode: null indexes / output");
+  LMSFC_LAUNCH(rans_decode_kernel, dim3(ceil_div(T * (ncp + 1) * 32, 128)), dim3(128), 0, ST(stream), packed, packed_words,
+               lane_offsets, indexes, n, items, lanes, tb, symbols_out, status, lg, ncp, ncp ? ckpt : (const uint32_t*)nullptr);
+  return LMSFC_OK;
+}
+
 extern "C" int lmsfc_rans_encode(const int32_t* symbols, const int32_t* indexes, int items, int64_t n, int lanes,
                                  const int32_t* cdfs, int rows, int cdf_stride, const int32_t* sizes,
                                  const int32_t* offsets, uint32_t* scratch, int64_t lane_cap, uint32_t* lane_words,
@@ -367,7 +479,7 @@ extern "C" int lmsfc_rans_encode(const int32_t* symbols, const int32_t* indexes,
   LMSFC_CHECK_ARG(T * lane_cap < (1ll << 32), "rans_encode: more than 2^32 words");
   if (T == 0) return LMSFC_OK;
   LMSFC_LAUNCH(rans_encode_kernel, dim3(ceil_div(T * 32, 128)), dim3(128), 0, ST(stream), symbols, indexes, n, items, lanes,
-               tb, scratch, lane_cap, lane_words, status);
+               tb, scratch, lane_cap, lane_words, status, 0, 0, (uint32_t*)nullptr);
   LMSFC_LAUNCH(rans_pack_kernel, dim3(ceil_div(T * 32, 256)), dim3(256), 0, ST(stream), (const uint32_t*)scratch,
                lane_cap, (const uint32_t*)lane_words, T, packed, packed_cap, lane_offsets, status);
   return LMSFC_OK;
@@ -385,7 +497,7 @@ extern "C" int lmsfc_rans_decode(const uint32_t* packed, int64_t packed_words, c
   LMSFC_CHECK_ARG(packed && lane_offsets && status && packed_words >= 2 * T, "rans_decode: string shorter than its flush words");
   LMSFC_CHECK_ARG(n == 0 || (indexes && symbols_out), "rans_decode: null indexes / output");
   LMSFC_LAUNCH(rans_decode_kernel, dim3(ceil_div(T * 32, 128)), dim3(128), 0, ST(stream), packed, packed_words, lane_offsets,
-               indexes, n, items, lanes, tb, symbols_out, status);
+               indexes, n, items, lanes, tb, symbols_out, status, 0, 0, (const uint32_t*)nullptr);
   return LMSFC_OK;
 }
 

@@ -89,6 +89,7 @@ class EntropyModel(nn.Module):
         # up to single counts of the 16-bit tables (inside the reference's +-2 tolerance for rebuilt tables).
         self.device_pmf = os.environ.get("LMSFC_DEVICE_PMF", "0") == "1"
         self.coder_lanes = 1     # strings per item (coder.py): 1 = the reference's bytes, K > 1 = interleaved container
+        self.coder_index = 0     # S > 0 (lanes = 1): decoder index every S symbols behind the reference string (coder.py)
 
     @property
     def offset(self):
@@ -189,7 +190,8 @@ class EntropyModel(nn.Module):
         self._check_cdf_length()
         self._check_offsets_size()
         return coder.encode_batch(symbols, indexes, self._quantized_cdf, self._cdf_length, self._offset,
-                                  self.entropy_coder_precision, lanes=int(self.coder_lanes))
+                                  self.entropy_coder_precision, lanes=int(self.coder_lanes),
+                                  index=int(self.coder_index) if int(self.coder_lanes) == 1 else 0)
 
     def decompress(self, strings, indexes, dtype: torch.dtype = torch.float, means=None):
         """:270-325."""

@@ -113,6 +113,38 @@ def main():
                          "encode_Msym_s": round(nsym / enc_us, 1), "decode_Msym_s": round(nsym / dec_us, 1),
                          "encode_GBps_algorithmic": round((16 * nsym + 4 * total_words) / enc_us / 1e3, 2)})
             print(rows[-1], flush=True)
+        # reference-format strings (K = 1) with the decoder index every S symbols behind them (coder.encode_batch(index=S))
+        for S in (4096, 1024, 256):
+            ncp = int(L.lib.lmsfc_rans_checkpoints(n, 1, S))
+            if ncp == 0:
+                continue
+            plain = c.encode_batch(ds, di, tc, ts, to)
+            strings = c.encode_batch(ds, di, tc, ts, to, index=S)
+            e2e_enc = wall(lambda: c.encode_batch(ds, di, tc, ts, to, index=S))
+            e2e_dec = wall(lambda: c.decode_batch(strings, di, tc, ts, to, lanes=1))
+            assert torch.equal(c.decode_batch(strings, di, tc, ts, to, lanes=1), ds)
+            # kernel alone: the tables as decode_batch uploads them
+            body = [np.frombuffer(a, dtype=np.uint32) for a in plain]
+            off = np.concatenate([[0], np.cumsum([b.size for b in body])])
+            tab = np.stack([np.frombuffer(b, dtype=np.uint32)[a.size: a.size + 3 * ncp].reshape(ncp, 3)
+                            for a, b in zip(body, strings)]).astype(np.int64)
+            tab[:, :, 2] = off[1:, None] - tab[:, :, 2]
+            d_packed = torch.from_numpy(np.concatenate(body).view(np.int32)).to(dev)
+            d_off = torch.from_numpy(off[:-1].astype(np.uint32).view(np.int32)).to(dev)
+            d_ck = torch.from_numpy(tab.astype(np.uint32).reshape(-1).view(np.int32)).to(dev)
+            out = torch.empty_like(ds)
+            status = torch.zeros(1, dtype=torch.int32, device=dev)
+
+            def dec_idx():
+                L.rans_decode_indexed(ptr(d_packed), int(off[-1]), ptr(d_off), ptr(di), items, n, 1, ptr(tc), tc.shape[0],
+                                      tc.shape[1], ptr(ts), ptr(to), ptr(out), ptr(status), S, ncp, ptr(d_ck), stream())
+            dec_us = ev_time(dec_idx)
+            assert torch.equal(out, ds) and int(status.item()) == 0
+            rows.append({"case": name, "symbols": items * n, "lanes_per_item": 1, "index_interval": S,
+                         "string_bytes": sum(map(len, strings)), "plain_bytes": sum(map(len, plain)),
+                         "decode_kernel_us": round(dec_us, 1), "encode_e2e_us": round(e2e_enc, 1),
+                         "decode_e2e_us": round(e2e_dec, 1), "decode_Msym_s": round(items * n / dec_us, 1)})
+            print(rows[-1], flush=True)
         if OR is not None and OR.ref_available():
             # the reference arm: compressai's own compiled coder driven as EntropyModel.compress does (1 thread)
             def ref_enc():
@@ -135,13 +167,13 @@ def main():
         feats = {k: v.to(torch.bfloat16).float()
                  for k, v in importlib.import_module(PKG + ".data").synth_features(spec, frames, H2, W2, device=dev).items()}
         inp = {"data": feats, "input_size": [(4 * H2, 4 * W2)], "org_input_size": {"height": 4 * H2, "width": 4 * W2}}
-        for K in (1, 64):
-            codec = codec_m.LMSFCCodec(eval_encode="bitrate", encoder_config={"qp": 3, "coder_lanes": K}, device=dev,
-                                       vision_model=None, dataset=None)
+        for K, S in ((1, 0), (1, 1024), (64, 0)):
+            codec = codec_m.LMSFCCodec(eval_encode="bitrate", encoder_config={"qp": 3, "coder_lanes": K, "coder_index": S},
+                                       device=dev, vision_model=None, dataset=None)
             res = codec.encode(inp, "", "", "")
             enc_us = wall(lambda: codec.encode(inp, "", "", ""), iters=5, warm=2)
             dec_us = wall(lambda: codec.decode(res["bitstream"], "", ""), iters=5, warm=2)
-            rows.append({"case": f"lmsfc codec, {frames} frame(s) {4 * H2}x{4 * W2}", "lanes_per_item": K,
+            rows.append({"case": f"lmsfc codec, {frames} frame(s) {4 * H2}x{4 * W2}", "lanes_per_item": K, "index_interval": S,
                          "bytes_per_frame": int(np.mean(res["bytes"])), "encode_ms_per_frame": round(enc_us / 1e3 / frames, 3),
                          "decode_ms_per_frame": round(dec_us / 1e3 / frames, 3)})
             print(rows[-1], flush=True)

@@ -164,3 +164,72 @@ def test_modules_compress_like_the_reference():
     tabs = [t.cpu().numpy() for t in (gc._quantized_cdf, gc._cdf_length, gc._offset)]
     assert strings == OR.compress(torch.round(y).int().cpu().numpy(), indexes.cpu().numpy(), *tabs)
     assert torch.equal(gc.decompress(strings, indexes), torch.round(y))
+
+
+# ---------------------------------------------------------------------------- decoder index (coder.encode_batch(index=S))
+@pytest.mark.parametrize("shape,S", [((1, 256, 13, 19), 1024), ((1, 256, 13, 19), 128), ((3, 256, 4, 4), 512),
+                                     ((2, 5000), 4096), ((2, 4096), 1024), ((1, 129), 128), ((2, 100), 128)])
+def test_indexed_strings_are_reference_strings_plus_a_trailer(shape, S):
+    """The bytes in front of the index are the reference's string; the stock decoder (oracle restatement of
+    rans_interface.cpp:215-288, which reads n symbols and never looks further) decodes the whole thing; the device decodes
+    it segment-parallel to the same symbols.  Escapes (bypass digits) fall on and around checkpoints."""
+    rng = np.random.default_rng(sum(shape) + S)
+    table, cdfs, sizes, offsets = _gc_tables()
+    sym, idx = _latent(rng, table, shape, outliers=0.01)
+    flat = sym.reshape(shape[0], -1)
+    flat[:, ::S] = 90000                        # an escape exactly on every checkpoint
+    flat[:, S - 1::S] = -90000                  # and right in front of it
+    c = coder()
+    plain = c.encode_batch(_t(sym), _t(idx), _t(cdfs), _t(sizes), _t(offsets))
+    s = c.encode_batch(_t(sym), _t(idx), _t(cdfs), _t(sizes), _t(offsets), index=S)
+    n = flat.shape[1]
+    ncp = (n + S - 1) // S - 1
+    for a, b in zip(plain, s):
+        assert b[:len(a)] == a
+        assert len(b) == len(a) + (12 * ncp + 12 if ncp else 0)
+    assert plain == [OR.encode(sym[i], idx[i], cdfs, sizes, offsets) for i in range(shape[0])]
+    assert np.array_equal(OR.decompress(s, idx, cdfs, sizes, offsets), sym)          # stock decoder: trailer ignored
+    out = c.decode_batch(s, _t(idx), _t(cdfs), _t(sizes), _t(offsets), lanes=1)
+    assert np.array_equal(out.cpu().numpy(), sym)
+    out = c.decode_batch(s, _t(idx), _t(cdfs), _t(sizes), _t(offsets))               # lane count read from the string: 1
+    assert np.array_equal(out.cpu().numpy(), sym)
+
+
+def test_corrupt_index_is_detected():
+    rng = np.random.default_rng(5)
+    table, cdfs, sizes, offsets = _gc_tables()
+    sym, idx = _latent(rng, table, (1, 8192))
+    c = coder()
+    s = c.encode_batch(_t(sym), _t(idx), _t(cdfs), _t(sizes), _t(offsets), index=1024)[0]
+    w = np.frombuffer(s, dtype=np.uint32).copy()
+    ncp = int(w[-3])
+    assert ncp == 7 and w[-1] == c.INDEX_MAGIC
+    bad = w.copy()
+    bad[w.size - 3 - 3 * ncp + 3 * 2] ^= 0x10          # state of checkpoint 3, low word
+    with pytest.raises(ValueError, match="decoder index"):
+        c.decode_batch([bad.tobytes()], _t(idx), _t(cdfs), _t(sizes), _t(offsets), lanes=1)
+    bad = w.copy()
+    bad[w.size - 3 - 3 * ncp + 3 * 4 + 2] += 1          # stream position of checkpoint 5
+    with pytest.raises(ValueError, match="decoder index"):
+        c.decode_batch([bad.tobytes()], _t(idx), _t(cdfs), _t(sizes), _t(offsets), lanes=1)
+    bad = w.copy()
+    bad[-3] = ncp + 1                                   # count disagrees with n: not an index, decoded as a plain string
+    out = c.decode_batch([bad.tobytes()], _t(idx), _t(cdfs), _t(sizes), _t(offsets), lanes=1)
+    assert np.array_equal(out.cpu().numpy(), sym)
+
+
+def test_modules_carry_the_index():
+    em = importlib.import_module(PKG + ".entropy_models")
+    gc = em.GaussianConditional(None).to(DEV)
+    gc.update_scale_table(OC.get_scale_table().tolist())
+    torch.manual_seed(1)
+    scales = torch.exp(torch.rand(2, 256, 13, 19, device=DEV) * 6 - 2)
+    y = torch.randn(2, 256, 13, 19, device=DEV) * scales
+    indexes = gc.build_indexes(scales)
+    plain = gc.compress(y, indexes)
+    gc.coder_index = 1024
+    s = gc.compress(y, indexes)
+    assert all(b[:len(a)] == a and len(b) > len(a) for a, b in zip(plain, s))
+    assert torch.equal(gc.decompress(s, indexes), torch.round(y))
+    gc.coder_index = 0
+    assert torch.equal(gc.decompress(s, indexes), torch.round(y))       # decoding needs no setting: the string says it
