@@ -46,7 +46,8 @@ typedef struct {
  * the batch it was computed in or on the device's SM count -- h_s(z_hat) picks CDF rows through hard thresholds
  * (entropy_models.py:684-689) and must be bit-identical in compress() and decompress(). */
 int lmsfc_set_batch_invariant(int on);
-/* out = act(conv(cat[src0,src1]) + bias).  Any of out_bf16 / out_f32 / out_abs (|.| as bf16, the
+/* out = act(conv(cat[src0,src1]) + bias).  relu: 0 none, 1 ReLU, 2 LeakyReLU(0.01) (the mean-scale hyperprior's
+ * activation, models/google.py:377-391).  Any of out_bf16 / out_f32 / out_abs (|.| as bf16, the
  * abs(y) fed to h_a, models/google.py:294) may be null. */
 int lmsfc_conv_forward(const lmsfc_conv_desc* d, const void* src0, const void* src1, const void* w,
                        const float* bias, int relu, void* out_bf16, float* out_f32, void* out_abs, void* stream);
@@ -147,7 +148,11 @@ int lmsfc_loss_finalize(const float* accum, const float* coef, int n_rate, int n
 
 /* ------------------------------------------------------------------ small gradients / layout */
 int lmsfc_relu_backward(void* g_bf16_inplace, const void* out_bf16, int64_t n, void* stream);
-/* gradient of a latent head that returned (fp32 y, bf16 |y|): g = [relu ? (y>0) : 1]*g_direct + sign(y)*g_abs */
+/* nn.LeakyReLU(slope)'s gradient from its output (models/google.py:377-391): g *= out > 0 ? 1 : slope, 0 <= slope < 1 */
+int lmsfc_leaky_relu_backward(void* g_bf16_inplace, const void* out_bf16, int64_t n, float slope, void* stream);
+/* gradient of a latent head that returned (fp32 y, bf16 |y|): g = [relu & 1 ? (y>0) : 1]*g_direct + sign(y)*g_abs;
+ * relu & 2: the head returned (fp32 y, bf16 y) (mean-scale hyperprior: h_a reads y itself, models/google.py:395): the
+ * sign factor is 1 */
 int lmsfc_abs_backward(const float* g_direct, const void* g_abs_bf16, const float* y, int64_t n, int relu,
                        void* g_out_bf16, void* stream);
 int lmsfc_colsum(const void* g_bf16, int64_t P, int C, float* out, void* stream);

@@ -62,6 +62,7 @@ _SIGS = {
     "lmsfc_mse_forward_backward_multi": [c_int, P, P, P, P, P, P, P],
     "lmsfc_loss_finalize": [P, P, c_int, c_int, c_float, P, P],
     "lmsfc_relu_backward": [P, P, c_int64, P],
+    "lmsfc_leaky_relu_backward": [P, P, c_int64, c_float, P],
     "lmsfc_abs_backward": [P, P, P, c_int64, c_int, P, P],
     "lmsfc_colsum": [P, c_int64, c_int, P, P],
     "lmsfc_colsum_static": [P, c_int64, c_int, P, P],

@@ -63,6 +63,9 @@ class LMSFCCodec(nn.Module):
                              base_stride=int(enc.get("base_stride", 4)))
         if spec is None:                                     # by the number of split tensors: 3 = JDE (cfgs/vision_model/default.yaml:33)
             spec = JDE_SPEC if len(split) == 3 else DEFAULT_SPEC
+        if enc.get("hyperprior"):                            # "scale" (default) | "mean-scale" (models/google.py:337-405)
+            import dataclasses
+            spec = dataclasses.replace(spec, hyperprior=str(enc["hyperprior"]), hyper_mid=int(enc.get("hyper_mid", 0)))
         self.spec = spec
         self.frame_chunk = int(enc.get("frame_chunk", 8))    # frames per device batch of a video-pipeline call
         self.lmbda = LAMBDAS[int(self.qp) % len(LAMBDAS)] if isinstance(self.qp, int) else float(self.qp)

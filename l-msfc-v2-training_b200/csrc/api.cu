@@ -396,7 +396,10 @@ extern "C" int lmsfc_loss_finalize(const float* accum, const float* coef, int n_
   return loss_finalize(accum, coef, n_rate, n_dist, lambda_scale, out, ST(stream));
 }
 extern "C" int lmsfc_relu_backward(void* g, const void* out, int64_t n, void* stream) {
-  return relu_bwd_bf16((bf16*)g, (const bf16*)out, n, ST(stream));
+  return relu_bwd_bf16((bf16*)g, (const bf16*)out, n, 0.f, ST(stream));
+}
+extern "C" int lmsfc_leaky_relu_backward(void* g, const void* out, int64_t n, float slope, void* stream) {
+  return relu_bwd_bf16((bf16*)g, (const bf16*)out, n, slope, ST(stream));
 }
 extern "C" int lmsfc_abs_backward(const float* g_direct, const void* g_abs, const float* y, int64_t n, int relu,
                                   void* g_out, void* stream) {

@@ -461,14 +461,16 @@ int reparam_bwd_multi(const float* g_eff, const float* params, const int64_t* ta
 }
 
 // ---------------------------------------------------------------- small activation gradients
-__global__ void relu_bwd_kernel(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n) {
+// slope 0: ReLU; slope > 0: LeakyReLU (the sign of the output is the sign of the input)
+__global__ void relu_bwd_kernel(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, float slope) {
   pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    if (!(__bfloat162float(out[i]) > 0.f)) g[i] = __float2bfloat16(0.f);
+    if (!(__bfloat162float(out[i]) > 0.f)) g[i] = __float2bfloat16(slope * __bfloat162float(g[i]));
 }
-int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, cudaStream_t s) {
+int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, float slope, cudaStream_t s) {
+  LMSFC_CHECK_ARG(slope >= 0.f && slope < 1.f, "relu_backward: slope %g outside [0, 1)", (double)slope);
   if (n == 0) return LMSFC_OK;
-  LMSFC_LAUNCH(relu_bwd_kernel, dim3(grid1d(n)), dim3(TPB), 0, s, g, out, n);
+  LMSFC_LAUNCH(relu_bwd_kernel, dim3(grid1d(n)), dim3(TPB), 0, s, g, out, n, slope);
   return LMSFC_OK;
 }
 // g_out = bf16(g_direct + sign(y) * g_abs): gradient of y feeding both GaussianConditional and h_a(|y|)
@@ -478,8 +480,8 @@ __global__ void abs_bwd_kernel(const float* gd, const __nv_bfloat16* ga, const f
   pdl_sync();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float yv = y[i];
-    const float sg = (yv > 0.f) ? 1.f : ((yv < 0.f) ? -1.f : 0.f);
-    const float d = (relu && !(yv > 0.f)) ? 0.f : (gd ? gd[i] : 0.f);
+    const float sg = (relu & 2) ? 1.f : ((yv > 0.f) ? 1.f : ((yv < 0.f) ? -1.f : 0.f));   // bit 1: second output was y, not |y|
+    const float d = ((relu & 1) && !(yv > 0.f)) ? 0.f : (gd ? gd[i] : 0.f);
     o[i] = __float2bfloat16(d + (ga ? sg * __bfloat162float(ga[i]) : 0.f));
   }
 }

@@ -147,9 +147,12 @@ __device__ __forceinline__ void epilogue_chunk(const IgemmParams& p, float (&v)[
 #pragma unroll
       for (int j = 0; j < W; ++j) v[j] += bv[j];
     }
-    if (p.relu) {
+    if (p.relu == 1) {
 #pragma unroll
       for (int j = 0; j < W; ++j) v[j] = fmaxf(v[j], 0.f);
+    } else if (p.relu == 2) {            // LeakyReLU(0.01): the mean-scale hyperprior's activation (models/google.py:377-391)
+#pragma unroll
+      for (int j = 0; j < W; ++j) v[j] = v[j] > 0.f ? v[j] : kLeakySlope * v[j];
     }
     if (p.out_f32) {
       float4* d = reinterpret_cast<float4*>(p.out_f32 + o);
@@ -765,9 +768,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) igemm_fwd_kernel(const __grid_
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] += bv[j];
           }
-          if (p.relu) {
+          if (p.relu == 1) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          } else if (p.relu == 2) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : kLeakySlope * v[j];
           }
           if (p.out_bf16) stage_bf16_32(srow_b + coff, v);
           if (p.out_f32) stage_f32_32(srow_f + coff * 2, v);

@@ -5,6 +5,7 @@
 namespace lmsfc {
 
 constexpr int kMaxTaps = 25;
+constexpr float kLeakySlope = 0.01f;   // nn.LeakyReLU's default negative_slope (IgemmParams::relu == 2)
 
 // epilogue modes of the forward/data-gradient kernel
 enum : int {

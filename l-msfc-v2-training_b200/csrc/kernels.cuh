@@ -74,7 +74,7 @@ int reparam_bwd_multi(const float* g_eff, const float* params, const int64_t* ta
                       int64_t max_n, float* g_params, cudaStream_t s);
 int colsum_bf16(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream_t s);
 int colsum_bf16_static(const __nv_bfloat16* g, int64_t P, int C, float* out, cudaStream_t s);   // no allocation
-int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, cudaStream_t s);
+int relu_bwd_bf16(__nv_bfloat16* g, const __nv_bfloat16* out, int64_t n, float slope, cudaStream_t s);
 int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, int64_t n, int relu, __nv_bfloat16* g_out,
             cudaStream_t s);
 int cast_f32_bf16(const float* in, __nv_bfloat16* out, int64_t n, cudaStream_t s);

@@ -274,8 +274,9 @@ def _conv_wgrad(state, d, x0, x1, g, weight, bias):
 
 
 class _ConvFn(torch.autograd.Function):
-    """conv / deconv (+bias, +ReLU) -- compressai/models/utils.py:128-146.
-    mode 0: returns bf16 activation; mode 1 (latent head): returns (fp32 y, bf16 |y|).
+    """conv / deconv (+bias, +ReLU / LeakyReLU) -- compressai/models/utils.py:128-146.
+    relu: 0 none, 1 ReLU, 2 LeakyReLU(0.01).  mode 0: returns bf16 activation; mode 1 (latent head): returns (fp32 y,
+    bf16 |y|); mode 2 (latent head of the mean-scale hyperprior, models/google.py:395-398): returns (fp32 y, bf16 y).
     `link` (GDNLink of the GDN that produced x0) / `side`: see GDNLink."""
 
     @staticmethod
@@ -289,9 +290,12 @@ class _ConvFn(torch.autograd.Function):
         out_b = out_f = out_a = None
         if mode == 0:
             out_b = empty_nhwc(B, state.cout, Ho, Wo, BF16, dev)
-        else:
+        elif mode == 1:
             out_f = empty_nhwc(B, state.cout, Ho, Wo, F32, dev)
             out_a = empty_nhwc(B, state.cout, Ho, Wo, BF16, dev)
+        else:
+            out_f = empty_nhwc(B, state.cout, Ho, Wo, F32, dev)
+            out_b = empty_nhwc(B, state.cout, Ho, Wo, BF16, dev)
         L.conv_forward(d, ptr(x0), ptr(x1), ptr(w), ptr(bias), int(relu), ptr(out_b), ptr(out_f), ptr(out_a), stream())
         ctx.state, ctx.relu, ctx.mode, ctx.shape = state, relu, mode, (B, H, W, Ho, Wo)
         ctx.weight, ctx.bias = weight, bias
@@ -302,7 +306,7 @@ class _ConvFn(torch.autograd.Function):
             ctx.save_for_backward(x0, x1, out_b if relu else None, None)
             return out_b
         ctx.save_for_backward(x0, x1, None, out_f)
-        return out_f, out_a
+        return out_f, (out_a if mode == 1 else out_b)
 
     @staticmethod
     def backward(ctx, *grads):
@@ -314,19 +318,28 @@ class _ConvFn(torch.autograd.Function):
             g = nhwc(grads[0], BF16)
             if ctx.relu:
                 g = g.clone(memory_format=CL)
-                L.relu_backward(ptr(g), ptr(out_relu), g.numel(), st)
+                if ctx.relu == 2:
+                    L.leaky_relu_backward(ptr(g), ptr(out_relu), g.numel(), LEAKY_SLOPE, st)
+                else:
+                    L.relu_backward(ptr(g), ptr(out_relu), g.numel(), st)
         else:
             g_direct, g_abs = grads
             g = empty_nhwc(B, state.cout, Ho, Wo, BF16, x0.device)
             gd = None if g_direct is None else nhwc(g_direct, F32)
             ga = None if g_abs is None else nhwc(g_abs, BF16)
-            L.abs_backward(ptr(gd), ptr(ga), ptr(y_f32), g.numel(), int(ctx.relu), ptr(g), st)
+            if ctx.relu == 2:
+                raise NotImplementedError("a latent head ends in no activation or ReLU (models/google.py:275-282)")
+            L.abs_backward(ptr(gd), ptr(ga), ptr(y_f32), g.numel(), int(ctx.relu) | (2 if ctx.mode == 2 else 0), ptr(g), st)
         # only source 0 is differentiable: source 1 is input data
         gx = _conv_backward(state, ctx.shape, x0, x1, g, ctx.weight, ctx.bias, ctx.need_dx, ctx.link, ctx.role)
         return gx, None, None, None, None, None, None, None, None, None
 
 
+LEAKY_SLOPE = 0.01     # nn.LeakyReLU's default; csrc/igemm.cuh kLeakySlope
+
+
 def conv_apply(state, x0, x1, weight, bias, relu=False, mode=0, out_hw=None, link=None, side=False):
+    relu = 2 if relu == "leaky" else int(relu)          # False / True / "leaky" -> the kernels' activation id
     x0 = nhwc(x0, BF16)
     if x1 is not None:
         x1 = nhwc(x1, BF16)
@@ -674,9 +687,11 @@ def quant_noise_apply(y, noise=None, rng=None, offset=1):
     return _QuantNoiseFn.apply(y, noise, rng, offset)
 
 
-def gc_likelihood_apply(y_hat, scales, scale_bound, lik_bound):
+def gc_likelihood_apply(y_hat, scales, scale_bound, lik_bound, means=None):
     """Gaussian likelihood of an already quantised latent (mode "given"); same node type as gc_apply."""
-    _, lik, _ = _GCFn.apply(_al16(nhwc(y_hat, F32)), _al16(nhwc(scales, F32)), None, None, 2, float(scale_bound), float(lik_bound), None, 0)
+    if means is not None:
+        means = _al16(nhwc(means, F32))
+    _, lik, _ = _GCFn.apply(_al16(nhwc(y_hat, F32)), _al16(nhwc(scales, F32)), means, None, 2, float(scale_bound), float(lik_bound), None, 0)
     return lik
 
 

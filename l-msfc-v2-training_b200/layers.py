@@ -71,11 +71,13 @@ class _ConvBase(nn.Module):
         return out
 
     def forward(self, x, x_cat=None, relu=False, out_hw=None, latent_head=False, link=None, side=False):
-        """`link` / `side`: the GDNLink of the GDN that produced `x` (see functional.GDNLink) -- lets this layer's
-        data-gradient kernel run that GDN's backward contraction in its epilogue."""
+        """relu: False / True / "leaky" (LeakyReLU(0.01)).  latent_head: True -> (fp32 y, bf16 |y|), "plain" -> (fp32 y,
+        bf16 y).  `link` / `side`: the GDNLink of the GDN that produced `x` (see functional.GDNLink) -- lets this
+        layer's data-gradient kernel run that GDN's backward contraction in its epilogue."""
         if (x_cat is None) != (self.concat_channels == 0):
             raise ValueError("concat source mismatch")
-        return Fn.conv_apply(self._state, x, x_cat, self.weight, self.bias, relu=relu, mode=1 if latent_head else 0,
+        mode = 2 if latent_head == "plain" else (1 if latent_head else 0)
+        return Fn.conv_apply(self._state, x, x_cat, self.weight, self.bias, relu=relu, mode=mode,
                              out_hw=out_hw, link=link, side=side)
 
     def forward_gdn(self, gdn, x, x_cat=None, out_hw=None, link=None):

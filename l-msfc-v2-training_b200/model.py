@@ -49,7 +49,13 @@ class LMSFC(nn.Module):
         self.g_a = g_a
         # keys "0","2","4" mirror the nn.Sequential(conv, ReLU, conv, ReLU, conv) of google.py:267-282
         self.h_a = nn.ModuleDict({"0": Conv(M, N, 3, 1), "2": Conv(N, N), "4": Conv(N, N)})
-        self.h_s = nn.ModuleDict({"0": Deconv(N, N), "2": Deconv(N, N), "4": Conv(N, M, 3, 1)})
+        if spec.mean_scale:       # models/google.py:377-391 (LeakyReLU between the layers, no final activation)
+            if spec.mid % 256:
+                raise ValueError(f"LMSFC on the B200 kernels: hyper_mid must be a multiple of 256, got {spec.mid}")
+            self.h_s = nn.ModuleDict({"0": Deconv(N, M), "2": Deconv(M, spec.mid), "4": Conv(spec.mid, 2 * M, 3, 1)})
+        else:
+            self.h_s = nn.ModuleDict({"0": Deconv(N, N), "2": Deconv(N, N), "4": Conv(N, M, 3, 1)})
+        self._act = "leaky" if spec.mean_scale else True
         self.entropy_bottleneck = EntropyBottleneck(N)
         self.gaussian_conditional = GaussianConditional(None, scale_bound=spec.scale_bound,
                                                         likelihood_bound=spec.likelihood_bound)
@@ -83,11 +89,11 @@ class LMSFC(nn.Module):
             y, z, z2_hw = self.analysis(ps)
             z_hat, z_lik = self.entropy_bottleneck(z, noise=noise_z)
             if self.training:
-                scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
+                scales, means = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
             else:                  # eval: the bits compress() / decompress() compute (batch-invariant tiling)
                 with L.batch_invariant():
-                    scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
-            y_hat, y_lik = self.gaussian_conditional(y, scales, noise=noise_y)
+                    scales, means = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
+            y_hat, y_lik = self.gaussian_conditional(y, scales, means=means, noise=noise_y)
             x_hat = self.synthesis(getattr(y_hat, Fn._BF16_ATTR), level_hw)
         else:
             # noise mode: y_hat = y + U needs no hyperprior -> g_s starts right away on this stream while
@@ -105,22 +111,24 @@ class LMSFC(nn.Module):
                 hs.wait_event(ev)
                 z, z2_hw = self.hyper_analysis(y_abs)
                 z_hat, z_lik = eb(z, noise=noise_z)
-                scales = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
+                scales, means = self.hyper_synthesis(getattr(z_hat, Fn._BF16_ATTR), z2_hw, y.shape[2:])
                 y_lik = Fn.gc_likelihood_apply(y_hat, scales, gc.scale_bound_value,
-                                               gc.likelihood_bound if gc.use_likelihood_bound else 0.0)
+                                               gc.likelihood_bound if gc.use_likelihood_bound else 0.0, means=means)
             x_hat = self.synthesis(y_hat_b, level_hw)
             main.wait_stream(hs)
-            for t in (z, z_hat, z_lik, scales, y_lik, getattr(z_lik, Fn._SUM_LN_ATTR), getattr(y_lik, Fn._SUM_LN_ATTR)):
-                t.record_stream(main)
+            for t in (z, z_hat, z_lik, scales, means, y_lik, getattr(z_lik, Fn._SUM_LN_ATTR), getattr(y_lik, Fn._SUM_LN_ATTR)):
+                if t is not None:
+                    t.record_stream(main)
         if self.training and noise_z is None and noise_y is None:
             self.entropy_bottleneck.rng.advance()      # ONE shared counter bump per step (EB and GC share the RNG)
         return {"x_hat": dict(zip(lv, x_hat)),
                 "likelihoods": {"y": y_lik, "z": z_lik},
-                "latents": {"y": y, "z": z, "y_hat": y_hat, "z_hat": z_hat, "scales": scales},
+                "latents": {"y": y, "z": z, "y_hat": y_hat, "z_hat": z_hat, "scales": scales, "means": means},
                 "inputs_nhwc": dict(zip(lv, ps))}
 
     def encode_y(self, ps):
-        """g_a: (pyramid levels, bf16 NHWC) -> y fp32 and |y| bf16 (the input of h_a, models/google.py:294)."""
+        """g_a: (pyramid levels, bf16 NHWC) -> y fp32 and the input of h_a in bf16: |y| (models/google.py:294), under the
+        mean-scale hyperprior y itself (:395)."""
         a, tags = self.g_a, self._tags
         # conv + GDN are one node each; the GDNLink lets the NEXT layer's data-gradient kernel run this GDN's backward
         e, link = getattr(a, f"conv{tags[0]}").forward_gdn(getattr(a, f"gdn{tags[0]}"), ps[0])
@@ -128,7 +136,7 @@ class LMSFC(nn.Module):
             self._gate(f"g_a.conv{tags[i]}.weight")
             e, link = getattr(a, f"conv{tags[i]}").forward_gdn(getattr(a, f"gdn{tags[i]}"), e, ps[i], link=link)
         self._gate(f"g_a.conv{tags[-1]}.weight")
-        return getattr(a, f"conv{tags[-1]}")(e, ps[-1], latent_head=True, link=link)
+        return getattr(a, f"conv{tags[-1]}")(e, ps[-1], latent_head="plain" if self.spec.mean_scale else True, link=link)
 
     def _gate(self, name):
         """Pipelined train step: wait (on the current stream) for the optimiser slice that starts at this parameter."""
@@ -140,8 +148,8 @@ class LMSFC(nn.Module):
     def hyper_analysis(self, y_abs):
         """h_a: |y| -> z fp32 and the spatial size of its middle activation."""
         self._gate("h_a.0.weight")
-        z1 = self.h_a["0"](y_abs, relu=True)
-        z2 = self.h_a["2"](z1, relu=True)
+        z1 = self.h_a["0"](y_abs, relu=self._act)
+        z2 = self.h_a["2"](z1, relu=self._act)
         z, _ = self.h_a["4"](z2, latent_head=True)
         return z, z2.shape[2:]
 
@@ -152,11 +160,16 @@ class LMSFC(nn.Module):
         return y, z, z2_hw
 
     def hyper_synthesis(self, z_hat_bf16, mid_hw, y_hw):
-        """h_s: z_hat -> scales (fp32, ReLU'd as models/google.py:275-282)."""
-        t = self.h_s["0"](z_hat_bf16, relu=True, out_hw=mid_hw)
-        t = self.h_s["2"](t, relu=True, out_hw=y_hw)
-        scales, _ = self.h_s["4"](t, relu=True, latent_head=True)
-        return scales
+        """h_s: z_hat -> (scales, None) (fp32, ReLU'd as models/google.py:275-282); mean-scale: -> (scales, means), the two
+        channel halves of the last layer's output (`chunk(2, 1)`, models/google.py:397-398)."""
+        t = self.h_s["0"](z_hat_bf16, relu=self._act, out_hw=mid_hw)
+        t = self.h_s["2"](t, relu=self._act, out_hw=y_hw)
+        if not self.spec.mean_scale:
+            scales, _ = self.h_s["4"](t, relu=True, latent_head=True)
+            return scales, None
+        params, _ = self.h_s["4"](t, latent_head="plain")
+        scales, means = params.chunk(2, 1)            # channel halves of an NHWC tensor: re-homed for the flat kernels
+        return scales.contiguous(memory_format=Fn.CL), means.contiguous(memory_format=Fn.CL)
 
     def synthesis(self, y_hat_bf16, level_hw):
         """g_s: y_hat -> the reconstructed levels (level 0 first), each cropped to its level's H x W."""
@@ -224,9 +237,9 @@ class LMSFC(nn.Module):
         z_strings = eb.compress(z)
         z_hat = eb.decompress(z_strings, z.shape[-2:])
         with L.batch_invariant():     # same bits whatever the batch: the decoder may see the frames one at a time
-            scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), mid_hw, y.shape[2:])
+            scales, means = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), mid_hw, y.shape[2:])
         indexes = gc.build_indexes(scales)
-        y_strings = gc.compress(y, indexes)
+        y_strings = gc.compress(y, indexes, means=means)
         return {"strings": [y_strings, z_strings], "shape": tuple(z.shape[-2:]), "y_hw": tuple(y.shape[2:]),
                 "mid_hw": tuple(mid_hw), "level_hw": [tuple(p.shape[2:]) for p in ps]}
 
@@ -239,9 +252,9 @@ class LMSFC(nn.Module):
             eb.coder_lanes = gc.coder_lanes = 0
         z_hat = eb.decompress(strings[1], shape)
         with L.batch_invariant():
-            scales = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), tuple(mid_hw), tuple(y_hw))
+            scales, means = self.hyper_synthesis(Fn.nhwc(z_hat.contiguous(), Fn.BF16), tuple(mid_hw), tuple(y_hw))
         indexes = gc.build_indexes(scales)
-        y_hat = gc.decompress(strings[0], indexes, z_hat.dtype)
+        y_hat = gc.decompress(strings[0], indexes, z_hat.dtype, means=means)
         x_hat = self.synthesis(Fn.nhwc(y_hat.contiguous(), Fn.BF16), [tuple(h) for h in level_hw])
         return {"x_hat": dict(zip(self.spec.levels, x_hat))}
 

@@ -13,6 +13,7 @@ from it, and so is the FLOP/byte counter used by bench.py.
           y  =     conv5s2(N+F -> M)(cat[e4, p5])          @ /64
     hyp:  z = h_a(|y|) ; z_hat, Lz = EntropyBottleneck(N)(z) ; s = h_s(z_hat)
           y_hat, Ly = GaussianConditional(None)(y, s)      (models/google.py:267-303)
+          hyperprior="mean-scale": z = h_a(y) ; (s, mu) = chunk(h_s(z_hat)) ; y_hat, Ly = GC(y, s, means=mu)  (:337-405)
     dec:  d5 = IGDN(deconv5s2(M -> N)(y_hat)) @ /32 ; p5_hat = conv3(N -> F)(d5)
           d4 = IGDN(deconv5s2(N -> N)(d5))    @ /16 ; p4_hat = conv3(N -> F)(d4)
           d3 = IGDN(deconv5s2(N -> N)(d4))    @ /8  ; p3_hat = conv3(N -> F)(d3)
@@ -49,12 +50,27 @@ class LMSFCSpec:
     likelihood_bound: float = 1e-9
     level_channels: Tuple[int, ...] = ()     # () -> F for every level
     base_stride: int = 4                     # input pixels per level-0 feature pixel (P2: 4; JDE's first split: 8)
+    # "scale": models/google.py:267-303 (h_a(|y|), ReLU, h_s -> scales).  "mean-scale": models/google.py:337-405 -- h_a(y),
+    # LeakyReLU, h_s: deconv(N -> M), deconv(M -> hyper_mid), conv3(hyper_mid -> 2M), chunk -> (scales, means).  The
+    # reference's middle width 3M/2 (= 384) is not a multiple of the 256-channel weight-gradient tile: default 2M.
+    hyperprior: str = "scale"
+    hyper_mid: int = 0                       # 0 -> 2 * M
 
     def __post_init__(self):
         if len(self.levels) < 2 or len(self.level_weights) != len(self.levels):
             raise ValueError("LMSFCSpec: at least two levels, one weight per level")
         if self.level_channels and len(self.level_channels) != len(self.levels):
             raise ValueError("LMSFCSpec: one channel count per level")
+        if self.hyperprior not in ("scale", "mean-scale"):
+            raise ValueError("LMSFCSpec: hyperprior is 'scale' or 'mean-scale'")
+
+    @property
+    def mean_scale(self):
+        return self.hyperprior == "mean-scale"
+
+    @property
+    def mid(self):
+        return self.hyper_mid or 2 * self.M
 
     @property
     def channels(self):
@@ -99,8 +115,12 @@ class LMSFCSpec:
                 L.append((f"g_a.gdn{self.tag(i)}", "gdn", 1, N, N, c(h), c(w), c(h), c(w)))
         yy = (c(shp[-1][0]), c(shp[-1][1]))
         z1 = (c(yy[0]), c(yy[1])); z2 = (c(z1[0]), c(z1[1]))
-        L += [("h_a.0", "conv", 3, M, N, *yy, *yy), ("h_a.2", "conv", 5, N, N, *yy, *z1), ("h_a.4", "conv", 5, N, N, *z1, *z2),
-              ("h_s.0", "deconv", 5, N, N, *z2, *z1), ("h_s.2", "deconv", 5, N, N, *z1, *yy), ("h_s.4", "conv", 3, N, M, *yy, *yy)]
+        L += [("h_a.0", "conv", 3, M, N, *yy, *yy), ("h_a.2", "conv", 5, N, N, *yy, *z1), ("h_a.4", "conv", 5, N, N, *z1, *z2)]
+        if self.mean_scale:
+            L += [("h_s.0", "deconv", 5, N, M, *z2, *z1), ("h_s.2", "deconv", 5, M, self.mid, *z1, *yy),
+                  ("h_s.4", "conv", 3, self.mid, 2 * M, *yy, *yy)]
+        else:
+            L += [("h_s.0", "deconv", 5, N, N, *z2, *z1), ("h_s.2", "deconv", 5, N, N, *z1, *yy), ("h_s.4", "conv", 3, N, M, *yy, *yy)]
         src = yy
         for i in range(n - 1, 0, -1):
             h, w = shp[i]
@@ -130,6 +150,9 @@ DEFAULT_SPEC = LMSFCSpec()
 # BASELINE configs[4]: JDE-1088x608, the three Darknet-53 split tensors (layers 36 / 61 / 74: 256 x 76 x 136,
 # 512 x 38 x 68, 1024 x 19 x 34; cfgs/vision_model/default.yaml:33, data/mpeg-fcm/MPEGTVDTRACKING/fpn-sizes)
 JDE_SPEC = LMSFCSpec(levels=("l36", "l61", "l74"), level_weights=(1.0, 1.0, 1.0), level_channels=(256, 512, 1024), base_stride=8)
+
+# the same pyramid under the mean-scale hyperprior of models/google.py:337-405
+MEAN_SCALE_SPEC = LMSFCSpec(hyperprior="mean-scale")
 
 # first six reference MSE lambdas, compressai/docs/source/zoo.rst:68
 LAMBDAS = (0.0018, 0.0035, 0.0067, 0.0130, 0.0250, 0.0483)

@@ -87,8 +87,15 @@ class OracleLMSFC(nn.Module):
             if not last:
                 setattr(g_a, f"gdn{t}", GDNParams(N))
         self.g_a = g_a
-        self.h_a = nn.Sequential(conv(M, N, 3, 1), nn.ReLU(), conv(N, N), nn.ReLU(), conv(N, N))
-        self.h_s = nn.Sequential(deconv(N, N), nn.ReLU(), deconv(N, N), nn.ReLU(), conv(N, M, 3, 1), nn.ReLU())
+        self.mean_scale = getattr(spec, "hyperprior", "scale") == "mean-scale"
+        if self.mean_scale:      # models/google.py:377-391; middle width from the spec (reference: M * 3 // 2)
+            mid = spec.mid
+            self.h_a = nn.Sequential(conv(M, N, 3, 1), nn.LeakyReLU(), conv(N, N), nn.LeakyReLU(), conv(N, N))
+            self.h_s = nn.Sequential(deconv(N, M), nn.LeakyReLU(), deconv(M, mid), nn.LeakyReLU(), conv(mid, 2 * M, 3, 1),
+                                     nn.Identity())
+        else:                    # models/google.py:267-282
+            self.h_a = nn.Sequential(conv(M, N, 3, 1), nn.ReLU(), conv(N, N), nn.ReLU(), conv(N, N))
+            self.h_s = nn.Sequential(deconv(N, N), nn.ReLU(), deconv(N, N), nn.ReLU(), conv(N, M, 3, 1), nn.ReLU())
         self.entropy_bottleneck = EBParams(N)
         g_s = nn.Module()
         for i in range(n - 1, 0, -1):
@@ -130,7 +137,7 @@ class OracleLMSFC(nn.Module):
         xs = [feats[k] for k in lv]
         y = self._analysis(xs)
         ha = self.h_a
-        z1 = ha[2](ha[1](ha[0](torch.abs(y))))
+        z1 = ha[2](ha[1](ha[0](y if self.mean_scale else torch.abs(y))))     # google.py:395 | :294
         z = ha[4](ha[3](z1))
         if training and noise_z is None:
             noise_z = torch.empty(z.shape[1], 1, z.numel() // z.shape[1], device=z.device).uniform_(-0.5, 0.5)
@@ -139,14 +146,17 @@ class OracleLMSFC(nn.Module):
         t = hs[1](self._crop(hs[0](z_hat), z1))
         t = hs[3](self._crop(hs[2](t), y))
         scales = hs[5](hs[4](t))
+        means = None
+        if self.mean_scale:
+            scales, means = scales.chunk(2, 1)                                  # google.py:397-398
         if training and noise_y is None:
             noise_y = torch.empty_like(y).uniform_(-0.5, 0.5)
-        y_hat, y_lik = O.gc_forward(y, scales, None, training, noise_y,
+        y_hat, y_lik = O.gc_forward(y, scales, means, training, noise_y,
                                     self.spec.scale_bound, self.spec.likelihood_bound)
         outs = self._synthesis(y_hat, [x.shape[-2:] for x in xs])
         return {"x_hat": dict(zip(lv, outs)),
                 "likelihoods": {"y": y_lik, "z": z_lik},
-                "latents": {"y": y, "z": z, "y_hat": y_hat, "z_hat": z_hat, "scales": scales}}
+                "latents": {"y": y, "z": z, "y_hat": y_hat, "z_hat": z_hat, "scales": scales, "means": means}}
 
 
     # ------------------------------------------------------------------ entropy-coded path (models/google.py:313-333)
@@ -171,7 +181,8 @@ class OracleLMSFC(nn.Module):
         hs = self.h_s
         t = hs[1](hs[0](z_hat)[..., : mid_hw[0], : mid_hw[1]])
         t = hs[3](hs[2](t)[..., : y_hw[0], : y_hw[1]])
-        return hs[5](hs[4](t))
+        p = hs[5](hs[4](t))
+        return tuple(p.chunk(2, 1)) if self.mean_scale else (p, None)
 
     @torch.no_grad()
     def compress(self, feats):
@@ -179,7 +190,7 @@ class OracleLMSFC(nn.Module):
         from . import rans as OR
         y = self._analysis([feats[k] for k in self.spec.levels])
         ha = self.h_a
-        z1 = ha[2](ha[1](ha[0](torch.abs(y))))
+        z1 = ha[2](ha[1](ha[0](y if self.mean_scale else torch.abs(y))))
         z = ha[4](ha[3](z1))
         med = self.entropy_bottleneck.quantiles[:, 0, 1].reshape(1, -1, 1, 1)
         cdf, off, ln = self._eb_tabs
@@ -187,10 +198,11 @@ class OracleLMSFC(nn.Module):
         z_idx = np.broadcast_to(np.arange(z.shape[1], dtype=np.int32).reshape(1, -1, 1, 1), z_sym.shape)
         z_strings = OR.compress(z_sym, z_idx, cdf, ln, off)
         z_hat = torch.from_numpy(OR.decompress(z_strings, z_idx, cdf, ln, off)).float() + med
-        scales = self._scales_from(z_hat, z1.shape[-2:], y.shape[-2:])
+        scales, means = self._scales_from(z_hat, z1.shape[-2:], y.shape[-2:])
         indexes = self.build_indexes(scales)
         cdf, off, ln = self._gc_tabs
-        y_strings = OR.compress(torch.round(y).int().numpy(), indexes.numpy(), cdf, ln, off)
+        y_sym = torch.round(y - means if means is not None else y).int()          # entropy_models.py:170-180, "symbols"
+        y_strings = OR.compress(y_sym.numpy(), indexes.numpy(), cdf, ln, off)
         return {"strings": [y_strings, z_strings], "shape": tuple(z.shape[-2:]), "y_hw": tuple(y.shape[-2:]),
                 "mid_hw": tuple(z1.shape[-2:]), "level_hw": [tuple(feats[k].shape[-2:]) for k in self.spec.levels]}
 
@@ -203,10 +215,12 @@ class OracleLMSFC(nn.Module):
         cdf, off, ln = self._eb_tabs
         z_idx = np.broadcast_to(np.arange(N, dtype=np.int32).reshape(1, -1, 1, 1), (B, N, *shape))
         z_hat = torch.from_numpy(OR.decompress(strings[1], z_idx, cdf, ln, off)).float() + med
-        scales = self._scales_from(z_hat, mid_hw, y_hw)
+        scales, means = self._scales_from(z_hat, mid_hw, y_hw)
         indexes = self.build_indexes(scales)
         cdf, off, ln = self._gc_tabs
         y_hat = torch.from_numpy(OR.decompress(strings[0], indexes.numpy(), cdf, ln, off)).float()
+        if means is not None:
+            y_hat = y_hat + means                                                 # dequantize, entropy_models.py:182-190
         return {"x_hat": dict(zip(self.spec.levels, self._synthesis(y_hat, level_hw)))}
 
     def aux_loss(self):

@@ -110,6 +110,53 @@ def test_frames_encoded_together_decode_one_at_a_time():
                 assert float((a - b).abs().max()) <= 2e-2 * float(b.abs().max()), k      # g_s itself may tile differently
 
 
+def test_mean_scale_hyperprior_round_trip(tmp_path):
+    """encoder_config {"hyperprior": "mean-scale"} (models/google.py:337-405): symbols are round(y - means), the decoder
+    adds the means back; decode(encode(x)) equals the eval forward bit for bit, the y strings are the ones the oracle's
+    coder makes from those symbols, and the oracle graph run on the same weights reconstructs the same pyramid."""
+    import numpy as np
+    from oracle import lmsfc as OL
+    from oracle import rans as OR
+    codec_m = importlib.import_module(PKG + ".codec")
+    torch.manual_seed(0)
+    vm = _FakeVisionModel()
+    codec = codec_m.LMSFCCodec(eval_encode="bpp", encoder_config={"qp": 3, "hyperprior": "mean-scale", "coder_index": 256},
+                               device="cuda", vision_model=vm, dataset=None)
+    m = codec.model
+    assert m.spec.mean_scale and m.h_s["4"].out_channels == 2 * m.spec.M
+    with torch.no_grad():                     # random-init means are ~0: move the last layer so that they matter
+        m.h_s["4"].bias[m.spec.M:].uniform_(-3.0, 3.0)
+    m.refresh_shadows()
+    feats = _features(2, 26, 38, "cuda")
+    inp = {"data": dict(feats), "input_size": [(104, 152)], "org_input_size": {"height": 104, "width": 152}}
+    res = codec.encode(inp, str(tmp_path), "feat", "ms")
+    dec = codec.decode(res["bitstream"], str(tmp_path), "ms")
+    with torch.no_grad():
+        out = m(feats)
+    means = out["latents"]["means"]
+    assert means is not None and float(means.abs().max()) > 1.0
+    for k in vm.split_layer_list:
+        assert torch.equal(dec["data"][k], out["x_hat"][k].float()), k
+    gc = m.gaussian_conditional
+    y_sym = torch.round(out["latents"]["y_hat"] - means).int().cpu().numpy()
+    sc = torch.clamp(out["latents"]["scales"].float().cpu(), min=0.11)
+    y_idx = torch.full(sc.shape, len(gc.scale_table) - 1).int()
+    for t in gc.scale_table.cpu()[:-1]:
+        y_idx -= (sc <= t).int()
+    tabs = [t.cpu().numpy() for t in (gc._quantized_cdf, gc._cdf_length, gc._offset)]
+    with torch.no_grad():
+        enc = m.compress(feats)
+    assert np.array_equal(OR.decompress(enc["strings"][0], y_idx.numpy(), *tabs), y_sym)
+    # the oracle graph (reference modules, fp32) on the same weights, eval mode: same pyramid within bf16 tolerance
+    ref = OL.OracleLMSFC(m.spec).cuda().eval()
+    ref.load_state_dict({k: v for k, v in m.state_dict().items() if k in ref.state_dict()}, strict=False)
+    with torch.no_grad():
+        o = ref(feats, training=False)
+    for k in vm.split_layer_list:
+        a, b = out["x_hat"][k].float(), o["x_hat"][k]
+        assert float((a - b).norm() / b.norm()) < 5e-2, k          # single latents may round to the neighbouring integer
+
+
 class _FakeJDE:
     split_layer_list = [36, 61, 74]          # cfgs/vision_model/default.yaml:33
     device = "cuda"

@@ -108,6 +108,34 @@ def test_conv_relu_and_latent_head(P):
     assert nerr(xa.grad, xr.grad) < 2e-2
 
 
+def test_conv_leaky_relu_and_plain_latent_head(P):
+    """The mean-scale hyperprior's pieces (models/google.py:377-398): LeakyReLU(0.01) in the conv epilogue and its
+    gradient from the output's sign; a latent head that returns (fp32 y, bf16 y) whose two gradients add."""
+    mod = P.layers.Deconv(256, 256).to(DEV)
+    x = bf(rnd(2, 256, 5, 4, seed=8))
+    xa = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_()
+    y = mod(xa, relu="leaky")
+    g = bf(rnd(*y.shape, seed=9))
+    y.backward(g.to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
+    xr = x.clone().requires_grad_()
+    w = bf(mod.weight.detach()).requires_grad_()
+    yr = F.leaky_relu(F.conv_transpose2d(xr, w, mod.bias, stride=2, padding=2, output_padding=1), 0.01)
+    yr.backward(g)
+    assert float((y.float() < 0).float().mean()) > 0.2          # the negative branch is exercised
+    assert nerr(y, yr) < 2e-2 and nerr(xa.grad, xr.grad) < 2e-2 and nerr(mod.weight.grad, w.grad) < 2e-2
+    head = P.layers.Conv(256, 512, 3, 1).to(DEV)
+    xa = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_()
+    yf, yb = head(xa, latent_head="plain")
+    yr = F.conv2d(x, bf(head.weight.detach()), head.bias, padding=1)
+    assert yf.dtype == torch.float32 and yb.dtype == torch.bfloat16 and nerr(yf, yr) < 1e-2 and nerr(yb, yr) < 2e-2
+    g1, g2 = bf(rnd(*yf.shape, seed=6)), bf(rnd(*yf.shape, seed=7))
+    torch.autograd.backward([yf, yb], [g1, g2.to(torch.bfloat16)])
+    xr = x.clone().requires_grad_()
+    yr = F.conv2d(xr, bf(head.weight.detach()), head.bias, padding=1)
+    yr.backward(g1 + g2)
+    assert nerr(xa.grad, xr.grad) < 2e-2
+
+
 # ---------------------------------------------------------------------------- GDN
 @pytest.mark.parametrize("inverse", [False, True])
 @pytest.mark.parametrize("shape", [(2, 256, 5, 7), (4, 256, 32, 32)])

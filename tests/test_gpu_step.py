@@ -60,14 +60,19 @@ def _pair(B, H2, W2, seed=0, spec=None):
 # model, the full-wave weight-gradient kernels); (1, 128, 192) = configs[0]; (1, 200, 304) = configs[3] (y 13 x 19,
 # ragged tiles at every level)
 # ("jde", 1, 76, 136) = configs[4]: the 3-scale 256 / 512 / 1024-channel JDE split (spec.JDE_SPEC), one 1088x608 frame
+# ("ms", ...) / ("ms16", ...): the same pyramid under the mean-scale hyperprior (spec.MEAN_SCALE_SPEC, models/google.py:337-405)
 @pytest.mark.parametrize("B,H2,W2", [(2, 32, 32), (1, 26, 38), (16, 64, 64), (1, 128, 192), (1, 200, 304), ("jde", 76, 136),
-                                     ("jde2", 20, 28)])
+                                     ("jde2", 20, 28), ("ms", 32, 32), ("ms1", 26, 38), ("ms16", 64, 64)])
 def test_forward_loss_and_gradients(B, H2, W2):
     from oracle import lmsfc as OL
-    jde = isinstance(B, str)
+    jde = isinstance(B, str) and B.startswith("jde")
+    ms = isinstance(B, str) and B.startswith("ms")
     if jde:
         B = 2 if B == "jde2" else 1
-    spec, net, ref, feats, nz, ny = _pair(B, H2, W2, spec=_mods()[0].JDE_SPEC if jde else None)
+    if ms:
+        B = {"ms": 2, "ms1": 1, "ms16": 16}[B]
+    sm = _mods()[0]
+    spec, net, ref, feats, nz, ny = _pair(B, H2, W2, spec=sm.JDE_SPEC if jde else (sm.MEAN_SCALE_SPEC if ms else None))
     _, _, train_m = _mods()
     lmbda = 0.013
     net.build_arena()
@@ -121,10 +126,11 @@ def test_forward_loss_and_gradients(B, H2, W2):
     assert main[0][2] < RELL2_MAX_MAIN, main[0]
 
 
-def test_train_steps_track_the_oracle():
+@pytest.mark.parametrize("variant", ["scale", "mean-scale"])
+def test_train_steps_track_the_oracle(variant):
     """Three optimiser steps (clip 1.0 + Adam 1e-4, aux Adam 1e-3) on both sides, same noise."""
     from oracle import lmsfc as OL
-    spec, net, ref, feats, nz, ny = _pair(2, 32, 32, seed=3)
+    spec, net, ref, feats, nz, ny = _pair(2, 32, 32, seed=3, spec=_mods()[0].MEAN_SCALE_SPEC if variant == "mean-scale" else None)
     _, _, train_m = _mods()
     ts = train_m.TrainStep(net, lmbda=0.013)
     opt, aux_opt = OL.configure_optimizers(ref)
