@@ -271,7 +271,7 @@ def kernel_rooflines(torch, L, layers, dev, timeit=None):
     step = torch.zeros(1, dtype=I32, device=dev)
     L.adam_prep(1e-4, None, 0.9, 0.999, 0.0, None, P(step), P(scratch), None, 1, None, L.stream())
     ms = timeit(lambda: L.adam_update(P(p_), P(m_), P(v_), P(g_), P(sh), n, 0.9, 0.999, 1e-8, P(scratch), 1, L.stream()), n=4)
-    hbm("adam_kernel", ms, n * 34, f"{n} parameters x 34 B (p,m,v read+written, g read+cleared, bf16 shadow written)")
+    hbm("adam_stream_kernel", ms, n * 34, f"{n} parameters x 34 B (p,m,v read+written, g read+cleared, bf16 shadow written)")
     ss = torch.zeros(1, dtype=F32, device=dev)
     ms = timeit([lambda b=b: L.sumsq(P(b), n, P(ss), None, L.stream()) for b in (p_, m_, v_)], n=6)
     hbm("sumsq_kernel", ms, n * 4, f"{n} gradients x 4 B (3 rotating buffers)")

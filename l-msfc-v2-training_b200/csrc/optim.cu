@@ -121,7 +121,8 @@ __device__ __forceinline__ void adam_quad(const float4& g, float4& m, float4& v,
   adam_one(g.z, m.z, v.z, p.z, clip, b1, b2, step_size, rs_bc2, eps);
   adam_one(g.w, m.w, v.w, p.w, clip, b1, b2, step_size, rs_bc2, eps);
 }
-__global__ void __launch_bounds__(TPB, 4) adam_kernel(AdamArgs a) {
+template <int TPB>
+__device__ __forceinline__ void adam_body(const AdamArgs& a) {
   pdl_sync();
   if (a.scratch[5] == 0.f) return;        // no update pending (see adam_prep_kernel)
   const float clip = a.scratch[0], bc1 = a.scratch[1], bc2 = a.scratch[2];
@@ -167,6 +168,107 @@ __global__ void __launch_bounds__(TPB, 4) adam_kernel(AdamArgs a) {
     if (a.zero_g) a.g[i] = 0.f;
   }
 }
+__global__ void __launch_bounds__(256, 4) adam_kernel(AdamArgs a) { adam_body<256>(a); }
+// ---------------------------------------------------------------- Adam as a bulk-copy pipeline (default for large slices)
+// One persistent CTA per SM whose memory traffic is asynchronous end to end: one thread issues cp.async.bulk loads of
+// the next chunks of p, m, v, g into a ring of shared-memory stages (mbarrier complete_tx), all threads update a landed
+// chunk in place, and the same thread sends it back with cp.async.bulk stores (p, m, v, the bf16 shadow, zeros for g) --
+// nothing waits on a load or a store except through the ring.  Chunk = 2048 parameters: 32 KB in, 36 KB out; 4 stages =
+// 144 KB + 8 KB of zeros.  Measured on a B200 over 27.9 M parameters (profiles/r2_adam_sms.txt): 5.68 TB/s on 148 SMs
+// (adam_kernel: 5.51), and the per-SM ceiling is ~80 GB/s whichever way the bytes move (a register-staged 1024-thread
+// CTA: 76): 96 SMs saturate HBM, 20 SMs reach 1.6 TB/s -- confining the optimiser to the SMs a 128-CTA GEMM leaves idle
+// is what the step effectively does already, and giving it fewer SMs on purpose only stretches it (LMSFC_ADAM_STREAM=n).
+namespace stream_adam {
+constexpr int kThreads = 512, kChunk = 2048, kStages = 4;
+constexpr int kStageBytes = 4 * kChunk * 4 + kChunk * 2;           // p, m, v, g fp32 + bf16 shadow
+constexpr int kSmemBytes = kStages * kStageBytes + kChunk * 4 + 64 + 1024;
+}  // namespace stream_adam
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* dst, uint32_t src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+__global__ void __launch_bounds__(stream_adam::kThreads, 1) adam_stream_kernel(AdamArgs a) {
+  using namespace stream_adam;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  float* zeros = (float*)(smem + kStages * kStageBytes);
+  uint64_t* full = (uint64_t*)(smem + kStages * kStageBytes + kChunk * 4);
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) mbar_init(&full[s], 1);
+    fence_barrier_init();
+  }
+  for (int i = tid; i < kChunk; i += kThreads) zeros[i] = 0.f;
+  fence_proxy_async_smem();
+  __syncthreads();
+  pdl_sync();
+  if (a.scratch[5] == 0.f) return;        // no update pending (see adam_prep_kernel)
+  const float clip = a.scratch[0], bc1 = a.scratch[1], bc2 = a.scratch[2];
+  const float step_size = a.scratch[4] / bc1, rs_bc2 = rsqrtf(bc2);
+  const int64_t nchunks = a.n / kChunk;                        // whole chunks go through the ring
+  const int64_t mine = blockIdx.x < nchunks ? (nchunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const uint32_t sbase = smem_u32(smem);
+  auto issue = [&](int64_t k) {                                // thread 0: loads of this CTA's k-th chunk
+    const int s = (int)(k % kStages);
+    const int64_t e = (blockIdx.x + k * gridDim.x) * kChunk;
+    const uint32_t d = sbase + s * kStageBytes;
+    mbar_arrive_expect_tx(&full[s], 4 * kChunk * 4);
+    bulk_load(d, a.p + e, kChunk * 4, &full[s]);
+    bulk_load(d + kChunk * 4, a.m + e, kChunk * 4, &full[s]);
+    bulk_load(d + 2 * kChunk * 4, a.v + e, kChunk * 4, &full[s]);
+    bulk_load(d + 3 * kChunk * 4, a.g + e, kChunk * 4, &full[s]);
+  };
+  if (tid == 0)
+    for (int64_t k = 0; k < kStages - 1 && k < mine; ++k) issue(k);
+  for (int64_t k = 0; k < mine; ++k) {
+    const int s = (int)(k % kStages);
+    mbar_wait(&full[s], (uint32_t)((k / kStages) & 1));
+    float4* sp = reinterpret_cast<float4*>(smem + s * kStageBytes);
+    float4* sm = sp + kChunk / 4;
+    float4* sv = sm + kChunk / 4;
+    const float4* sg = sv + kChunk / 4;
+    uint2* sh = reinterpret_cast<uint2*>(smem + s * kStageBytes + 4 * kChunk * 4);
+#pragma unroll
+    for (int q = tid; q < kChunk / 4; q += kThreads) {
+      const float4 g = sg[q];
+      float4 m = sm[q], v = sv[q], p = sp[q];
+      adam_quad(g, m, v, p, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
+      sm[q] = m; sv[q] = v; sp[q] = p;
+      sh[q] = make_uint2(pack_bf16(p.x, p.y), pack_bf16(p.z, p.w));
+    }
+    fence_proxy_async_smem();              // generic-proxy writes -> visible to the bulk stores
+    __syncthreads();
+    if (tid == 0) {
+      const int64_t e = (blockIdx.x + k * gridDim.x) * kChunk;
+      const uint32_t d = sbase + s * kStageBytes;
+      bulk_store(a.p + e, d, kChunk * 4);
+      bulk_store(a.m + e, d + kChunk * 4, kChunk * 4);
+      bulk_store(a.v + e, d + 2 * kChunk * 4, kChunk * 4);
+      if (a.p_bf16) bulk_store(a.p_bf16 + e, d + 4 * kChunk * 4, kChunk * 2);
+      if (a.zero_g) bulk_store(a.g + e, smem_u32(zeros), kChunk * 4);
+      bulk_commit_group();
+      if (k + kStages - 1 < mine) {
+        bulk_wait_group_read<1>();         // the stage consumed in the previous iteration has been read out
+        issue(k + kStages - 1);
+      }
+    }
+  }
+  if (tid == 0) bulk_wait_group_read<0>();
+  // what is left of the slice (< one chunk): the last CTA, plain loads and stores
+  if (blockIdx.x == gridDim.x - 1) {
+    for (int64_t i = nchunks * kChunk + tid; i < a.n; i += kThreads) {
+      float m = a.m[i], v = a.v[i], p = a.p[i];
+      adam_one(a.g[i], m, v, p, clip, a.beta1, a.beta2, step_size, rs_bc2, a.eps);
+      a.m[i] = m; a.v[i] = v; a.p[i] = p;
+      if (a.p_bf16) a.p_bf16[i] = __float2bfloat16(p);
+      if (a.zero_g) a.g[i] = 0.f;
+    }
+  }
+}
 int adam_prep(const AdamArgs& a, cudaStream_t s) {
   LMSFC_LAUNCH(adam_prep_kernel, dim3(1), dim3(1), 0, s, a);
   return LMSFC_OK;
@@ -179,6 +281,21 @@ int adam_update(const AdamArgs& a, cudaStream_t s) {
   // stream and take every SM an Adam CTA leaves (a GEMM CTA cannot join an SM in the L1-heavy split)
   const int64_t quads = (a.n + 3) / 4, want = (quads + 8 * TPB - 1) / (8 * TPB);
   const int grid = (int)max((int64_t)1, want);
+  // LMSFC_ADAM_STREAM: number of SMs (= CTAs) of the bulk-copy pipeline; unset: all of them; 0: adam_kernel only
+  static const int stream_sms = [] {
+    const char* e = getenv("LMSFC_ADAM_STREAM");
+    if (e) return atoi(e);
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    return sms;
+  }();
+  if (stream_sms > 0 && a.n >= (int64_t)stream_sms * stream_adam::kChunk) {
+    static const cudaError_t attr = cudaFuncSetAttribute(adam_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                         stream_adam::kSmemBytes);
+    LMSFC_CUDA(attr);
+    LMSFC_LAUNCH(adam_stream_kernel, dim3(stream_sms), dim3(stream_adam::kThreads), stream_adam::kSmemBytes, s, a);
+    return LMSFC_OK;
+  }
   LMSFC_LAUNCH(adam_kernel, dim3(grid), dim3(TPB), 0, s, a);
   return LMSFC_OK;
 }

@@ -5,7 +5,7 @@ import csv, io, json, subprocess, sys
 
 UNIT = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 # bench.py name -> (substring of the demangled kernel name, grid x or None)
-WANT = {"igemm_fwd_kernel<256>": "igemm_fwd_kernel<256", "wgrad_kernel": "wgrad_kernel", "adam_kernel": "adam_kernel",
+WANT = {"igemm_fwd_kernel<256>": "igemm_fwd_kernel<256", "wgrad_kernel": "wgrad_kernel", "adam_stream_kernel": "adam_stream_kernel",
         "sumsq_kernel": "sumsq_kernel", "mse_multi_kernel": "mse_multi_kernel", "gc_forward_kernel": "gc_forward_kernel",
         "gc_backward_kernel": "gc_backward_kernel", "eb_forward_kernel": "eb_forward_kernel",
         "eb_backward_kernel": "eb_backward_kernel"}
