@@ -24,6 +24,7 @@ __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g
                                                     int overwrite) {
   pdl_sync();
   float local = 0.f;
+#pragma unroll 8
   for (int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; i < n4; i += (int64_t)gridDim.x * TPB) {
     const float4 v = __ldg(g + i);
     local += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
@@ -68,7 +69,10 @@ int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, int overwr
   LMSFC_CHECK_ARG(((uintptr_t)g & 15) == 0, "sumsq: pointer must be 16-byte aligned");
   if (int rc = ensure_reduce_scratch()) return rc;
   const int64_t n4 = n / 4;
-  LMSFC_LAUNCH(sumsq_kernel, dim3(grid1d(n4 > 0 ? n4 : 1)), dim3(TPB), 0, s, (const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum,
+  // >= 8 float4 per thread: the slices of the sliced norm (2-3 M gradients each) sit on the step's tail, and a grid of a
+  // thousand blocks with one or two loads each spends its time in the last-block hand-over, not in HBM
+  const int grid = grid1d((n4 + 7) / 8 > 0 ? (n4 + 7) / 8 : 1);
+  LMSFC_LAUNCH(sumsq_kernel, dim3(grid), dim3(TPB), 0, s, (const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum,
                red_scratch(s), red_count(s) + 63, set_flag, overwrite);
   return LMSFC_OK;
 }
