@@ -179,6 +179,10 @@ int lmsfc_sumsq(const float* g, int64_t n, float* accum, int* set_flag, void* st
  * order (set_flag as above). */
 int lmsfc_sumsq_part(const float* g, int64_t n, float* out, void* stream);
 int lmsfc_sum_parts(const float* parts, int n, float* out, int* set_flag, void* stream);
+/* the closing slice: parts[index] = sum(g[0:n]^2) and, in the same launch, *out = parts[0] + ... + parts[nparts-1] in
+ * index order (the other parts are complete on `stream`); saves the separate lmsfc_sum_parts launch on the step's tail */
+int lmsfc_sumsq_part_final(const float* g, int64_t n, float* parts, int index, int nparts, float* out, int* set_flag,
+                           void* stream);
 /* clip_grad_norm_(max_norm) + torch.optim.Adam step over a flat fp32 arena; p_bf16 (nullable) gets
  * the bf16 shadow; step (device int) is incremented; scratch (>=8 floats) receives
  * {clip_coef, bias_corr1, bias_corr2, grad_norm, lr, active, -, -}.  sumsq null or max_norm<=0 -> no clipping. */

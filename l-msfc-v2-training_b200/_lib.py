@@ -72,6 +72,7 @@ _SIGS = {
     "lmsfc_sumsq": [P, c_int64, P, P, P],
     "lmsfc_sumsq_part": [P, c_int64, P, P],
     "lmsfc_sum_parts": [P, c_int, P, P, P],
+    "lmsfc_sumsq_part_final": [P, c_int64, P, c_int, c_int, P, P, P],
     "lmsfc_adam_step": [P, P, P, P, P, c_int64, c_float, c_float, c_float, c_float, c_float, P, P, P, P],
     "lmsfc_adam_prep": [c_float, P, c_float, c_float, c_float, P, P, P, P, c_int, P, P],
     "lmsfc_adam_update": [P, P, P, P, P, c_int64, c_float, c_float, c_float, P, c_int, P],

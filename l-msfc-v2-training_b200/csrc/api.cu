@@ -423,6 +423,11 @@ extern "C" int lmsfc_nchw_to_nhwc_bf16(const float* in, void* out, int B, int C,
 extern "C" int lmsfc_sumsq(const float* g, int64_t n, float* accum, int* set_flag, void* stream) {
   return sumsq_f32(g, n, accum, set_flag, 0, ST(stream));
 }
+extern "C" int lmsfc_sumsq_part_final(const float* g, int64_t n, float* parts, int index, int nparts, float* out,
+                                      int* set_flag, void* stream) {
+  LMSFC_CHECK_ARG(parts != nullptr && out != nullptr && nparts >= 1 && index >= 0 && index < nparts, "sumsq_part_final: bad arguments");
+  return sumsq_f32(g, n, parts + index, set_flag, 1, ST(stream), parts, nparts, out);
+}
 extern "C" int lmsfc_sumsq_part(const float* g, int64_t n, float* out, void* stream) {
   LMSFC_CHECK_ARG(out != nullptr, "sumsq_part: null result");
   if (n == 0) return sum_parts(nullptr, 0, out, nullptr, ST(stream));

@@ -80,7 +80,8 @@ int abs_bwd(const float* g_direct, const __nv_bfloat16* g_abs, const float* y, i
 int cast_f32_bf16(const float* in, __nv_bfloat16* out, int64_t n, cudaStream_t s);
 int cast_bf16_f32(const __nv_bfloat16* in, float* out, int64_t n, cudaStream_t s);
 int nchw_to_nhwc_bf16(const float* in, __nv_bfloat16* out, int B, int C, int HW, cudaStream_t s);
-int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, int overwrite, cudaStream_t s);
+int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, int overwrite, cudaStream_t s, const float* parts = nullptr,
+              int nparts = 0, float* total = nullptr);
 int sum_parts(const float* parts, int n, float* out, int* set_flag, cudaStream_t s);
 struct AdamArgs {
   float *p, *m, *v;

@@ -21,7 +21,7 @@ inline int grid1d(int64_t work_items) {
 // never drift apart (float atomics made the norm differ in the last bits from run to run and rank to rank).
 __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g, int64_t n4, const float* tail, int ntail,
                                                     float* accum, float* partial, unsigned int* counter, int* set_flag,
-                                                    int overwrite) {
+                                                    int overwrite, const float* parts, int nparts, float* total) {
   pdl_sync();
   float local = 0.f;
 #pragma unroll 8
@@ -48,6 +48,11 @@ __global__ void __launch_bounds__(TPB) sumsq_kernel(const float4* __restrict__ g
     v = block_sum(v, red);                                                               // fixed tree
     if (threadIdx.x == 0) {
       if (overwrite) *accum = v; else *accum += v;
+      if (parts) {                      // the last slice of a sliced norm also adds the parts up, in index order
+        float t = 0.f;
+        for (int i = 0; i < nparts; ++i) t += (parts + i == accum) ? *accum : __ldcg(parts + i);
+        *total = t;
+      }
       if (set_flag) *set_flag = 1;      // "an update is pending" (pipelined train step), consumed by adam_prep
     }
   }
@@ -64,7 +69,9 @@ int sum_parts(const float* parts, int n, float* out, int* set_flag, cudaStream_t
   LMSFC_LAUNCH(sum_parts_kernel, dim3(1), dim3(1), 0, s, parts, n, out, set_flag);
   return LMSFC_OK;
 }
-int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, int overwrite, cudaStream_t s) {
+int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, int overwrite, cudaStream_t s, const float* parts,
+              int nparts, float* total) {
+  LMSFC_CHECK_ARG(n > 0 || parts == nullptr, "sumsq: the closing slice of a sliced norm cannot be empty");
   if (n == 0) return LMSFC_OK;
   LMSFC_CHECK_ARG(((uintptr_t)g & 15) == 0, "sumsq: pointer must be 16-byte aligned");
   if (int rc = ensure_reduce_scratch()) return rc;
@@ -73,7 +80,7 @@ int sumsq_f32(const float* g, int64_t n, float* accum, int* set_flag, int overwr
   // thousand blocks with one or two loads each spends its time in the last-block hand-over, not in HBM
   const int grid = grid1d((n4 + 7) / 8 > 0 ? (n4 + 7) / 8 : 1);
   LMSFC_LAUNCH(sumsq_kernel, dim3(grid), dim3(TPB), 0, s, (const float4*)g, n4, g + n4 * 4, (int)(n - n4 * 4), accum,
-               red_scratch(s), red_count(s) + 63, set_flag, overwrite);
+               red_scratch(s), red_count(s) + 63, set_flag, overwrite, parts, nparts, total);
   return LMSFC_OK;
 }
 

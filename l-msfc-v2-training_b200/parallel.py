@@ -192,9 +192,15 @@ class SlicedNorm(BucketedGradReducer):
         self.L = L
         super().__init__(model, edges=edges)
         self.parts = torch.zeros(len(self.buckets), dtype=torch.float32, device=self.grads.device)
+        self.outputs = None       # (sumsq, pending_flag or None): lets the LAST slice's launch add the parts up itself
+        self._closed = False
 
     def sync_replicas(self, optimizers=None):
         pass
+
+    def begin(self):
+        self._closed = False
+        return super().begin()
 
     def _launch(self, i):
         self.launched.append(i)
@@ -203,17 +209,25 @@ class SlicedNorm(BucketedGradReducer):
         with torch.cuda.stream(self.comm_stream):
             for ev in evs:
                 self.comm_stream.wait_event(ev)
-            self.L.sumsq_part(self.grads[b["lo"]:].data_ptr(), b["hi"] - b["lo"], self.parts[i:].data_ptr(),
-                              torch.cuda.current_stream().cuda_stream)
+            st = torch.cuda.current_stream().cuda_stream
+            if self.outputs is not None and len(self.launched) == len(self.buckets) and b["hi"] > b["lo"]:
+                sumsq, flag = self.outputs            # every other part is complete on this stream
+                self.L.sumsq_part_final(self.grads[b["lo"]:].data_ptr(), b["hi"] - b["lo"], self.parts.data_ptr(), i,
+                                        len(self.buckets), sumsq.data_ptr(), None if flag is None else flag.data_ptr(), st)
+                self._closed = True
+            else:
+                self.L.sumsq_part(self.grads[b["lo"]:].data_ptr(), b["hi"] - b["lo"], self.parts[i:].data_ptr(), st)
 
     def finish(self, sumsq, pending_flag=None):
         if self._pending is not None:
             for i in range(len(self.buckets)):
                 if i not in self.launched:
                     self._launch(i)
-        with torch.cuda.stream(self.comm_stream):
-            self.L.sum_parts(self.parts.data_ptr(), len(self.buckets), sumsq.data_ptr(),
-                             None if pending_flag is None else pending_flag.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        same = self.outputs is not None and self.outputs[0] is sumsq and self.outputs[1] is pending_flag
+        if not (self._closed and same):
+            with torch.cuda.stream(self.comm_stream):
+                self.L.sum_parts(self.parts.data_ptr(), len(self.buckets), sumsq.data_ptr(),
+                                 None if pending_flag is None else pending_flag.data_ptr(), torch.cuda.current_stream().cuda_stream)
         torch.cuda.current_stream().wait_stream(self.comm_stream)
         self._pending = None
 

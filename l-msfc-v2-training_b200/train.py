@@ -73,6 +73,8 @@ class TrainStep:
         # single GPU, pipelined order: the gradient norm slice by slice beside the backward pass
         self.norms = (SlicedNorm(model, [lo for lo, _, _ in self._slices()])
                       if (self.reducer is None and clip_max_norm > 0 and os.environ.get("LMSFC_SLICED_NORM", "1") == "1") else None)
+        if self.norms is not None:       # the slice that completes last adds the parts up in its own launch
+            self.norms.outputs = (self.opt["net"].sumsq, self.pending_flag)
         if side_streams:
             Fn.SideStreams.enable(self.arena.device)
         self.gate_stream = torch.cuda.Stream(device=self.arena.device, priority=-1) if self.sharded else None
