@@ -369,6 +369,16 @@ class GDNState:
         self.beta_eff = self.gamma_bf = self.g_beta_eff = self.g_gamma_eff = None
 
 
+def wait_gdn_gate(arena):
+    """Pipelined train step: the reparametrised beta / gamma of this step are produced on the optimiser stream behind the
+    first slice's update (train.TrainStep._apply_pending); the first GDN launch of the forward pass waits for them (every
+    later stream of the forward pass forks from this one behind that point)."""
+    if arena is not None and arena.gates:
+        ev = arena.gates.pop("gdn", None)
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+
+
 class _GDNFn(torch.autograd.Function):
     """compressai/layers/gdn.py:77-92 with the NonNegativeParametrizer of beta / gamma
     (ops/parametrizers.py:60-63) and LowerBound's custom gradient (ops/bound_ops.py:40-42)."""
@@ -387,6 +397,7 @@ class _GDNFn(torch.autograd.Function):
             gamma_bf = torch.empty((C, C), dtype=BF16, device=dev)
             L.reparam_forward(ptr(beta), C, state.beta_bound, PEDESTAL, ptr(beta_eff), None, st)
             L.reparam_forward(ptr(gamma), C * C, state.gamma_bound, PEDESTAL, None, ptr(gamma_bf), st)
+        wait_gdn_gate(arena)
         train = any(ctx.needs_input_grad[:3])
         x2 = torch.empty_like(x) if train else None      # inference: x^2 never leaves the GEMM's producer warps
         y = torch.empty_like(x)
@@ -473,12 +484,14 @@ class _ConvGDNFn(torch.autograd.Function):
         if train:
             x, rn, x2 = (empty_nhwc(B, C, Ho, Wo, BF16, dev) for _ in range(3))
         if C == 256 and L.gdn_fusable(d, inference=not train):
+            wait_gdn_gate(arena)
             L.conv_gdn_forward(d, ptr(x0), ptr(x1), ptr(cstate.w_direct), ptr(bias), ptr(gamma_bf), ptr(beta_eff),
                                int(gstate.inverse), ptr(x), ptr(x2), ptr(y), ptr(rn), st)
         else:
             if x is None:
                 x = empty_nhwc(B, C, Ho, Wo, BF16, dev)
             L.conv_forward(d, ptr(x0), ptr(x1), ptr(cstate.w_direct), ptr(bias), 0, ptr(x), None, None, st)
+            wait_gdn_gate(arena)
             L.gdn_forward(ptr(x), ptr(gamma_bf), ptr(beta_eff), int(gstate.inverse), B * Ho * Wo, C, ptr(x2), ptr(y), ptr(rn), st)
         ctx.cstate, ctx.gstate, ctx.shape = cstate, gstate, (B, H, W, Ho, Wo)
         ctx.weight, ctx.bias, ctx.beta, ctx.gamma = weight, bias, beta, gamma

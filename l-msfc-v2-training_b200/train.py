@@ -154,9 +154,17 @@ class TrainStep:
                     if self.sharded:
                         self.reducer.wait_pushed(i)
                     if i == 0:
+                        if os_ is not None:                        # "start": the first convolution needs its weights only,
+                            ev = torch.cuda.Event()                # not the reparametrised GDN operands
+                            ev.record()
+                            arena.gates[gate] = ev
                         arena._grads_all[arena.n_net:].zero_()     # GDN effective-gradient scratch
                         arena.prepare()                            # GDN group (first in the arena) -> effective beta / gamma
-                    if os_ is not None:
+                        if os_ is not None:                        # waited for in front of the first GDN launch
+                            ev = torch.cuda.Event()                # (functional.wait_gdn_gate)
+                            ev.record()
+                            arena.gates["gdn"] = ev
+                    elif os_ is not None:
                         ev = torch.cuda.Event()
                         ev.record()
                         arena.gates[gate] = ev
