@@ -142,6 +142,15 @@ int lmsfc_mse_forward_backward(const void* xhat, const void* x, int64_t n, float
  * sse[l] += ..., grad (nullable array, nullable entries). */
 int lmsfc_mse_forward_backward_multi(int nlev, const void* const* xhat, const void* const* x, const int64_t* n,
                                      const float* grad_coef, float* sse, void* const* grad, void* stream);
+/* RateDistortionLoss.forward + the gradient w.r.t. every reconstructed level in ONE launch (losses/rate_distortion.py:
+ * 47-59): lmsfc_mse_forward_backward_multi with the per-level sums reduced in a fixed order (block partials, last block),
+ * and that last block forms out4 = {loss, bpp, D, *extra}: bpp = rate_coef * sum_k *rate[k] (device scalars sum(ln L_k)
+ * left by the likelihood kernels, HOST array of n_rate <= 8 pointers), D = sum_l dist_coef[l] * sse_l (host array),
+ * loss = lambda_scale * D + bpp; extra (nullable device scalar) rides along, e.g. the step's aux loss.  Nothing has to be
+ * zeroed beforehand, and the loss value is bit-reproducible (no float atomics). */
+int lmsfc_rd_loss(int nlev, const void* const* xhat, const void* const* x, const int64_t* n, const float* grad_coef,
+                  void* const* grad, int n_rate, const float* const* rate, float rate_coef, const float* dist_coef,
+                  float lambda_scale, const float* extra, float* out4, void* stream);
 /* out[0]=bpp=sum_{i<n_rate} accum[i]*coef[i]; out[1]=D=sum over the next n_dist; out[2]=lambda_scale*D+bpp */
 int lmsfc_loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale, float* out,
                         void* stream);

@@ -60,6 +60,7 @@ _SIGS = {
     "lmsfc_gc_pmf": [P, P, c_int, c_int, P, c_int, P, P],
     "lmsfc_mse_forward_backward": [P, P, c_int64, c_float, P, P, P],
     "lmsfc_mse_forward_backward_multi": [c_int, P, P, P, P, P, P, P],
+    "lmsfc_rd_loss": [c_int, P, P, P, P, P, c_int, P, c_float, P, c_float, P, P, P],
     "lmsfc_loss_finalize": [P, P, c_int, c_int, c_float, P, P],
     "lmsfc_relu_backward": [P, P, c_int64, P],
     "lmsfc_leaky_relu_backward": [P, P, c_int64, c_float, P],

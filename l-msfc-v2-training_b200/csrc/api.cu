@@ -391,6 +391,13 @@ extern "C" int lmsfc_mse_forward_backward_multi(int nlev, const void* const* xha
   LMSFC_CHECK_ARG(xhat && x && n && grad_coef && sse, "mse_multi: null operand");
   return mse_fwd_bwd_multi(nlev, xhat, x, n, grad_coef, sse, grad, ST(stream));
 }
+extern "C" int lmsfc_rd_loss(int nlev, const void* const* xhat, const void* const* x, const int64_t* n, const float* grad_coef,
+                             void* const* grad, int n_rate, const float* const* rate, float rate_coef,
+                             const float* dist_coef, float lambda_scale, const float* extra, float* out4, void* stream) {
+  LMSFC_CHECK_ARG(xhat && x && n && grad_coef, "rd_loss: null argument array");
+  return rd_loss_multi(nlev, xhat, x, n, grad_coef, grad, n_rate, rate, rate_coef, dist_coef, lambda_scale, extra, out4,
+                       ST(stream));
+}
 extern "C" int lmsfc_loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale,
                                    float* out, void* stream) {
   return loss_finalize(accum, coef, n_rate, n_dist, lambda_scale, out, ST(stream));

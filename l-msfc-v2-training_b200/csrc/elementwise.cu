@@ -62,7 +62,18 @@ struct MseMultiArgs {
   float coef[kMseMaxLevels];
   int blk_end[kMseMaxLevels];     // blocks [blk_end[l-1], blk_end[l]) work on level l
   int nlev;
-  float* sse;                     // [nlev]
+  float* sse;                     // [nlev]; accumulated (+=) by float atomics, or -- with out4 -- overwritten by the last block
+  // ---- the whole RD loss in this launch (out4 != null): per-level sums through a two-stage, fixed-order reduction,
+  // then the last block forms bpp / D / loss itself (losses/rate_distortion.py:47-59)
+  float* out4;                    // {loss, bpp, D, *extra}
+  const float* rate[kMseMaxLevels];   // device scalars sum(ln L_k), reduced by the likelihood kernels
+  int n_rate;
+  float rate_coef;                // 1 / (-ln 2 * num_pixels)
+  float dist_coef[kMseMaxLevels]; // w_l / n_l
+  float lambda_scale;
+  const float* extra;             // nullable: one more scalar to ride along (the step's aux loss)
+  float* partial;                 // [gridDim.x] block partials
+  unsigned int* counter;
 };
 __global__ void __launch_bounds__(TPB) mse_multi_kernel(const __grid_constant__ MseMultiArgs a) {
   pdl_sync();
@@ -88,12 +99,76 @@ __global__ void __launch_bounds__(TPB) mse_multi_kernel(const __grid_constant__ 
   }
   __shared__ float red[32];
   local = block_sum(local, red);
-  if (threadIdx.x == 0) atomicAdd(a.sse + l, local);
+  if (!a.out4) {
+    if (threadIdx.x == 0) atomicAdd(a.sse + l, local);
+    return;
+  }
+  __shared__ unsigned int is_last;
+  if (threadIdx.x == 0) {
+    __stcg(a.partial + blockIdx.x, local);
+    __threadfence();
+    const unsigned int prev = atomicAdd(a.counter, 1u);
+    is_last = (prev == gridDim.x - 1) ? 1u : 0u;
+    if (is_last) *a.counter = 0;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  float d = 0.f;
+  for (int lv = 0; lv < a.nlev; ++lv) {                     // fixed order: the loss is bit-reproducible
+    const int lo_b = lv ? a.blk_end[lv - 1] : 0, hi_b = a.blk_end[lv];
+    float v = 0.f;
+    for (int b = lo_b + (int)threadIdx.x; b < hi_b; b += TPB) v += __ldcg(a.partial + b);
+    __syncthreads();                                        // red[] is reused
+    v = block_sum(v, red);
+    if (threadIdx.x == 0) {
+      if (a.sse) a.sse[lv] = v;
+      d += v * a.dist_coef[lv];
+    }
+  }
+  if (threadIdx.x == 0) {
+    float bpp = 0.f;
+    for (int i = 0; i < a.n_rate; ++i) bpp += *a.rate[i] * a.rate_coef;
+    a.out4[0] = a.lambda_scale * d + bpp;
+    a.out4[1] = bpp;
+    a.out4[2] = d;
+    a.out4[3] = a.extra ? *a.extra : 0.f;
+  }
+}
+static int mse_multi_fill(MseMultiArgs& a, int nlev, const void* const* xhat, const void* const* x, const int64_t* n,
+                          const float* grad_coef, void* const* grad, int* grid);
+// RateDistortionLoss in ONE launch: all levels' squared errors + gradients, then bpp / D / loss by the last block
+int rd_loss_multi(int nlev, const void* const* xhat, const void* const* x, const int64_t* n, const float* grad_coef,
+                  void* const* grad, int n_rate, const float* const* rate, float rate_coef, const float* dist_coef,
+                  float lambda_scale, const float* extra, float* out4, cudaStream_t s) {
+  LMSFC_CHECK_ARG(out4 != nullptr && n_rate >= 0 && n_rate <= kMseMaxLevels && (n_rate == 0 || rate) && dist_coef,
+                  "rd_loss: bad arguments (at most %d likelihood terms)", kMseMaxLevels);
+  MseMultiArgs a;
+  int grid = 0;
+  if (int rc = mse_multi_fill(a, nlev, xhat, x, n, grad_coef, grad, &grid)) return rc;
+  if (int rc = ensure_reduce_scratch()) return rc;
+  for (int i = 0; i < n_rate; ++i) {
+    LMSFC_CHECK_ARG(rate[i] != nullptr, "rd_loss: null likelihood sum %d", i);
+    a.rate[i] = rate[i];
+  }
+  for (int l = 0; l < nlev; ++l) a.dist_coef[l] = dist_coef[l];
+  a.out4 = out4; a.n_rate = n_rate; a.rate_coef = rate_coef; a.lambda_scale = lambda_scale; a.extra = extra;
+  a.partial = red_scratch(s); a.counter = red_count(s) + 62;
+  LMSFC_LAUNCH(mse_multi_kernel, dim3(grid), dim3(TPB), 0, s, a);
+  return LMSFC_OK;
 }
 int mse_fwd_bwd_multi(int nlev, const void* const* xhat, const void* const* x, const int64_t* n, const float* grad_coef,
                       float* sse, void* const* grad, cudaStream_t s) {
-  LMSFC_CHECK_ARG(nlev >= 1 && nlev <= kMseMaxLevels, "mse_multi: %d levels (max %d)", nlev, kMseMaxLevels);
   MseMultiArgs a;
+  int grid = 0;
+  if (int rc = mse_multi_fill(a, nlev, xhat, x, n, grad_coef, grad, &grid)) return rc;
+  a.sse = sse;
+  LMSFC_LAUNCH(mse_multi_kernel, dim3(grid), dim3(TPB), 0, s, a);
+  return LMSFC_OK;
+}
+static int mse_multi_fill(MseMultiArgs& a, int nlev, const void* const* xhat, const void* const* x, const int64_t* n,
+                          const float* grad_coef, void* const* grad, int* grid) {
+  LMSFC_CHECK_ARG(nlev >= 1 && nlev <= kMseMaxLevels, "mse_multi: %d levels (max %d)", nlev, kMseMaxLevels);
   memset(&a, 0, sizeof(a));
   int64_t total8 = 0;
   for (int l = 0; l < nlev; ++l) {
@@ -109,8 +184,8 @@ int mse_fwd_bwd_multi(int nlev, const void* const* xhat, const void* const* x, c
     end += (int)max((int64_t)1, min(want, max(share, (int64_t)1)));
     a.blk_end[l] = end;
   }
-  a.nlev = nlev; a.sse = sse;
-  LMSFC_LAUNCH(mse_multi_kernel, dim3(end), dim3(TPB), 0, s, a);
+  a.nlev = nlev;
+  *grid = end;
   return LMSFC_OK;
 }
 

@@ -60,6 +60,9 @@ int mse_fwd_bwd(const __nv_bfloat16* xhat, const __nv_bfloat16* x, int64_t n, fl
 constexpr int kMseMaxLevels = 8;
 int mse_fwd_bwd_multi(int nlev, const void* const* xhat, const void* const* x, const int64_t* n, const float* grad_coef,
                       float* sse, void* const* grad, cudaStream_t s);
+int rd_loss_multi(int nlev, const void* const* xhat, const void* const* x, const int64_t* n, const float* grad_coef,
+                  void* const* grad, int n_rate, const float* const* rate, float rate_coef, const float* dist_coef,
+                  float lambda_scale, const float* extra, float* out4, cudaStream_t s);
 int loss_finalize(const float* accum, const float* coef, int n_rate, int n_dist, float lambda_scale, float* out,
                   cudaStream_t s);
 int square_bf16(const __nv_bfloat16* x, __nv_bfloat16* x2, int64_t n, cudaStream_t s);

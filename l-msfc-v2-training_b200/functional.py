@@ -811,28 +811,42 @@ class _RDLossFn(torch.autograd.Function):
     gradient d loss / d xhat_l (the loss is assumed to be the root of backward)."""
 
     @staticmethod
-    def forward(ctx, lmbda_scale, num_pixels, weights, n_lev, n_lik, *tensors):
+    def forward(ctx, lmbda_scale, num_pixels, weights, n_lev, n_lik, extra, *tensors):
         xh = tensors[:n_lev]
         xt = tensors[n_lev:2 * n_lev]
         liks = tensors[2 * n_lev:2 * n_lev + n_lik]
         dev, st = xh[0].device, stream()
-        accum = torch.zeros(n_lik + n_lev, dtype=F32, device=dev)
+        ctx.set_materialize_grads(False)          # bpp / mse carry no gradient: no zero tensors made for them
         rate_c = 1.0 / (-math.log(2) * num_pixels)
-        coef = [rate_c] * n_lik
-        for i, lk in enumerate(liks):
-            s = getattr(lk, _SUM_LN_ATTR, None)
-            accum[i:i + 1] = s if s is not None else torch.log(lk.float()).sum()
         import ctypes
-        grads = [torch.empty_like(xh[i]) if ctx.needs_input_grad[5 + i] else None for i in range(n_lev)]
+        grads = [torch.empty_like(xh[i]) if ctx.needs_input_grad[6 + i] else None for i in range(n_lev)]
         ns = [xh[i].numel() for i in range(n_lev)]
         VP, I64, F32A = ctypes.c_void_p * n_lev, ctypes.c_int64 * n_lev, ctypes.c_float * n_lev
-        L.mse_forward_backward_multi(n_lev, VP(*[ptr(t) for t in xh]), VP(*[ptr(t) for t in xt]), I64(*ns),
-                                     F32A(*[lmbda_scale * weights[i] * 2.0 / ns[i] for i in range(n_lev)]),
-                                     ptr(accum[n_lik:]), VP(*[ptr(g) for g in grads]), st)   # all levels, one launch
-        coef += [weights[i] / ns[i] for i in range(n_lev)]
-        coef_t = _const_tensor(tuple(coef), dev)
-        out = torch.empty(3, dtype=F32, device=dev)
-        L.loss_finalize(ptr(accum), ptr(coef_t), n_lik, n_lev, lmbda_scale, ptr(out), st)
+        gcoef = F32A(*[lmbda_scale * weights[i] * 2.0 / ns[i] for i in range(n_lev)])
+        sums = [getattr(lk, _SUM_LN_ATTR, None) for lk in liks]
+        if all(s_ is not None for s_ in sums) and n_lik <= 8:
+            # the whole loss in ONE launch behind the last reconstruction: squared errors + gradients of all levels,
+            # fixed-order reduction, bpp / D / loss (+ the aux loss riding along) by the last block (lmsfc_rd_loss)
+            out4 = torch.empty(4, dtype=F32, device=dev)
+            RP = ctypes.c_void_p * max(n_lik, 1)
+            L.rd_loss(n_lev, VP(*[ptr(t) for t in xh]), VP(*[ptr(t) for t in xt]), I64(*ns), gcoef,
+                      VP(*[ptr(g) for g in grads]), n_lik, RP(*[ptr(s_) for s_ in sums]), rate_c,
+                      F32A(*[weights[i] / ns[i] for i in range(n_lev)]), lmbda_scale, ptr(extra), ptr(out4), st)
+            out = (out4[0], out4[1], out4[2])
+            ctx.scalars4 = out4
+        else:
+            accum = torch.zeros(n_lik + n_lev, dtype=F32, device=dev)
+            coef = [rate_c] * n_lik
+            for i, lk in enumerate(liks):
+                accum[i:i + 1] = sums[i] if sums[i] is not None else torch.log(lk.float()).sum()
+            L.mse_forward_backward_multi(n_lev, VP(*[ptr(t) for t in xh]), VP(*[ptr(t) for t in xt]), I64(*ns), gcoef,
+                                         ptr(accum[n_lik:]), VP(*[ptr(g) for g in grads]), st)   # all levels, one launch
+            coef += [weights[i] / ns[i] for i in range(n_lev)]
+            coef_t = _const_tensor(tuple(coef), dev)
+            o3 = torch.empty(3, dtype=F32, device=dev)
+            L.loss_finalize(ptr(accum), ptr(coef_t), n_lik, n_lev, lmbda_scale, ptr(o3), st)
+            out = (o3[2], o3[0], o3[1])
+            ctx.scalars4 = None
         # likelihoods produced by the fused entropy kernels take d loss / d L = rate_c / L inside their
         # own backward (RateHook); any other likelihood tensor gets an explicit gradient
         ctx.fused = []
@@ -843,20 +857,27 @@ class _RDLossFn(torch.autograd.Function):
                 hook.coef = rate_c
         ctx.grads, ctx.rate_c, ctx.n_lev = grads, rate_c, n_lev
         ctx.save_for_backward(*[lk for lk, f in zip(liks, ctx.fused) if not f])
-        return out[2], out[0], out[1]
+        _RDLossFn.last_scalars4 = ctx.scalars4
+        return out
 
     @staticmethod
     def backward(ctx, g_loss, g_bpp, g_mse):
         plain = iter(ctx.saved_tensors)
         g_liks = [None if f else ctx.rate_c / next(plain) for f in ctx.fused]
-        return (None, None, None, None, None, *ctx.grads, *([None] * ctx.n_lev), *g_liks)
+        return (None, None, None, None, None, None, *ctx.grads, *([None] * ctx.n_lev), *g_liks)
 
 
-def rd_loss_apply(x_hats, targets, liks, lmbda_scale, num_pixels, weights):
+def rd_loss_apply(x_hats, targets, liks, lmbda_scale, num_pixels, weights, extra=None, with_scalars=False):
+    """-> (loss, bpp, mse) [, scalars4]: scalars4 = the device vector {loss, bpp, mse, *extra} the loss kernel wrote (None
+    on the fallback path); `extra`: a device scalar to ride along (the aux loss of a train step)."""
     xh = [nhwc(t, BF16) for t in x_hats]
     xt = [nhwc(t, BF16) for t in targets]
     for a, b in zip(xh, xt):
         if a.shape != b.shape:
             raise ValueError(f"x_hat {tuple(a.shape)} vs target {tuple(b.shape)}")
-    return _RDLossFn.apply(float(lmbda_scale), float(num_pixels), [float(w) for w in weights], len(xh), len(liks),
-                           *xh, *xt, *liks)
+    if extra is not None:
+        extra = extra.detach().reshape(-1).to(F32)
+    loss, bpp, mse = _RDLossFn.apply(float(lmbda_scale), float(num_pixels), [float(w) for w in weights], len(xh), len(liks),
+                                     extra, *xh, *xt, *liks)
+    s4, _RDLossFn.last_scalars4 = _RDLossFn.last_scalars4, None
+    return (loss, bpp, mse, s4) if with_scalars else (loss, bpp, mse)

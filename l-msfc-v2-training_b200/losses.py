@@ -20,14 +20,19 @@ class RateDistortionLoss(nn.Module):
         self.return_type = return_type
         self.spec = spec
 
-    def forward(self, output, target):
+    def forward(self, output, target, extra=None):
+        """extra (optional device scalar, e.g. the aux loss): rides along in out["scalars"] = {loss, bpp, mse, extra},
+        written by the loss kernel itself -- a train step reads its four numbers back as one 16-byte vector."""
         lv = self.spec.levels
         x_hat = output["x_hat"]
         nhwc_in = output.get("inputs_nhwc")
         targets = [nhwc_in[k] if nhwc_in is not None else target[k] for k in lv]
         B, _, H2, W2 = targets[0].shape
         num_pixels = self.spec.num_pixels(B, H2, W2)
-        loss, bpp, mse = Fn.rd_loss_apply([x_hat[k] for k in lv], targets, list(output["likelihoods"].values()),
-                                          self.lmbda * self.spec.distortion_scale, num_pixels, self.spec.level_weights)
+        loss, bpp, mse, s4 = Fn.rd_loss_apply([x_hat[k] for k in lv], targets, list(output["likelihoods"].values()),
+                                              self.lmbda * self.spec.distortion_scale, num_pixels, self.spec.level_weights,
+                                              extra=extra, with_scalars=True)
         out = {"bpp_loss": bpp, "mse_loss": mse, "loss": loss}
+        if s4 is not None and extra is not None:
+            out["scalars"] = s4
         return out if self.return_type == "all" else out[self.return_type]

@@ -62,6 +62,7 @@ class TrainStep:
         # (raised by the gradient-norm kernel, consumed by the update's prep kernel) so that a captured replay after
         # flush() applies nothing; the aux optimiser follows the net optimiser's decision
         self.pending_flag = torch.zeros(1, dtype=torch.int32, device=self.arena.device)
+        self._one = torch.ones((), dtype=torch.float32, device=self.arena.device)
         self.opt["net"].pending_flag = self.pending_flag
         self.opt["aux"].gate = self.opt["net"]
         if self.sharded:
@@ -193,10 +194,10 @@ class TrainStep:
         if Fn.SideStreams.opt is not None:       # gradient buffers are cleared by the update pass: join before backward
             torch.cuda.current_stream().wait_stream(Fn.SideStreams.opt)
         self.arena.gates = {}
-        crit = self.criterion(out, feats)
-        if aux is not None:
+        crit = self.criterion(out, feats, extra=aux)
+        if aux is not None and "scalars" not in crit:
             crit["scalars"] = torch.stack([crit["loss"].detach(), crit["bpp_loss"].detach(), crit["mse_loss"].detach(), aux])
-        crit["loss"].backward()
+        crit["loss"].backward(self._one)          # a kept 1.0: no ones_like fill between the loss and the first dgrad
         if self.reducer is not None:
             self.reducer.mark_ready(self.reducer.eb_names)
             if self.sharded:                     # publishes this rank's squared norm and raises the pending flag

@@ -305,6 +305,45 @@ def test_rd_loss_vs_oracle(P):
         torch.testing.assert_close(a.grad, b.grad, rtol=1e-5, atol=1e-9)
 
 
+def test_rd_loss_single_launch_vs_oracle(P):
+    """lmsfc_rd_loss: the likelihood kernels' sum(ln L) scalars, every level's squared error and gradient, and the final
+    bpp / D / loss (+ a scalar riding along) in one launch; twice in a row gives bit-identical numbers (fixed-order
+    reduction, nothing to zero beforehand)."""
+    from oracle import ops as O
+    spec = P.spec.DEFAULT_SPEC
+    shapes = [(3, 256, 40, 24), (3, 256, 20, 12), (3, 256, 10, 6), (3, 256, 5, 3)]
+    xh = [bf(rnd(*s, seed=50 + i)).requires_grad_() for i, s in enumerate(shapes)]
+    xt = [bf(rnd(*s, seed=60 + i)) for i, s in enumerate(shapes)]
+    y = rnd(3, 256, 3, 2, seed=70, scale=3.0)
+    scales = torch.rand(3, 256, 3, 2, device=DEV) * 2 + 0.05
+    noise = torch.rand(3, 256, 3, 2, device=DEV) - 0.5
+    lmbda, npix = 0.013, spec.num_pixels(3, 40, 24)
+    extra = torch.tensor(123.5, device=DEV)
+    vals = []
+    for _ in range(2):
+        xa = [t.detach().to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_() for t in xh]
+        ya = y.clone().requires_grad_()
+        _, lik = P.functional.gc_apply(ya, scales, None, noise, "noise", 0.11, 1e-9)
+        loss, bpp, mse, s4 = P.functional.rd_loss_apply(xa, xt, [lik], lmbda * 255 ** 2, npix, spec.level_weights,
+                                                         extra=extra, with_scalars=True)
+        assert s4 is not None
+        loss.backward()
+        torch.cuda.synchronize()
+        vals.append([float(v) for v in s4] + [float(ya.grad.abs().sum())])
+    assert vals[0] == vals[1]
+    assert vals[0][:3] == [float(loss), float(bpp), float(mse)] and vals[0][3] == 123.5
+    yr = y.clone().requires_grad_()
+    _, lik_r = O.gc_forward(yr, scales, None, True, noise)
+    ref = O.rd_loss([lik_r], xh, xt, lmbda, npix, spec.level_weights)
+    ref["loss"].backward()
+    assert abs(float(loss) - float(ref["loss"])) < 1e-3 * abs(float(ref["loss"]))
+    assert abs(float(bpp) - float(ref["bpp_loss"])) < 1e-4 * abs(float(ref["bpp_loss"]))
+    assert abs(float(mse) - float(ref["mse_loss"])) < 1e-3 * abs(float(ref["mse_loss"]))
+    for a, b in zip(xa, xh):
+        assert nerr(a.grad, b.grad) < 1e-2
+    assert nerr(ya.grad, yr.grad) < 1e-3
+
+
 def test_fused_clip_adam_vs_torch(P):
     n = 10000 + 3
     p0, g0 = rnd(n, seed=50), rnd(n, seed=51, scale=0.05)
