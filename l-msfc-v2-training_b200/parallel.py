@@ -7,6 +7,8 @@ backward produces them); as soon as the last weight-gradient kernel of a bucket 
 the remaining dgrad / wgrad work.  `quantiles` (aux loss) are data independent and identical on
 every rank: they are never reduced.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -191,6 +193,10 @@ class SlicedNorm(BucketedGradReducer):
         from . import _lib as L
         self.L = L
         super().__init__(model, edges=edges)
+        # high priority: a slice's norm is a few microseconds of work that must not queue behind a 148-CTA weight-gradient
+        # launch of the NEXT slice (it trickled out on the step's tail otherwise)
+        if os.environ.get("LMSFC_NORM_PRIO", "1") == "1":
+            self.comm_stream = torch.cuda.Stream(device=self.grads.device, priority=-1)
         self.parts = torch.zeros(len(self.buckets), dtype=torch.float32, device=self.grads.device)
         self.outputs = None       # (sumsq, pending_flag or None): lets the LAST slice's launch add the parts up itself
         self._closed = False
