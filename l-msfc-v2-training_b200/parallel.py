@@ -337,6 +337,8 @@ class ShardedExchange(BucketedGradReducer):
         if os.environ.get("LMSFC_VERBOSE") and self.rank == 0:
             print(f"[lmsfc exchange] world {self.world}, units {self.units}, fp32_end {self.fp32_end}, "
                   f"multicast {self.multicast}", flush=True)
+        if os.environ.get("LMSFC_XCHG_PRIO", "1") == "1":     # exchange kernels ahead of queued weight-gradient CTAs
+            self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
         L.xchg_init()
         dist.barrier(group=process_group)            # every rank's buffers are mapped and zeroed before the first signal
 
