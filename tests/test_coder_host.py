@@ -76,3 +76,55 @@ def test_bin_v3_round_trip_v2_still_read_and_bad_magic(tmp_path):
     bad.write_bytes(b"LMSF\x01" + b"\0" * 64)                          # the v1 (raw symbol) container is not read
     with pytest.raises(ValueError):
         codec._read_bin(str(bad))
+
+
+def test_decoder_index_trailer_is_found_only_when_it_fits_the_symbol_count():
+    """coder._strip_index: the trailer `ncp x {state lo, state hi, words written}, ncp, S, "CKPT"` behind a reference string
+    is accepted when every field agrees with n (ncp = ceil(n / S) - 1); anything else stays a plain string."""
+    c = importlib.import_module(PKG + ".coder")
+    L = importlib.import_module(PKG + "._lib")
+    body = np.arange(100, dtype=np.uint32) + 1000
+    n, S = 5000, 1024
+    ncp = (n + S - 1) // S - 1
+    assert ncp == 4 == L.lib.lmsfc_rans_checkpoints(n, 1, S)
+    table = (np.arange(3 * ncp, dtype=np.uint32) + 7).reshape(ncp, 3)
+    s = np.concatenate([body, table.reshape(-1), np.array([ncp, S, c.INDEX_MAGIC], np.uint32)])
+    w, interval, tab = c._strip_index(s, n)
+    assert interval == S and w.tolist() == body.tolist() and tab.tolist() == table.tolist()
+    for other_n in (4096, 5121, 100):                       # a different symbol count: ncp does not match -> plain string
+        w, interval, tab = c._strip_index(s, other_n)
+        assert interval == 0 and tab is None and w.size == s.size
+    bad = s.copy(); bad[-2] = 1000                           # interval not a power of two
+    assert c._strip_index(bad, n)[2] is None
+    bad = s.copy(); bad[-1] ^= 1                             # no magic
+    assert c._strip_index(bad, n)[2] is None
+    assert c._strip_index(s[-8:], n)[2] is None              # too short to hold the table it announces
+    # checkpoint counts of the C ABI: the longest lane decides
+    assert L.lib.lmsfc_rans_checkpoints(1024, 1, 1024) == 0 and L.lib.lmsfc_rans_checkpoints(1025, 1, 1024) == 1
+    assert L.lib.lmsfc_rans_checkpoints(63232, 1, 1024) == 61 and L.lib.lmsfc_rans_checkpoints(63232, 64, 256) == 3
+    assert L.lib.lmsfc_rans_checkpoints(0, 1, 1024) == 0
+    import torch
+    z = torch.zeros(1, 4, dtype=torch.int32)
+    with pytest.raises(ValueError, match="lanes = 1"):
+        c.encode_batch(z, z, z, z, z, lanes=4, index=1024)
+
+
+def test_mean_scale_spec_and_codec_option():
+    spec_m = importlib.import_module(PKG + ".spec")
+    sp, ms = spec_m.DEFAULT_SPEC, spec_m.MEAN_SCALE_SPEC
+    assert ms.mean_scale and not sp.mean_scale and ms.mid == 2 * ms.M
+    by_name = {l[0]: l for l in ms.conv_layers(64, 64)}
+    assert by_name["h_s.0"][3:5] == (ms.N, ms.M) and by_name["h_s.2"][3:5] == (ms.M, ms.mid) and by_name["h_s.4"][3:5] == (ms.mid, 2 * ms.M)
+    assert ms.flops_fwd(64, 64) > sp.flops_fwd(64, 64)
+    assert ms.gate_names() == sp.gate_names()
+    with pytest.raises(ValueError):
+        spec_m.LMSFCSpec(hyperprior="median")
+    # the oracle builds the same graph from the same spec (reference modules: LeakyReLU, 2M-channel h_s, chunk)
+    import torch
+    from oracle import lmsfc as OL
+    net = OL.OracleLMSFC(ms)
+    assert isinstance(net.h_a[1], torch.nn.LeakyReLU) and net.h_s[4].out_channels == 2 * ms.M and net.h_s[2].out_channels == ms.mid
+    feats = OL.synth_features(ms, 1, 16, 16)
+    with torch.no_grad():
+        out = net(feats, training=False)
+    assert out["latents"]["means"].shape == out["latents"]["y"].shape == out["latents"]["scales"].shape
