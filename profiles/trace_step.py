@@ -40,7 +40,8 @@ ev.sort(key=lambda e: e["ts"])
 n = len(ev) // 3
 ev = ev[2 * n:]                        # the last replay
 t0 = ev[0]["ts"]
-out = open(sys.argv[1] if rank == 0 else os.devnull, "w") if len(sys.argv) > 1 else sys.stdout
+# rank 0 writes out.txt, rank k > 0 out.txt.rank<k> (absolute times are per-rank clocks: compare durations and order)
+out = open(sys.argv[1] + (f".rank{rank}" if rank else ""), "w") if len(sys.argv) > 1 else (sys.stdout if rank == 0 else open(os.devnull, "w"))
 streams = {}
 for e in ev:
     s = e["args"].get("stream", -1)
