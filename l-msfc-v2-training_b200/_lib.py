@@ -147,7 +147,9 @@ _FUSABLE = {}
 # inside the step the forward fusion loses: the separate square / GDN kernels overlapped the convolution's tail through
 # programmatic dependent launch, the fused CTA (512 TMEM columns, 213 KB) keeps its SM to itself until it exits.
 # Inference (no gradient) always takes the fused forward: y is the only tensor written.
-FUSE_MODE = int(os.environ.get("LMSFC_FUSE", "2"))
+# Re-measured on the final round-2 tree (profiles/tools/fuse_ab2.sh, same box, two runs each): 2: 0.9661 / 0.9673,
+# 6: 0.9643 / 0.9649, 7: 0.9835 / 0.9825, 0: 0.972, 3: 0.986 -> 6 (the heads' gradient rides into the fused kernel as addend).
+FUSE_MODE = int(os.environ.get("LMSFC_FUSE", "6"))
 
 
 def gdn_fusable(desc, dgrad=False, n_in=0, inference=False):
