@@ -300,7 +300,9 @@ int adam_update(const AdamArgs& a, cudaStream_t s) {
     if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
     return sms;
   }();
-  if (stream_sms > 0 && a.n >= (int64_t)stream_sms * stream_adam::kChunk) {
+  // bulk copies want 16-byte aligned global addresses (arena slices are 256-byte aligned; a caller's odd bf16 pointer
+  // takes the register-staged kernel)
+  if (stream_sms > 0 && a.n >= (int64_t)stream_sms * stream_adam::kChunk && ((uintptr_t)a.p_bf16 & 15) == 0) {
     static const cudaError_t attr = cudaFuncSetAttribute(adam_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                          stream_adam::kSmemBytes);
     LMSFC_CUDA(attr);
