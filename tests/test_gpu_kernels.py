@@ -344,8 +344,10 @@ def test_rd_loss_single_launch_vs_oracle(P):
     assert nerr(ya.grad, yr.grad) < 1e-3
 
 
-def test_fused_clip_adam_vs_torch(P):
-    n = 10000 + 3
+# 10003: the register-staged kernel with a scalar tail; 148 * 2048 * 3 + 1237: the bulk-copy pipeline (adam_stream_kernel,
+# one persistent CTA per SM, whole 2048-parameter chunks) with a ragged remainder handled by its last CTA
+@pytest.mark.parametrize("n", [10000 + 3, 148 * 2048 * 3 + 1237])
+def test_fused_clip_adam_vs_torch(P, n):
     p0, g0 = rnd(n, seed=50), rnd(n, seed=51, scale=0.05)
     p = p0.clone()
     g = g0.clone()
@@ -361,6 +363,19 @@ def test_fused_clip_adam_vs_torch(P):
     torch.testing.assert_close(p, pr.detach(), rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(opt.bf16_shadow.float(), p.to(torch.bfloat16).float())
     assert abs(float(opt.grad_norm) - float((g0 * 3).norm())) < 1e-3 * float((g0 * 3).norm())
+    # the same update slice by slice with the gradient cleared in the same pass (the pipelined step's form)
+    g.copy_(g0)
+    pr.grad = g0.clone()
+    torch.nn.utils.clip_grad_norm_([pr], 1.0)
+    ropt.step()
+    opt.accumulate_norm()
+    opt.prep()
+    cut = (n // 3) // 64 * 64
+    opt.update(0, cut, zero_grad=True)
+    opt.update(cut, n, zero_grad=True)
+    torch.testing.assert_close(p, pr.detach(), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(opt.bf16_shadow.float(), p.to(torch.bfloat16).float())
+    assert float(g.abs().max()) == 0.0
 
 
 def test_cdf_device_bit_exact(P, golden):
