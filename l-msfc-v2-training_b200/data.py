@@ -181,6 +181,8 @@ def run_steps(train_step, loader: ShardLoader, steps: int, log_every: int = 0):
     ready = [torch.cuda.Event(), torch.cuda.Event()]
     consumed = [torch.cuda.Event(), torch.cuda.Event()]
     staged = [torch.cuda.Event(), torch.cuda.Event()]
+    read = [torch.cuda.Event(), torch.cuda.Event()]
+    read_stream = torch.cuda.Stream(device=dev)
     slots = [None, None]
     scalars = torch.zeros(steps, 4).pin_memory()
     for i in range(steps + 1):
@@ -201,11 +203,16 @@ def run_steps(train_step, loader: ShardLoader, steps: int, log_every: int = 0):
         if i >= 1:
             b = (i - 1) % 2
             main.wait_event(ready[b])
+            if i >= 3:
+                main.wait_event(read[b])         # this graph's scalars of two steps ago have left the device
             out = train_step.replay(buffer=b)
             consumed[b].record(main)
-            scalars[i - 1].copy_(out["scalars"], non_blocking=True)
+            with torch.cuda.stream(read_stream):     # the 16-byte read-back on its own stream: the next replay does not
+                read_stream.wait_event(consumed[b])  # queue behind a device-to-host copy
+                scalars[i - 1].copy_(out["scalars"], non_blocking=True)
+                read[b].record(read_stream)
             if log_every and i % log_every == 0:
-                torch.cuda.current_stream().synchronize()
+                read[b].synchronize()
                 print(f"step {i}: loss {scalars[i - 1, 0]:.4f} bpp {scalars[i - 1, 1]:.4f} mse {scalars[i - 1, 2]:.6f}")
     torch.cuda.synchronize()
     for b in (0, 1):
