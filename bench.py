@@ -374,7 +374,8 @@ def run_b200(args):
         if not loss_check["ok"]:
             raise SystemExit(f"bench.py: first-step loss {first_loss} differs from the oracle's {pin['loss']} (rel {rel:.3e})")
     note("eager step done")
-    ts.capture(feats, warmup=1, pipelined=not args.sequential, n_buffers=2)
+    NB = int(os.environ.get("LMSFC_BENCH_BUFFERS", "2"))      # device input buffers (= captured graphs) of the e2e loop
+    ts.capture(feats, warmup=1, pipelined=not args.sequential, n_buffers=NB)
     launches_per_step = ts.launches_per_step               # launches of this library recorded into the graph
     torch.cuda.synchronize()
     note("graph captured")
@@ -402,35 +403,36 @@ def run_b200(args):
     ms = e0.elapsed_time(e1)
     # ---- end to end: pinned host features -> H2D (copy stream, double buffered) -> step -> D2H loss
     copy_stream = torch.cuda.Stream(device=dev)
-    dbuf = [ts.input_buffers(0), ts.input_buffers(1)]     # H2D lands directly in the buffers the two graphs read
+    dbuf = [ts.input_buffers(k) for k in range(NB)]       # H2D lands directly in the buffers the captured graphs read
     loss_host = torch.zeros(args.steps, 4).pin_memory()
     main = torch.cuda.current_stream()
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
-    ready = [torch.cuda.Event(), torch.cuda.Event()]
-    consumed = [torch.cuda.Event(), torch.cuda.Event()]
-    read = [torch.cuda.Event(), torch.cuda.Event()]
+    ready = [torch.cuda.Event() for _ in range(NB)]
+    consumed = [torch.cuda.Event() for _ in range(NB)]
+    read = [torch.cuda.Event() for _ in range(NB)]
     read_stream = torch.cuda.Stream(device=dev)   # the 16-byte result leaves on its own stream: the next step's graph
-    for i in range(args.steps + 1):               # does not queue behind a device-to-host copy
-        if i < args.steps:                   # stage step i's inputs
-            b = i % 2
+    for i in range(args.steps + NB - 1):          # does not queue behind a device-to-host copy
+        if i < args.steps:                   # stage step i's inputs, NB - 1 steps ahead of their use
+            b = i % NB
             with torch.cuda.stream(copy_stream):
-                if i >= 2:
+                if i >= NB:
                     copy_stream.wait_event(consumed[b])
                 for k, v in host[i % nbuf].items():
                     dbuf[b][k].copy_(v, non_blocking=True)
                 ready[b].record(copy_stream)
-        if i >= 1:                           # run step i-1
-            b = (i - 1) % 2
+        j = i - (NB - 1)
+        if j >= 0:                           # run step j
+            b = j % NB
             main.wait_event(ready[b])
-            if i >= 3:
-                main.wait_event(read[b])     # this graph's result of two steps ago has been read
+            if j >= NB:
+                main.wait_event(read[b])     # this graph's result of NB steps ago has been read
             out = ts.replay(buffer=b)
             consumed[b].record(main)
             with torch.cuda.stream(read_stream):
                 read_stream.wait_event(consumed[b])
-                loss_host[i - 1].copy_(out["scalars"], non_blocking=True)
+                loss_host[j].copy_(out["scalars"], non_blocking=True)
                 read[b].record(read_stream)
     main.wait_stream(read_stream)            # the last result is on the host before the clock stops
     f1.record()
