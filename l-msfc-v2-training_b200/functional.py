@@ -833,7 +833,7 @@ class _RDLossFn(torch.autograd.Function):
                       VP(*[ptr(g) for g in grads]), n_lik, RP(*[ptr(s_) for s_ in sums]), rate_c,
                       F32A(*[weights[i] / ns[i] for i in range(n_lev)]), lmbda_scale, ptr(extra), ptr(out4), st)
             out = (out4[0], out4[1], out4[2])
-            ctx.scalars4 = out4
+            scalars4 = out4.detach()
         else:
             accum = torch.zeros(n_lik + n_lev, dtype=F32, device=dev)
             coef = [rate_c] * n_lik
@@ -846,7 +846,7 @@ class _RDLossFn(torch.autograd.Function):
             o3 = torch.empty(3, dtype=F32, device=dev)
             L.loss_finalize(ptr(accum), ptr(coef_t), n_lik, n_lev, lmbda_scale, ptr(o3), st)
             out = (o3[2], o3[0], o3[1])
-            ctx.scalars4 = None
+            scalars4 = None
         # likelihoods produced by the fused entropy kernels take d loss / d L = rate_c / L inside their
         # own backward (RateHook); any other likelihood tensor gets an explicit gradient
         ctx.fused = []
@@ -857,11 +857,12 @@ class _RDLossFn(torch.autograd.Function):
                 hook.coef = rate_c
         ctx.grads, ctx.rate_c, ctx.n_lev = grads, rate_c, n_lev
         ctx.save_for_backward(*[lk for lk, f in zip(liks, ctx.fused) if not f])
-        _RDLossFn.last_scalars4 = ctx.scalars4
-        return out
+        if scalars4 is not None:
+            ctx.mark_non_differentiable(scalars4)
+        return (*out, scalars4)                  # the fourth output carries no gradient (None on the fallback path)
 
     @staticmethod
-    def backward(ctx, g_loss, g_bpp, g_mse):
+    def backward(ctx, g_loss, g_bpp, g_mse, g_scalars=None):
         plain = iter(ctx.saved_tensors)
         g_liks = [None if f else ctx.rate_c / next(plain) for f in ctx.fused]
         return (None, None, None, None, None, None, *ctx.grads, *([None] * ctx.n_lev), *g_liks)
@@ -877,7 +878,6 @@ def rd_loss_apply(x_hats, targets, liks, lmbda_scale, num_pixels, weights, extra
             raise ValueError(f"x_hat {tuple(a.shape)} vs target {tuple(b.shape)}")
     if extra is not None:
         extra = extra.detach().reshape(-1).to(F32)
-    loss, bpp, mse = _RDLossFn.apply(float(lmbda_scale), float(num_pixels), [float(w) for w in weights], len(xh), len(liks),
-                                     extra, *xh, *xt, *liks)
-    s4, _RDLossFn.last_scalars4 = _RDLossFn.last_scalars4, None
+    loss, bpp, mse, s4 = _RDLossFn.apply(float(lmbda_scale), float(num_pixels), [float(w) for w in weights], len(xh), len(liks),
+                                         extra, *xh, *xt, *liks)
     return (loss, bpp, mse, s4) if with_scalars else (loss, bpp, mse)
