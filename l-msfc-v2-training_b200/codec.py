@@ -22,7 +22,6 @@ from typing import Dict
 import torch
 import torch.nn as nn
 
-from . import functional as Fn
 from .model import LMSFC
 from .spec import DEFAULT_SPEC, JDE_SPEC, LAMBDAS, LMSFCSpec
 

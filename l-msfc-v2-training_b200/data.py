@@ -14,7 +14,7 @@ import glob
 import os
 import queue
 import threading
-from typing import Dict, List, Sequence, Tuple
+from typing import Dict, List, Tuple
 
 import torch
 

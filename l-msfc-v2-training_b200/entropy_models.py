@@ -7,7 +7,6 @@ lmsfc_eb_* / lmsfc_gc_* (quantise + likelihood + bound + sum-ln fused), the inte
 lmsfc_pmf_rows_to_cdf.  Entropy *coding* (compress / decompress / build_indexes,
 SURVEY.md §8f-1) runs in csrc/rans.cu through coder.py: strings byte-identical to the reference's rANS.
 """
-import math
 from typing import Any, List, Optional, Tuple, Union
 
 import numpy as np

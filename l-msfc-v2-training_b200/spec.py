@@ -26,7 +26,7 @@ from it, and so is the FLOP/byte counter used by bench.py.
 
 Odd sizes: every deconv output is cropped to the target level's H x W.
 """
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Tuple
 
 
